@@ -1,0 +1,117 @@
+/* orb_math_shared.h — float/double arithmetic that must give the SAME BITS on
+ * the host (g++ -ffp-contract=off) and on the device (nvcc).  Every operation
+ * is an explicitly rounded IEEE add/mul/div so that neither compiler can fuse
+ * a multiply-add.
+ *
+ *  - orb_fast_atan2_deg : the polynomial of cv::fastAtan2 (OpenCV 4.13
+ *    semantics), called at src/ORBextractor.cc:103.
+ *  - orb_sincos_deg     : a = cos(angle*pi/180), b = sin(...) for
+ *    src/ORBextractor.cc:112-113.  Documented deviation 3:
+ *    evaluated in double with a fixed range reduction + fixed polynomial and
+ *    rounded to float, instead of libm cosf/sinf whose bits are machine
+ *    dependent.
+ */
+#ifndef ORB_MATH_SHARED_H_
+#define ORB_MATH_SHARED_H_
+
+#if defined(__CUDA_ARCH__)
+#define ORB_HD __host__ __device__ __forceinline__
+#define ORB_FMUL(a, b) __fmul_rn((a), (b))
+#define ORB_FADD(a, b) __fadd_rn((a), (b))
+#define ORB_FSUB(a, b) __fsub_rn((a), (b))
+#define ORB_FDIV(a, b) __fdiv_rn((a), (b))
+#define ORB_DMUL(a, b) __dmul_rn((a), (b))
+#define ORB_DADD(a, b) __dadd_rn((a), (b))
+#define ORB_DSUB(a, b) __dsub_rn((a), (b))
+#else
+#if defined(__CUDACC__)
+#define ORB_HD __host__ __device__ inline
+#else
+#define ORB_HD static inline
+#endif
+#define ORB_FMUL(a, b) ((float)(a) * (float)(b))
+#define ORB_FADD(a, b) ((float)(a) + (float)(b))
+#define ORB_FSUB(a, b) ((float)(a) - (float)(b))
+#define ORB_FDIV(a, b) ((float)(a) / (float)(b))
+#define ORB_DMUL(a, b) ((double)(a) * (double)(b))
+#define ORB_DADD(a, b) ((double)(a) + (double)(b))
+#define ORB_DSUB(a, b) ((double)(a) - (double)(b))
+#endif
+
+/* cv::fastAtan2(y, x) in degrees, fp32, no FMA. */
+ORB_HD float orb_fast_atan2_deg(float y, float x) {
+  const float k = (float)(180.0 / 3.14159265358979323846);
+  const float p1 = ORB_FMUL(0.9997878412794807f, k);
+  const float p3 = ORB_FMUL(-0.3258083974640975f, k);
+  const float p5 = ORB_FMUL(0.1555786518463281f, k);
+  const float p7 = ORB_FMUL(-0.04432655554792128f, k);
+  const float eps = (float)2.2204460492503131e-16;
+  float ax = x < 0.f ? -x : x;
+  float ay = y < 0.f ? -y : y;
+  float a, c, c2;
+  if (ax >= ay) {
+    c = ORB_FDIV(ay, ORB_FADD(ax, eps));
+    c2 = ORB_FMUL(c, c);
+    a = ORB_FMUL(ORB_FADD(ORB_FMUL(ORB_FADD(ORB_FMUL(ORB_FADD(ORB_FMUL(p7, c2), p5), c2), p3), c2), p1), c);
+  } else {
+    c = ORB_FDIV(ax, ORB_FADD(ay, eps));
+    c2 = ORB_FMUL(c, c);
+    a = ORB_FSUB(90.f,
+                 ORB_FMUL(ORB_FADD(ORB_FMUL(ORB_FADD(ORB_FMUL(ORB_FADD(ORB_FMUL(p7, c2), p5), c2), p3), c2), p1), c));
+  }
+  if (x < 0.f) a = ORB_FSUB(180.f, a);
+  if (y < 0.f) a = ORB_FSUB(360.f, a);
+  return a;
+}
+
+/* sin and cos of a float angle given in DEGREES, as the reference computes
+ * them: angle_rad = (float)angle_deg * factorPI (fp32 product,
+ * src/ORBextractor.cc:107,112), then cos/sin of that float, rounded to float.
+ * The cos/sin themselves are evaluated in double (Cody-Waite reduction by
+ * pi/2 + degree-13/14 polynomials; |error| < 1e-15, i.e. the float result is
+ * the correctly rounded one except with probability ~1e-8). */
+ORB_HD void orb_sincos_deg(float angle_deg, float* cos_out, float* sin_out) {
+  const float factorPI = (float)(3.14159265358979323846 / 180.0);
+  const float ang = ORB_FMUL(angle_deg, factorPI);
+  double x = (double)ang;
+  double ax = x < 0.0 ? -x : x;
+  /* quadrant: k = round-to-nearest(ax * 2/pi) via truncation of +0.5 */
+  int k = (int)ORB_DADD(ORB_DMUL(ax, 0.63661977236758134308), 0.5);
+  double kd = (double)k;
+  const double PIO2_HI = 1.57079632673412561417e+00; /* first 33 bits of pi/2 */
+  const double PIO2_LO = 6.07710050650619224932e-11; /* pi/2 - PIO2_HI */
+  double r = ORB_DSUB(ORB_DSUB(ax, ORB_DMUL(kd, PIO2_HI)), ORB_DMUL(kd, PIO2_LO));
+  double z = ORB_DMUL(r, r);
+  /* sin(r) = r + r*z*(S1 + z*(S2 + ... )) */
+  const double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03,
+               S3 = -1.98412698298579493134e-04, S4 = 2.75573137070700676789e-06,
+               S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
+  double ps = ORB_DADD(S5, ORB_DMUL(z, S6));
+  ps = ORB_DADD(S4, ORB_DMUL(z, ps));
+  ps = ORB_DADD(S3, ORB_DMUL(z, ps));
+  ps = ORB_DADD(S2, ORB_DMUL(z, ps));
+  ps = ORB_DADD(S1, ORB_DMUL(z, ps));
+  double s = ORB_DADD(r, ORB_DMUL(ORB_DMUL(r, z), ps));
+  /* cos(r) = 1 - z/2 + z*z*(C1 + z*(C2 + ...)) */
+  const double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03,
+               C3 = 2.48015872894767294178e-05, C4 = -2.75573143513906633035e-07,
+               C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
+  double pc = ORB_DADD(C5, ORB_DMUL(z, C6));
+  pc = ORB_DADD(C4, ORB_DMUL(z, pc));
+  pc = ORB_DADD(C3, ORB_DMUL(z, pc));
+  pc = ORB_DADD(C2, ORB_DMUL(z, pc));
+  pc = ORB_DADD(C1, ORB_DMUL(z, pc));
+  double c = ORB_DADD(ORB_DSUB(1.0, ORB_DMUL(0.5, z)), ORB_DMUL(ORB_DMUL(z, z), pc));
+  double sn, cs;
+  switch (k & 3) {
+    case 0: sn = s; cs = c; break;
+    case 1: sn = c; cs = -s; break;
+    case 2: sn = -s; cs = -c; break;
+    default: sn = -c; cs = s; break;
+  }
+  if (x < 0.0) sn = -sn;
+  *cos_out = (float)cs;
+  *sin_out = (float)sn;
+}
+
+#endif /* ORB_MATH_SHARED_H_ */

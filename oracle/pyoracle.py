@@ -1,0 +1,350 @@
+"""ctypes binding of the CPU ORACLE (oracle/_ref/liborb_oracle.so).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs.  The product package
+(my_orb_slam2_b200) never imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_ref", "liborb_oracle.so")
+
+KEYPOINT_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"),
+     ("class_id", "<i4")]
+)
+assert KEYPOINT_DTYPE.itemsize == 28
+
+FLAG_LIBM_SINCOS = 1
+FLAG_TIE_BY_ADDRESS = 2
+
+
+class ExtractorParams(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32)]
+
+
+class ExtractorInfo(C.Structure):
+    _fields_ = [("nlevels", C.c_int32), ("scale_factor", C.c_float), ("scale_factors", C.c_float * 16),
+                ("inv_scale_factors", C.c_float * 16), ("level_sigma2", C.c_float * 16),
+                ("inv_level_sigma2", C.c_float * 16), ("features_per_level", C.c_int32 * 16),
+                ("umax", C.c_int32 * 16), ("capacity", C.c_int32)]
+
+
+class FrameView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("u_right", C.c_void_p), ("desc", C.c_void_p),
+                ("mp_obs", C.c_void_p), ("min_x", C.c_float), ("min_y", C.c_float), ("max_x", C.c_float),
+                ("max_y", C.c_float), ("grid_inv_w", C.c_float), ("grid_inv_h", C.c_float), ("nlevels", C.c_int32),
+                ("scale_factors", C.c_void_p)]
+
+
+class MapPointsView(C.Structure):
+    _fields_ = [("m", C.c_int32), ("proj_x", C.c_void_p), ("proj_y", C.c_void_p), ("proj_xr", C.c_void_p),
+                ("level", C.c_void_p), ("view_cos", C.c_void_p), ("in_view", C.c_void_p), ("obs", C.c_void_p),
+                ("desc", C.c_void_p)]
+
+
+class LastFrameView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("valid", C.c_void_p), ("world_pos", C.c_void_p), ("obs", C.c_void_p),
+                ("desc", C.c_void_p), ("octave", C.c_void_p), ("angle", C.c_void_p), ("tcw", C.c_float * 12)]
+
+
+class CameraPose(C.Structure):
+    _fields_ = [("tcw", C.c_float * 12), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("mbf", C.c_float), ("mb", C.c_float)]
+
+
+class KeyFrameView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("u_right", C.c_void_p), ("desc", C.c_void_p),
+                ("has_mp", C.c_void_p), ("n_nodes", C.c_int32), ("node_ids", C.c_void_p),
+                ("node_offsets", C.c_void_p), ("node_features", C.c_void_p), ("nlevels", C.c_int32),
+                ("scale_factors", C.c_void_p), ("level_sigma2", C.c_void_p)]
+
+
+def build(force=False):
+    """Compile the oracle with its Makefile (no-op when up to date)."""
+    if force or not os.path.exists(_SO):
+        subprocess.check_call(["make", "-C", _HERE] + (["-B"] if force else []))
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        L = C.CDLL(_SO)
+        L.orc_fast_atan2.restype = C.c_float
+        L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orc_ic_angle.restype = C.c_float
+        L.orc_ic_angle.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.orc_sincos_deg.argtypes = [C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_orb_descriptor.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.orc_extractor_create.restype = C.c_void_p
+        L.orc_extractor_create.argtypes = [C.POINTER(ExtractorParams), C.c_int]
+        L.orc_extractor_destroy.argtypes = [C.c_void_p]
+        L.orc_extractor_info.argtypes = [C.c_void_p, C.POINTER(ExtractorInfo)]
+        L.orc_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_extractor_level_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orc_extractor_level_ptr.restype = C.c_void_p
+        L.orc_extractor_level_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.orc_extractor_blurred_ptr.restype = C.c_void_p
+        L.orc_extractor_blurred_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.orc_extractor_candidates.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_extractor_level_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.orc_distribute_octtree.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.orc_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                         C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_search_by_projection_map.argtypes = [C.POINTER(FrameView), C.POINTER(MapPointsView), C.c_float,
+                                                   C.c_float, C.c_void_p]
+        L.orc_search_by_projection_last.argtypes = [C.POINTER(FrameView), C.POINTER(CameraPose),
+                                                    C.POINTER(LastFrameView), C.c_float, C.c_int, C.c_int, C.c_void_p]
+        L.orc_search_for_triangulation.argtypes = [C.POINTER(KeyFrameView), C.POINTER(KeyFrameView), C.c_void_p,
+                                                   C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_hamming_bruteforce.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_void_p,
+                                             C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _u8(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a
+
+
+# ---------------------------------------------------------------- primitives
+def resize_linear(src, dw, dh):
+    src = _u8(src)
+    dst = np.empty((dh, dw), np.uint8)
+    lib().orc_resize_linear_u8(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(dst), dw, dh, dw)
+    return dst
+
+
+def gaussian_blur7(src):
+    src = _u8(src)
+    dst = np.empty_like(src)
+    lib().orc_gaussian_blur7_u8(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(dst), src.shape[1])
+    return dst
+
+
+def fast9_16(roi, threshold, nms=True):
+    roi = _u8(roi)
+    cap = roi.size
+    xs = np.empty(cap, np.int32)
+    ys = np.empty(cap, np.int32)
+    sc = np.empty(cap, np.int32)
+    n = lib().orc_fast9_16(_p(roi), roi.shape[1], roi.shape[0], roi.shape[1], threshold, int(nms), cap, _p(xs),
+                           _p(ys), _p(sc))
+    return xs[:n].copy(), ys[:n].copy(), sc[:n].copy()
+
+
+def fast_atan2(y, x):
+    return lib().orc_fast_atan2(float(y), float(x))
+
+
+def sincos_deg(angle, use_libm=False):
+    c = np.zeros(1, np.float32)
+    s = np.zeros(1, np.float32)
+    lib().orc_sincos_deg(float(angle), int(use_libm), _p(c), _p(s))
+    return c[0], s[0]
+
+
+def descriptor_distance(a, b):
+    a = _u8(a)
+    b = _u8(b)
+    return lib().orc_descriptor_distance(_p(a), _p(b))
+
+
+def ic_angle(img, x, y):
+    img = _u8(img)
+    return lib().orc_ic_angle(_p(img), img.shape[1], int(x), int(y))
+
+
+def orb_descriptor(blurred, x, y, angle, use_libm=False):
+    blurred = _u8(blurred)
+    d = np.zeros(32, np.uint8)
+    lib().orc_orb_descriptor(_p(blurred), blurred.shape[1], int(x), int(y), float(angle), int(use_libm), _p(d))
+    return d
+
+
+def distribute_octtree(xs, ys, scores, min_x, max_x, min_y, max_y, n_target, flags=0):
+    xs = np.ascontiguousarray(xs, np.int32)
+    ys = np.ascontiguousarray(ys, np.int32)
+    sc = np.ascontiguousarray(scores, np.int32)
+    kept = np.empty(max(len(xs), 1), np.int32)
+    n = lib().orc_distribute_octtree(_p(xs), _p(ys), _p(sc), len(xs), min_x, max_x, min_y, max_y, n_target, flags,
+                                     len(kept), _p(kept))
+    if n < 0:
+        raise RuntimeError("orc_distribute_octtree failed: %d" % n)
+    return kept[:n].copy()
+
+
+# ---------------------------------------------------------------- extractor
+class Extractor:
+    """CPU oracle of ORBextractor (reference: include/ORBextractor.h:45-108)."""
+
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th, min_th, flags=0):
+        self.params = ExtractorParams(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        self._h = lib().orc_extractor_create(C.byref(self.params), flags)
+        if not self._h:
+            raise ValueError("bad extractor parameters")
+        self.info = ExtractorInfo()
+        lib().orc_extractor_info(self._h, C.byref(self.info))
+        self.nlevels = nlevels
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_extractor_destroy(self._h)
+            self._h = None
+
+    def extract(self, image):
+        image = _u8(image)
+        cap = self.info.capacity
+        kps = np.zeros(cap, KEYPOINT_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = lib().orc_extract(self._h, _p(image), image.shape[1], image.shape[0], image.shape[1], _p(kps), _p(desc),
+                              cap)
+        if n < 0:
+            raise RuntimeError("orc_extract failed: %d" % n)
+        assert n <= cap
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, lv, blurred=False):
+        w = C.c_int()
+        h = C.c_int()
+        if lib().orc_extractor_level_size(self._h, lv, C.byref(w), C.byref(h)) != 0:
+            raise IndexError(lv)
+        st = C.c_int()
+        fn = lib().orc_extractor_blurred_ptr if blurred else lib().orc_extractor_level_ptr
+        ptr = fn(self._h, lv, C.byref(st))
+        if not ptr:
+            return None
+        buf = (C.c_uint8 * (w.value * h.value)).from_address(ptr)
+        return np.frombuffer(buf, np.uint8).reshape(h.value, w.value).copy()
+
+    def candidates(self, lv):
+        n = lib().orc_extractor_candidates(self._h, lv, 0, None, None, None)
+        xs = np.empty(n, np.int32)
+        ys = np.empty(n, np.int32)
+        sc = np.empty(n, np.int32)
+        lib().orc_extractor_candidates(self._h, lv, n, _p(xs), _p(ys), _p(sc))
+        return xs, ys, sc
+
+    def level_keypoints(self, lv):
+        n = lib().orc_extractor_level_keypoints(self._h, lv, 0, None)
+        k = np.zeros(n, KEYPOINT_DTYPE)
+        lib().orc_extractor_level_keypoints(self._h, lv, n, _p(k))
+        return k
+
+
+def stereo_matches(ext_left, ext_right, kp_l, desc_l, kp_r, desc_r, mbf, mb):
+    """Frame::ComputeStereoMatches on the pyramids of the last extract() of both extractors."""
+    kp_l = np.ascontiguousarray(kp_l, KEYPOINT_DTYPE)
+    kp_r = np.ascontiguousarray(kp_r, KEYPOINT_DTYPE)
+    desc_l = _u8(desc_l)
+    desc_r = _u8(desc_r)
+    ur = np.empty(len(kp_l), np.float32)
+    dp = np.empty(len(kp_l), np.float32)
+    n = lib().orc_stereo_matches(ext_left._h, ext_right._h, _p(kp_l), _p(desc_l), len(kp_l), _p(kp_r), _p(desc_r),
+                                 len(kp_r), mbf, mb, _p(ur), _p(dp))
+    return ur, dp, n
+
+
+# ---------------------------------------------------------------- matcher views
+class _Keep:
+    """Holds numpy arrays alive next to the ctypes struct that points into them."""
+
+    def __init__(self, struct, arrays):
+        self.struct = struct
+        self.arrays = arrays
+
+
+def make_frame_view(keys_un, u_right, desc, mp_obs, bounds, scale_factors, cls=FrameView):
+    keys_un = np.ascontiguousarray(keys_un, KEYPOINT_DTYPE)
+    u_right = np.ascontiguousarray(u_right, np.float32)
+    desc = _u8(desc)
+    mp_obs = np.ascontiguousarray(mp_obs, np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    min_x, min_y, max_x, max_y = [np.float32(v) for v in bounds]
+    inv_w = np.float32(64) / np.float32(max_x - min_x)  # Frame.cc:117 (static_cast<float>(COLS)/(max-min))
+    inv_h = np.float32(48) / np.float32(max_y - min_y)
+    v = cls(len(keys_un), _p(keys_un).value, _p(u_right).value, _p(desc).value, _p(mp_obs).value, min_x, min_y, max_x,
+            max_y, inv_w, inv_h, len(sf), _p(sf).value)
+    return _Keep(v, [keys_un, u_right, desc, mp_obs, sf])
+
+
+def make_mappoints_view(proj_x, proj_y, proj_xr, level, view_cos, in_view, obs, desc, cls=MapPointsView):
+    arrs = [np.ascontiguousarray(proj_x, np.float32), np.ascontiguousarray(proj_y, np.float32),
+            np.ascontiguousarray(proj_xr, np.float32), np.ascontiguousarray(level, np.int32),
+            np.ascontiguousarray(view_cos, np.float32), np.ascontiguousarray(in_view, np.uint8),
+            np.ascontiguousarray(obs, np.int32), _u8(desc)]
+    v = cls(len(arrs[0]), *[_p(a).value for a in arrs])
+    return _Keep(v, arrs)
+
+
+def make_lastframe_view(valid, world_pos, obs, desc, octave, angle, tcw, cls=LastFrameView):
+    arrs = [np.ascontiguousarray(valid, np.uint8), np.ascontiguousarray(world_pos, np.float32),
+            np.ascontiguousarray(obs, np.int32), _u8(desc), np.ascontiguousarray(octave, np.int32),
+            np.ascontiguousarray(angle, np.float32)]
+    t = (C.c_float * 12)(*[float(x) for x in np.asarray(tcw, np.float32).reshape(-1)[:12]])
+    v = cls(len(arrs[0]), *[_p(a).value for a in arrs], t)
+    return _Keep(v, arrs)
+
+
+def make_camera_pose(tcw, fx, fy, cx, cy, mbf, mb, cls=CameraPose):
+    t = (C.c_float * 12)(*[float(x) for x in np.asarray(tcw, np.float32).reshape(-1)[:12]])
+    return cls(t, fx, fy, cx, cy, mbf, mb)
+
+
+def make_keyframe_view(keys_un, u_right, desc, has_mp, node_ids, node_offsets, node_features, scale_factors,
+                       level_sigma2, cls=KeyFrameView):
+    arrs = [np.ascontiguousarray(keys_un, KEYPOINT_DTYPE), np.ascontiguousarray(u_right, np.float32), _u8(desc),
+            np.ascontiguousarray(has_mp, np.uint8), np.ascontiguousarray(node_ids, np.uint32),
+            np.ascontiguousarray(node_offsets, np.int32), np.ascontiguousarray(node_features, np.int32),
+            np.ascontiguousarray(scale_factors, np.float32), np.ascontiguousarray(level_sigma2, np.float32)]
+    v = cls(len(arrs[0]), _p(arrs[0]).value, _p(arrs[1]).value, _p(arrs[2]).value, _p(arrs[3]).value, len(arrs[4]),
+            _p(arrs[4]).value, _p(arrs[5]).value, _p(arrs[6]).value, len(arrs[7]), _p(arrs[7]).value,
+            _p(arrs[8]).value)
+    return _Keep(v, arrs)
+
+
+def search_by_projection_map(frame, mps, th, nnratio):
+    assigned = np.empty(frame.struct.n, np.int32)
+    n = lib().orc_search_by_projection_map(C.byref(frame.struct), C.byref(mps.struct), th, nnratio, _p(assigned))
+    return assigned, n
+
+
+def search_by_projection_last(cur, cam, last, th, mono, check_ori):
+    assigned = np.empty(cur.struct.n, np.int32)
+    n = lib().orc_search_by_projection_last(C.byref(cur.struct), C.byref(cam), C.byref(last.struct), th, int(mono),
+                                            int(check_ori), _p(assigned))
+    return assigned, n
+
+
+def search_for_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_ori):
+    F12 = np.ascontiguousarray(F12, np.float32).reshape(9)
+    pairs = np.empty((max(kf1.struct.n, 1), 2), np.int32)
+    n = lib().orc_search_for_triangulation(C.byref(kf1.struct), C.byref(kf2.struct), _p(F12), ex, ey,
+                                           int(only_stereo), int(check_ori), _p(pairs), len(pairs))
+    return pairs[:n].copy()
+
+
+def hamming_bruteforce(query, mapd, index_base=0):
+    query = _u8(query)
+    mapd = _u8(mapd)
+    best = np.empty(len(query), np.uint64)
+    second = np.empty(len(query), np.uint64)
+    lib().orc_hamming_bruteforce(_p(query), len(query), _p(mapd), len(mapd), index_base, _p(best), _p(second))
+    return best, second
