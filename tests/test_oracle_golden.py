@@ -1,0 +1,98 @@
+"""CPU oracle vs the committed cv2-4.13 golden fixtures (tests/golden/gen_golden.py) and known-answer vectors.
+
+These pin the oracle: every pixel primitive in the fixtures came from the real OpenCV call the reference makes
+(src/ORBextractor.cc:103,830,835,1108,1142)."""
+import os
+
+import numpy as np
+import pytest
+
+CASES = ["small_a", "small_b", "small_noise"]
+
+
+def _extractor(oracle, params, flags=0):
+    p = params
+    return oracle.Extractor(int(p[0]), float(p[1]), int(p[2]), int(p[3]), int(p[4]), flags)
+
+
+def test_primitives_match_cv2_fixture(oracle, golden_dir):
+    g = np.load(os.path.join(golden_dir, "primitives.npz"))
+    assert np.array_equal(oracle.resize_linear(g["src"], 109, 81), g["resized"])
+    assert np.array_equal(oracle.gaussian_blur7(g["src"]), g["blurred"])
+    at = np.array([oracle.fast_atan2(y, x) for y, x in zip(g["atan_y"], g["atan_x"])], np.float32)
+    assert np.array_equal(at, g["atan"])
+    xs, ys, sc = oracle.fast9_16(g["fast_roi"], 20, True)
+    assert np.array_equal(np.stack([xs, ys, sc], 1).reshape(-1, 3), g["fast_kps"].reshape(-1, 3))
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_extract_matches_cv2_fixture(oracle, golden_dir, name):
+    g = np.load(os.path.join(golden_dir, "extract_%s.npz" % name))
+    ex = _extractor(oracle, g["params"])
+    kp, desc = ex.extract(g["image"])
+    gk = g["keypoints"]
+    assert len(kp) == len(gk)
+    assert np.array_equal(kp["x"], gk[:, 0]) and np.array_equal(kp["y"], gk[:, 1])
+    assert np.array_equal(kp["size"], gk[:, 2])
+    assert np.array_equal(kp["angle"], gk[:, 3])  # bit-equal, tolerance of north_star is 1e-3 deg
+    assert np.array_equal(kp["response"], gk[:, 4])
+    assert np.array_equal(kp["octave"], gk[:, 5].astype(np.int32))
+    assert np.array_equal(desc, g["descriptors"])
+    nl = int(g["params"][2])
+    assert np.array_equal(ex.level(nl - 1), g["level_last"])
+    for lv in range(nl):
+        xs, ys, sc = ex.candidates(lv)
+        assert np.array_equal(np.stack([xs, ys, sc], 1).reshape(-1, 3), g["cand_%d" % lv].reshape(-1, 3))
+
+
+def test_quotas_and_umax(oracle):
+    # quotas and umax of the constructor (src/ORBextractor.cc:435-469)
+    want = {1000: [217, 181, 151, 126, 105, 87, 73, 60], 2000: [434, 362, 302, 251, 209, 175, 145, 122],
+            1200: [261, 217, 181, 151, 126, 105, 87, 72]}
+    for nf, q in want.items():
+        ex = oracle.Extractor(nf, 1.2, 8, 20, 7)
+        assert list(ex.info.features_per_level)[:8] == q
+        assert list(ex.info.umax) == [15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3]
+
+
+def test_descriptor_distance_kats(oracle):
+    z = np.zeros(32, np.uint8)
+    f = np.full(32, 255, np.uint8)
+    assert oracle.descriptor_distance(z, z) == 0
+    assert oracle.descriptor_distance(z, f) == 256
+    rng = np.random.default_rng(3)
+    for _ in range(200):
+        a = rng.integers(0, 256, 32, dtype=np.uint8)
+        b = rng.integers(0, 256, 32, dtype=np.uint8)
+        assert oracle.descriptor_distance(a, b) == int(np.unpackbits(a ^ b).sum())
+    one = z.copy()
+    one[17] = 0x10
+    assert oracle.descriptor_distance(z, one) == 1
+
+
+def test_sincos_matches_correctly_rounded(oracle):
+    import math
+    rng = np.random.default_rng(5)
+    bad = 0
+    for a in rng.uniform(0, 360, 20000).astype(np.float32):
+        ang = np.float32(a) * np.float32(np.pi / 180.0)
+        c, s = oracle.sincos_deg(a)
+        bad += (c != np.float32(math.cos(float(ang)))) + (s != np.float32(math.sin(float(ang))))
+    assert bad == 0
+
+
+def test_flat_and_empty(oracle):
+    from my_orb_slam2_b200 import synth
+    ex = oracle.Extractor(500, 1.2, 8, 20, 7)
+    kp, desc = ex.extract(synth.flat_image(320, 240))
+    assert len(kp) == 0 and desc.shape == (0, 32)
+
+
+def test_hamming_bruteforce_ties_lowest_index(oracle):
+    q = np.zeros((2, 32), np.uint8)
+    m = np.zeros((5, 32), np.uint8)
+    m[0, 0] = 3
+    m[1, 0] = 1
+    m[2, 0] = 1
+    best, second = oracle.hamming_bruteforce(q, m, index_base=100)
+    assert int(best[0]) == (0 << 32) | 103 and int(second[0]) == (0 << 32) | 104
