@@ -1,0 +1,178 @@
+/* orbfe.h — C ABI of liborbfe.so: the B200 (sm_100a) ORB front end.
+ *
+ * This is the drop-in boundary.  The reference has no FFI: its boundary is
+ * the C++ classes ORBextractor / ORBmatcher / Frame.  The
+ * compat classes (compat/) keep those signatures and call the functions
+ * below; the Python harness binds the same functions with ctypes.  Every
+ * entry point names the reference interface it replaces (paths relative to
+ * the reference repository).
+ *
+ * Conventions: plain C types only; all functions return 0 on success and a
+ * negative orbfe_status on failure (the reference has no error channel: its
+ * calls are void / return a count, SURVEY.md 8(b) "Error conventions").
+ * "host" pointers are ordinary (pageable or pinned) CPU memory, "device"
+ * pointers are CUDA device memory on the handle's device.  There is no CPU
+ * fallback: every function fails with ORBFE_ERR_CUDA when no device works.
+ */
+#ifndef ORBFE_H_
+#define ORBFE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "orbfe_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum orbfe_status {
+  ORBFE_OK = 0,
+  ORBFE_ERR_ARG = -1,      /* bad argument */
+  ORBFE_ERR_CUDA = -2,     /* CUDA runtime error (see orbfe_last_error) */
+  ORBFE_ERR_CAPACITY = -3, /* an output or internal slab was too small */
+  ORBFE_ERR_STATE = -4     /* call order (e.g. stereo before extract) */
+} orbfe_status;
+
+/* Text of the last error on the calling thread ("" if none). */
+const char* orbfe_last_error(void);
+/* Library version / build string (contains "sm_100a"). */
+const char* orbfe_version(void);
+/* Number of CUDA devices visible (0 when none / no driver). */
+int orbfe_device_count(void);
+
+/* ------------------------------------------------------------------ */
+/* ORBextractor  (include/ORBextractor.h:45-108, src/ORBextractor.cc)  */
+/* ------------------------------------------------------------------ */
+typedef struct orbfe_extractor orbfe_extractor;
+
+/* ORBextractor::ORBextractor (src/ORBextractor.cc:410-470).  The image size
+ * is fixed per handle (the camera's); max_batch images can be processed by
+ * one call.  Each handle owns a CUDA stream and its device arenas, so two
+ * handles may be driven concurrently from two host threads like the left /
+ * right extractors of src/Frame.cc:89-92. */
+int orbfe_extractor_create(const orbfe_extractor_params* params, int width, int height, int max_batch, int device,
+                           orbfe_extractor** out);
+void orbfe_extractor_destroy(orbfe_extractor* e);
+/* The six getters + mnFeaturesPerLevel + umax (include/ORBextractor.h:63-83). */
+int orbfe_extractor_get_info(const orbfe_extractor* e, orbfe_extractor_info* info);
+
+/* ORBextractor::operator() (src/ORBextractor.cc:1065-1127) for one image:
+ * host image in, host keypoints / descriptors out (caller allocated,
+ * `capacity` entries; info.capacity is always enough).  Synchronous. */
+int orbfe_extract(orbfe_extractor* e, const uint8_t* image, int row_stride, orbfe_keypoint* keypoints,
+                  uint8_t* descriptors, int capacity, int32_t* n_out);
+
+/* Same for `batch` images: image b starts at images + b*image_stride bytes;
+ * outputs for image b start at keypoints + b*capacity, descriptors +
+ * b*capacity*32; counts[b] keypoints are valid.  Synchronous. */
+int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* images, size_t image_stride, int row_stride, int batch,
+                        orbfe_keypoint* keypoints, uint8_t* descriptors, int capacity, int32_t* counts);
+
+/* Asynchronous pieces of the same call, for pipelining:
+ *   upload  : host (ideally pinned) or device images -> level 0 of the pyramids
+ *   run     : all kernels, results stay on the device
+ *   download: results -> host
+ *   sync    : wait for the handle's stream. */
+int orbfe_extract_upload(orbfe_extractor* e, const uint8_t* images, size_t image_stride, int row_stride, int batch,
+                         int images_on_device);
+int orbfe_extract_run(orbfe_extractor* e, int batch);
+int orbfe_extract_download(orbfe_extractor* e, int batch, orbfe_keypoint* keypoints, uint8_t* descriptors,
+                           int capacity, int32_t* counts);
+int orbfe_extractor_sync(orbfe_extractor* e);
+/* The handle's cudaStream_t (as void*), for event timing by the caller. */
+void* orbfe_extractor_stream(orbfe_extractor* e);
+/* Kernels launched by this handle since creation. */
+int64_t orbfe_extractor_launch_count(const orbfe_extractor* e);
+
+/* ORBextractor::mvImagePyramid (include/ORBextractor.h:85), device resident:
+ * level `level` of image `image_index` of the last run. */
+int orbfe_extractor_level(const orbfe_extractor* e, int image_index, int level, const uint8_t** device_ptr,
+                          int* pitch, int* width, int* height);
+/* ... and a copy of it to the host (dst_stride >= width). */
+int orbfe_extractor_download_level(orbfe_extractor* e, int image_index, int level, uint8_t* dst, int dst_stride);
+
+/* Device-resident results of the last run (for chaining without a host trip):
+ * keypoints of image b at keypoints + b*capacity, descriptors likewise. */
+int orbfe_extractor_device_results(const orbfe_extractor* e, const orbfe_keypoint** keypoints,
+                                   const uint8_t** descriptors, const int32_t** counts, int* capacity);
+
+/* Stage dumps of the last run, used by the parity tests only:
+ * FAST candidates of a level (src/ORBextractor.cc:801-850; x,y relative to
+ * minBorder) in the reference's append order, and the keypoints kept by
+ * DistributeOctTree (:539-765) in its list order (level coordinates). */
+int orbfe_extractor_debug_candidates(orbfe_extractor* e, int image_index, int level, int cap, int32_t* xs,
+                                     int32_t* ys, int32_t* scores, int32_t* n_out);
+int orbfe_extractor_debug_level_keypoints(orbfe_extractor* e, int image_index, int level, int cap, int32_t* xs,
+                                          int32_t* ys, int32_t* scores, int32_t* n_out);
+
+/* ------------------------------------------------------------------ */
+/* Frame::ComputeStereoMatches  (src/Frame.cc:496-686)                 */
+/* ------------------------------------------------------------------ */
+/* Runs on the device-resident pyramids, keypoints and descriptors of the last
+ * run of `left` and `right` (same batch, same image size, same device);
+ * u_right / depth are host arrays with left-capacity entries per image
+ * (mvuRight, mvDepth; -1 = no match); n_matched[b] = matches kept.
+ * mb is explicit (SURVEY.md 8(c) deviation 2).  Synchronous. */
+int orbfe_stereo_match(orbfe_extractor* left, orbfe_extractor* right, int batch, float mbf, float mb,
+                       float* u_right, float* depth, int capacity, int32_t* n_matched);
+/* Asynchronous variant: results stay on the device (queued on left's stream
+ * after both handles' work). */
+int orbfe_stereo_match_run(orbfe_extractor* left, orbfe_extractor* right, int batch, float mbf, float mb);
+int orbfe_stereo_match_download(orbfe_extractor* left, int batch, float* u_right, float* depth, int capacity,
+                                int32_t* n_matched);
+
+/* ------------------------------------------------------------------ */
+/* ORBmatcher  (include/ORBmatcher.h:45-114, src/ORBmatcher.cc)        */
+/* ------------------------------------------------------------------ */
+typedef struct orbfe_matcher orbfe_matcher;
+/* A matcher context owns a stream + workspace; one per host thread (the
+ * reference constructs ORBmatcher objects on the stack per use). */
+int orbfe_matcher_create(int device, orbfe_matcher** out);
+void orbfe_matcher_destroy(orbfe_matcher* m);
+int64_t orbfe_matcher_launch_count(const orbfe_matcher* m);
+void* orbfe_matcher_stream(orbfe_matcher* m);
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1715-1731) for n pairs
+ * (host arrays a, b: n x 32 bytes; out: n ints). */
+int orbfe_descriptor_distance(orbfe_matcher* m, const uint8_t* a, const uint8_t* b, int n, int32_t* out);
+
+/* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th)
+ * (src/ORBmatcher.cc:46-132).  assigned[f] = index of the map point this call
+ * wrote into F.mvpMapPoints[f], -1 = untouched.  *n_matches = return value. */
+int orbfe_search_by_projection_map(orbfe_matcher* m, const orbfe_frame_view* frame,
+                                   const orbfe_mappoints_view* mps, float th, float nnratio, int32_t* assigned,
+                                   int32_t* n_matches);
+
+/* ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)
+ * (src/ORBmatcher.cc:1392-1538) incl. the rotation histogram (:1499-1535). */
+int orbfe_search_by_projection_last(orbfe_matcher* m, const orbfe_frame_view* cur, const orbfe_camera_pose* cam,
+                                    const orbfe_lastframe_view* last, float th, int mono, int check_ori,
+                                    int32_t* assigned, int32_t* n_matches);
+
+/* ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:702-872): pairs =
+ * (idx1, idx2) sorted by idx1, at most cap written, *n_pairs = total. */
+int orbfe_search_for_triangulation(orbfe_matcher* m, const orbfe_keyframe_view* kf1,
+                                   const orbfe_keyframe_view* kf2, const float* F12, float ex, float ey,
+                                   int only_stereo, int check_ori, int32_t* pairs, int cap, int32_t* n_pairs);
+
+/* Brute-force Hamming (BASELINE.json config 5): per query the two smallest
+ * keys (dist << 32 | index_base + j) over the map shard; ties -> lowest index.
+ * Host arrays in/out. */
+int orbfe_hamming_bruteforce(orbfe_matcher* m, const uint8_t* query, int nq, const uint8_t* map, int nm,
+                             int64_t index_base, uint64_t* best, uint64_t* second);
+/* Same on device pointers, asynchronous on the matcher's stream: the per-shard
+ * step of the multi-GPU path (the cross-shard exchange is an NCCL all-gather /
+ * min all-reduce on best/second done by the caller, then orbfe_hamming_merge). */
+int orbfe_hamming_bruteforce_device(orbfe_matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm,
+                                    int64_t index_base, uint64_t* d_best, uint64_t* d_second);
+/* Merge `shards` per-shard (best, second) pairs (device arrays laid out
+ * [shard][nq]) into the global top-2 (device arrays [nq]). */
+int orbfe_hamming_merge_device(orbfe_matcher* m, const uint64_t* d_best_all, const uint64_t* d_second_all,
+                               int shards, int nq, uint64_t* d_best, uint64_t* d_second);
+int orbfe_matcher_sync(orbfe_matcher* m);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBFE_H_ */

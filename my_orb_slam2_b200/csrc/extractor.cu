@@ -1,0 +1,477 @@
+// extractor.cu — host side of the ORBextractor entry points of include/orbfe.h:
+// constructor tables (reference: src/ORBextractor.cc:410-470), per-level geometry
+// (:785-799, :1133-1134), device arenas, and the kernel schedule of operator()
+// (:1065-1127).  No CPU computation of results happens here: everything below the
+// geometry tables runs in the sm_100a kernels of k_*.cu.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+#include "extractor.h"
+#include "kernels.h"
+
+namespace orbfe {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+static inline int cv_round(float v) { return (int)nearbyintf(v); }    // cvRound: half to even
+static inline int cv_round(double v) { return (int)nearbyint(v); }
+
+// ORBextractor::ORBextractor (src/ORBextractor.cc:410-470)
+static void build_info(const orbfe_extractor_params& p, orbfe_extractor_info* info) {
+  memset(info, 0, sizeof(*info));
+  const int L = p.nlevels;
+  const double sf = (double)p.scale_factor;  // member is `double scaleFactor` (include/ORBextractor.h:95)
+  info->nlevels = L;
+  info->scale_factor = p.scale_factor;
+  info->scale_factors[0] = 1.0f;
+  info->level_sigma2[0] = 1.0f;
+  for (int i = 1; i < L; ++i) {
+    info->scale_factors[i] = (float)((double)info->scale_factors[i - 1] * sf);  // :421
+    info->level_sigma2[i] = info->scale_factors[i] * info->scale_factors[i];    // :422
+  }
+  for (int i = 0; i < L; ++i) {
+    info->inv_scale_factors[i] = 1.0f / info->scale_factors[i];  // :429
+    info->inv_level_sigma2[i] = 1.0f / info->level_sigma2[i];    // :430
+  }
+  const float factor = (float)(1.0 / sf);  // :435
+  float desired = (float)p.nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)L));
+  int sum = 0;
+  for (int lv = 0; lv < L - 1; ++lv) {
+    info->features_per_level[lv] = cv_round(desired);  // :441
+    sum += info->features_per_level[lv];
+    desired *= factor;
+  }
+  info->features_per_level[L - 1] = p.nfeatures - sum > 0 ? p.nfeatures - sum : 0;  // :446
+  // umax (:454-469)
+  const int half = 15;
+  int* umax = info->umax;
+  const int vmax = (int)floor(half * sqrt(2.f) / 2 + 1);
+  const int vmin = (int)ceil(half * sqrt(2.f) / 2);
+  const double hp2 = (double)half * half;
+  for (int v = 0; v <= vmax; ++v) umax[v] = cv_round(sqrt(hp2 - (double)v * v));
+  for (int v = half, v0 = 0; v >= vmin; --v) {
+    while (umax[v0] == umax[v0 + 1]) ++v0;
+    umax[v] = v0;
+    ++v0;
+  }
+}
+
+// cv::resize INTER_LINEAR coefficient tables
+static void build_resize_tables(int sw, int sh, int dw, int dh, std::vector<XTab>& xt, std::vector<YTab>& yt) {
+  const double scale_x = (double)sw / dw, scale_y = (double)sh / dh;
+  for (int x = 0; x < dw; ++x) {
+    float fx = (float)((x + 0.5) * scale_x - 0.5);
+    int sx = (int)floorf(fx);
+    fx -= sx;
+    if (sx < 0) { sx = 0; fx = 0.f; }
+    if (sx >= sw - 1) { sx = sw - 1; fx = 0.f; }
+    XTab t;
+    t.sx0 = sx;
+    t.sx1 = sx + 1 < sw ? sx + 1 : sw - 1;
+    t.a0 = (short)cv_round((1.f - fx) * 2048.f);
+    t.a1 = (short)cv_round(fx * 2048.f);
+    xt.push_back(t);
+  }
+  for (int y = 0; y < dh; ++y) {
+    float fy = (float)((y + 0.5) * scale_y - 0.5);
+    int sy = (int)floorf(fy);
+    fy -= sy;
+    YTab t;
+    t.b0 = (short)cv_round((1.f - fy) * 2048.f);
+    t.b1 = (short)cv_round(fy * 2048.f);
+    t.sy0 = sy < 0 ? 0 : (sy > sh - 1 ? sh - 1 : sy);
+    t.sy1 = sy + 1 < 0 ? 0 : (sy + 1 > sh - 1 ? sh - 1 : sy + 1);
+    yt.push_back(t);
+  }
+}
+
+static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>& yt) {
+  PyrGeom& g = e->geom;
+  memset(&g, 0, sizeof(g));
+  const orbfe_extractor_info& info = e->info;
+  g.nlevels = info.nlevels;
+  g.ini_th = e->params.ini_th_fast < 0 ? 0 : (e->params.ini_th_fast > 255 ? 255 : e->params.ini_th_fast);
+  g.min_th = e->params.min_th_fast < 0 ? 0 : (e->params.min_th_fast > 255 ? 255 : e->params.min_th_fast);
+  unsigned long long pyr_off = 0;
+  int cells = 0, cand = 0, kept = 0, node_cap_max = 8;
+  for (int l = 0; l < g.nlevels; ++l) {
+    LevelGeom& L = g.lv[l];
+    L.scale = info.scale_factors[l];
+    L.inv_scale = info.inv_scale_factors[l];
+    L.kp_size = (float)(int)(31 * L.scale);  // :857
+    L.w = cv_round((float)e->width * L.inv_scale);  // :1133-1134
+    L.h = cv_round((float)e->height * L.inv_scale);
+    if (L.w < 1 || L.h < 1) { set_error("level %d of a %dx%d image is empty", l, e->width, e->height); return ORBFE_ERR_ARG; }
+    if (L.w > 4096 + 2 * kMinBorder || L.h > 4096 + 2 * kMinBorder) { set_error("image too large"); return ORBFE_ERR_ARG; }
+    L.pitch = (int)align_up((size_t)L.w, 128);
+    L.lvl_bytes = (unsigned)L.pitch * (unsigned)L.h;
+    L.lvl_base = pyr_off;
+    pyr_off += (unsigned long long)L.lvl_bytes * e->max_batch;
+    L.max_bx = L.w - kMinBorder;
+    L.max_by = L.h - kMinBorder;
+    const float width = (float)(L.max_bx - kMinBorder), height = (float)(L.max_by - kMinBorder);
+    L.n_cols = width > 0 ? (int)(width / 30.f) : 0;   // :796-797
+    L.n_rows = height > 0 ? (int)(height / 30.f) : 0;
+    if (L.n_cols <= 0 || L.n_rows <= 0) { L.n_cols = L.n_rows = 0; L.w_cell = L.h_cell = 1; }
+    else {
+      L.w_cell = (int)ceilf(width / L.n_cols);  // :798-799
+      L.h_cell = (int)ceilf(height / L.n_rows);
+    }
+    if (L.n_rows > 255 || L.n_cols > 255) { set_error("image too large"); return ORBFE_ERR_ARG; }
+    L.cell_base = cells;
+    cells += L.n_cols * L.n_rows;
+    L.quota = info.features_per_level[l];
+    L.n_ini = 1;
+    L.h_x = 1.f;
+    int cap = 0;
+    if (L.n_cols > 0) {
+      L.n_ini = (int)roundf(width / (float)(L.max_by - kMinBorder));  // :543 (float / int)
+      if (L.n_ini < 1) { set_error("level %d is taller than wide: the reference divides by zero here", l); return ORBFE_ERR_ARG; }
+      L.h_x = width / (float)L.n_ini;  // :545
+      // strict 8-neighbour maxima cannot be adjacent: at most ceil(w/2)*ceil(h/2) per detection window
+      for (int i = 0; i < L.n_rows; ++i)
+        for (int j = 0; j < L.n_cols; ++j) {
+          const int x0 = kMinBorder + j * L.w_cell, y0 = kMinBorder + i * L.h_cell;
+          if (y0 >= L.max_by - 3 || x0 >= L.max_bx - 6) continue;
+          const int cw = std::min(x0 + L.w_cell + 6, L.max_bx) - x0, ch = std::min(y0 + L.h_cell + 6, L.max_by) - y0;
+          if (cw < 7 || ch < 7) continue;
+          cap += ((cw - 6 + 1) / 2) * ((ch - 6 + 1) / 2);
+        }
+    }
+    L.cand_off = cand;
+    L.cand_cap = cap;
+    cand += (int)align_up((size_t)cap, 4);
+    L.node_cap = std::max(L.quota + 3, 4 * L.n_ini) + 1;
+    node_cap_max = std::max(node_cap_max, L.node_cap);
+    L.kept_off = kept;
+    L.kept_cap = L.node_cap;
+    kept += (int)align_up((size_t)L.kept_cap, 4);
+    if (l > 0) {
+      L.xtab_off = (int)xt.size();
+      L.ytab_off = (int)yt.size();
+      build_resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, L.w, L.h, xt, yt);
+    }
+  }
+  g.total_cells = cells;
+  g.cand_total = std::max(cand, 4);
+  g.kept_total = std::max(kept, 4);
+  g.out_cap = (int)align_up((size_t)kept + 8, 8);
+  g.max_node_cap = node_cap_max;
+  if (g.out_cap > 65535) { set_error("nfeatures too large (capacity %d > 65535)", g.out_cap); return ORBFE_ERR_ARG; }
+  e->pyr_bytes = (size_t)pyr_off;
+  e->info.capacity = g.out_cap;
+  return ORBFE_OK;
+}
+
+template <typename T>
+static cudaError_t dalloc(T** p, size_t n) {
+  return cudaMalloc(reinterpret_cast<void**>(p), std::max<size_t>(n, 1) * sizeof(T));
+}
+
+static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::vector<YTab>& yt) {
+  const PyrGeom& g = e->geom;
+  ExtractorArena& a = e->arena;
+  const size_t B = (size_t)e->max_batch;
+  ORBFE_CUDA(dalloc(&a.pyr, e->pyr_bytes + 256));
+  ORBFE_CUDA(dalloc(&a.xtab, xt.size()));
+  ORBFE_CUDA(dalloc(&a.ytab, yt.size()));
+  ORBFE_CUDA(dalloc(&a.cand, B * g.cand_total));
+  ORBFE_CUDA(dalloc(&a.node_of, B * g.cand_total));
+  ORBFE_CUDA(dalloc(&a.cand_count, B * kMaxLevels));
+  ORBFE_CUDA(dalloc(&a.kept, B * g.kept_total));
+  ORBFE_CUDA(dalloc(&a.kept_count, B * kMaxLevels));
+  ORBFE_CUDA(dalloc(&a.out_kp, B * g.out_cap));
+  ORBFE_CUDA(dalloc(&a.out_desc, B * g.out_cap * 32));
+  ORBFE_CUDA(dalloc(&a.out_count, B));
+  ORBFE_CUDA(dalloc(&a.flags, B));
+  ORBFE_CUDA(dalloc(&a.st_uright, B * g.out_cap));
+  ORBFE_CUDA(dalloc(&a.st_depth, B * g.out_cap));
+  ORBFE_CUDA(dalloc(&a.st_sad, B * g.out_cap));
+  ORBFE_CUDA(dalloc(&a.st_count, B));
+  if (!xt.empty()) ORBFE_CUDA(cudaMemcpy(a.xtab, xt.data(), xt.size() * sizeof(XTab), cudaMemcpyHostToDevice));
+  if (!yt.empty()) ORBFE_CUDA(cudaMemcpy(a.ytab, yt.data(), yt.size() * sizeof(YTab), cudaMemcpyHostToDevice));
+  ORBFE_CUDA(cudaMemset(a.pyr, 0, e->pyr_bytes + 256));
+  ORBFE_CUDA(cudaMemset(a.out_count, 0, B * sizeof(int32_t)));
+  ORBFE_CUDA(cudaMemset(a.kept_count, 0, B * kMaxLevels * sizeof(int32_t)));
+  ORBFE_CUDA(cudaMemset(a.flags, 0, B * sizeof(int32_t)));
+  ORBFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&e->h_flags), B * sizeof(int32_t), cudaHostAllocDefault));
+  return ORBFE_OK;
+}
+
+static void free_arenas(Extractor* e) {
+  ExtractorArena& a = e->arena;
+  cudaFree(a.pyr); cudaFree(a.xtab); cudaFree(a.ytab); cudaFree(a.cand); cudaFree(a.node_of);
+  cudaFree(a.cand_count); cudaFree(a.kept); cudaFree(a.kept_count); cudaFree(a.out_kp); cudaFree(a.out_desc);
+  cudaFree(a.out_count); cudaFree(a.flags); cudaFree(a.st_uright); cudaFree(a.st_depth); cudaFree(a.st_sad);
+  cudaFree(a.st_count);
+  if (e->h_flags) cudaFreeHost(e->h_flags);
+  a = ExtractorArena();
+}
+
+}  // namespace orbfe
+
+using namespace orbfe;
+
+extern "C" {
+
+const char* orbfe_last_error(void) { return orbfe::g_err; }
+
+const char* orbfe_version(void) { return "orbfe-b200 0.1 (CUDA, sm_100a)"; }
+
+int orbfe_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int orbfe_extractor_create(const orbfe_extractor_params* params, int width, int height, int max_batch, int device,
+                           orbfe_extractor** out) {
+  ORBFE_ARG(params && out);
+  ORBFE_ARG(params->nlevels >= 1 && params->nlevels <= kMaxLevels && params->nfeatures >= 1);
+  ORBFE_ARG(params->scale_factor > 1.0f);
+  ORBFE_ARG(width > 0 && height > 0 && max_batch >= 1);
+  *out = nullptr;
+  int ndev = 0;
+  ORBFE_CUDA(cudaGetDeviceCount(&ndev));
+  ORBFE_ARG(device >= 0 && device < ndev);
+  Extractor* e = new (std::nothrow) Extractor();
+  ORBFE_ARG(e != nullptr);
+  e->params = *params;
+  e->width = width;
+  e->height = height;
+  e->max_batch = max_batch;
+  e->device = device;
+  build_info(*params, &e->info);
+  std::vector<XTab> xt;
+  std::vector<YTab> yt;
+  int rc = build_geometry(e, xt, yt);
+  if (rc != ORBFE_OK) { delete e; return rc; }
+  DeviceGuard guard(device);
+  rc = alloc_arenas(e, xt, yt);
+  if (rc == ORBFE_OK && cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    set_error("cudaStreamCreate failed");
+    rc = ORBFE_ERR_CUDA;
+  }
+  if (rc == ORBFE_OK && cudaEventCreateWithFlags(&e->done, cudaEventDisableTiming) != cudaSuccess) rc = ORBFE_ERR_CUDA;
+  if (rc == ORBFE_OK) rc = configure_kernels(e->geom);
+  if (rc != ORBFE_OK) { free_arenas(e); if (e->stream) cudaStreamDestroy(e->stream); delete e; return rc; }
+  *out = reinterpret_cast<orbfe_extractor*>(e);
+  return ORBFE_OK;
+}
+
+void orbfe_extractor_destroy(orbfe_extractor* h) {
+  if (!h) return;
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  DeviceGuard guard(e->device);
+  cudaStreamSynchronize(e->stream);
+  free_arenas(e);
+  if (e->done) cudaEventDestroy(e->done);
+  cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int orbfe_extractor_get_info(const orbfe_extractor* h, orbfe_extractor_info* info) {
+  ORBFE_ARG(h && info);
+  *info = reinterpret_cast<const Extractor*>(h)->info;
+  return ORBFE_OK;
+}
+
+void* orbfe_extractor_stream(orbfe_extractor* h) { return h ? reinterpret_cast<Extractor*>(h)->stream : nullptr; }
+
+int64_t orbfe_extractor_launch_count(const orbfe_extractor* h) {
+  return h ? reinterpret_cast<const Extractor*>(h)->launches : 0;
+}
+
+int orbfe_extractor_sync(orbfe_extractor* h) {
+  ORBFE_ARG(h);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  DeviceGuard guard(e->device);
+  ORBFE_CUDA(cudaStreamSynchronize(e->stream));
+  return ORBFE_OK;
+}
+
+int orbfe_extract_upload(orbfe_extractor* h, const uint8_t* images, size_t image_stride, int row_stride, int batch,
+                         int images_on_device) {
+  ORBFE_ARG(h && images);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  ORBFE_ARG(batch >= 1 && batch <= e->max_batch && row_stride >= e->width);
+  DeviceGuard guard(e->device);
+  const LevelGeom& L0 = e->geom.lv[0];
+  const cudaMemcpyKind kind = images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  uint8_t* dst = e->arena.pyr + L0.lvl_base;
+  if (batch == 1 || image_stride == (size_t)row_stride * e->height) {
+    // images are back to back: one 2-D copy of batch*height rows (level-major arena: image b at b*pitch*h)
+    ORBFE_CUDA(cudaMemcpy2DAsync(dst, L0.pitch, images, row_stride, e->width, (size_t)e->height * batch, kind,
+                                 e->stream));
+  } else {
+    for (int b = 0; b < batch; ++b)
+      ORBFE_CUDA(cudaMemcpy2DAsync(dst + (size_t)b * L0.lvl_bytes, L0.pitch, images + (size_t)b * image_stride,
+                                   row_stride, e->width, e->height, kind, e->stream));
+  }
+  return ORBFE_OK;
+}
+
+int orbfe_extract_run(orbfe_extractor* h, int batch) {
+  ORBFE_ARG(h);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  ORBFE_ARG(batch >= 1 && batch <= e->max_batch);
+  DeviceGuard guard(e->device);
+  const PyrGeom& g = e->geom;
+  const ExtractorArena& a = e->arena;
+  ORBFE_CUDA(cudaMemsetAsync(a.cand_count, 0, (size_t)batch * kMaxLevels * sizeof(int32_t), e->stream));
+  ORBFE_CUDA(cudaMemsetAsync(a.flags, 0, (size_t)batch * sizeof(int32_t), e->stream));
+  for (int l = 1; l < g.nlevels; ++l) launch_pyramid_level(g, a, l, batch, e->stream);  // ComputePyramid (:1075)
+  if (g.total_cells > 0) launch_fast_cells(g, a, batch, e->stream);                      // :776-850
+  launch_quadtree(g, a, batch, e->stream);                                               // :853
+  launch_describe(g, a, batch, e->stream);                                               // :873-874, :1096-1126
+  e->launches += (g.nlevels - 1) + (g.total_cells > 0 ? 1 : 0) + 2;
+  e->last_batch = batch;
+  ORBFE_CUDA(cudaGetLastError());
+  return ORBFE_OK;
+}
+
+int orbfe_extract_download(orbfe_extractor* h, int batch, orbfe_keypoint* keypoints, uint8_t* descriptors,
+                           int capacity, int32_t* counts) {
+  ORBFE_ARG(h && counts && capacity >= 0);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  ORBFE_ARG(batch >= 1 && batch <= e->max_batch);
+  DeviceGuard guard(e->device);
+  const PyrGeom& g = e->geom;
+  const ExtractorArena& a = e->arena;
+  const int ncopy = capacity < g.out_cap ? capacity : g.out_cap;
+  ORBFE_CUDA(cudaMemcpyAsync(counts, a.out_count, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+  ORBFE_CUDA(cudaMemcpyAsync(e->h_flags, a.flags, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+  if (ncopy > 0 && keypoints)
+    ORBFE_CUDA(cudaMemcpy2DAsync(keypoints, (size_t)capacity * sizeof(orbfe_keypoint), a.out_kp,
+                                 (size_t)g.out_cap * sizeof(orbfe_keypoint), (size_t)ncopy * sizeof(orbfe_keypoint),
+                                 batch, cudaMemcpyDeviceToHost, e->stream));
+  if (ncopy > 0 && descriptors)
+    ORBFE_CUDA(cudaMemcpy2DAsync(descriptors, (size_t)capacity * 32, a.out_desc, (size_t)g.out_cap * 32,
+                                 (size_t)ncopy * 32, batch, cudaMemcpyDeviceToHost, e->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(e->stream));
+  for (int b = 0; b < batch; ++b) {
+    if (e->h_flags[b]) { set_error("image %d: internal slab overflow (flags=%d)", b, e->h_flags[b]); return ORBFE_ERR_CAPACITY; }
+    if (counts[b] > capacity) { set_error("image %d: %d keypoints > capacity %d", b, counts[b], capacity); return ORBFE_ERR_CAPACITY; }
+  }
+  return ORBFE_OK;
+}
+
+int orbfe_extract_batch(orbfe_extractor* h, const uint8_t* images, size_t image_stride, int row_stride, int batch,
+                        orbfe_keypoint* keypoints, uint8_t* descriptors, int capacity, int32_t* counts) {
+  ORBFE_ARG(h && counts);
+  if (!images) {  // empty image: the reference returns silently with no keypoints (:1068)
+    for (int b = 0; b < batch; ++b) counts[b] = 0;
+    return ORBFE_OK;
+  }
+  int rc = orbfe_extract_upload(h, images, image_stride, row_stride, batch, 0);
+  if (rc != ORBFE_OK) return rc;
+  rc = orbfe_extract_run(h, batch);
+  if (rc != ORBFE_OK) return rc;
+  return orbfe_extract_download(h, batch, keypoints, descriptors, capacity, counts);
+}
+
+int orbfe_extract(orbfe_extractor* h, const uint8_t* image, int row_stride, orbfe_keypoint* keypoints,
+                  uint8_t* descriptors, int capacity, int32_t* n_out) {
+  ORBFE_ARG(n_out);
+  return orbfe_extract_batch(h, image, 0, row_stride, 1, keypoints, descriptors, capacity, n_out);
+}
+
+int orbfe_extractor_level(const orbfe_extractor* h, int image_index, int level, const uint8_t** device_ptr, int* pitch,
+                          int* width, int* height) {
+  ORBFE_ARG(h);
+  const Extractor* e = reinterpret_cast<const Extractor*>(h);
+  ORBFE_ARG(level >= 0 && level < e->geom.nlevels && image_index >= 0 && image_index < e->max_batch);
+  const LevelGeom& L = e->geom.lv[level];
+  if (device_ptr) *device_ptr = e->arena.pyr + L.lvl_base + (size_t)image_index * L.lvl_bytes;
+  if (pitch) *pitch = L.pitch;
+  if (width) *width = L.w;
+  if (height) *height = L.h;
+  return ORBFE_OK;
+}
+
+int orbfe_extractor_download_level(orbfe_extractor* h, int image_index, int level, uint8_t* dst, int dst_stride) {
+  ORBFE_ARG(h && dst);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  const uint8_t* src = nullptr;
+  int pitch = 0, w = 0, hh = 0;
+  int rc = orbfe_extractor_level(h, image_index, level, &src, &pitch, &w, &hh);
+  if (rc != ORBFE_OK) return rc;
+  ORBFE_ARG(dst_stride >= w);
+  DeviceGuard guard(e->device);
+  ORBFE_CUDA(cudaMemcpy2DAsync(dst, dst_stride, src, pitch, w, hh, cudaMemcpyDeviceToHost, e->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(e->stream));
+  return ORBFE_OK;
+}
+
+int orbfe_extractor_device_results(const orbfe_extractor* h, const orbfe_keypoint** keypoints,
+                                   const uint8_t** descriptors, const int32_t** counts, int* capacity) {
+  ORBFE_ARG(h);
+  const Extractor* e = reinterpret_cast<const Extractor*>(h);
+  if (keypoints) *keypoints = e->arena.out_kp;
+  if (descriptors) *descriptors = e->arena.out_desc;
+  if (counts) *counts = e->arena.out_count;
+  if (capacity) *capacity = e->geom.out_cap;
+  return ORBFE_OK;
+}
+
+static int debug_list(Extractor* e, const LevelGeom* sort_geom, const uint32_t* d_list, const int32_t* d_count,
+                      int off, int lcap, int cap, int32_t* xs, int32_t* ys, int32_t* scores, int32_t* n_out) {
+  DeviceGuard guard(e->device);
+  int32_t n = 0;
+  ORBFE_CUDA(cudaStreamSynchronize(e->stream));
+  ORBFE_CUDA(cudaMemcpy(&n, d_count, sizeof(n), cudaMemcpyDeviceToHost));
+  if (n > lcap) n = lcap;
+  std::vector<uint32_t> tmp((size_t)std::max(n, 1));
+  if (n > 0) ORBFE_CUDA(cudaMemcpy(tmp.data(), d_list + off, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  if (sort_geom) {  // the reference's append order: cell row, cell column, row-major inside the cell (:801-846)
+    const LevelGeom& L = *sort_geom;
+    auto key = [&](uint32_t c) {
+      const unsigned long long x = cand_x(c), y = cand_y(c);
+      return ((unsigned long long)((y - 3) / L.h_cell) << 40) | ((unsigned long long)((x - 3) / L.w_cell) << 32) |
+             (y << 16) | x;
+    };
+    std::sort(tmp.begin(), tmp.begin() + n, [&](uint32_t p, uint32_t q) { return key(p) < key(q); });
+  }
+  for (int i = 0; i < n && i < cap; ++i) {
+    if (xs) xs[i] = cand_x(tmp[i]);
+    if (ys) ys[i] = cand_y(tmp[i]);
+    if (scores) scores[i] = cand_score(tmp[i]);
+  }
+  *n_out = n;
+  return ORBFE_OK;
+}
+
+int orbfe_extractor_debug_candidates(orbfe_extractor* h, int image_index, int level, int cap, int32_t* xs, int32_t* ys,
+                                     int32_t* scores, int32_t* n_out) {
+  ORBFE_ARG(h && n_out);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  ORBFE_ARG(level >= 0 && level < e->geom.nlevels && image_index >= 0 && image_index < e->max_batch);
+  const LevelGeom& L = e->geom.lv[level];
+  return debug_list(e, &L, e->arena.cand + (size_t)image_index * e->geom.cand_total,
+                    e->arena.cand_count + image_index * kMaxLevels + level, L.cand_off, L.cand_cap, cap, xs, ys, scores,
+                    n_out);
+}
+
+int orbfe_extractor_debug_level_keypoints(orbfe_extractor* h, int image_index, int level, int cap, int32_t* xs,
+                                          int32_t* ys, int32_t* scores, int32_t* n_out) {
+  ORBFE_ARG(h && n_out);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  ORBFE_ARG(level >= 0 && level < e->geom.nlevels && image_index >= 0 && image_index < e->max_batch);
+  const LevelGeom& L = e->geom.lv[level];
+  return debug_list(e, nullptr, e->arena.kept + (size_t)image_index * e->geom.kept_total,
+                    e->arena.kept_count + image_index * kMaxLevels + level, L.kept_off, L.kept_cap, cap, xs, ys, scores,
+                    n_out);
+}
+
+}  // extern "C"

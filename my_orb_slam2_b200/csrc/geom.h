@@ -1,0 +1,56 @@
+// geom.h — per-level geometry of one extractor handle, computed once on the host
+// (src/ORBextractor.cc:410-470, :785-799, :1133-1134) and passed BY VALUE to every
+// kernel (no __constant__ state: two handles run concurrently, src/Frame.cc:89-92).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+
+namespace orbfe {
+
+constexpr int kMinBorder = 16;   // EDGE_THRESHOLD-3 (src/ORBextractor.cc:785)
+constexpr int kMaxLevels = 16;
+
+struct LevelGeom {
+  int w, h, pitch;          // level image; pitch multiple of 128
+  int max_bx, max_by;       // w-16, h-16 (:787-788)
+  int n_cols, n_rows;       // cell grid (:796-797); 0 => level has no cells
+  int w_cell, h_cell;       // (:798-799)
+  int cell_base;            // id of this level's first cell within one image
+  int quota;                // mnFeaturesPerLevel[level] (:435-446)
+  int n_ini;                // quadtree roots (:543)
+  float h_x;                // root width (:545)
+  int node_cap;             // max quadtree nodes alive
+  int cand_off, cand_cap;   // slice of the per-image candidate array
+  int kept_off, kept_cap;   // slice of the per-image kept-keypoint array
+  int xtab_off, ytab_off;   // resize coefficient tables (level >= 1)
+  float scale;              // mvScaleFactor[level]
+  float inv_scale;          // mvInvScaleFactor[level]
+  float kp_size;            // (float)(int)(PATCH_SIZE*scale) (:857)
+  unsigned long long lvl_base;  // byte offset of image 0 of this level in the pyramid arena
+  unsigned lvl_bytes;           // pitch*h
+};
+
+struct PyrGeom {
+  int nlevels;
+  int total_cells;  // per image
+  int cand_total;   // per image candidate capacity (sum over levels)
+  int kept_total;   // per image kept capacity (sum over levels)
+  int out_cap;      // per image output capacity (info.capacity)
+  int ini_th, min_th;
+  int max_node_cap;
+  LevelGeom lv[kMaxLevels];
+};
+
+// resize tables (cv::resize INTER_LINEAR)
+struct XTab { int sx0, sx1; short a0, a1; };          // per destination column
+struct YTab { int sy0, sy1; short b0, b1; };          // per destination row
+
+// candidate / kept keypoint record: x | y<<12 | score<<24, x,y relative to minBorder
+__host__ __device__ inline uint32_t pack_cand(int x, int y, int score) {
+  return (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)score << 24);
+}
+__host__ __device__ inline int cand_x(uint32_t c) { return (int)(c & 0xFFFu); }
+__host__ __device__ inline int cand_y(uint32_t c) { return (int)((c >> 12) & 0xFFFu); }
+__host__ __device__ inline int cand_score(uint32_t c) { return (int)(c >> 24); }
+
+}  // namespace orbfe

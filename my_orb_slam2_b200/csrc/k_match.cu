@@ -1,0 +1,135 @@
+// k_match.cu — Hamming kernels of the ORBmatcher path.
+//
+// ORBmatcher::DescriptorDistance (reference: src/ORBmatcher.cc:1715-1731) is a SWAR
+// popcount of 8 x 32-bit XORs; on the device it is 8 x POPC.  The brute-force kernel
+// (BASELINE.json config 5) is bound by the POPC pipe (16 results/clk/SM), so it is
+// organised to keep every other cost off the critical pipe:
+//   * each thread keeps QPT query descriptors in registers (8 words each);
+//   * a CTA streams its slice of the map through shared memory in tiles; all lanes
+//     read the same map descriptor (2 x LDS.128 broadcast) and reuse it for QPT pairs;
+//   * best / second best are tracked as 32-bit keys dist<<20 | local index, updated
+//     branch-free with 3 min/max (ties -> lowest index falls out of the packing);
+//   * per (query, map slice) partial top-2 go to a small workspace and a second kernel
+//     merges slices (and, multi-GPU, shards) as 64-bit keys dist<<32 | global index.
+#include "match_kernels.h"
+
+namespace orbfe {
+
+constexpr int BF_T = 128;        // threads per CTA
+constexpr int BF_QPT = 4;        // queries per thread
+constexpr int BF_TILE = 256;     // map descriptors per shared-memory tile (8 KB)
+
+__global__ void descriptor_distance_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
+                                           int32_t* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 a0 = __ldg(a + 2 * i), a1 = __ldg(a + 2 * i + 1), b0 = __ldg(b + 2 * i), b1 = __ldg(b + 2 * i + 1);
+  out[i] = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// grid: (ceil(nq / (BF_T*BF_QPT)), n_slices).  Slice s covers map rows [s*slice_len, min(nm,(s+1)*slice_len)).
+__global__ void __launch_bounds__(BF_T) hamming_bruteforce_kernel(const uint4* __restrict__ query, int nq,
+                                                                  const uint4* __restrict__ map, int nm, int slice_len,
+                                                                  long long index_base,
+                                                                  unsigned long long* __restrict__ part_best,
+                                                                  unsigned long long* __restrict__ part_second) {
+  __shared__ uint4 tile[BF_TILE * 2];
+  const int tid = threadIdx.x;
+  const int q0 = (blockIdx.x * BF_T + tid) * BF_QPT;
+  const int m_begin = blockIdx.y * slice_len;
+  const int m_end = min(nm, m_begin + slice_len);
+  uint32_t q[BF_QPT][8];
+#pragma unroll
+  for (int k = 0; k < BF_QPT; ++k) {
+    const int qi = min(q0 + k, nq - 1);
+    const uint4 lo = __ldg(query + 2 * qi), hi = __ldg(query + 2 * qi + 1);
+    q[k][0] = lo.x; q[k][1] = lo.y; q[k][2] = lo.z; q[k][3] = lo.w;
+    q[k][4] = hi.x; q[k][5] = hi.y; q[k][6] = hi.z; q[k][7] = hi.w;
+  }
+  uint32_t b1[BF_QPT], b2[BF_QPT];
+#pragma unroll
+  for (int k = 0; k < BF_QPT; ++k) { b1[k] = 0xFFFFFFFFu; b2[k] = 0xFFFFFFFFu; }
+
+  for (int t0 = m_begin; t0 < m_end; t0 += BF_TILE) {
+    const int tn = min(BF_TILE, m_end - t0);
+    __syncthreads();
+    for (int i = tid; i < tn * 2; i += BF_T) tile[i] = __ldg(map + 2 * (size_t)t0 + i);
+    __syncthreads();
+    const uint32_t jbase = (uint32_t)(t0 - m_begin);
+#pragma unroll 4
+    for (int j = 0; j < tn; ++j) {
+      const uint4 lo = tile[2 * j], hi = tile[2 * j + 1];
+#pragma unroll
+      for (int k = 0; k < BF_QPT; ++k) {
+        const uint32_t d = __popc(q[k][0] ^ lo.x) + __popc(q[k][1] ^ lo.y) + __popc(q[k][2] ^ lo.z) +
+                           __popc(q[k][3] ^ lo.w) + __popc(q[k][4] ^ hi.x) + __popc(q[k][5] ^ hi.y) +
+                           __popc(q[k][6] ^ hi.z) + __popc(q[k][7] ^ hi.w);
+        const uint32_t key = (d << 20) + (jbase + (uint32_t)j);
+        b2[k] = min(b2[k], max(b1[k], key));
+        b1[k] = min(b1[k], key);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < BF_QPT; ++k) {
+    const int qi = q0 + k;
+    if (qi < nq) {
+      const size_t o = (size_t)blockIdx.y * nq + qi;
+      const unsigned long long base = (unsigned long long)(index_base + m_begin);
+      part_best[o] = b1[k] == 0xFFFFFFFFu ? ~0ull
+                                          : ((unsigned long long)(b1[k] >> 20) << 32) | (base + (b1[k] & 0xFFFFFu));
+      part_second[o] = b2[k] == 0xFFFFFFFFu ? ~0ull
+                                            : ((unsigned long long)(b2[k] >> 20) << 32) | (base + (b2[k] & 0xFFFFFu));
+    }
+  }
+}
+
+// top-2 of the union of `parts` (best, second) pairs per query; arrays laid out [part][nq]
+__global__ void hamming_merge_kernel(const unsigned long long* __restrict__ best_all,
+                                     const unsigned long long* __restrict__ second_all, int parts, int nq,
+                                     unsigned long long* __restrict__ best, unsigned long long* __restrict__ second) {
+  const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (qi >= nq) return;
+  unsigned long long b1 = ~0ull, b2 = ~0ull;
+  for (int p = 0; p < parts; ++p) {
+    const unsigned long long x = best_all[(size_t)p * nq + qi], y = second_all[(size_t)p * nq + qi];
+    if (x < b1) { b2 = b1; b1 = x; } else if (x < b2) b2 = x;
+    if (y < b2) b2 = y;  // y >= x, so it can only be a second best
+  }
+  best[qi] = b1;
+  second[qi] = b2;
+}
+
+void launch_descriptor_distance(const uint8_t* a, const uint8_t* b, int n, int32_t* out, cudaStream_t s) {
+  descriptor_distance_kernel<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint4*>(a),
+                                                             reinterpret_cast<const uint4*>(b), n, out);
+}
+
+int bruteforce_slices(int nq, int nm, int* slice_len) {
+  // enough CTAs for ~3 waves of 148 SMs, slices a multiple of the tile, at most 2^20 rows per slice
+  const int qblocks = (nq + BF_T * BF_QPT - 1) / (BF_T * BF_QPT);
+  int want = (148 * 3 + qblocks - 1) / qblocks;
+  int len = (nm + want - 1) / want;
+  len = (len + BF_TILE - 1) / BF_TILE * BF_TILE;
+  if (len < BF_TILE) len = BF_TILE;
+  if (len > (1 << 20)) len = 1 << 20;
+  *slice_len = len;
+  return (nm + len - 1) / len;
+}
+
+void launch_hamming_bruteforce(const uint8_t* query, int nq, const uint8_t* map, int nm, int slice_len, int slices,
+                               long long index_base, unsigned long long* part_best, unsigned long long* part_second,
+                               cudaStream_t s) {
+  dim3 grid((nq + BF_T * BF_QPT - 1) / (BF_T * BF_QPT), slices);
+  hamming_bruteforce_kernel<<<grid, BF_T, 0, s>>>(reinterpret_cast<const uint4*>(query), nq,
+                                                  reinterpret_cast<const uint4*>(map), nm, slice_len, index_base,
+                                                  part_best, part_second);
+}
+
+void launch_hamming_merge(const unsigned long long* best_all, const unsigned long long* second_all, int parts, int nq,
+                          unsigned long long* best, unsigned long long* second, cudaStream_t s) {
+  hamming_merge_kernel<<<(nq + 255) / 256, 256, 0, s>>>(best_all, second_all, parts, nq, best, second);
+}
+
+}  // namespace orbfe

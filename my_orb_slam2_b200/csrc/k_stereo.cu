@@ -1,0 +1,218 @@
+// k_stereo.cu — Frame::ComputeStereoMatches (reference: src/Frame.cc:496-686) on the
+// device-resident outputs of the left and right extractor handles.
+//
+// Kernel 1, one warp per left keypoint (8 per CTA; the right keypoints' row bands,
+// x and octave are staged once per CTA in shared memory):
+//   * row-band candidates (:511-531,:549): right keypoint iR is a candidate of row
+//     int(vL) iff floor(yR - r) <= int(vL) <= ceil(yR + r), r = 2*scale[octave(iR)];
+//     the per-row index vectors of the reference are in ascending iR, and the best
+//     Hamming distance is taken with a strict '<' (:581), so the winner is the
+//     lexicographic minimum of (distance, iR) — a warp min-reduction of dist<<16|iR;
+//   * 11x11 SAD over shifts -5..+5 on the left keypoint's pyramid level (:591-631),
+//     computed in int32 (all operands are integers), one warp reduction
+//     per shift; parabola fit, disparity gate and depth (:633-667) by lane 0 with
+//     explicitly rounded fp32 operations.
+// Kernel 2, one CTA per image: median of the kept SADs and the 1.5*1.4*median cut
+// (:672-685).  Order of vDistIdx does not matter: the cut removes every match whose
+// SAD is >= the threshold.
+#include <climits>
+
+#include "kernels.h"
+
+namespace orbfe {
+
+constexpr int ST_WARPS = 8;
+constexpr int ST_CHUNK = 2048;
+constexpr int TH_HIGH = ORBFE_TH_HIGH, TH_LOW = ORBFE_TH_LOW;
+
+__device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
+  return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+         __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__global__ void __launch_bounds__(ST_WARPS * 32) stereo_match_kernel(
+    const __grid_constant__ PyrGeom g, const uint8_t* __restrict__ pyrL, const uint8_t* __restrict__ pyrR,
+    const orbfe_keypoint* __restrict__ kpL, const uint8_t* __restrict__ descL, const int32_t* __restrict__ cntL,
+    const orbfe_keypoint* __restrict__ kpR, const uint8_t* __restrict__ descR, const int32_t* __restrict__ cntR,
+    float mbf, float mb, float* __restrict__ u_right, float* __restrict__ depth, int32_t* __restrict__ sad_out) {
+  __shared__ short2 s_band[ST_CHUNK];   // (minr, maxr)
+  __shared__ float s_x[ST_CHUNK];
+  __shared__ int8_t s_oct[ST_CHUNK];
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.y;
+  const int nL = cntL[b], nR = cntR[b];
+  const int iL = blockIdx.x * ST_WARPS + warp;
+  if (blockIdx.x * ST_WARPS >= nL) return;  // whole CTA idle
+  const bool active = iL < nL;
+  const orbfe_keypoint* kl = kpL + (size_t)b * g.out_cap;
+  const orbfe_keypoint* kr = kpR + (size_t)b * g.out_cap;
+  const int n_rows = g.lv[0].h;                  // mvImagePyramid[0].rows (:503)
+  const float maxD = __fdiv_rn(mbf, mb);         // :536
+  float uL = 0.f, vL = 0.f;
+  int levelL = 0, rowi = -1;
+  uint4 d0 = make_uint4(0, 0, 0, 0), d1 = d0;
+  if (active) {
+    uL = kl[iL].x; vL = kl[iL].y; levelL = kl[iL].octave;
+    rowi = (int)vL;  // :549
+    const uint4* dp = reinterpret_cast<const uint4*>(descL + ((size_t)b * g.out_cap + iL) * 32);
+    d0 = __ldg(dp); d1 = __ldg(dp + 1);
+  }
+  const float minU = __fsub_rn(uL, maxD), maxU = uL;  // :554-555 (minD = 0)
+  const bool searchable = active && rowi >= 0 && rowi < n_rows && !(maxU < 0.f);
+  unsigned best = ((unsigned)TH_HIGH << 16);  // bestDist = TH_HIGH, strict '<' below (:560,:581)
+
+  for (int base = 0; base < nR; base += ST_CHUNK) {
+    const int cn = min(ST_CHUNK, nR - base);
+    __syncthreads();
+    for (int i = threadIdx.x; i < cn; i += ST_WARPS * 32) {
+      const orbfe_keypoint k = kr[base + i];
+      const float r = __fmul_rn(2.0f, g.lv[k.octave].scale);           // :525
+      const int maxr = (int)ceilf(__fadd_rn(k.y, r)), minr = (int)floorf(__fsub_rn(k.y, r));
+      s_band[i] = make_short2((short)max(minr, -32768), (short)min(maxr, 32767));
+      s_x[i] = k.x;
+      s_oct[i] = (int8_t)k.octave;
+    }
+    __syncthreads();
+    if (searchable) {
+      for (int i = lane; i < cn; i += 32) {
+        const short2 bd = s_band[i];
+        const int o = s_oct[i];
+        const float uR = s_x[i];
+        if (rowi >= bd.x && rowi <= bd.y && o >= levelL - 1 && o <= levelL + 1 && uR >= minU && uR <= maxU) {
+          const uint4* dp = reinterpret_cast<const uint4*>(descR + ((size_t)b * g.out_cap + base + i) * 32);
+          const unsigned dist = (unsigned)hamming256(d0, d1, __ldg(dp), __ldg(dp + 1));
+          best = min(best, (dist << 16) | (unsigned)(base + i));
+        }
+      }
+    }
+  }
+  if (!active) return;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+
+  const size_t oidx = (size_t)b * g.out_cap + iL;
+  float res_u = -1.f, res_d = -1.f;
+  int res_sad = -1;
+  const int bestDist = (int)(best >> 16);
+  if (searchable && bestDist < (TH_HIGH + TH_LOW) / 2) {  // :591
+    const int bestIdxR = (int)(best & 0xFFFFu);
+    const float uR0 = kr[bestIdxR].x;
+    const LevelGeom& LV = g.lv[levelL];
+    const float sf = LV.inv_scale;
+    const float scaleduL = roundf(__fmul_rn(uL, sf));
+    const float scaledvL = roundf(__fmul_rn(vL, sf));
+    const float scaleduR0 = roundf(__fmul_rn(uR0, sf));
+    const int w = 5, Lh = 5;
+    const int cuL = (int)scaleduL, cvL = (int)scaledvL, cuR = (int)scaleduR0;
+    const float iniu = scaleduR0 + Lh - w, endu = scaleduR0 + Lh + w + 1;
+    const bool ok = !(cvL - w < 0 || cvL + w >= LV.h || cuL - w < 0 || cuL + w >= LV.w) &&
+                    !(iniu < 0.f || endu >= (float)LV.w) && !(cuR - Lh - w < 0);  // :612-615 + memory guards
+    if (ok) {
+      const uint8_t* imL = pyrL + LV.lvl_base + (size_t)b * LV.lvl_bytes;
+      const uint8_t* imR = pyrR + LV.lvl_base + (size_t)b * LV.lvl_bytes;
+      const int centerL = __ldg(imL + (size_t)cvL * LV.pitch + cuL);
+      int sad[11];
+#pragma unroll
+      for (int s = 0; s < 11; ++s) sad[s] = 0;
+      for (int p = lane; p < 121; p += 32) {
+        const int dy = p / 11 - w, dx = p - (p / 11) * 11 - w;
+        const int lv = (int)__ldg(imL + (size_t)(cvL + dy) * LV.pitch + cuL + dx) - centerL;
+        const uint8_t* rr = imR + (size_t)(cvL + dy) * LV.pitch + cuR + dx;
+#pragma unroll
+        for (int s = 0; s < 11; ++s) {
+          const int centerR = __ldg(imR + (size_t)cvL * LV.pitch + cuR + s - Lh);
+          sad[s] += abs(lv - ((int)__ldg(rr + s - Lh) - centerR));
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < 11; ++s) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sad[s] += __shfl_xor_sync(0xffffffffu, sad[s], o);
+      }
+      int bestSad = INT_MAX, bestInc = 0;
+#pragma unroll
+      for (int s = 0; s < 11; ++s)
+        if (sad[s] < bestSad) { bestSad = sad[s]; bestInc = s - Lh; }  // strict '<': first minimum (:624)
+      if (!(bestInc == -Lh || bestInc == Lh)) {  // :633
+        float d1f = 0.f, d2f = 0.f, d3f = 0.f;
+#pragma unroll
+        for (int s = 1; s < 10; ++s)
+          if (s == bestInc + Lh) { d1f = (float)sad[s - 1]; d2f = (float)sad[s]; d3f = (float)sad[s + 1]; }
+        // deltaR = (d1-d3)/(2*(d1+d3-2*d2))  (:644), every step rounded to fp32
+        const float den = __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1f, d3f), __fmul_rn(2.0f, d2f)));
+        const float deltaR = __fdiv_rn(__fsub_rn(d1f, d3f), den);
+        if (!(deltaR < -1.f || deltaR > 1.f)) {  // NaN passes, as in the reference (:646)
+          float bestuR = __fmul_rn(LV.scale, __fadd_rn(__fadd_rn(scaleduR0, (float)bestInc), deltaR));  // :653
+          float disparity = __fsub_rn(uL, bestuR);
+          if (disparity >= 0.f && disparity < maxD) {
+            if (disparity <= 0.f) {
+              disparity = (float)0.01;                       // :661
+              bestuR = (float)((double)uL - 0.01);           // :662
+            }
+            res_d = __fdiv_rn(mbf, disparity);
+            res_u = bestuR;
+            res_sad = bestSad;
+          }
+        }
+      }
+    }
+  }
+  if (lane == 0) { u_right[oidx] = res_u; depth[oidx] = res_d; sad_out[oidx] = res_sad; }
+}
+
+// median cut (:672-685)
+__global__ void __launch_bounds__(1024) stereo_median_kernel(const __grid_constant__ PyrGeom g,
+                                                             const int32_t* __restrict__ cntL,
+                                                             float* __restrict__ u_right, float* __restrict__ depth,
+                                                             const int32_t* __restrict__ sad,
+                                                             int32_t* __restrict__ n_matched) {
+  extern __shared__ int s_sad[];  // out_cap
+  __shared__ int s_n, s_median, s_removed;
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int nL = cntL[b];
+  const size_t off = (size_t)b * g.out_cap;
+  if (tid == 0) { s_n = 0; s_median = 0; s_removed = 0; }
+  __syncthreads();
+  for (int i = tid; i < nL; i += blockDim.x) {
+    const int v = sad[off + i];
+    if (v >= 0) s_sad[atomicAdd(&s_n, 1)] = v;
+  }
+  __syncthreads();
+  const int n = s_n;
+  if (n == 0) {  // the reference indexes an empty vector here; we return (SURVEY.md 8(c) deviation 2)
+    if (tid == 0) n_matched[b] = 0;
+    return;
+  }
+  const int kth = n / 2;
+  for (int i = tid; i < n; i += blockDim.x) {
+    const int v = s_sad[i];
+    int less = 0, leq = 0;
+    for (int j = 0; j < n; ++j) { const int t = s_sad[j]; less += t < v; leq += t <= v; }
+    if (less <= kth && kth < leq) s_median = v;  // all writers store the same value
+  }
+  __syncthreads();
+  const float thDist = 1.5f * 1.4f * (float)s_median;  // :674
+  for (int i = tid; i < nL; i += blockDim.x) {
+    const int v = sad[off + i];
+    if (v >= 0 && !((float)v < thDist)) {
+      u_right[off + i] = -1.f;
+      depth[off + i] = -1.f;
+      atomicAdd(&s_removed, 1);
+    }
+  }
+  __syncthreads();
+  if (tid == 0) n_matched[b] = n - s_removed;
+}
+
+void launch_stereo(const PyrGeom& g, const ExtractorArena& l, const ExtractorArena& r, int batch, float mbf, float mb,
+                   cudaStream_t s) {
+  dim3 grid((g.out_cap + ST_WARPS - 1) / ST_WARPS, batch);
+  stereo_match_kernel<<<grid, ST_WARPS * 32, 0, s>>>(g, l.pyr, r.pyr, l.out_kp, l.out_desc, l.out_count, r.out_kp,
+                                                     r.out_desc, r.out_count, mbf, mb, l.st_uright, l.st_depth,
+                                                     l.st_sad);
+  stereo_median_kernel<<<batch, 1024, (size_t)g.out_cap * sizeof(int), s>>>(g, l.out_count, l.st_uright, l.st_depth,
+                                                                            l.st_sad, l.st_count);
+}
+
+}  // namespace orbfe

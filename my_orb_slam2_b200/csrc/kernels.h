@@ -1,0 +1,49 @@
+// kernels.h — host-side launchers of the sm_100a kernels (one .cu per stage).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "geom.h"
+#include "../../include/orbfe_types.h"
+
+namespace orbfe {
+
+// device arenas of one extractor handle (all sized for max_batch images)
+struct ExtractorArena {
+  uint8_t* pyr = nullptr;          // level-major: lv[l].lvl_base + b*lv[l].lvl_bytes
+  XTab* xtab = nullptr;
+  YTab* ytab = nullptr;
+  uint32_t* cand = nullptr;        // [batch][cand_total]
+  uint16_t* node_of = nullptr;     // [batch][cand_total]
+  int32_t* cand_count = nullptr;   // [batch][kMaxLevels]
+  uint32_t* kept = nullptr;        // [batch][kept_total]
+  int32_t* kept_count = nullptr;   // [batch][kMaxLevels]
+  orbfe_keypoint* out_kp = nullptr;  // [batch][out_cap]
+  uint8_t* out_desc = nullptr;       // [batch][out_cap][32]
+  int32_t* out_count = nullptr;      // [batch]
+  int32_t* flags = nullptr;          // [batch] overflow / error bits
+  // stereo results (left handle only)
+  float* st_uright = nullptr;   // [batch][out_cap]
+  float* st_depth = nullptr;    // [batch][out_cap]
+  int32_t* st_sad = nullptr;    // [batch][out_cap]
+  int32_t* st_count = nullptr;  // [batch]
+};
+
+enum : int { FLAG_CAND_OVERFLOW = 1, FLAG_NODE_OVERFLOW = 2, FLAG_OUT_OVERFLOW = 4 };
+
+// ComputePyramid (src/ORBextractor.cc:1129-1154): level `lvl` from level lvl-1 for `batch` images
+void launch_pyramid_level(const PyrGeom& g, const ExtractorArena& a, int lvl, int batch, cudaStream_t s);
+// cell loop of ComputeKeyPointsOctTree (:776-850): FAST + cell-local NMS + per-cell threshold fallback
+void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
+// DistributeOctTree (:539-765): one CTA per (level, image)
+void launch_quadtree(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
+size_t quadtree_smem_bytes(int node_cap);
+// computeOrientation (:472-479) + GaussianBlur (:1108) + computeDescriptors (:1056-1063) + rescale (:1117-1123)
+void launch_describe(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
+// Frame::ComputeStereoMatches (src/Frame.cc:496-686)
+void launch_stereo(const PyrGeom& g, const ExtractorArena& left, const ExtractorArena& right, int batch, float mbf,
+                   float mb, cudaStream_t s);
+
+constexpr int kLaunchesPerExtract(int nlevels) { return (nlevels - 1) + 3; }
+constexpr int kLaunchesPerStereo = 2;
+
+}  // namespace orbfe

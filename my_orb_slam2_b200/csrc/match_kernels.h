@@ -1,0 +1,96 @@
+// match_kernels.h — launchers of the ORBmatcher kernels (k_match.cu, k_search.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "../../include/orbfe_types.h"
+
+namespace orbfe {
+
+// ---- k_match.cu ----
+void launch_descriptor_distance(const uint8_t* a, const uint8_t* b, int n, int32_t* out, cudaStream_t s);
+int bruteforce_slices(int nq, int nm, int* slice_len);
+void launch_hamming_bruteforce(const uint8_t* query, int nq, const uint8_t* map, int nm, int slice_len, int slices,
+                               long long index_base, unsigned long long* part_best, unsigned long long* part_second,
+                               cudaStream_t s);
+void launch_hamming_merge(const unsigned long long* best_all, const unsigned long long* second_all, int parts, int nq,
+                          unsigned long long* best, unsigned long long* second, cudaStream_t s);
+
+// ---- k_search.cu ----
+// Device mirror of orbfe_frame_view + the 64x48 grid of Frame::AssignFeaturesToGrid (src/Frame.cc:243-258) in CSR form.
+struct DevFrame {
+  int n;
+  const orbfe_keypoint* keys;
+  const float* u_right;
+  const uint8_t* desc;
+  const int32_t* mp_obs;
+  float min_x, min_y, max_x, max_y, inv_w, inv_h;
+  int nlevels;
+  const float* scale;        // device copy of mvScaleFactors
+  int32_t* cell_start;       // [64*48 + 1]
+  int32_t* cell_items;       // [n]
+};
+
+struct DevMapPoints {
+  int m;
+  const float *proj_x, *proj_y, *proj_xr, *view_cos;
+  const int32_t *level, *obs;
+  const uint8_t* in_view;
+  const uint8_t* desc;
+};
+
+struct DevLastFrame {
+  int n;
+  const uint8_t* valid;
+  const float* world_pos;
+  const int32_t *obs, *octave;
+  const float* angle;
+  const uint8_t* desc;
+  float tlc_z;  // z of LastFrame.Rcw*twc + tcw (src/ORBmatcher.cc:1410), computed by the launcher kernel
+};
+
+struct DevKeyFrame {
+  int n;
+  const orbfe_keypoint* keys;
+  const float* u_right;
+  const uint8_t* desc;
+  const uint8_t* has_mp;
+  int n_nodes;
+  const uint32_t* node_ids;
+  const int32_t *node_offsets, *node_features;
+  const float *scale, *sigma2;
+};
+
+// scratch of one search call (all device pointers, sized by the caller)
+struct SearchScratch {
+  int32_t* cand_count;   // [rows + 1] -> exclusive offsets after the scan
+  uint32_t* cand;        // [total] idx | dist<<16 | octave<<25
+  int32_t* cand_capacity_needed;  // [1] total candidates (device)
+  int32_t* result;       // [rows] chosen feature per row (-1 none)
+  int32_t* block_a;      // [n features] first blocking claimer (iteration t)
+  int32_t* block_b;      // [n features] (iteration t+1)
+  int32_t* assigned;     // [n features] output
+  int32_t* counters;     // [8] misc: 0 nmatches, 1 changed flag, 2 iterations
+  float* proj;           // [rows*4] u, v, invz, radius (last-frame overload)
+  int32_t* hist;         // [32]
+};
+
+void launch_build_grid(const DevFrame& f, cudaStream_t s);
+// SearchByProjection(Frame&, vector<MapPoint*>&, th): pass 1 counts, pass 2 fills (after a scan of cand_count)
+void launch_sbp_map_candidates(const DevFrame& f, const DevMapPoints& mp, float th, const SearchScratch& sc, int fill,
+                               cudaStream_t s);
+void launch_sbp_last_candidates(const DevFrame& f, const DevLastFrame& lf, const orbfe_camera_pose& cam, float th,
+                                int mono, const SearchScratch& sc, int fill, cudaStream_t s);
+void launch_scan_counts(int32_t* counts, int rows, int32_t* total, cudaStream_t s);
+// ordered claim resolution + rotation histogram; mode 0 = map overload (ratio test), 1 = last frame
+void launch_resolve(const DevFrame& f, int rows, const int32_t* row_obs, const float* row_angle, int mode,
+                    float nnratio, int check_ori, const SearchScratch& sc, cudaStream_t s);
+// SearchForTriangulation
+float host_tlc_z(const float* tcw_cur, const float* tcw_last);
+void launch_triangulation(const DevKeyFrame& k1, const DevKeyFrame& k2, const float* F12 /*device, 9*/, float ex,
+                          float ey, int only_stereo, int check_ori, int32_t* matches12 /*[k1.n]*/,
+                          int32_t* flags /*[k1.n+1]*/, int32_t* pairs, int cap, int32_t* n_pairs, int total_entries,
+                          cudaStream_t s);
+
+}  // namespace orbfe

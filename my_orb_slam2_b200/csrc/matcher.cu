@@ -1,0 +1,428 @@
+// matcher.cu — host side of the ORBmatcher entry points of include/orbfe.h.
+// A matcher context owns a stream, one pinned staging buffer and one device buffer;
+// every call packs the caller's struct-of-array views into the staging buffer, uploads
+// them with ONE copy, runs the kernels of k_match.cu / k_search.cu and reads back the
+// small result arrays.  No result is computed on the host.
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+#include "common.cuh"
+#include "match_kernels.h"
+
+namespace orbfe {
+
+struct Matcher {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  uint8_t* d_buf = nullptr;   // device arena
+  uint8_t* h_buf = nullptr;   // pinned mirror of its upload prefix
+  size_t cap = 0, off = 0;
+  uint32_t* d_cand = nullptr; // candidate lists (grown on demand)
+  size_t cand_cap = 0;
+  int32_t* h_small = nullptr; // pinned, 16 ints
+  int64_t launches = 0;
+};
+
+static int arena_reserve(Matcher* m, size_t bytes) {
+  m->off = 0;
+  if (bytes <= m->cap) return ORBFE_OK;
+  if (m->d_buf) cudaFree(m->d_buf);
+  if (m->h_buf) cudaFreeHost(m->h_buf);
+  m->d_buf = nullptr; m->h_buf = nullptr; m->cap = 0;
+  const size_t want = align_up(bytes + bytes / 4, 1 << 16);
+  ORBFE_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_buf), want));
+  ORBFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&m->h_buf), want, cudaHostAllocDefault));
+  m->cap = want;
+  return ORBFE_OK;
+}
+
+// copy n elements into the staging buffer; returns the matching DEVICE pointer
+template <typename T>
+static const T* arena_put(Matcher* m, const T* src, size_t n) {
+  m->off = align_up(m->off, 256);
+  T* d = reinterpret_cast<T*>(m->d_buf + m->off);
+  if (n) memcpy(m->h_buf + m->off, src, n * sizeof(T));
+  m->off += n * sizeof(T);
+  return d;
+}
+
+template <typename T>
+static T* arena_alloc(Matcher* m, size_t n) {
+  m->off = align_up(m->off, 256);
+  T* d = reinterpret_cast<T*>(m->d_buf + m->off);
+  m->off += n * sizeof(T);
+  return d;
+}
+
+static size_t padded(size_t bytes) { return align_up(bytes, 256) + 256; }
+
+static int ensure_cand(Matcher* m, size_t n) {
+  if (n <= m->cand_cap) return ORBFE_OK;
+  if (m->d_cand) cudaFree(m->d_cand);
+  m->d_cand = nullptr; m->cand_cap = 0;
+  const size_t want = n + n / 2 + 1024;
+  ORBFE_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_cand), want * sizeof(uint32_t)));
+  m->cand_cap = want;
+  return ORBFE_OK;
+}
+
+static size_t frame_bytes(const orbfe_frame_view* f) {
+  const size_t n = (size_t)f->n;
+  return padded(n * sizeof(orbfe_keypoint)) + padded(n * 4) + padded(n * 32) + padded(n * 4) +
+         padded((size_t)f->nlevels * 4);
+}
+
+static void put_frame(Matcher* m, const orbfe_frame_view* f, DevFrame* d) {
+  d->n = f->n;
+  d->keys = arena_put(m, f->keys_un, f->n);
+  d->u_right = arena_put(m, f->u_right, f->n);
+  d->desc = arena_put(m, f->desc, (size_t)f->n * 32);
+  d->mp_obs = arena_put(m, f->mp_obs, f->n);
+  d->scale = arena_put(m, f->scale_factors, f->nlevels);
+  d->min_x = f->min_x; d->min_y = f->min_y; d->max_x = f->max_x; d->max_y = f->max_y;
+  d->inv_w = f->grid_inv_w; d->inv_h = f->grid_inv_h;
+  d->nlevels = f->nlevels;
+}
+
+static int check_frame(const orbfe_frame_view* f) {
+  ORBFE_ARG(f && f->n >= 0 && f->n <= 65535);
+  ORBFE_ARG(f->n == 0 || (f->keys_un && f->u_right && f->desc && f->mp_obs));
+  ORBFE_ARG(f->scale_factors && f->nlevels >= 1 && f->nlevels <= 16);
+  return ORBFE_OK;
+}
+
+// scratch shared by both SearchByProjection overloads
+static size_t scratch_bytes(int rows, int nfeat) {
+  return padded(((size_t)rows + 1) * 4) + padded((size_t)rows * 4) + 3 * padded((size_t)nfeat * 4) + padded(64) +
+         padded(((size_t)ORBFE_GRID_COLS * ORBFE_GRID_ROWS + 1) * 4) + padded((size_t)nfeat * 4);
+}
+
+static void alloc_scratch(Matcher* m, int rows, int nfeat, DevFrame* f, SearchScratch* sc) {
+  sc->cand_count = arena_alloc<int32_t>(m, (size_t)rows + 1);
+  sc->result = arena_alloc<int32_t>(m, rows);
+  sc->block_a = arena_alloc<int32_t>(m, nfeat);
+  sc->block_b = arena_alloc<int32_t>(m, nfeat);
+  sc->assigned = arena_alloc<int32_t>(m, nfeat);
+  sc->counters = arena_alloc<int32_t>(m, 16);
+  sc->cand_capacity_needed = sc->counters + 8;
+  f->cell_start = arena_alloc<int32_t>(m, (size_t)ORBFE_GRID_COLS * ORBFE_GRID_ROWS + 1);
+  f->cell_items = arena_alloc<int32_t>(m, nfeat);
+  sc->cand = nullptr;
+  sc->proj = nullptr;
+  sc->hist = nullptr;
+}
+
+}  // namespace orbfe
+
+using namespace orbfe;
+
+extern "C" {
+
+int orbfe_matcher_create(int device, orbfe_matcher** out) {
+  ORBFE_ARG(out);
+  *out = nullptr;
+  int ndev = 0;
+  ORBFE_CUDA(cudaGetDeviceCount(&ndev));
+  ORBFE_ARG(device >= 0 && device < ndev);
+  Matcher* m = new (std::nothrow) Matcher();
+  ORBFE_ARG(m != nullptr);
+  m->device = device;
+  DeviceGuard guard(device);
+  if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaHostAlloc(reinterpret_cast<void**>(&m->h_small), 64, cudaHostAllocDefault) != cudaSuccess) {
+    set_error("matcher: stream / pinned allocation failed");
+    delete m;
+    return ORBFE_ERR_CUDA;
+  }
+  *out = reinterpret_cast<orbfe_matcher*>(m);
+  return ORBFE_OK;
+}
+
+void orbfe_matcher_destroy(orbfe_matcher* h) {
+  if (!h) return;
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  cudaStreamSynchronize(m->stream);
+  if (m->d_buf) cudaFree(m->d_buf);
+  if (m->h_buf) cudaFreeHost(m->h_buf);
+  if (m->d_cand) cudaFree(m->d_cand);
+  if (m->h_small) cudaFreeHost(m->h_small);
+  cudaStreamDestroy(m->stream);
+  delete m;
+}
+
+int64_t orbfe_matcher_launch_count(const orbfe_matcher* h) { return h ? reinterpret_cast<const Matcher*>(h)->launches : 0; }
+void* orbfe_matcher_stream(orbfe_matcher* h) { return h ? reinterpret_cast<Matcher*>(h)->stream : nullptr; }
+
+int orbfe_matcher_sync(orbfe_matcher* h) {
+  ORBFE_ARG(h);
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  return ORBFE_OK;
+}
+
+int orbfe_descriptor_distance(orbfe_matcher* h, const uint8_t* a, const uint8_t* b, int n, int32_t* out) {
+  ORBFE_ARG(h && n >= 0);
+  if (n == 0) return ORBFE_OK;
+  ORBFE_ARG(a && b && out);
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  int rc = arena_reserve(m, 2 * padded((size_t)n * 32) + padded((size_t)n * 4));
+  if (rc != ORBFE_OK) return rc;
+  const uint8_t* da = arena_put(m, a, (size_t)n * 32);
+  const uint8_t* db = arena_put(m, b, (size_t)n * 32);
+  const size_t up = m->off;
+  int32_t* dout = arena_alloc<int32_t>(m, n);
+  ORBFE_CUDA(cudaMemcpyAsync(m->d_buf, m->h_buf, up, cudaMemcpyHostToDevice, m->stream));
+  launch_descriptor_distance(da, db, n, dout, m->stream);
+  m->launches += 1;
+  ORBFE_CUDA(cudaMemcpyAsync(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  ORBFE_CUDA(cudaGetLastError());
+  return ORBFE_OK;
+}
+
+int orbfe_hamming_merge_device(orbfe_matcher* h, const uint64_t* d_best_all, const uint64_t* d_second_all, int shards,
+                               int nq, uint64_t* d_best, uint64_t* d_second) {
+  ORBFE_ARG(h && d_best_all && d_second_all && d_best && d_second && shards >= 1 && nq >= 1);
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  launch_hamming_merge(reinterpret_cast<const unsigned long long*>(d_best_all),
+                       reinterpret_cast<const unsigned long long*>(d_second_all), shards, nq,
+                       reinterpret_cast<unsigned long long*>(d_best), reinterpret_cast<unsigned long long*>(d_second),
+                       m->stream);
+  m->launches += 1;
+  ORBFE_CUDA(cudaGetLastError());
+  return ORBFE_OK;
+}
+
+int orbfe_hamming_bruteforce_device(orbfe_matcher* h, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm,
+                                    int64_t index_base, uint64_t* d_best, uint64_t* d_second) {
+  ORBFE_ARG(h && d_query && d_best && d_second && nq >= 1 && nm >= 0);
+  ORBFE_ARG(nm == 0 || d_map);
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  int slice_len = 0;
+  const int slices = nm > 0 ? bruteforce_slices(nq, nm, &slice_len) : 0;
+  // the partial results live in the candidate buffer (2 x slices x nq u64)
+  const size_t part_words = (size_t)std::max(slices, 1) * nq * 2 /*u64 -> u32*/ * 2;
+  int rc = ensure_cand(m, part_words + 64);
+  if (rc != ORBFE_OK) return rc;
+  unsigned long long* pb = reinterpret_cast<unsigned long long*>(m->d_cand);
+  unsigned long long* ps = pb + (size_t)std::max(slices, 1) * nq;
+  if (slices == 0) {
+    ORBFE_CUDA(cudaMemsetAsync(d_best, 0xFF, (size_t)nq * 8, m->stream));
+    ORBFE_CUDA(cudaMemsetAsync(d_second, 0xFF, (size_t)nq * 8, m->stream));
+    return ORBFE_OK;
+  }
+  launch_hamming_bruteforce(d_query, nq, d_map, nm, slice_len, slices, index_base, pb, ps, m->stream);
+  launch_hamming_merge(pb, ps, slices, nq, reinterpret_cast<unsigned long long*>(d_best),
+                       reinterpret_cast<unsigned long long*>(d_second), m->stream);
+  m->launches += 2;
+  ORBFE_CUDA(cudaGetLastError());
+  return ORBFE_OK;
+}
+
+int orbfe_hamming_bruteforce(orbfe_matcher* h, const uint8_t* query, int nq, const uint8_t* map, int nm,
+                             int64_t index_base, uint64_t* best, uint64_t* second) {
+  ORBFE_ARG(h && nq >= 0 && nm >= 0);
+  if (nq == 0) return ORBFE_OK;
+  ORBFE_ARG(query && best && second && (nm == 0 || map));
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  int rc = arena_reserve(m, padded((size_t)nq * 32) + padded((size_t)nm * 32) + 2 * padded((size_t)nq * 8));
+  if (rc != ORBFE_OK) return rc;
+  const uint8_t* dq = arena_put(m, query, (size_t)nq * 32);
+  const uint8_t* dm = arena_put(m, map, (size_t)nm * 32);
+  const size_t up = m->off;
+  uint64_t* db = arena_alloc<uint64_t>(m, nq);
+  uint64_t* ds = arena_alloc<uint64_t>(m, nq);
+  ORBFE_CUDA(cudaMemcpyAsync(m->d_buf, m->h_buf, up, cudaMemcpyHostToDevice, m->stream));
+  rc = orbfe_hamming_bruteforce_device(h, dq, nq, dm, nm, index_base, db, ds);
+  if (rc != ORBFE_OK) return rc;
+  ORBFE_CUDA(cudaMemcpyAsync(best, db, (size_t)nq * 8, cudaMemcpyDeviceToHost, m->stream));
+  ORBFE_CUDA(cudaMemcpyAsync(second, ds, (size_t)nq * 8, cudaMemcpyDeviceToHost, m->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  return ORBFE_OK;
+}
+
+// shared tail of the two SearchByProjection overloads: scan, fill, resolve, read back
+static int finish_projection(Matcher* m, DevFrame& df, int rows, const int32_t* row_obs, const float* row_angle,
+                             int mode, float nnratio, int check_ori, SearchScratch& sc,
+                             void (*launch_fill)(void*, int), void* ctx, int32_t* assigned, int32_t* n_matches) {
+  launch_scan_counts(sc.cand_count, rows, sc.cand_capacity_needed, m->stream);
+  ORBFE_CUDA(cudaMemcpyAsync(m->h_small, sc.cand_capacity_needed, 4, cudaMemcpyDeviceToHost, m->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  const int total = m->h_small[0];
+  int rc = ensure_cand(m, (size_t)total + 16);
+  if (rc != ORBFE_OK) return rc;
+  sc.cand = m->d_cand;
+  launch_fill(ctx, 1);
+  launch_resolve(df, rows, row_obs, row_angle, mode, nnratio, check_ori, sc, m->stream);
+  m->launches += 3;
+  if (df.n > 0) ORBFE_CUDA(cudaMemcpyAsync(assigned, sc.assigned, (size_t)df.n * 4, cudaMemcpyDeviceToHost, m->stream));
+  ORBFE_CUDA(cudaMemcpyAsync(m->h_small, sc.counters, 16, cudaMemcpyDeviceToHost, m->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  ORBFE_CUDA(cudaGetLastError());
+  if (n_matches) *n_matches = m->h_small[0];
+  return ORBFE_OK;
+}
+
+int orbfe_search_by_projection_map(orbfe_matcher* h, const orbfe_frame_view* frame, const orbfe_mappoints_view* mps,
+                                   float th, float nnratio, int32_t* assigned, int32_t* n_matches) {
+  ORBFE_ARG(h && mps && mps->m >= 0);
+  int rc = check_frame(frame);
+  if (rc != ORBFE_OK) return rc;
+  ORBFE_ARG(frame->n == 0 || assigned);
+  if (n_matches) *n_matches = 0;
+  for (int i = 0; i < frame->n; ++i) assigned[i] = -1;
+  if (mps->m == 0 || frame->n == 0) return ORBFE_OK;
+  ORBFE_ARG(mps->proj_x && mps->proj_y && mps->proj_xr && mps->level && mps->view_cos && mps->in_view && mps->obs &&
+            mps->desc);
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  const size_t M = (size_t)mps->m;
+  rc = arena_reserve(m, frame_bytes(frame) + 6 * padded(M * 4) + padded(M) + padded(M * 32) +
+                            scratch_bytes(mps->m, frame->n));
+  if (rc != ORBFE_OK) return rc;
+  DevFrame f;
+  put_frame(m, frame, &f);
+  DevMapPoints d;
+  d.m = mps->m;
+  d.proj_x = arena_put(m, mps->proj_x, M);
+  d.proj_y = arena_put(m, mps->proj_y, M);
+  d.proj_xr = arena_put(m, mps->proj_xr, M);
+  d.view_cos = arena_put(m, mps->view_cos, M);
+  d.level = arena_put(m, mps->level, M);
+  d.obs = arena_put(m, mps->obs, M);
+  d.in_view = arena_put(m, mps->in_view, M);
+  d.desc = arena_put(m, mps->desc, M * 32);
+  const size_t up = m->off;
+  SearchScratch sc;
+  alloc_scratch(m, mps->m, frame->n, &f, &sc);
+  ORBFE_CUDA(cudaMemcpyAsync(m->d_buf, m->h_buf, up, cudaMemcpyHostToDevice, m->stream));
+  launch_build_grid(f, m->stream);
+  launch_sbp_map_candidates(f, d, th, sc, 0, m->stream);
+  m->launches += 2;
+  struct Ctx { Matcher* m; DevFrame* f; DevMapPoints* d; float th; SearchScratch* sc; } ctx = {m, &f, &d, th, &sc};
+  auto fill = [](void* p, int fl) {
+    Ctx* c = static_cast<Ctx*>(p);
+    launch_sbp_map_candidates(*c->f, *c->d, c->th, *c->sc, fl, c->m->stream);
+  };
+  return finish_projection(m, f, mps->m, d.obs, nullptr, 0, nnratio, 0, sc, fill, &ctx, assigned, n_matches);
+}
+
+int orbfe_search_by_projection_last(orbfe_matcher* h, const orbfe_frame_view* cur, const orbfe_camera_pose* cam,
+                                    const orbfe_lastframe_view* last, float th, int mono, int check_ori,
+                                    int32_t* assigned, int32_t* n_matches) {
+  ORBFE_ARG(h && cam && last && last->n >= 0);
+  int rc = check_frame(cur);
+  if (rc != ORBFE_OK) return rc;
+  ORBFE_ARG(cur->n == 0 || assigned);
+  if (n_matches) *n_matches = 0;
+  for (int i = 0; i < cur->n; ++i) assigned[i] = -1;
+  if (last->n == 0 || cur->n == 0) return ORBFE_OK;
+  ORBFE_ARG(last->valid && last->world_pos && last->obs && last->desc && last->octave && last->angle);
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  const size_t N = (size_t)last->n;
+  rc = arena_reserve(m, frame_bytes(cur) + padded(N) + padded(N * 12) + 3 * padded(N * 4) + padded(N * 32) +
+                            scratch_bytes(last->n, cur->n));
+  if (rc != ORBFE_OK) return rc;
+  DevFrame f;
+  put_frame(m, cur, &f);
+  DevLastFrame d;
+  d.n = last->n;
+  d.valid = arena_put(m, last->valid, N);
+  d.world_pos = arena_put(m, last->world_pos, N * 3);
+  d.obs = arena_put(m, last->obs, N);
+  d.octave = arena_put(m, last->octave, N);
+  d.angle = arena_put(m, last->angle, N);
+  d.desc = arena_put(m, last->desc, N * 32);
+  d.tlc_z = host_tlc_z(cam->tcw, last->tcw);  // pose algebra on 24 scalars (src/ORBmatcher.cc:1403-1413)
+  const size_t up = m->off;
+  SearchScratch sc;
+  alloc_scratch(m, last->n, cur->n, &f, &sc);
+  ORBFE_CUDA(cudaMemcpyAsync(m->d_buf, m->h_buf, up, cudaMemcpyHostToDevice, m->stream));
+  launch_build_grid(f, m->stream);
+  launch_sbp_last_candidates(f, d, *cam, th, mono, sc, 0, m->stream);
+  m->launches += 2;
+  struct Ctx { Matcher* m; DevFrame* f; DevLastFrame* d; const orbfe_camera_pose* cam; float th; int mono; SearchScratch* sc; }
+      ctx = {m, &f, &d, cam, th, mono, &sc};
+  auto fill = [](void* p, int fl) {
+    Ctx* c = static_cast<Ctx*>(p);
+    launch_sbp_last_candidates(*c->f, *c->d, *c->cam, c->th, c->mono, *c->sc, fl, c->m->stream);
+  };
+  return finish_projection(m, f, last->n, d.obs, d.angle, 1, 0.f, check_ori, sc, fill, &ctx, assigned, n_matches);
+}
+
+static int check_kf(const orbfe_keyframe_view* k) {
+  ORBFE_ARG(k && k->n >= 0 && k->n_nodes >= 0);
+  ORBFE_ARG(k->n == 0 || (k->keys_un && k->u_right && k->desc && k->has_mp));
+  ORBFE_ARG(k->node_offsets && (k->n_nodes == 0 || (k->node_ids && k->node_features)));
+  ORBFE_ARG(k->scale_factors && k->level_sigma2 && k->nlevels >= 1 && k->nlevels <= 16);
+  return ORBFE_OK;
+}
+
+static size_t kf_bytes(const orbfe_keyframe_view* k) {
+  const size_t n = (size_t)k->n, e = (size_t)k->node_offsets[k->n_nodes];
+  return padded(n * sizeof(orbfe_keypoint)) + padded(n * 4) + padded(n * 32) + padded(n) +
+         2 * padded(((size_t)k->n_nodes + 1) * 4) + padded(e * 4) + 2 * padded((size_t)k->nlevels * 4);
+}
+
+static void put_kf(Matcher* m, const orbfe_keyframe_view* k, DevKeyFrame* d) {
+  d->n = k->n;
+  d->keys = arena_put(m, k->keys_un, k->n);
+  d->u_right = arena_put(m, k->u_right, k->n);
+  d->desc = arena_put(m, k->desc, (size_t)k->n * 32);
+  d->has_mp = arena_put(m, k->has_mp, k->n);
+  d->n_nodes = k->n_nodes;
+  d->node_ids = arena_put(m, k->node_ids, k->n_nodes);
+  d->node_offsets = arena_put(m, k->node_offsets, (size_t)k->n_nodes + 1);
+  d->node_features = arena_put(m, k->node_features, (size_t)k->node_offsets[k->n_nodes]);
+  d->scale = arena_put(m, k->scale_factors, k->nlevels);
+  d->sigma2 = arena_put(m, k->level_sigma2, k->nlevels);
+}
+
+int orbfe_search_for_triangulation(orbfe_matcher* h, const orbfe_keyframe_view* kf1, const orbfe_keyframe_view* kf2,
+                                   const float* F12, float ex, float ey, int only_stereo, int check_ori, int32_t* pairs,
+                                   int cap, int32_t* n_pairs) {
+  ORBFE_ARG(h && F12 && n_pairs && cap >= 0 && (cap == 0 || pairs));
+  int rc = check_kf(kf1);
+  if (rc != ORBFE_OK) return rc;
+  rc = check_kf(kf2);
+  if (rc != ORBFE_OK) return rc;
+  *n_pairs = 0;
+  if (kf1->n == 0 || kf2->n == 0 || kf1->n_nodes == 0 || kf2->n_nodes == 0) return ORBFE_OK;
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  const size_t n1 = (size_t)kf1->n;
+  const int out_cap = (int)std::min<size_t>((size_t)cap, n1);
+  rc = arena_reserve(m, kf_bytes(kf1) + kf_bytes(kf2) + padded(64) + 2 * padded((n1 + 1) * 4) +
+                            padded((size_t)out_cap * 8 + 8) + padded(64));
+  if (rc != ORBFE_OK) return rc;
+  DevKeyFrame a, b;
+  put_kf(m, kf1, &a);
+  put_kf(m, kf2, &b);
+  const float* dF = arena_put(m, F12, 9);
+  const size_t up = m->off;
+  int32_t* matches12 = arena_alloc<int32_t>(m, n1);
+  int32_t* flags = arena_alloc<int32_t>(m, n1 + 1);
+  int32_t* dpairs = arena_alloc<int32_t>(m, (size_t)out_cap * 2 + 2);
+  int32_t* dn = arena_alloc<int32_t>(m, 16);
+  ORBFE_CUDA(cudaMemcpyAsync(m->d_buf, m->h_buf, up, cudaMemcpyHostToDevice, m->stream));
+  launch_triangulation(a, b, dF, ex, ey, only_stereo, check_ori, matches12, flags, dpairs, out_cap, dn,
+                       kf1->node_offsets[kf1->n_nodes], m->stream);
+  m->launches += 3;
+  ORBFE_CUDA(cudaMemcpyAsync(m->h_small, dn, 4, cudaMemcpyDeviceToHost, m->stream));
+  if (out_cap > 0)
+    ORBFE_CUDA(cudaMemcpyAsync(pairs, dpairs, (size_t)out_cap * 8, cudaMemcpyDeviceToHost, m->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  ORBFE_CUDA(cudaGetLastError());
+  *n_pairs = m->h_small[0];
+  return ORBFE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,63 @@
+// stereo.cu — host side of orbfe_stereo_match*: Frame::ComputeStereoMatches
+// (reference: src/Frame.cc:496-686) on the device-resident results of two extractor
+// handles.  The kernels are in k_stereo.cu.
+#include "common.cuh"
+#include "extractor.h"
+#include "kernels.h"
+
+using namespace orbfe;
+
+extern "C" {
+
+int orbfe_stereo_match_run(orbfe_extractor* hl, orbfe_extractor* hr, int batch, float mbf, float mb) {
+  ORBFE_ARG(hl && hr);
+  Extractor* l = reinterpret_cast<Extractor*>(hl);
+  Extractor* r = reinterpret_cast<Extractor*>(hr);
+  ORBFE_ARG(l->device == r->device && l->width == r->width && l->height == r->height);
+  ORBFE_ARG(l->geom.nlevels == r->geom.nlevels && l->geom.out_cap == r->geom.out_cap);
+  ORBFE_ARG(l->params.scale_factor == r->params.scale_factor);
+  ORBFE_ARG(batch >= 1 && batch <= l->max_batch && batch <= r->max_batch);
+  if (l->last_batch < batch || r->last_batch < batch) {
+    set_error("orbfe_stereo_match: run the extractors on %d images first", batch);
+    return ORBFE_ERR_STATE;
+  }
+  ORBFE_ARG(mb > 0.f);
+  DeviceGuard guard(l->device);
+  if (l != r) {  // order left's stream after right's queued work (the join at src/Frame.cc:91-92)
+    ORBFE_CUDA(cudaEventRecord(r->done, r->stream));
+    ORBFE_CUDA(cudaStreamWaitEvent(l->stream, r->done, 0));
+  }
+  launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream);
+  l->launches += kLaunchesPerStereo;
+  ORBFE_CUDA(cudaGetLastError());
+  return ORBFE_OK;
+}
+
+int orbfe_stereo_match_download(orbfe_extractor* hl, int batch, float* u_right, float* depth, int capacity,
+                                int32_t* n_matched) {
+  ORBFE_ARG(hl && capacity >= 0);
+  Extractor* l = reinterpret_cast<Extractor*>(hl);
+  ORBFE_ARG(batch >= 1 && batch <= l->max_batch);
+  DeviceGuard guard(l->device);
+  const int cap = l->geom.out_cap;
+  const int ncopy = capacity < cap ? capacity : cap;
+  if (u_right && ncopy > 0)
+    ORBFE_CUDA(cudaMemcpy2DAsync(u_right, (size_t)capacity * 4, l->arena.st_uright, (size_t)cap * 4, (size_t)ncopy * 4,
+                                 batch, cudaMemcpyDeviceToHost, l->stream));
+  if (depth && ncopy > 0)
+    ORBFE_CUDA(cudaMemcpy2DAsync(depth, (size_t)capacity * 4, l->arena.st_depth, (size_t)cap * 4, (size_t)ncopy * 4,
+                                 batch, cudaMemcpyDeviceToHost, l->stream));
+  if (n_matched)
+    ORBFE_CUDA(cudaMemcpyAsync(n_matched, l->arena.st_count, (size_t)batch * 4, cudaMemcpyDeviceToHost, l->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(l->stream));
+  return ORBFE_OK;
+}
+
+int orbfe_stereo_match(orbfe_extractor* hl, orbfe_extractor* hr, int batch, float mbf, float mb, float* u_right,
+                       float* depth, int capacity, int32_t* n_matched) {
+  int rc = orbfe_stereo_match_run(hl, hr, batch, mbf, mb);
+  if (rc != ORBFE_OK) return rc;
+  return orbfe_stereo_match_download(hl, batch, u_right, depth, capacity, n_matched);
+}
+
+}  // extern "C"

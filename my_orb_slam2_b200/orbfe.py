@@ -1,0 +1,321 @@
+"""ctypes binding of liborbfe.so — the C ABI declared in include/orbfe.h.
+
+The library is the product: hand-written sm_100a CUDA kernels behind plain-C entry points.  This module only
+marshals numpy arrays; it never computes results itself and has NO fallback: if the shared library is missing
+or no CUDA device works, the calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liborbfe.so")
+
+KEYPOINT_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"),
+     ("class_id", "<i4")]
+)
+assert KEYPOINT_DTYPE.itemsize == 28  # layout of cv::KeyPoint / orbfe_keypoint
+
+
+class OrbfeError(RuntimeError):
+    pass
+
+
+class ExtractorParams(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32)]
+
+
+class ExtractorInfo(C.Structure):
+    _fields_ = [("nlevels", C.c_int32), ("scale_factor", C.c_float), ("scale_factors", C.c_float * 16),
+                ("inv_scale_factors", C.c_float * 16), ("level_sigma2", C.c_float * 16),
+                ("inv_level_sigma2", C.c_float * 16), ("features_per_level", C.c_int32 * 16),
+                ("umax", C.c_int32 * 16), ("capacity", C.c_int32)]
+
+
+class FrameView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("u_right", C.c_void_p), ("desc", C.c_void_p),
+                ("mp_obs", C.c_void_p), ("min_x", C.c_float), ("min_y", C.c_float), ("max_x", C.c_float),
+                ("max_y", C.c_float), ("grid_inv_w", C.c_float), ("grid_inv_h", C.c_float), ("nlevels", C.c_int32),
+                ("scale_factors", C.c_void_p)]
+
+
+class MapPointsView(C.Structure):
+    _fields_ = [("m", C.c_int32), ("proj_x", C.c_void_p), ("proj_y", C.c_void_p), ("proj_xr", C.c_void_p),
+                ("level", C.c_void_p), ("view_cos", C.c_void_p), ("in_view", C.c_void_p), ("obs", C.c_void_p),
+                ("desc", C.c_void_p)]
+
+
+class LastFrameView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("valid", C.c_void_p), ("world_pos", C.c_void_p), ("obs", C.c_void_p),
+                ("desc", C.c_void_p), ("octave", C.c_void_p), ("angle", C.c_void_p), ("tcw", C.c_float * 12)]
+
+
+class CameraPose(C.Structure):
+    _fields_ = [("tcw", C.c_float * 12), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("mbf", C.c_float), ("mb", C.c_float)]
+
+
+class KeyFrameView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("u_right", C.c_void_p), ("desc", C.c_void_p),
+                ("has_mp", C.c_void_p), ("n_nodes", C.c_int32), ("node_ids", C.c_void_p),
+                ("node_offsets", C.c_void_p), ("node_features", C.c_void_p), ("nlevels", C.c_int32),
+                ("scale_factors", C.c_void_p), ("level_sigma2", C.c_void_p)]
+
+
+# every symbol include/orbfe.h declares: name -> (restype, argtypes)
+_P = C.c_void_p
+_I = C.c_int
+_F = C.c_float
+SYMBOLS = {
+    "orbfe_last_error": (C.c_char_p, []),
+    "orbfe_version": (C.c_char_p, []),
+    "orbfe_device_count": (_I, []),
+    "orbfe_extractor_create": (_I, [C.POINTER(ExtractorParams), _I, _I, _I, _I, C.POINTER(_P)]),
+    "orbfe_extractor_destroy": (None, [_P]),
+    "orbfe_extractor_get_info": (_I, [_P, C.POINTER(ExtractorInfo)]),
+    "orbfe_extract": (_I, [_P, _P, _I, _P, _P, _I, _P]),
+    "orbfe_extract_batch": (_I, [_P, _P, C.c_size_t, _I, _I, _P, _P, _I, _P]),
+    "orbfe_extract_upload": (_I, [_P, _P, C.c_size_t, _I, _I, _I]),
+    "orbfe_extract_run": (_I, [_P, _I]),
+    "orbfe_extract_download": (_I, [_P, _I, _P, _P, _I, _P]),
+    "orbfe_extractor_sync": (_I, [_P]),
+    "orbfe_extractor_stream": (_P, [_P]),
+    "orbfe_extractor_launch_count": (C.c_int64, [_P]),
+    "orbfe_extractor_level": (_I, [_P, _I, _I, C.POINTER(_P), C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)]),
+    "orbfe_extractor_download_level": (_I, [_P, _I, _I, _P, _I]),
+    "orbfe_extractor_device_results": (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_I)]),
+    "orbfe_extractor_debug_candidates": (_I, [_P, _I, _I, _I, _P, _P, _P, _P]),
+    "orbfe_extractor_debug_level_keypoints": (_I, [_P, _I, _I, _I, _P, _P, _P, _P]),
+    "orbfe_stereo_match": (_I, [_P, _P, _I, _F, _F, _P, _P, _I, _P]),
+    "orbfe_stereo_match_run": (_I, [_P, _P, _I, _F, _F]),
+    "orbfe_stereo_match_download": (_I, [_P, _I, _P, _P, _I, _P]),
+    "orbfe_matcher_create": (_I, [_I, C.POINTER(_P)]),
+    "orbfe_matcher_destroy": (None, [_P]),
+    "orbfe_matcher_launch_count": (C.c_int64, [_P]),
+    "orbfe_matcher_stream": (_P, [_P]),
+    "orbfe_descriptor_distance": (_I, [_P, _P, _P, _I, _P]),
+    "orbfe_search_by_projection_map": (_I, [_P, C.POINTER(FrameView), C.POINTER(MapPointsView), _F, _F, _P, _P]),
+    "orbfe_search_by_projection_last": (_I, [_P, C.POINTER(FrameView), C.POINTER(CameraPose),
+                                             C.POINTER(LastFrameView), _F, _I, _I, _P, _P]),
+    "orbfe_search_for_triangulation": (_I, [_P, C.POINTER(KeyFrameView), C.POINTER(KeyFrameView), _P, _F, _F, _I, _I,
+                                            _P, _I, _P]),
+    "orbfe_hamming_bruteforce": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
+    "orbfe_hamming_bruteforce_device": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
+    "orbfe_hamming_merge_device": (_I, [_P, _P, _P, _I, _I, _P, _P]),
+    "orbfe_matcher_sync": (_I, [_P]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load liborbfe.so (fails loudly when it was not built: there is no other implementation)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise OrbfeError("%s is missing: build it with `make -C my_orb_slam2_b200/csrc` (or "
+                             "__graft_entry__.build()); there is no CPU fallback" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise OrbfeError("orbfe status %d: %s" % (rc, lib().orbfe_last_error().decode()))
+
+
+def device_count():
+    return lib().orbfe_device_count()
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _u8(a):
+    return np.ascontiguousarray(a, dtype=np.uint8)
+
+
+class Extractor:
+    """Thin object wrapper of the orbfe_extractor_* functions (one handle = one stream + its device arenas)."""
+
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th, min_th, width, height, max_batch=1, device=0):
+        self.params = ExtractorParams(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        self.width, self.height, self.max_batch, self.device = width, height, max_batch, device
+        h = C.c_void_p()
+        check(lib().orbfe_extractor_create(C.byref(self.params), width, height, max_batch, device, C.byref(h)))
+        self._h = h
+        self.info = ExtractorInfo()
+        check(lib().orbfe_extractor_get_info(self._h, C.byref(self.info)))
+        self.capacity = self.info.capacity
+        self.nlevels = nlevels
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbfe_extractor_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- synchronous calls ---------------------------------------------------------------
+    def extract(self, image):
+        """ORBextractor::operator() on one H x W uint8 image -> (keypoints[n], descriptors[n,32])."""
+        kps, desc, counts = self.extract_batch(image[None])
+        return kps[0][:counts[0]].copy(), desc[0][:counts[0]].copy()
+
+    def extract_batch(self, images):
+        images = _u8(images)
+        b, h, w = images.shape
+        if (w, h) != (self.width, self.height):
+            raise ValueError("image size %dx%d != handle size %dx%d" % (w, h, self.width, self.height))
+        kps = np.zeros((b, self.capacity), KEYPOINT_DTYPE)
+        desc = np.zeros((b, self.capacity, 32), np.uint8)
+        counts = np.zeros(b, np.int32)
+        check(lib().orbfe_extract_batch(self._h, _p(images), h * w, w, b, _p(kps), _p(desc), self.capacity,
+                                        _p(counts)))
+        return kps, desc, counts
+
+    # -- asynchronous pieces ---------------------------------------------------------------
+    def upload(self, images_ptr, batch, image_stride=None, row_stride=None, on_device=False):
+        check(lib().orbfe_extract_upload(self._h, images_ptr, image_stride or self.width * self.height,
+                                         row_stride or self.width, batch, int(on_device)))
+
+    def run(self, batch):
+        check(lib().orbfe_extract_run(self._h, batch))
+
+    def download(self, batch, kps, desc, counts):
+        check(lib().orbfe_extract_download(self._h, batch, _p(kps), _p(desc), kps.shape[-1], _p(counts)))
+
+    def sync(self):
+        check(lib().orbfe_extractor_sync(self._h))
+
+    @property
+    def stream(self):
+        return lib().orbfe_extractor_stream(self._h)
+
+    @property
+    def launch_count(self):
+        return lib().orbfe_extractor_launch_count(self._h)
+
+    # -- pyramid / stage dumps ------------------------------------------------------------
+    def level_shape(self, lv):
+        w, h, pitch, ptr = C.c_int(), C.c_int(), C.c_int(), C.c_void_p()
+        check(lib().orbfe_extractor_level(self._h, 0, lv, C.byref(ptr), C.byref(pitch), C.byref(w), C.byref(h)))
+        return h.value, w.value
+
+    def level(self, lv, image_index=0):
+        """mvImagePyramid[lv] of image `image_index` of the last run, copied to the host."""
+        h, w = self.level_shape(lv)
+        out = np.empty((h, w), np.uint8)
+        check(lib().orbfe_extractor_download_level(self._h, image_index, lv, _p(out), w))
+        return out
+
+    def _debug(self, fn, lv, image_index):
+        n = C.c_int32()
+        check(fn(self._h, image_index, lv, 0, None, None, None, C.byref(n)))
+        xs, ys, sc = (np.empty(max(n.value, 1), np.int32) for _ in range(3))
+        check(fn(self._h, image_index, lv, n.value, _p(xs), _p(ys), _p(sc), C.byref(n)))
+        return xs[:n.value], ys[:n.value], sc[:n.value]
+
+    def candidates(self, lv, image_index=0):
+        return self._debug(lib().orbfe_extractor_debug_candidates, lv, image_index)
+
+    def level_keypoints(self, lv, image_index=0):
+        return self._debug(lib().orbfe_extractor_debug_level_keypoints, lv, image_index)
+
+
+def stereo_match(left, right, batch, mbf, mb):
+    """Frame::ComputeStereoMatches on the resident results of two Extractor handles -> (uRight, depth, n)."""
+    ur = np.empty((batch, left.capacity), np.float32)
+    dp = np.empty((batch, left.capacity), np.float32)
+    n = np.zeros(batch, np.int32)
+    check(lib().orbfe_stereo_match(left._h, right._h, batch, mbf, mb, _p(ur), _p(dp), left.capacity, _p(n)))
+    return ur, dp, n
+
+
+class Matcher:
+    """Thin object wrapper of the orbfe_matcher_* / search functions."""
+
+    def __init__(self, device=0):
+        h = C.c_void_p()
+        check(lib().orbfe_matcher_create(device, C.byref(h)))
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbfe_matcher_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launch_count(self):
+        return lib().orbfe_matcher_launch_count(self._h)
+
+    @property
+    def stream(self):
+        return lib().orbfe_matcher_stream(self._h)
+
+    def sync(self):
+        check(lib().orbfe_matcher_sync(self._h))
+
+    def descriptor_distance(self, a, b):
+        a, b = _u8(a).reshape(-1, 32), _u8(b).reshape(-1, 32)
+        out = np.empty(len(a), np.int32)
+        check(lib().orbfe_descriptor_distance(self._h, _p(a), _p(b), len(a), _p(out)))
+        return out
+
+    def search_by_projection_map(self, frame, mps, th, nnratio):
+        assigned = np.empty(max(frame.struct.n, 1), np.int32)
+        n = C.c_int32()
+        check(lib().orbfe_search_by_projection_map(self._h, C.byref(frame.struct), C.byref(mps.struct), th, nnratio,
+                                                   _p(assigned), C.byref(n)))
+        return assigned[:frame.struct.n], n.value
+
+    def search_by_projection_last(self, cur, cam, last, th, mono, check_ori):
+        assigned = np.empty(max(cur.struct.n, 1), np.int32)
+        n = C.c_int32()
+        check(lib().orbfe_search_by_projection_last(self._h, C.byref(cur.struct), C.byref(cam), C.byref(last.struct),
+                                                    th, int(mono), int(check_ori), _p(assigned), C.byref(n)))
+        return assigned[:cur.struct.n], n.value
+
+    def search_for_triangulation(self, kf1, kf2, F12, ex, ey, only_stereo, check_ori):
+        F12 = np.ascontiguousarray(F12, np.float32).reshape(9)
+        pairs = np.empty((max(kf1.struct.n, 1), 2), np.int32)
+        n = C.c_int32()
+        check(lib().orbfe_search_for_triangulation(self._h, C.byref(kf1.struct), C.byref(kf2.struct), _p(F12), ex, ey,
+                                                   int(only_stereo), int(check_ori), _p(pairs), len(pairs),
+                                                   C.byref(n)))
+        return pairs[:n.value].copy()
+
+    def hamming_bruteforce(self, query, mapd, index_base=0):
+        query, mapd = _u8(query).reshape(-1, 32), _u8(mapd).reshape(-1, 32)
+        best = np.empty(len(query), np.uint64)
+        second = np.empty(len(query), np.uint64)
+        check(lib().orbfe_hamming_bruteforce(self._h, _p(query), len(query), _p(mapd), len(mapd), index_base,
+                                             _p(best), _p(second)))
+        return best, second
+
+    def hamming_bruteforce_device(self, d_query, nq, d_map, nm, index_base, d_best, d_second):
+        """Device-pointer variant (ints from torch .data_ptr()); asynchronous on the matcher's stream."""
+        check(lib().orbfe_hamming_bruteforce_device(self._h, d_query, nq, d_map, nm, index_base, d_best, d_second))
+
+    def hamming_merge_device(self, d_best_all, d_second_all, shards, nq, d_best, d_second):
+        check(lib().orbfe_hamming_merge_device(self._h, d_best_all, d_second_all, shards, nq, d_best, d_second))

@@ -110,3 +110,139 @@ def flip_bits(desc, p, rng):
     """Flip each of the 256 bits of every descriptor with probability p."""
     flips = rng.random((desc.shape[0], 256)) < p
     return desc ^ np.packbits(flips, axis=1, bitorder="little")
+
+
+# --------------------------------------------------------------------------------------------------------
+# Matcher workloads (BASELINE.json configs 4 and 5; SURVEY.md 8(d)).  Plain dicts of numpy arrays so that
+# both the product views (my_orb_slam2_b200.frontend) and the test-side checker views can be built
+# from the same data.
+# --------------------------------------------------------------------------------------------------------
+def scale_factors(nlevels=8, sf=1.2):
+    out = [np.float32(1.0)]
+    for _ in range(1, nlevels):
+        out.append(np.float32(float(out[-1]) * float(np.float32(sf))))
+    return np.array(out, np.float32)
+
+
+def frame_arrays(kps, desc, bounds, seed=0, stereo_frac=0.6, taken_frac=0.05, nlevels=8):
+    """Frame members read by SearchByProjection: mvKeysUn, mvuRight, mDescriptors, mvpMapPoints[i]->Observations()."""
+    rng = np.random.default_rng([seed, 10])
+    n = len(kps)
+    u_right = np.where(rng.random(n) < stereo_frac, kps["x"] - rng.uniform(2, 60, n).astype(np.float32), -1.0)
+    mp_obs = np.where(rng.random(n) < taken_frac, rng.integers(0, 4, n), -1).astype(np.int32)
+    return dict(keys_un=kps, u_right=u_right.astype(np.float32), desc=desc, mp_obs=mp_obs, bounds=bounds,
+                scale_factors=scale_factors(nlevels))
+
+
+def map_points_case(frame, n_map=20000, n_true=1500, seed=0, bf=386.1448):
+    """Local map of config 4: n_true points that really project onto frame features + distractors."""
+    rng = np.random.default_rng([seed, 11])
+    kps, desc = frame["keys_un"], frame["desc"]
+    n = len(kps)
+    min_x, min_y, max_x, max_y = frame["bounds"]
+    src = rng.integers(0, n, n_true)  # with replacement: several map points compete for one feature
+    t_desc = flip_bits(desc[src], 0.08, rng)
+    t_x = kps["x"][src] + rng.normal(0, 1.5, n_true)
+    t_y = kps["y"][src] + rng.normal(0, 1.5, n_true)
+    t_lvl = np.clip(kps["octave"][src] + rng.integers(0, 2, n_true), 0, 7)
+    n_d = n_map - n_true
+    d_desc = rng.integers(0, 256, (n_d, 32), dtype=np.uint8)
+    d_x = rng.uniform(min_x, max_x, n_d)
+    d_y = rng.uniform(min_y, max_y, n_d)
+    d_lvl = rng.integers(0, 8, n_d)
+    perm = rng.permutation(n_map)
+    proj_x = np.concatenate([t_x, d_x])[perm].astype(np.float32)
+    proj_y = np.concatenate([t_y, d_y])[perm].astype(np.float32)
+    level = np.concatenate([t_lvl, d_lvl])[perm].astype(np.int32)
+    mdesc = np.concatenate([t_desc, d_desc])[perm]
+    z = rng.uniform(5, 80, n_map)
+    proj_xr = (proj_x - bf / z).astype(np.float32)
+    view_cos = rng.uniform(0.9, 1.0, n_map).astype(np.float32)
+    view_cos[rng.random(n_map) < 0.3] = np.float32(0.9995)  # some inside the narrow-radius branch
+    in_view = (rng.random(n_map) >= 0.1).astype(np.uint8)
+    obs = rng.integers(1, 12, n_map).astype(np.int32)
+    obs[rng.random(n_map) < 0.02] = 0  # map points without observations do not block later ones
+    return dict(proj_x=proj_x, proj_y=proj_y, proj_xr=proj_xr, level=level, view_cos=view_cos, in_view=in_view,
+                obs=obs, desc=mdesc)
+
+
+def last_frame_case(frame, seed=0, fx=718.856, fy=718.856, cx=607.1928, cy=185.2157, bf=386.1448, tz=0.0):
+    """A previous frame whose map points re-project near the current frame's features (config 4, overload ii).
+    tz: translation of the last camera along the optical axis relative to the current one (>mb: forward)."""
+    rng = np.random.default_rng([seed, 12])
+    kps, desc = frame["keys_un"], frame["desc"]
+    n = len(kps)
+    ang = 0.01
+    R = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+    t = np.array([0.05, -0.02, 0.1])
+    tcw = np.hstack([R, t[:, None]]).astype(np.float32)
+    z = rng.uniform(4, 60, n)
+    u = kps["x"] + rng.normal(0, 2.0, n)
+    v = kps["y"] + rng.normal(0, 2.0, n)
+    pc = np.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], 1)
+    pw = (pc - t) @ R  # R^T (pc - t)
+    tl = t + np.array([0.0, 0.0, tz])
+    tcw_last = np.hstack([R, tl[:, None]]).astype(np.float32)
+    valid = (rng.random(n) < 0.8).astype(np.uint8)
+    obs = rng.integers(1, 9, n).astype(np.int32)
+    obs[rng.random(n) < 0.03] = 0
+    angle = (kps["angle"] + 20.0 + rng.normal(0, 4.0, n)) % 360.0
+    wild = rng.random(n) < 0.1
+    angle[wild] = rng.uniform(0, 360, wild.sum())
+    d = flip_bits(desc, 0.06, rng)
+    octave = np.clip(kps["octave"] + rng.integers(-1, 2, n), 0, 7).astype(np.int32)
+    return dict(valid=valid, world_pos=pw.astype(np.float32), obs=obs, desc=d, octave=octave,
+                angle=angle.astype(np.float32), tcw=tcw_last), dict(tcw=tcw, fx=fx, fy=fy, cx=cx, cy=cy, mbf=bf,
+                                                                    mb=bf / fx)
+
+
+def keyframe_pair_case(kps, desc, seed=0, n_nodes=100, nlevels=8):
+    """Two keyframes for SearchForTriangulation: kf2 = kf1 shifted along x (epipolar lines are image rows)."""
+    rng = np.random.default_rng([seed, 13])
+    n = len(kps)
+    sf = scale_factors(nlevels)
+    sig2 = (sf * sf).astype(np.float32)
+    k2 = kps.copy()
+    k2["x"] = kps["x"] - rng.uniform(3, 40, n).astype(np.float32)
+    k2["y"] = kps["y"] + rng.normal(0, 0.7, n).astype(np.float32)
+    k2["angle"] = (kps["angle"] + rng.normal(0, 3.0, n)) % 360.0
+    d2 = flip_bits(desc, 0.05, rng)
+    perm = rng.permutation(n)  # kf2 stores its features in another order
+    k2, d2 = k2[perm], d2[perm]
+    node1 = rng.integers(0, n_nodes, n).astype(np.uint32) * 7 + 3
+    node2 = node1[perm].copy()
+    moved = rng.random(n) < 0.1
+    node2[moved] = rng.integers(0, n_nodes + 20, moved.sum()).astype(np.uint32) * 7 + 3
+
+    def csr(node):
+        ids = np.unique(node)
+        order = np.lexsort((np.arange(len(node)), node))
+        counts = np.array([(node == i).sum() for i in ids])
+        return ids.astype(np.uint32), np.concatenate([[0], np.cumsum(counts)]).astype(np.int32), order.astype(np.int32)
+
+    def kf(k, d, node, s):
+        r = np.random.default_rng([seed, s])
+        ids, offs, feats = csr(node)
+        return dict(keys_un=k, u_right=np.where(r.random(len(k)) < 0.5, k["x"] - 5.0, -1.0).astype(np.float32), desc=d,
+                    has_mp=(r.random(len(k)) < 0.3).astype(np.uint8), node_ids=ids, node_offsets=offs,
+                    node_features=feats, scale_factors=sf, level_sigma2=sig2)
+
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32)
+    return kf(kps, desc, node1, 14), kf(k2, d2, node2, 15), F12, (np.float32(2000.0), np.float32(180.0))
+
+
+def bruteforce_case(nq=8192, nm=1 << 20, n_planted=4096, seed=1):
+    """Config 5: uniform random queries / map with planted near-duplicates (<= 20 flipped bits)."""
+    rng = np.random.default_rng([seed, 16])
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    m = rng.integers(0, 256, (nm, 32), dtype=np.uint8)
+    n_planted = min(n_planted, nq, nm)
+    qi = rng.permutation(nq)[:n_planted]
+    mi = rng.permutation(nm)[:n_planted]
+    planted = q[qi].copy()
+    for r in range(n_planted):
+        bits = rng.permutation(256)[:rng.integers(0, 21)]
+        for bpos in bits:
+            planted[r, bpos >> 3] ^= np.uint8(1 << (bpos & 7))
+    m[mi] = planted
+    return q, m

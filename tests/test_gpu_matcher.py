@@ -1,0 +1,130 @@
+"""GPU parity of the ORBmatcher path against the CPU oracle: DescriptorDistance, brute-force top-2,
+SearchByProjection (both overloads, incl. the sequential claim and the rotation histogram) and
+SearchForTriangulation.  All outputs are indices / integers: bit-exact."""
+import numpy as np
+import pytest
+
+from cases import extract_with_oracle, views
+from my_orb_slam2_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def fe():
+    from my_orb_slam2_b200 import frontend
+    return frontend
+
+
+@pytest.fixture(scope="module")
+def kitti_features(oracle):
+    params, img, ex, (kp, desc) = extract_with_oracle(oracle, "kitti", 0)
+    return kp, desc
+
+
+def test_descriptor_distance(fe, oracle):
+    from my_orb_slam2_b200 import orbfe
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 256, (1000, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (1000, 32), dtype=np.uint8)
+    a[0] = 0; b[0] = 0; a[1] = 0; b[1] = 255
+    got = orbfe.Matcher().descriptor_distance(a, b)
+    want = np.unpackbits(a ^ b, axis=1).sum(1)
+    assert np.array_equal(got, want) and got[0] == 0 and got[1] == 256
+    assert fe.ORBmatcher.DescriptorDistance(a[5], b[5]) == oracle.descriptor_distance(a[5], b[5])
+
+
+@pytest.mark.parametrize("nq,nm,base", [(1, 1, 0), (7, 33, 5), (600, 5000, 1 << 33), (8192, 20000, 0)])
+def test_bruteforce_vs_oracle(oracle, nq, nm, base):
+    from my_orb_slam2_b200 import orbfe
+    q, m = synth.bruteforce_case(nq, nm, min(nq, nm) // 2, seed=nq)
+    if nm > 40:
+        m[17] = m[3]  # exact duplicates: ties must go to the lowest index
+        m[29] = m[3]
+        q[0] = m[3]
+    best, second = orbfe.Matcher().hamming_bruteforce(q, m, base)
+    ob, os_ = oracle.hamming_bruteforce(q, m, base)
+    assert np.array_equal(best, ob) and np.array_equal(second, os_)
+
+
+def test_bruteforce_full_size_properties():
+    """Config 5 per-GPU shard (8192 x 131072) and a 1M map: checked through properties the oracle-free way:
+    planted duplicates are found, sharded top-2 merged == unsharded top-2, best <= second."""
+    from my_orb_slam2_b200 import orbfe
+    q, m = synth.bruteforce_case(8192, 1 << 20, 4096, seed=1)
+    mt = orbfe.Matcher()
+    best, second = mt.hamming_bruteforce(q, m, 0)
+    assert np.all(best <= second)
+    # exact check on a sample of queries with numpy
+    for qi in [0, 1, 777, 8191]:
+        d = np.unpackbits(q[qi][None] ^ m, axis=1).sum(1).astype(np.uint64)
+        keys = np.sort((d << np.uint64(32)) | np.arange(len(m), dtype=np.uint64))
+        assert best[qi] == keys[0] and second[qi] == keys[1]
+    assert (best >> np.uint64(32) <= 20).sum() >= 4096 - 8  # planted near-duplicates found
+    # 8 shards merged on the host == unsharded
+    shard = (1 << 20) // 8
+    parts = [mt.hamming_bruteforce(q, m[i * shard:(i + 1) * shard], i * shard) for i in range(8)]
+    allk = np.sort(np.concatenate([np.stack(p, 1) for p in parts], 1), axis=1)
+    assert np.array_equal(allk[:, 0], best) and np.array_equal(allk[:, 1], second)
+
+
+@pytest.mark.parametrize("th,seed", [(1.0, 0), (3.0, 1), (5.0, 2)])
+def test_search_by_projection_map(fe, oracle, kitti_features, th, seed):
+    kp, desc = kitti_features
+    frame = synth.frame_arrays(kp, desc, (0.0, 0.0, 1241.0, 376.0), seed=seed)
+    mps = synth.map_points_case(frame, 20000, 1500, seed=seed)
+    ofv, omv = views(oracle, frame=frame, mps=mps)
+    want, wn = oracle.search_by_projection_map(ofv, omv, th, 0.8)
+    fv, mv = views(fe, frame=frame, mps=mps)
+    got, gn = fe.ORBmatcher(0.8).SearchByProjection(fv, mv, th)
+    assert gn == wn and np.array_equal(got, want)
+    assert wn > 300
+
+
+def test_search_by_projection_map_heavy_conflicts(fe, oracle, kitti_features):
+    # every map point is a "true" one drawn with replacement from 200 features: long claim chains
+    kp, desc = kitti_features
+    frame = synth.frame_arrays(kp[:200], desc[:200], (0.0, 0.0, 1241.0, 376.0), seed=4, taken_frac=0.0)
+    mps = synth.map_points_case(frame, 3000, 3000, seed=4)
+    ofv, omv = views(oracle, frame=frame, mps=mps)
+    want, wn = oracle.search_by_projection_map(ofv, omv, 5.0, 0.8)
+    fv, mv = views(fe, frame=frame, mps=mps)
+    got, gn = fe.ORBmatcher(0.8).SearchByProjection(fv, mv, 5.0)
+    assert gn == wn and np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("tz,mono,check_ori,th", [(0.0, False, True, 7.0), (2.0, False, True, 7.0),
+                                                    (-2.0, False, True, 15.0), (2.0, True, False, 15.0)])
+def test_search_by_projection_last(fe, oracle, kitti_features, tz, mono, check_ori, th):
+    kp, desc = kitti_features
+    frame = synth.frame_arrays(kp, desc, (0.0, 0.0, 1241.0, 376.0), seed=7)
+    last, cam = synth.last_frame_case(frame, seed=7, tz=tz)
+    ofv, olv, ocv = views(oracle, frame=frame, last=last, cam=cam)
+    want, wn = oracle.search_by_projection_last(ofv, ocv, olv, th, mono, check_ori)
+    fv, lv, cv = views(fe, frame=frame, last=last, cam=cam)
+    got, gn = fe.ORBmatcher(0.9, check_ori).SearchByProjection(fv, lv, th, bMono=mono, cam=cv)
+    assert gn == wn and np.array_equal(got, want)
+    assert wn > 300
+
+
+@pytest.mark.parametrize("only_stereo,check_ori", [(False, False), (False, True), (True, True)])
+def test_search_for_triangulation(fe, oracle, kitti_features, only_stereo, check_ori):
+    kp, desc = kitti_features
+    k1, k2, F12, ep = synth.keyframe_pair_case(kp, desc, seed=3)
+    want = oracle.search_for_triangulation(views(oracle, kf=k1), views(oracle, kf=k2), F12, float(ep[0]), float(ep[1]),
+                                           only_stereo, check_ori)
+    got = fe.ORBmatcher(0.6, check_ori).SearchForTriangulation(views(fe, kf=k1), views(fe, kf=k2), F12, ep, only_stereo)
+    assert np.array_equal(got, want)
+    assert len(want) > (50 if only_stereo else 300)
+
+
+def test_empty_inputs(fe):
+    from my_orb_slam2_b200 import orbfe
+    mt = orbfe.Matcher()
+    kp = np.zeros(0, orbfe.KEYPOINT_DTYPE)
+    frame = synth.frame_arrays(kp, np.zeros((0, 32), np.uint8), (0.0, 0.0, 100.0, 100.0))
+    mps = synth.map_points_case(synth.frame_arrays(np.zeros(1, orbfe.KEYPOINT_DTYPE), np.zeros((1, 32), np.uint8),
+                                                   (0.0, 0.0, 100.0, 100.0)), 10, 5)
+    fv, mv = views(fe, frame=frame, mps=mps)
+    got, n = mt.search_by_projection_map(fv, mv, 1.0, 0.8)
+    assert n == 0 and len(got) == 0
