@@ -157,7 +157,7 @@ int orbfe_search_for_triangulation(orbfe_matcher* m, const orbfe_keyframe_view* 
                                    int only_stereo, int check_ori, int32_t* pairs, int cap, int32_t* n_pairs);
 
 /* Brute-force Hamming (BASELINE.json config 5): per query the two smallest
- * keys (dist << 32 | index_base + j) over the map shard; ties -> lowest index.
+ * keys (dist << 32 | index_base + j) over the map shard (index_base + nm <= 2^32); ties -> lowest index.
  * Host arrays in/out. */
 int orbfe_hamming_bruteforce(orbfe_matcher* m, const uint8_t* query, int nq, const uint8_t* map, int nm,
                              int64_t index_base, uint64_t* best, uint64_t* second);

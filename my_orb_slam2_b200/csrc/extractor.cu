@@ -216,6 +216,11 @@ static void free_arenas(Extractor* e) {
   cudaFree(a.out_count); cudaFree(a.flags); cudaFree(a.st_uright); cudaFree(a.st_depth); cudaFree(a.st_sad);
   cudaFree(a.st_count);
   if (e->h_flags) cudaFreeHost(e->h_flags);
+  if (e->prof_ev) {
+    for (int i = 0; i < Extractor::kProfRuns * 8; ++i) cudaEventDestroy(e->prof_ev[i]);
+    delete[] e->prof_ev;
+    e->prof_ev = nullptr;
+  }
   a = ExtractorArena();
 }
 
@@ -331,13 +336,58 @@ int orbfe_extract_run(orbfe_extractor* h, int batch) {
   const ExtractorArena& a = e->arena;
   ORBFE_CUDA(cudaMemsetAsync(a.cand_count, 0, (size_t)batch * kMaxLevels * sizeof(int32_t), e->stream));
   ORBFE_CUDA(cudaMemsetAsync(a.flags, 0, (size_t)batch * sizeof(int32_t), e->stream));
+  cudaEvent_t* ev = (e->profiling && e->prof_runs < Extractor::kProfRuns) ? e->prof_ev + 5 * e->prof_runs : nullptr;
+  if (ev) cudaEventRecord(ev[0], e->stream);
   for (int l = 1; l < g.nlevels; ++l) launch_pyramid_level(g, a, l, batch, e->stream);  // ComputePyramid (:1075)
+  if (ev) cudaEventRecord(ev[1], e->stream);
   if (g.total_cells > 0) launch_fast_cells(g, a, batch, e->stream);                      // :776-850
+  if (ev) cudaEventRecord(ev[2], e->stream);
   launch_quadtree(g, a, batch, e->stream);                                               // :853
+  if (ev) cudaEventRecord(ev[3], e->stream);
   launch_describe(g, a, batch, e->stream);                                               // :873-874, :1096-1126
+  if (ev) { cudaEventRecord(ev[4], e->stream); ++e->prof_runs; }
   e->launches += (g.nlevels - 1) + (g.total_cells > 0 ? 1 : 0) + 2;
   e->last_batch = batch;
   ORBFE_CUDA(cudaGetLastError());
+  return ORBFE_OK;
+}
+
+int orbfe_extractor_set_profiling(orbfe_extractor* h, int enable) {
+  ORBFE_ARG(h);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  DeviceGuard guard(e->device);
+  if (enable && !e->prof_ev) {
+    const int n = Extractor::kProfRuns * 8;
+    e->prof_ev = new cudaEvent_t[n];
+    for (int i = 0; i < n; ++i) ORBFE_CUDA(cudaEventCreate(&e->prof_ev[i]));
+  }
+  e->profiling = enable != 0;
+  e->prof_runs = 0;
+  e->prof_stereo_runs = 0;
+  return ORBFE_OK;
+}
+
+int orbfe_extractor_stage_times(orbfe_extractor* h, float* ms, int32_t* runs, int32_t* stereo_runs) {
+  ORBFE_ARG(h && ms);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  DeviceGuard guard(e->device);
+  ORBFE_CUDA(cudaStreamSynchronize(e->stream));
+  for (int s = 0; s < Extractor::kStages; ++s) ms[s] = 0.f;
+  for (int r = 0; r < e->prof_runs; ++r)
+    for (int s = 0; s < 4; ++s) {
+      float t = 0.f;
+      ORBFE_CUDA(cudaEventElapsedTime(&t, e->prof_ev[5 * r + s], e->prof_ev[5 * r + s + 1]));
+      ms[s] += t;
+    }
+  cudaEvent_t* sev = e->prof_ev ? e->prof_ev + 5 * Extractor::kProfRuns : nullptr;
+  for (int r = 0; r < e->prof_stereo_runs; ++r)
+    for (int s = 0; s < 2; ++s) {
+      float t = 0.f;
+      ORBFE_CUDA(cudaEventElapsedTime(&t, sev[3 * r + s], sev[3 * r + s + 1]));
+      ms[4 + s] += t;
+    }
+  if (runs) *runs = e->prof_runs;
+  if (stereo_runs) *stereo_runs = e->prof_stereo_runs;
   return ORBFE_OK;
 }
 

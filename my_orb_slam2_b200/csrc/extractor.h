@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cstdint>
+
 #include "geom.h"
 #include "kernels.h"
 #include "../../include/orbfe.h"
@@ -20,6 +22,12 @@ struct Extractor {
   int32_t* h_flags = nullptr;   // pinned
   int64_t launches = 0;
   int last_batch = 0;
+  // optional per-stage CUDA-event timing (bench.py roofline): ring of runs x (kStages+1) events
+  static constexpr int kStages = 6;   // pyramid, fast, quadtree, describe, stereo match, stereo median
+  static constexpr int kProfRuns = 256;
+  bool profiling = false;
+  cudaEvent_t* prof_ev = nullptr;     // [kProfRuns][5] extractor stages; [kProfRuns][3] stereo stages after them
+  int prof_runs = 0, prof_stereo_runs = 0;
 };
 
 // opt in to large dynamic shared memory etc.; defined in k_quadtree.cu

@@ -21,6 +21,8 @@
 // x | y<<12 | score<<24 with x,y relative to minBorder, as the reference stores
 // them (:841-846).  List order is not the reference's; the consumer
 // (k_quadtree.cu) breaks ties by the reference's order key computed from (x,y).
+#include <cstdio>
+
 #include "kernels.h"
 
 namespace orbfe {
@@ -49,19 +51,23 @@ __device__ __forceinline__ int corner_strength(const uint8_t* p) {
   d[4] = v - p[3];            d[5] = v - p[-RS + 3];      d[6] = v - p[-2 * RS + 2];  d[7] = v - p[-3 * RS + 1];
   d[8] = v - p[-3 * RS];      d[9] = v - p[-3 * RS - 1];  d[10] = v - p[-2 * RS - 2]; d[11] = v - p[-RS - 3];
   d[12] = v - p[-3];          d[13] = v - p[RS - 3];      d[14] = v - p[2 * RS - 2];  d[15] = v - p[3 * RS - 1];
-  int lo1[16], hi1[16], lo2[16], hi2[16];
+  // min over every 9-arc of d (darker ring) and of e = -d (brighter ring).  NB: written with two min chains on
+  // purpose: ptxas 12.9 drops the negation when max(a, -b) is fused into VIMNMX3 on sm_100a (measured).
+  int e[16];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) { lo1[i] = min(d[i], d[(i + 1) & 15]); hi1[i] = max(d[i], d[(i + 1) & 15]); }
+  for (int i = 0; i < 16; ++i) e[i] = -d[i];
+  int a1[16], b1[16], a2[16], b2[16];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) { lo2[i] = min(lo1[i], lo1[(i + 2) & 15]); hi2[i] = max(hi1[i], hi1[(i + 2) & 15]); }
+  for (int i = 0; i < 16; ++i) { a1[i] = min(d[i], d[(i + 1) & 15]); b1[i] = min(e[i], e[(i + 1) & 15]); }
 #pragma unroll
-  for (int i = 0; i < 16; ++i) { lo1[i] = min(lo2[i], lo2[(i + 4) & 15]); hi1[i] = max(hi2[i], hi2[(i + 4) & 15]); }
+  for (int i = 0; i < 16; ++i) { a2[i] = min(a1[i], a1[(i + 2) & 15]); b2[i] = min(b1[i], b1[(i + 2) & 15]); }
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { a1[i] = min(a2[i], a2[(i + 4) & 15]); b1[i] = min(b2[i], b2[(i + 4) & 15]); }
   int best = 0;
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
-    const int lo9 = min(lo1[i], d[(i + 8) & 15]);
-    const int hi9 = max(hi1[i], d[(i + 8) & 15]);
-    best = max(best, max(lo9, -hi9));
+    best = max(best, min(a1[i], d[(i + 8) & 15]));
+    best = max(best, min(b1[i], e[(i + 8) & 15]));
   }
   return best;
 }
@@ -101,6 +107,12 @@ __global__ void __launch_bounds__(FAST_T) fast_cells_kernel(const __grid_constan
   for (int i = tid; i < (ROI_MAX * RS) / 4; i += FAST_T) reinterpret_cast<uint32_t*>(score)[i] = 0u;
   __syncthreads();
 
+#ifdef ORBFE_DEBUG_FAST
+  if (blockIdx.x == 0 && b == 0 && tid == 0) {
+    printf("DBG cell0 lvl %d x0 %d y0 %d cw %d ch %d pitch %d ini %d min %d wcell %d hcell %d ncols %d\n", lvl, x0, y0, cw, ch, L.pitch, g.ini_th, g.min_th, L.w_cell, L.h_cell, L.n_cols);
+    for (int r = 0; r < 8; ++r) { for (int c = 0; c < 12; ++c) printf("%3d ", roi[r * RS + c]); printf("\n"); }
+  }
+#endif
   const int t_lo = min(g.ini_th, g.min_th);
   const int dw = cw - 6, dh = ch - 6, npx = dw * dh;
   // stage 1: quick reject
@@ -175,6 +187,12 @@ __global__ void __launch_bounds__(FAST_T) fast_cells_kernel(const __grid_constan
   }
   __syncthreads();
   const int ne = n2;
+#ifdef ORBFE_DEBUG_FAST
+  if (blockIdx.x == 0 && b == 0 && tid == 0) {
+    printf("DBG n1 %d nc %d n3 %d n_hi %d ne %d\n", n1, c2, c3, n_hi, ne);
+    for (int i = 0; i < ne; ++i) printf("DBG emit pos %d -> x %d y %d score %d\n", list2[i], list2[i] % RS, list2[i] / RS, score[list2[i]]);
+  }
+#endif
   if (ne == 0) return;
   if (tid == 0) out_base = atomicAdd(&cand_count[b * kMaxLevels + lvl], ne);
   __syncthreads();

@@ -206,13 +206,16 @@ __global__ void __launch_bounds__(1024) stereo_median_kernel(const __grid_consta
 }
 
 void launch_stereo(const PyrGeom& g, const ExtractorArena& l, const ExtractorArena& r, int batch, float mbf, float mb,
-                   cudaStream_t s) {
+                   cudaStream_t s, cudaEvent_t* ev) {
+  if (ev) cudaEventRecord(ev[0], s);
   dim3 grid((g.out_cap + ST_WARPS - 1) / ST_WARPS, batch);
   stereo_match_kernel<<<grid, ST_WARPS * 32, 0, s>>>(g, l.pyr, r.pyr, l.out_kp, l.out_desc, l.out_count, r.out_kp,
                                                      r.out_desc, r.out_count, mbf, mb, l.st_uright, l.st_depth,
                                                      l.st_sad);
+  if (ev) cudaEventRecord(ev[1], s);
   stereo_median_kernel<<<batch, 1024, (size_t)g.out_cap * sizeof(int), s>>>(g, l.out_count, l.st_uright, l.st_depth,
                                                                             l.st_sad, l.st_count);
+  if (ev) cudaEventRecord(ev[2], s);
 }
 
 }  // namespace orbfe

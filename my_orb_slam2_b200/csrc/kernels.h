@@ -41,7 +41,7 @@ size_t quadtree_smem_bytes(int node_cap);
 void launch_describe(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
 // Frame::ComputeStereoMatches (src/Frame.cc:496-686)
 void launch_stereo(const PyrGeom& g, const ExtractorArena& left, const ExtractorArena& right, int batch, float mbf,
-                   float mb, cudaStream_t s);
+                   float mb, cudaStream_t s, cudaEvent_t* stage_events /* 3 or nullptr */);
 
 constexpr int kLaunchesPerExtract(int nlevels) { return (nlevels - 1) + 3; }
 constexpr int kLaunchesPerStereo = 2;

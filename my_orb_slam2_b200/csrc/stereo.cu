@@ -27,7 +27,10 @@ int orbfe_stereo_match_run(orbfe_extractor* hl, orbfe_extractor* hr, int batch, 
     ORBFE_CUDA(cudaEventRecord(r->done, r->stream));
     ORBFE_CUDA(cudaStreamWaitEvent(l->stream, r->done, 0));
   }
-  launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream);
+  cudaEvent_t* ev = nullptr;
+  if (l->profiling && l->prof_ev && l->prof_stereo_runs < Extractor::kProfRuns)
+    ev = l->prof_ev + 5 * Extractor::kProfRuns + 3 * l->prof_stereo_runs++;
+  launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream, ev);
   l->launches += kLaunchesPerStereo;
   ORBFE_CUDA(cudaGetLastError());
   return ORBFE_OK;
