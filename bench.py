@@ -1,0 +1,392 @@
+#!/usr/bin/env python3
+"""bench.py — the headline metric of BASELINE.json on its configuration:
+
+    frames/sec of ORB extract + match on KITTI-shaped 1241x376 stereo pairs, 2000 features per image
+    (configs[1]: ORB extraction of both images + Frame::ComputeStereoMatches), plus p50 frame latency.
+
+A "step" is one pass of the hot path over one batch of `--batch` synthetic stereo pairs per GPU.
+  value : whole-job stereo frames/s with the inputs already resident in HBM (device images -> pyramid level 0 ->
+          all kernels -> results left on the device), timed with CUDA events on the handles' streams.
+  e2e   : the same through the C ABI with HOST buffers: pinned host images -> H2D -> kernels -> keypoints,
+          descriptors, uRight, depth back in host memory, every step, inside the timed region.
+  roofline / stages : per-stage CUDA-event times recorded inside the timed region by the library itself.
+  cpu_baseline      : the CPU oracle (a port of the reference's code path; the reference itself cannot be built here)
+                      timed single-threaded on a bounded sample of the same workload.
+`--impl reference` times that CPU path on all host cores instead of the GPU path.
+Multi-GPU (`torchrun ... bench.py --gpus N`): frames are sharded by rank, no data-path collective ("weak").
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from my_orb_slam2_b200 import synth  # noqa: E402
+
+SHAPE = "kitti"
+W, H = synth.SHAPES[SHAPE]
+S = synth.SETTINGS[SHAPE]
+PARAMS = (S["nfeatures"], S["scale_factor"], S["nlevels"], S["ini_th"], S["min_th"])
+MBF = np.float32(S["bf"])
+MB = np.float32(S["bf"]) / np.float32(S["fx"])
+N_UNIQUE = 8  # distinct synthetic pairs; the batch cycles through them (each copy has its own buffers)
+
+
+def make_pairs(n_unique, seed0):
+    pairs = [synth.synth_pair(W, H, seed0 + i) for i in range(n_unique)]
+    return np.stack([p[0] for p in pairs]), np.stack([p[1] for p in pairs])
+
+
+def level_pixels():
+    """Sum over the 8 pyramid levels of w*h (1,444,097 for KITTI)."""
+    sf, tot = np.float32(1.0), 0
+    for lv in range(S["nlevels"]):
+        inv = np.float32(1.0) / sf
+        tot += int(np.rint(np.float32(W) * inv)) * int(np.rint(np.float32(H) * inv))
+        sf = np.float32(float(sf) * float(np.float32(S["scale_factor"])))
+    return tot
+
+
+class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons during the timed region (NVML)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                 "hw_power_brake": 0x80}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def result(self):
+        self.stop_flag = True
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+def cpu_pair_seconds(pyoracle, left, right):
+    """One stereo frame through the CPU oracle (extract L, extract R, ComputeStereoMatches); returns seconds."""
+    t0 = time.perf_counter()
+    oL, oR = pyoracle.Extractor(*PARAMS), pyoracle.Extractor(*PARAMS)
+    kl, dl = oL.extract(left)
+    kr, dr = oR.extract(right)
+    pyoracle.stereo_matches(oL, oR, kl, dl, kr, dr, MBF, MB)
+    return time.perf_counter() - t0
+
+
+_CPU_STATE = {}
+
+
+def _cpu_init(per_core):
+    """Pool initializer: each worker process generates its own frames and extractors once, outside any timing."""
+    from oracle import pyoracle
+    lefts, rights = make_pairs(per_core, 1000 + (os.getpid() % 9973))
+    _CPU_STATE.update(lefts=lefts, rights=rights, oL=pyoracle.Extractor(*PARAMS), oR=pyoracle.Extractor(*PARAMS),
+                      po=pyoracle)
+
+
+def _cpu_worker(reps):
+    st = _CPU_STATE
+    po, oL, oR = st["po"], st["oL"], st["oR"]
+    t0 = time.perf_counter()
+    for r in range(reps):
+        for i in range(len(st["lefts"])):
+            kl, dl = oL.extract(st["lefts"][i])
+            kr, dr = oR.extract(st["rights"][i])
+            po.stereo_matches(oL, oR, kl, dl, kr, dr, MBF, MB)
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port; /root/reference needs OpenCV C++ and cannot be built)
+    on all host cores, one instance per core, each looping over its own frames."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    from oracle import pyoracle
+    pyoracle.build()
+    cores = os.cpu_count() or 1
+    per_core = 2
+    reps = 4
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores, initializer=_cpu_init, initargs=(per_core,)) as pool:
+        for _ in range(args.warmup):
+            pool.map(_cpu_worker, [1] * cores, chunksize=1)
+        times = []
+        for _ in range(args.steps):
+            t0 = time.perf_counter()
+            pool.map(_cpu_worker, [reps] * cores, chunksize=1)
+            times.append(time.perf_counter() - t0)
+    frames = cores * per_core * reps
+    total = sum(times)
+    value = frames * args.steps / total
+    line = {
+        "impl": "reference", "metric": "stereo frames/sec, ORB extract (L+R) + ComputeStereoMatches, KITTI 1241x376 2k feat",
+        "value": value, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "configs[1]: KITTI00-shaped stereo pair 1241x376, 2000 features, extract + ComputeStereoMatches",
+                   "frames_per_step": frames},
+        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port",
+                         "sample": "%d stereo frames per step, one oracle instance per core" % frames},
+        "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from my_orb_slam2_b200 import orbfe
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if orbfe.device_count() < 1:
+        raise RuntimeError("bench.py: no CUDA device; the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    B = args.batch
+    dev = torch.device("cuda", local)
+
+    # ---- synthetic inputs: frames sharded by rank (rank r owns seeds 100*r ...) ----
+    lefts_u, rights_u = make_pairs(N_UNIQUE, 100 * rank)
+    idx = np.arange(B) % N_UNIQUE
+    h_left = torch.empty((B, H, W), dtype=torch.uint8).pin_memory()
+    h_right = torch.empty((B, H, W), dtype=torch.uint8).pin_memory()
+    h_left.numpy()[:] = lefts_u[idx]
+    h_right.numpy()[:] = rights_u[idx]
+    d_left = h_left.to(dev)
+    d_right = h_right.to(dev)
+
+    L = orbfe.Extractor(*PARAMS, W, H, max_batch=B, device=local)
+    R = orbfe.Extractor(*PARAMS, W, H, max_batch=B, device=local)
+    cap = L.capacity
+    sL = torch.cuda.ExternalStream(L.stream, device=dev)
+    sR = torch.cuda.ExternalStream(R.stream, device=dev)
+    lib = orbfe.lib()
+
+    def step_device():
+        L.upload(d_left.data_ptr(), B, on_device=True)
+        R.upload(d_right.data_ptr(), B, on_device=True)
+        L.run(B)
+        R.run(B)
+        orbfe.check(lib.orbfe_stereo_match_run(L._h, R._h, B, MBF, MB))
+
+    # host result buffers (pinned) for the e2e leg
+    kpL = torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory()
+    kpR = torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory()
+    dsL = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    dsR = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    cntL = torch.zeros(B, dtype=torch.int32).pin_memory()
+    cntR = torch.zeros(B, dtype=torch.int32).pin_memory()
+    ur = torch.empty((B, cap), dtype=torch.float32).pin_memory()
+    dp = torch.empty((B, cap), dtype=torch.float32).pin_memory()
+    nm = torch.zeros(B, dtype=torch.int32).pin_memory()
+
+    def step_e2e():
+        L.upload(h_left.data_ptr(), B)
+        R.upload(h_right.data_ptr(), B)
+        L.run(B)
+        R.run(B)
+        orbfe.check(lib.orbfe_stereo_match_run(L._h, R._h, B, MBF, MB))
+        # right results first (its stream is independent), then left + stereo
+        orbfe.check(lib.orbfe_extract_download(R._h, B, kpR.data_ptr(), dsR.data_ptr(), cap, cntR.data_ptr()))
+        orbfe.check(lib.orbfe_extract_download(L._h, B, kpL.data_ptr(), dsL.data_ptr(), cap, cntL.data_ptr()))
+        orbfe.check(lib.orbfe_stereo_match_download(L._h, B, ur.data_ptr(), dp.data_ptr(), cap, nm.data_ptr()))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident leg (value) ----
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    L.set_profiling(True)
+    R.set_profiling(True)
+    launches0 = L.launch_count + R.launch_count
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(sL)
+    sR.wait_event(e0)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(sL)  # left's stream is last: the stereo kernels wait for the right handle's stream
+    barrier()
+    ms_dev = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.result()
+    launches = L.launch_count + R.launch_count - launches0
+    stL, runsL, srunsL = L.stage_times()
+    stR, runsR, _ = R.stage_times()
+    L.set_profiling(False)
+    R.set_profiling(False)
+    # a few copies per step (cudaMemcpy2DAsync D2D of level 0) are not kernels of ours and are not counted
+
+    # ---- end-to-end leg (host buffers through the C ABI) ----
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    t_e2e = max_over_ranks(time.perf_counter() - t0)
+    n_left = int(cntL.numpy().sum())
+    n_match = int(nm.numpy().sum())
+
+    # ---- latency leg: one pair in flight, host pointer in -> results on host ----
+    lat = []
+    if rank == 0:
+        L1 = orbfe.Extractor(*PARAMS, W, H, max_batch=1, device=local)
+        R1 = orbfe.Extractor(*PARAMS, W, H, max_batch=1, device=local)
+        for i in range(args.latency_frames + 10):
+            j = i % B
+            t1 = time.perf_counter()
+            L1.upload(h_left[j].data_ptr(), 1)
+            R1.upload(h_right[j].data_ptr(), 1)
+            L1.run(1)
+            R1.run(1)
+            orbfe.check(lib.orbfe_stereo_match_run(L1._h, R1._h, 1, MBF, MB))
+            orbfe.check(lib.orbfe_extract_download(R1._h, 1, kpR.data_ptr(), dsR.data_ptr(), cap, cntR.data_ptr()))
+            orbfe.check(lib.orbfe_extract_download(L1._h, 1, kpL.data_ptr(), dsL.data_ptr(), cap, cntL.data_ptr()))
+            orbfe.check(lib.orbfe_stereo_match_download(L1._h, 1, ur.data_ptr(), dp.data_ptr(), cap, nm.data_ptr()))
+            if i >= 10:
+                lat.append(1e3 * (time.perf_counter() - t1))
+        L1.close()
+        R1.close()
+
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- CPU baseline on a bounded sample (rank 0, N=1 only) ----
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import pyoracle
+        pyoracle.build()
+        t_cpu, n_cpu = 0.0, 0
+        while t_cpu < args.cpu_seconds:
+            t_cpu += cpu_pair_seconds(pyoracle, lefts_u[n_cpu % N_UNIQUE], rights_u[n_cpu % N_UNIQUE])
+            n_cpu += 1
+        cpu = {"value": n_cpu / t_cpu, "unit": "frames/s", "cores": 1, "kind": "port",
+               "sample": "%d stereo frames (extract L+R sequentially + ComputeStereoMatches), single thread; "
+                         "the reference uses 2 threads for L/R (src/Frame.cc:89-92)" % n_cpu}
+
+    # ---- roofline of the dominant kernel ----
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    lp = level_pixels()
+    kp_per_img = n_left / max(B, 1)
+    # algorithmic bytes per IMAGE of each stage ("Kernels"): compulsory reads + writes, no re-reads
+    alg = {
+        "pyramid": (lp - W * H) + (lp - int(W / 1.2 ** 7) * int(H / 1.2 ** 7)),  # read levels 0..6, write levels 1..7
+        "fast": lp + 4 * 13000,                  # read every level once, write ~13 k candidates x 4 B
+        "quadtree": 13000 * (4 + 2) + 2000 * 4,  # candidates + node ids in, kept out
+        "blur": 2 * lp,                          # read every level once, write its blurred copy
+        "describe": kp_per_img * (749 + 512 + 28 + 32 + 4),  # disc + pattern gathers in, keypoint + descriptor out
+    }
+    stage_ms = {k: (stL[k] + stR.get(k, 0.0)) for k in stL}
+    runs = max(runsL + runsR, 1)
+    per_launch = {k: stage_ms[k] / runs for k in ("pyramid", "fast", "quadtree", "blur", "describe")}
+    per_launch["stereo_match"] = stL["stereo_match"] / max(srunsL, 1)
+    per_launch["stereo_median"] = stL["stereo_median"] / max(srunsL, 1)
+    dom = max(("pyramid", "fast", "quadtree", "blur", "describe"), key=lambda k: per_launch[k])
+    achieved = alg[dom] * B / (per_launch[dom] * 1e-3) / 1e9 if per_launch[dom] > 0 else 0.0
+    b_extract = W * H + lp + kp_per_img * 60  # compulsory bytes of the whole extraction per image
+    frames = B * args.steps * world
+    value = frames / (ms_dev * 1e-3)
+    line = {
+        "metric": "stereo frames/sec, ORB extract (L+R) + ComputeStereoMatches, KITTI 1241x376 2k feat",
+        "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "configs[1]: KITTI00-shaped stereo pair 1241x376, 2000 features, extract + ComputeStereoMatches",
+                   "pairs_per_step_per_gpu": B, "unique_pairs": N_UNIQUE,
+                   "l2": "inputs + pyramids of one step = %.0f MB > 126 MB L2" % (2 * B * (W * H + lp * 1.03) / 1e6),
+                   "keypoints_per_image": kp_per_img, "stereo_matches_per_frame": n_match / max(B, 1)},
+        "e2e": {"value": B * args.steps * world / t_e2e, "unit": "frames/s", "h2d_bytes_per_step": 2 * B * W * H,
+                "d2h_bytes_per_step": int(2 * B * cap * 60 + 2 * B * cap * 4 + 3 * B * 4)},
+        "latency_ms_p50": float(np.percentile(lat, 50)) if lat else None,
+        "latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
+                     "frac": achieved / peak_gbs, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg[dom] * B,
+                     "extract_frac": (b_extract * 2 * B * args.steps / (ms_dev * 1e-3) / 1e9) / peak_gbs},
+        "stages_ms_per_launch": per_launch,
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="stereo pairs per step per GPU")
+    ap.add_argument("--latency-frames", type=int, default=200)
+    ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

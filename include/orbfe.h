@@ -85,6 +85,13 @@ void* orbfe_extractor_stream(orbfe_extractor* e);
 /* Kernels launched by this handle since creation. */
 int64_t orbfe_extractor_launch_count(const orbfe_extractor* e);
 
+/* Per-stage device timing with CUDA events on the handle's stream (off by default).  After enabling, every
+ * orbfe_extract_run / orbfe_stereo_match_run records events around its stages (up to 256 runs); stage_times
+ * waits for the stream and returns the summed milliseconds of ms[0..6] = pyramid, FAST, quadtree,
+ * blur, orient+describe, stereo match, stereo median cut, and how many runs they cover. */
+int orbfe_extractor_set_profiling(orbfe_extractor* e, int enable);
+int orbfe_extractor_stage_times(orbfe_extractor* e, float* ms, int32_t* runs, int32_t* stereo_runs);
+
 /* ORBextractor::mvImagePyramid (include/ORBextractor.h:85), device resident:
  * level `level` of image `image_index` of the last run. */
 int orbfe_extractor_level(const orbfe_extractor* e, int image_index, int level, const uint8_t** device_ptr,

@@ -104,7 +104,7 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
   g.ini_th = e->params.ini_th_fast < 0 ? 0 : (e->params.ini_th_fast > 255 ? 255 : e->params.ini_th_fast);
   g.min_th = e->params.min_th_fast < 0 ? 0 : (e->params.min_th_fast > 255 ? 255 : e->params.min_th_fast);
   unsigned long long pyr_off = 0;
-  int cells = 0, cand = 0, kept = 0, node_cap_max = 8;
+  int cells = 0, cand = 0, kept = 0, node_cap_max = 8, blur_tiles = 0;
   for (int l = 0; l < g.nlevels; ++l) {
     LevelGeom& L = g.lv[l];
     L.scale = info.scale_factors[l];
@@ -113,7 +113,7 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
     L.w = cv_round((float)e->width * L.inv_scale);  // :1133-1134
     L.h = cv_round((float)e->height * L.inv_scale);
     if (L.w < 1 || L.h < 1) { set_error("level %d of a %dx%d image is empty", l, e->width, e->height); return ORBFE_ERR_ARG; }
-    if (L.w > 4096 + 2 * kMinBorder || L.h > 4096 + 2 * kMinBorder) { set_error("image too large"); return ORBFE_ERR_ARG; }
+    if (L.w > 4096 + 2 * kMinBorder || L.h > 4096 + 2 * kMinBorder || L.h > 8000) { set_error("image too large"); return ORBFE_ERR_ARG; }
     L.pitch = (int)align_up((size_t)L.w, 128);
     L.lvl_bytes = (unsigned)L.pitch * (unsigned)L.h;
     L.lvl_base = pyr_off;
@@ -131,6 +131,8 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
     if (L.n_rows > 255 || L.n_cols > 255) { set_error("image too large"); return ORBFE_ERR_ARG; }
     L.cell_base = cells;
     cells += L.n_cols * L.n_rows;
+    L.blur_tile_base = blur_tiles;
+    blur_tiles += ((L.w + 127) / 128) * ((L.h + 127) / 128);
     L.quota = info.features_per_level[l];
     L.n_ini = 1;
     L.h_x = 1.f;
@@ -164,6 +166,7 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
     }
   }
   g.total_cells = cells;
+  g.blur_tiles = blur_tiles;
   g.cand_total = std::max(cand, 4);
   g.kept_total = std::max(kept, 4);
   g.out_cap = (int)align_up((size_t)kept + 8, 8);
@@ -184,6 +187,7 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
   ExtractorArena& a = e->arena;
   const size_t B = (size_t)e->max_batch;
   ORBFE_CUDA(dalloc(&a.pyr, e->pyr_bytes + 256));
+  ORBFE_CUDA(dalloc(&a.blur, e->pyr_bytes + 256));
   ORBFE_CUDA(dalloc(&a.xtab, xt.size()));
   ORBFE_CUDA(dalloc(&a.ytab, yt.size()));
   ORBFE_CUDA(dalloc(&a.cand, B * g.cand_total));
@@ -199,9 +203,14 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
   ORBFE_CUDA(dalloc(&a.st_depth, B * g.out_cap));
   ORBFE_CUDA(dalloc(&a.st_sad, B * g.out_cap));
   ORBFE_CUDA(dalloc(&a.st_count, B));
+  a.st_items_per_kp = stereo_items_per_kp(g);
+  ORBFE_CUDA(dalloc(&a.st_band, B * g.out_cap));
+  ORBFE_CUDA(dalloc(&a.st_bucket_start, B * ((size_t)(g.lv[0].h + 7) / 8 + 2)));
+  ORBFE_CUDA(dalloc(&a.st_bucket_items, B * g.out_cap * a.st_items_per_kp));
   if (!xt.empty()) ORBFE_CUDA(cudaMemcpy(a.xtab, xt.data(), xt.size() * sizeof(XTab), cudaMemcpyHostToDevice));
   if (!yt.empty()) ORBFE_CUDA(cudaMemcpy(a.ytab, yt.data(), yt.size() * sizeof(YTab), cudaMemcpyHostToDevice));
   ORBFE_CUDA(cudaMemset(a.pyr, 0, e->pyr_bytes + 256));
+  ORBFE_CUDA(cudaMemset(a.blur, 0, e->pyr_bytes + 256));
   ORBFE_CUDA(cudaMemset(a.out_count, 0, B * sizeof(int32_t)));
   ORBFE_CUDA(cudaMemset(a.kept_count, 0, B * kMaxLevels * sizeof(int32_t)));
   ORBFE_CUDA(cudaMemset(a.flags, 0, B * sizeof(int32_t)));
@@ -211,13 +220,13 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
 
 static void free_arenas(Extractor* e) {
   ExtractorArena& a = e->arena;
-  cudaFree(a.pyr); cudaFree(a.xtab); cudaFree(a.ytab); cudaFree(a.cand); cudaFree(a.node_of);
+  cudaFree(a.pyr); cudaFree(a.blur); cudaFree(a.xtab); cudaFree(a.ytab); cudaFree(a.cand); cudaFree(a.node_of);
   cudaFree(a.cand_count); cudaFree(a.kept); cudaFree(a.kept_count); cudaFree(a.out_kp); cudaFree(a.out_desc);
   cudaFree(a.out_count); cudaFree(a.flags); cudaFree(a.st_uright); cudaFree(a.st_depth); cudaFree(a.st_sad);
-  cudaFree(a.st_count);
+  cudaFree(a.st_count); cudaFree(a.st_band); cudaFree(a.st_bucket_start); cudaFree(a.st_bucket_items);
   if (e->h_flags) cudaFreeHost(e->h_flags);
   if (e->prof_ev) {
-    for (int i = 0; i < Extractor::kProfRuns * 8; ++i) cudaEventDestroy(e->prof_ev[i]);
+    for (int i = 0; i < Extractor::kProfRuns * 9; ++i) cudaEventDestroy(e->prof_ev[i]);
     delete[] e->prof_ev;
     e->prof_ev = nullptr;
   }
@@ -336,7 +345,7 @@ int orbfe_extract_run(orbfe_extractor* h, int batch) {
   const ExtractorArena& a = e->arena;
   ORBFE_CUDA(cudaMemsetAsync(a.cand_count, 0, (size_t)batch * kMaxLevels * sizeof(int32_t), e->stream));
   ORBFE_CUDA(cudaMemsetAsync(a.flags, 0, (size_t)batch * sizeof(int32_t), e->stream));
-  cudaEvent_t* ev = (e->profiling && e->prof_runs < Extractor::kProfRuns) ? e->prof_ev + 5 * e->prof_runs : nullptr;
+  cudaEvent_t* ev = (e->profiling && e->prof_runs < Extractor::kProfRuns) ? e->prof_ev + 6 * e->prof_runs : nullptr;
   if (ev) cudaEventRecord(ev[0], e->stream);
   for (int l = 1; l < g.nlevels; ++l) launch_pyramid_level(g, a, l, batch, e->stream);  // ComputePyramid (:1075)
   if (ev) cudaEventRecord(ev[1], e->stream);
@@ -344,9 +353,11 @@ int orbfe_extract_run(orbfe_extractor* h, int batch) {
   if (ev) cudaEventRecord(ev[2], e->stream);
   launch_quadtree(g, a, batch, e->stream);                                               // :853
   if (ev) cudaEventRecord(ev[3], e->stream);
+  launch_blur_levels(g, a, batch, e->stream);                                            // :1107-1108
+  if (ev) cudaEventRecord(ev[4], e->stream);
   launch_describe(g, a, batch, e->stream);                                               // :873-874, :1096-1126
-  if (ev) { cudaEventRecord(ev[4], e->stream); ++e->prof_runs; }
-  e->launches += (g.nlevels - 1) + (g.total_cells > 0 ? 1 : 0) + 2;
+  if (ev) { cudaEventRecord(ev[5], e->stream); ++e->prof_runs; }
+  e->launches += (g.nlevels - 1) + (g.total_cells > 0 ? 1 : 0) + 3;
   e->last_batch = batch;
   ORBFE_CUDA(cudaGetLastError());
   return ORBFE_OK;
@@ -357,7 +368,7 @@ int orbfe_extractor_set_profiling(orbfe_extractor* h, int enable) {
   Extractor* e = reinterpret_cast<Extractor*>(h);
   DeviceGuard guard(e->device);
   if (enable && !e->prof_ev) {
-    const int n = Extractor::kProfRuns * 8;
+    const int n = Extractor::kProfRuns * 9;
     e->prof_ev = new cudaEvent_t[n];
     for (int i = 0; i < n; ++i) ORBFE_CUDA(cudaEventCreate(&e->prof_ev[i]));
   }
@@ -374,17 +385,17 @@ int orbfe_extractor_stage_times(orbfe_extractor* h, float* ms, int32_t* runs, in
   ORBFE_CUDA(cudaStreamSynchronize(e->stream));
   for (int s = 0; s < Extractor::kStages; ++s) ms[s] = 0.f;
   for (int r = 0; r < e->prof_runs; ++r)
-    for (int s = 0; s < 4; ++s) {
+    for (int s = 0; s < 5; ++s) {
       float t = 0.f;
-      ORBFE_CUDA(cudaEventElapsedTime(&t, e->prof_ev[5 * r + s], e->prof_ev[5 * r + s + 1]));
+      ORBFE_CUDA(cudaEventElapsedTime(&t, e->prof_ev[6 * r + s], e->prof_ev[6 * r + s + 1]));
       ms[s] += t;
     }
-  cudaEvent_t* sev = e->prof_ev ? e->prof_ev + 5 * Extractor::kProfRuns : nullptr;
+  cudaEvent_t* sev = e->prof_ev ? e->prof_ev + 6 * Extractor::kProfRuns : nullptr;
   for (int r = 0; r < e->prof_stereo_runs; ++r)
     for (int s = 0; s < 2; ++s) {
       float t = 0.f;
       ORBFE_CUDA(cudaEventElapsedTime(&t, sev[3 * r + s], sev[3 * r + s + 1]));
-      ms[4 + s] += t;
+      ms[5 + s] += t;
     }
   if (runs) *runs = e->prof_runs;
   if (stereo_runs) *stereo_runs = e->prof_stereo_runs;

@@ -23,10 +23,10 @@ struct Extractor {
   int64_t launches = 0;
   int last_batch = 0;
   // optional per-stage CUDA-event timing (bench.py roofline): ring of runs x (kStages+1) events
-  static constexpr int kStages = 6;   // pyramid, fast, quadtree, describe, stereo match, stereo median
+  static constexpr int kStages = 7;   // pyramid, fast, quadtree, blur, describe, stereo match, stereo median
   static constexpr int kProfRuns = 256;
   bool profiling = false;
-  cudaEvent_t* prof_ev = nullptr;     // [kProfRuns][5] extractor stages; [kProfRuns][3] stereo stages after them
+  cudaEvent_t* prof_ev = nullptr;     // [kProfRuns][6] extractor stage events; [kProfRuns][3] stereo events after them
   int prof_runs = 0, prof_stereo_runs = 0;
 };
 

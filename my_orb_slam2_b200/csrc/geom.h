@@ -16,6 +16,7 @@ struct LevelGeom {
   int n_cols, n_rows;       // cell grid (:796-797); 0 => level has no cells
   int w_cell, h_cell;       // (:798-799)
   int cell_base;            // id of this level's first cell within one image
+  int blur_tile_base;       // id of this level's first 128x128 blur tile within one image
   int quota;                // mnFeaturesPerLevel[level] (:435-446)
   int n_ini;                // quadtree roots (:543)
   float h_x;                // root width (:545)
@@ -33,6 +34,7 @@ struct LevelGeom {
 struct PyrGeom {
   int nlevels;
   int total_cells;  // per image
+  int blur_tiles;   // per image
   int cand_total;   // per image candidate capacity (sum over levels)
   int kept_total;   // per image kept capacity (sum over levels)
   int out_cap;      // per image output capacity (info.capacity)

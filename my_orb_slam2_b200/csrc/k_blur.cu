@@ -1,0 +1,105 @@
+// k_blur.cu — GaussianBlur(level, 7x7, sigma 2, BORDER_REFLECT_101) of every pyramid level (reference:
+// src/ORBextractor.cc:1107-1108; OpenCV 4.13 fixed-point semantics):
+//   kernel (8.8 fixed point) [18 34 48 56 48 34 18], h = sum k*p (exact, <= 65280), v = sum k*h,
+//   dst = (v + 32768) >> 16.
+// The reference blurs whole levels; so does this kernel (2000 keypoints x 37x37 windows would blur MORE pixels than
+// the whole pyramid has), but in one launch over all levels and images and without any intermediate buffer:
+//   * a thread owns a 4-pixel-wide, 32-row-tall strip; per source row it loads the three aligned words that cover
+//     columns x-4..x+7, forms the four 7-tap horizontal sums with funnel shifts + two DP4A each, and keeps the last
+//     seven rows of sums in registers (sliding window) for the vertical pass;
+//   * one 32-bit store per 4 output pixels; reads are served by L1/L2 (each source word is read by 3 lanes and each
+//     source row by the strips above/below only at the 6 halo rows);
+//   * reflect-101 at the level edges: rows by index reflection, columns by byte shuffles (left edge) or a byte-wise
+//     slow path (last words of a row).
+// HBM-bound by design: reads each level once, writes it once.
+#include "kernels.h"
+
+namespace orbfe {
+
+constexpr int BL_TX = 32, BL_TY = 4, BL_ROWS = 32;  // CTA covers 128 x 128 pixels
+
+__device__ __forceinline__ int reflect101i(int p, int len) {
+  if (p < 0) p = -p;
+  if (p >= len) p = 2 * (len - 1) - p;
+  return p;
+}
+
+__global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid_constant__ PyrGeom g,
+                                                                    const uint8_t* __restrict__ pyr,
+                                                                    uint8_t* __restrict__ blur) {
+  int tile = blockIdx.x;
+  int lvl = 0;
+  while (lvl + 1 < g.nlevels && tile >= g.lv[lvl + 1].blur_tile_base) ++lvl;
+  const LevelGeom& L = g.lv[lvl];
+  tile -= L.blur_tile_base;
+  const int tiles_x = (L.w + 127) / 128;
+  const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
+  const int b = blockIdx.y;
+  const int x4 = (tx * BL_TX + threadIdx.x) * 4;
+  const int y0 = (ty * BL_TY + threadIdx.y) * BL_ROWS;
+  if (x4 >= L.w || y0 >= L.h) return;
+  const uint8_t* src = pyr + L.lvl_base + (size_t)b * L.lvl_bytes;
+  uint8_t* dst = blur + L.lvl_base + (size_t)b * L.lvl_bytes;
+  const int w = L.w, h = L.h, pitch = L.pitch;
+  const bool slow = (x4 + 7 >= w);  // the words of this strip reach past the last column
+  const bool left = (x4 == 0);
+  const unsigned K_LO = 0x38302212u;  // 18,34,48,56 (byte 0 first)
+  const unsigned K_HI = 0x00122230u;  // 48,34,18,0
+
+  unsigned win[7][4];
+#pragma unroll
+  for (int i = 0; i < 7; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) win[i][j] = 0;
+
+  const int rows = min(BL_ROWS, h - y0);
+#pragma unroll 1
+  for (int r = 0; r < rows + 6; ++r) {
+    const int y = reflect101i(y0 + r - 3, h);
+    const uint8_t* row = src + (size_t)y * pitch;
+    unsigned w0, w1, w2;
+    if (!slow) {
+      w1 = __ldg(reinterpret_cast<const unsigned*>(row + x4));
+      w2 = __ldg(reinterpret_cast<const unsigned*>(row + x4 + 4));
+      w0 = left ? __byte_perm(w1, 0, 0x1230) : __ldg(reinterpret_cast<const unsigned*>(row + x4 - 4));
+    } else {
+      unsigned t[3] = {0, 0, 0};
+#pragma unroll
+      for (int i = 0; i < 12; ++i) {
+        const int c = reflect101i(x4 - 4 + i, w);
+        t[i >> 2] |= (unsigned)__ldg(row + c) << (8 * (i & 3));
+      }
+      w0 = t[0]; w1 = t[1]; w2 = t[2];
+    }
+    // horizontal sums of the 4 pixels: taps are bytes j+1 .. j+7 of (w0,w1,w2)
+    unsigned hs[4];
+    hs[0] = __dp4a(__funnelshift_r(w0, w1, 8), K_LO, __dp4a(__funnelshift_r(w1, w2, 8), K_HI, 0u));
+    hs[1] = __dp4a(__funnelshift_r(w0, w1, 16), K_LO, __dp4a(__funnelshift_r(w1, w2, 16), K_HI, 0u));
+    hs[2] = __dp4a(__funnelshift_r(w0, w1, 24), K_LO, __dp4a(__funnelshift_r(w1, w2, 24), K_HI, 0u));
+    hs[3] = __dp4a(w1, K_LO, __dp4a(w2, K_HI, 0u));
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) win[i][j] = win[i + 1][j];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) win[6][j] = hs[j];
+    if (r >= 6) {
+      unsigned out = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const unsigned v = 18u * (win[0][j] + win[6][j]) + 34u * (win[1][j] + win[5][j]) +
+                           48u * (win[2][j] + win[4][j]) + 56u * win[3][j];
+        out |= ((v + 32768u) >> 16) << (8 * j);
+      }
+      *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * pitch + x4) = out;
+    }
+  }
+}
+
+void launch_blur_levels(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
+  dim3 grid(g.blur_tiles, batch);
+  dim3 block(BL_TX, BL_TY);
+  blur_levels_kernel<<<grid, block, 0, s>>>(g, a.pyr, a.blur);
+}
+
+}  // namespace orbfe

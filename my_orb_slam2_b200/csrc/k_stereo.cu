@@ -1,8 +1,9 @@
 // k_stereo.cu — Frame::ComputeStereoMatches (reference: src/Frame.cc:496-686) on the
 // device-resident outputs of the left and right extractor handles.
 //
-// Kernel 1, one warp per left keypoint (8 per CTA; the right keypoints' row bands,
-// x and octave are staged once per CTA in shared memory):
+// Kernel 0, one CTA per image: the row table of :511-531 as buckets of 8 image rows (CSR in global memory): right
+// keypoint iR goes into every bucket its band [floor(yR-r), ceil(yR+r)] touches; its exact band, x and octave are
+// stored next to it.  Kernel 1, one warp per left keypoint, scans only the bucket of row int(vL):
 //   * row-band candidates (:511-531,:549): right keypoint iR is a candidate of row
 //     int(vL) iff floor(yR - r) <= int(vL) <= ceil(yR + r), r = 2*scale[octave(iR)];
 //     the per-row index vectors of the reference are in ascending iR, and the best
@@ -22,7 +23,8 @@
 namespace orbfe {
 
 constexpr int ST_WARPS = 8;
-constexpr int ST_CHUNK = 2048;
+constexpr int ST_BROWS = 8;       // image rows per bucket of the row table
+constexpr int ST_MAXB = 1024;     // buckets per image (rows <= 8192)
 constexpr int TH_HIGH = ORBFE_TH_HIGH, TH_LOW = ORBFE_TH_LOW;
 
 __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
@@ -30,60 +32,103 @@ __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const 
          __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+// row table (:511-531) as 8-row buckets; one CTA per image
+__global__ void __launch_bounds__(512) stereo_bucket_kernel(const __grid_constant__ PyrGeom g,
+                                                            const orbfe_keypoint* __restrict__ kpR,
+                                                            const int32_t* __restrict__ cntR, int4* __restrict__ band,
+                                                            int32_t* __restrict__ bucket_start,
+                                                            int32_t* __restrict__ bucket_items, int items_per_kp) {
+  __shared__ int s_cnt[ST_MAXB + 1];
+  __shared__ int s_wtmp[32];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int nR = cntR[b];
+  const int n_rows = g.lv[0].h;
+  const int nb = (n_rows + ST_BROWS - 1) / ST_BROWS;
+  const orbfe_keypoint* kr = kpR + (size_t)b * g.out_cap;
+  int4* bands = band + (size_t)b * g.out_cap;
+  int32_t* bstart = bucket_start + (size_t)b * (nb + 1);
+  int32_t* bitems = bucket_items + (size_t)b * g.out_cap * items_per_kp;
+  for (int i = tid; i <= nb; i += 512) s_cnt[i] = 0;
+  __syncthreads();
+  for (int i = tid; i < nR; i += 512) {
+    const orbfe_keypoint k = kr[i];
+    const float r = __fmul_rn(2.0f, g.lv[k.octave].scale);  // :525
+    const int maxr = (int)ceilf(__fadd_rn(k.y, r)), minr = (int)floorf(__fsub_rn(k.y, r));
+    bands[i] = make_int4(minr, maxr, __float_as_int(k.x), k.octave);
+    const int lo = max(minr, 0) / ST_BROWS, hi = min(maxr, n_rows - 1) / ST_BROWS;
+    for (int q = lo; q <= hi; ++q) atomicAdd(&s_cnt[q], 1);
+  }
+  __syncthreads();
+  // exclusive scan of s_cnt[0..nb) by warp 0 (nb <= 1024)
+  if (tid < 32) {
+    const int per = (nb + 31) / 32;
+    const int beg = min(tid * per, nb), end = min(beg + per, nb);
+    int s = 0;
+    for (int i = beg; i < end; ++i) s += s_cnt[i];
+    int v = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, v, o);
+      if (tid >= o) v += t;
+    }
+    int run = v - s;
+    for (int i = beg; i < end; ++i) { const int t = s_cnt[i]; s_cnt[i] = run; run += t; }
+    if (tid == 31) s_cnt[nb] = v;
+  }
+  (void)s_wtmp;
+  __syncthreads();
+  for (int i = tid; i <= nb; i += 512) bstart[i] = s_cnt[i];
+  __syncthreads();
+  const int cap_items = g.out_cap * items_per_kp;
+  for (int i = tid; i < nR; i += 512) {
+    const int4 bd = bands[i];
+    const int lo = max(bd.x, 0) / ST_BROWS, hi = min(bd.y, n_rows - 1) / ST_BROWS;
+    for (int q = lo; q <= hi; ++q) {
+      const int slot = atomicAdd(&s_cnt[q], 1);
+      if (slot < cap_items) bitems[slot] = i;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(ST_WARPS * 32) stereo_match_kernel(
     const __grid_constant__ PyrGeom g, const uint8_t* __restrict__ pyrL, const uint8_t* __restrict__ pyrR,
     const orbfe_keypoint* __restrict__ kpL, const uint8_t* __restrict__ descL, const int32_t* __restrict__ cntL,
-    const orbfe_keypoint* __restrict__ kpR, const uint8_t* __restrict__ descR, const int32_t* __restrict__ cntR,
+    const orbfe_keypoint* __restrict__ kpR, const uint8_t* __restrict__ descR, const int4* __restrict__ band,
+    const int32_t* __restrict__ bucket_start, const int32_t* __restrict__ bucket_items, int items_per_kp,
     float mbf, float mb, float* __restrict__ u_right, float* __restrict__ depth, int32_t* __restrict__ sad_out) {
-  __shared__ short2 s_band[ST_CHUNK];   // (minr, maxr)
-  __shared__ float s_x[ST_CHUNK];
-  __shared__ int8_t s_oct[ST_CHUNK];
-
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = blockIdx.y;
-  const int nL = cntL[b], nR = cntR[b];
+  const int nL = cntL[b];
   const int iL = blockIdx.x * ST_WARPS + warp;
-  if (blockIdx.x * ST_WARPS >= nL) return;  // whole CTA idle
-  const bool active = iL < nL;
+  if (iL >= nL) return;
+  const bool active = true;
   const orbfe_keypoint* kl = kpL + (size_t)b * g.out_cap;
   const orbfe_keypoint* kr = kpR + (size_t)b * g.out_cap;
   const int n_rows = g.lv[0].h;                  // mvImagePyramid[0].rows (:503)
   const float maxD = __fdiv_rn(mbf, mb);         // :536
-  float uL = 0.f, vL = 0.f;
-  int levelL = 0, rowi = -1;
-  uint4 d0 = make_uint4(0, 0, 0, 0), d1 = d0;
-  if (active) {
-    uL = kl[iL].x; vL = kl[iL].y; levelL = kl[iL].octave;
-    rowi = (int)vL;  // :549
-    const uint4* dp = reinterpret_cast<const uint4*>(descL + ((size_t)b * g.out_cap + iL) * 32);
-    d0 = __ldg(dp); d1 = __ldg(dp + 1);
-  }
+  const float uL = kl[iL].x, vL = kl[iL].y;
+  const int levelL = kl[iL].octave;
+  const int rowi = (int)vL;  // :549
+  const uint4* dpl = reinterpret_cast<const uint4*>(descL + ((size_t)b * g.out_cap + iL) * 32);
+  const uint4 d0 = __ldg(dpl), d1 = __ldg(dpl + 1);
   const float minU = __fsub_rn(uL, maxD), maxU = uL;  // :554-555 (minD = 0)
-  const bool searchable = active && rowi >= 0 && rowi < n_rows && !(maxU < 0.f);
+  const bool searchable = rowi >= 0 && rowi < n_rows && !(maxU < 0.f);
   unsigned best = ((unsigned)TH_HIGH << 16);  // bestDist = TH_HIGH, strict '<' below (:560,:581)
-
-  for (int base = 0; base < nR; base += ST_CHUNK) {
-    const int cn = min(ST_CHUNK, nR - base);
-    __syncthreads();
-    for (int i = threadIdx.x; i < cn; i += ST_WARPS * 32) {
-      const orbfe_keypoint k = kr[base + i];
-      const float r = __fmul_rn(2.0f, g.lv[k.octave].scale);           // :525
-      const int maxr = (int)ceilf(__fadd_rn(k.y, r)), minr = (int)floorf(__fsub_rn(k.y, r));
-      s_band[i] = make_short2((short)max(minr, -32768), (short)min(maxr, 32767));
-      s_x[i] = k.x;
-      s_oct[i] = (int8_t)k.octave;
-    }
-    __syncthreads();
-    if (searchable) {
-      for (int i = lane; i < cn; i += 32) {
-        const short2 bd = s_band[i];
-        const int o = s_oct[i];
-        const float uR = s_x[i];
-        if (rowi >= bd.x && rowi <= bd.y && o >= levelL - 1 && o <= levelL + 1 && uR >= minU && uR <= maxU) {
-          const uint4* dp = reinterpret_cast<const uint4*>(descR + ((size_t)b * g.out_cap + base + i) * 32);
-          const unsigned dist = (unsigned)hamming256(d0, d1, __ldg(dp), __ldg(dp + 1));
-          best = min(best, (dist << 16) | (unsigned)(base + i));
-        }
+  if (searchable) {
+    const int nb = (n_rows + ST_BROWS - 1) / ST_BROWS;
+    const int32_t* bstart = bucket_start + (size_t)b * (nb + 1);
+    const int32_t* bitems = bucket_items + (size_t)b * g.out_cap * items_per_kp;
+    const int4* bands = band + (size_t)b * g.out_cap;
+    const int bk = rowi / ST_BROWS;
+    const int beg = bstart[bk], end = bstart[bk + 1];
+    for (int p = beg + lane; p < end; p += 32) {
+      const int iR = bitems[p];
+      const int4 bd = __ldg(bands + iR);  // minr, maxr, x bits, octave
+      const float uR = __int_as_float(bd.z);
+      if (rowi >= bd.x && rowi <= bd.y && bd.w >= levelL - 1 && bd.w <= levelL + 1 && uR >= minU && uR <= maxU) {
+        const uint4* dp = reinterpret_cast<const uint4*>(descR + ((size_t)b * g.out_cap + iR) * 32);
+        const unsigned dist = (unsigned)hamming256(d0, d1, __ldg(dp), __ldg(dp + 1));
+        best = min(best, (dist << 16) | (unsigned)iR);
       }
     }
   }
@@ -95,7 +140,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32) stereo_match_kernel(
   float res_u = -1.f, res_d = -1.f;
   int res_sad = -1;
   const int bestDist = (int)(best >> 16);
-  if (searchable && bestDist < (TH_HIGH + TH_LOW) / 2) {  // :591
+  if (bestDist < (TH_HIGH + TH_LOW) / 2) {  // :591 (bestDist stays TH_HIGH when not searchable)
     const int bestIdxR = (int)(best & 0xFFFFu);
     const float uR0 = kr[bestIdxR].x;
     const LevelGeom& LV = g.lv[levelL];
@@ -208,14 +253,22 @@ __global__ void __launch_bounds__(1024) stereo_median_kernel(const __grid_consta
 void launch_stereo(const PyrGeom& g, const ExtractorArena& l, const ExtractorArena& r, int batch, float mbf, float mb,
                    cudaStream_t s, cudaEvent_t* ev) {
   if (ev) cudaEventRecord(ev[0], s);
+  stereo_bucket_kernel<<<batch, 512, 0, s>>>(g, r.out_kp, r.out_count, l.st_band, l.st_bucket_start, l.st_bucket_items,
+                                            l.st_items_per_kp);
   dim3 grid((g.out_cap + ST_WARPS - 1) / ST_WARPS, batch);
   stereo_match_kernel<<<grid, ST_WARPS * 32, 0, s>>>(g, l.pyr, r.pyr, l.out_kp, l.out_desc, l.out_count, r.out_kp,
-                                                     r.out_desc, r.out_count, mbf, mb, l.st_uright, l.st_depth,
-                                                     l.st_sad);
+                                                     r.out_desc, l.st_band, l.st_bucket_start, l.st_bucket_items,
+                                                     l.st_items_per_kp, mbf, mb, l.st_uright, l.st_depth, l.st_sad);
   if (ev) cudaEventRecord(ev[1], s);
   stereo_median_kernel<<<batch, 1024, (size_t)g.out_cap * sizeof(int), s>>>(g, l.out_count, l.st_uright, l.st_depth,
                                                                             l.st_sad, l.st_count);
   if (ev) cudaEventRecord(ev[2], s);
+}
+
+int stereo_items_per_kp(const PyrGeom& g) {
+  float smax = 1.f;
+  for (int i = 0; i < g.nlevels; ++i) smax = g.lv[i].scale > smax ? g.lv[i].scale : smax;
+  return (int)((4.f * smax + 3.f) / ST_BROWS) + 2;  // buckets one band can touch
 }
 
 }  // namespace orbfe

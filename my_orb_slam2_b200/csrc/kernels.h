@@ -10,6 +10,7 @@ namespace orbfe {
 // device arenas of one extractor handle (all sized for max_batch images)
 struct ExtractorArena {
   uint8_t* pyr = nullptr;          // level-major: lv[l].lvl_base + b*lv[l].lvl_bytes
+  uint8_t* blur = nullptr;         // blurred levels, same layout as pyr
   XTab* xtab = nullptr;
   YTab* ytab = nullptr;
   uint32_t* cand = nullptr;        // [batch][cand_total]
@@ -26,6 +27,10 @@ struct ExtractorArena {
   float* st_depth = nullptr;    // [batch][out_cap]
   int32_t* st_sad = nullptr;    // [batch][out_cap]
   int32_t* st_count = nullptr;  // [batch]
+  int4* st_band = nullptr;             // [batch][out_cap] right keypoint: minr, maxr, x bits, octave
+  int32_t* st_bucket_start = nullptr;  // [batch][rows/8 + 2]
+  int32_t* st_bucket_items = nullptr;  // [batch][out_cap * st_items_per_kp]
+  int st_items_per_kp = 0;
 };
 
 enum : int { FLAG_CAND_OVERFLOW = 1, FLAG_NODE_OVERFLOW = 2, FLAG_OUT_OVERFLOW = 4 };
@@ -37,13 +42,16 @@ void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cud
 // DistributeOctTree (:539-765): one CTA per (level, image)
 void launch_quadtree(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
 size_t quadtree_smem_bytes(int node_cap);
-// computeOrientation (:472-479) + GaussianBlur (:1108) + computeDescriptors (:1056-1063) + rescale (:1117-1123)
+// GaussianBlur(7x7, sigma 2) of every level (:1107-1108), one launch
+void launch_blur_levels(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
+// computeOrientation (:472-479) + computeDescriptors (:1056-1063) + rescale (:1117-1123)
 void launch_describe(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
 // Frame::ComputeStereoMatches (src/Frame.cc:496-686)
 void launch_stereo(const PyrGeom& g, const ExtractorArena& left, const ExtractorArena& right, int batch, float mbf,
                    float mb, cudaStream_t s, cudaEvent_t* stage_events /* 3 or nullptr */);
 
 constexpr int kLaunchesPerExtract(int nlevels) { return (nlevels - 1) + 3; }
-constexpr int kLaunchesPerStereo = 2;
+constexpr int kLaunchesPerStereo = 3;
+int stereo_items_per_kp(const PyrGeom& g);
 
 }  // namespace orbfe

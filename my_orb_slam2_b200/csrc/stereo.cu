@@ -29,7 +29,7 @@ int orbfe_stereo_match_run(orbfe_extractor* hl, orbfe_extractor* hr, int batch, 
   }
   cudaEvent_t* ev = nullptr;
   if (l->profiling && l->prof_ev && l->prof_stereo_runs < Extractor::kProfRuns)
-    ev = l->prof_ev + 5 * Extractor::kProfRuns + 3 * l->prof_stereo_runs++;
+    ev = l->prof_ev + 6 * Extractor::kProfRuns + 3 * l->prof_stereo_runs++;
   launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream, ev);
   l->launches += kLaunchesPerStereo;
   ORBFE_CUDA(cudaGetLastError());

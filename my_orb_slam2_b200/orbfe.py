@@ -84,6 +84,8 @@ SYMBOLS = {
     "orbfe_extractor_sync": (_I, [_P]),
     "orbfe_extractor_stream": (_P, [_P]),
     "orbfe_extractor_launch_count": (C.c_int64, [_P]),
+    "orbfe_extractor_set_profiling": (_I, [_P, _I]),
+    "orbfe_extractor_stage_times": (_I, [_P, _P, _P, _P]),
     "orbfe_extractor_level": (_I, [_P, _I, _I, C.POINTER(_P), C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)]),
     "orbfe_extractor_download_level": (_I, [_P, _I, _I, _P, _I]),
     "orbfe_extractor_device_results": (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_I)]),
@@ -208,6 +210,17 @@ class Extractor:
     @property
     def launch_count(self):
         return lib().orbfe_extractor_launch_count(self._h)
+
+    def set_profiling(self, enable=True):
+        check(lib().orbfe_extractor_set_profiling(self._h, int(enable)))
+
+    def stage_times(self):
+        """Summed CUDA-event milliseconds per stage since set_profiling(True): dict + number of runs covered."""
+        ms = np.zeros(7, np.float32)
+        runs, sruns = C.c_int32(), C.c_int32()
+        check(lib().orbfe_extractor_stage_times(self._h, _p(ms), C.byref(runs), C.byref(sruns)))
+        names = ["pyramid", "fast", "quadtree", "blur", "describe", "stereo_match", "stereo_median"]
+        return dict(zip(names, [float(x) for x in ms])), runs.value, sruns.value
 
     # -- pyramid / stage dumps ------------------------------------------------------------
     def level_shape(self, lv):
