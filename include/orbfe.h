@@ -80,6 +80,9 @@ int orbfe_extract_run(orbfe_extractor* e, int batch);
 int orbfe_extract_download(orbfe_extractor* e, int batch, orbfe_keypoint* keypoints, uint8_t* descriptors,
                            int capacity, int32_t* counts);
 int orbfe_extractor_sync(orbfe_extractor* e);
+/* Make `e` issue its work on `other`'s stream from now on (e.g. the left and right extractor of a stereo rig in
+ * throughput mode: one in-order stream, no cross-stream events).  `other` must outlive `e`'s use of it. */
+int orbfe_extractor_share_stream(orbfe_extractor* e, orbfe_extractor* other);
 /* The handle's cudaStream_t (as void*), for event timing by the caller. */
 void* orbfe_extractor_stream(orbfe_extractor* e);
 /* Kernels launched by this handle since creation. */

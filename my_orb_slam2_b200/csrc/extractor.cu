@@ -188,6 +188,7 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
   const size_t B = (size_t)e->max_batch;
   ORBFE_CUDA(dalloc(&a.pyr, e->pyr_bytes + 256));
   ORBFE_CUDA(dalloc(&a.blur, e->pyr_bytes + 256));
+  ORBFE_CUDA(dalloc(&a.stage, B * (size_t)e->width * e->height));
   ORBFE_CUDA(dalloc(&a.xtab, xt.size()));
   ORBFE_CUDA(dalloc(&a.ytab, yt.size()));
   ORBFE_CUDA(dalloc(&a.cand, B * g.cand_total));
@@ -220,7 +221,7 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
 
 static void free_arenas(Extractor* e) {
   ExtractorArena& a = e->arena;
-  cudaFree(a.pyr); cudaFree(a.blur); cudaFree(a.xtab); cudaFree(a.ytab); cudaFree(a.cand); cudaFree(a.node_of);
+  cudaFree(a.pyr); cudaFree(a.blur); cudaFree(a.stage); cudaFree(a.xtab); cudaFree(a.ytab); cudaFree(a.cand); cudaFree(a.node_of);
   cudaFree(a.cand_count); cudaFree(a.kept); cudaFree(a.kept_count); cudaFree(a.out_kp); cudaFree(a.out_desc);
   cudaFree(a.out_count); cudaFree(a.flags); cudaFree(a.st_uright); cudaFree(a.st_depth); cudaFree(a.st_sad);
   cudaFree(a.st_count); cudaFree(a.st_band); cudaFree(a.st_bucket_start); cudaFree(a.st_bucket_items);
@@ -291,7 +292,7 @@ void orbfe_extractor_destroy(orbfe_extractor* h) {
   cudaStreamSynchronize(e->stream);
   free_arenas(e);
   if (e->done) cudaEventDestroy(e->done);
-  cudaStreamDestroy(e->stream);
+  if (e->owns_stream) cudaStreamDestroy(e->stream);
   delete e;
 }
 
@@ -305,6 +306,19 @@ void* orbfe_extractor_stream(orbfe_extractor* h) { return h ? reinterpret_cast<E
 
 int64_t orbfe_extractor_launch_count(const orbfe_extractor* h) {
   return h ? reinterpret_cast<const Extractor*>(h)->launches : 0;
+}
+
+int orbfe_extractor_share_stream(orbfe_extractor* h, orbfe_extractor* other) {
+  ORBFE_ARG(h && other && h != other);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  Extractor* o = reinterpret_cast<Extractor*>(other);
+  ORBFE_ARG(e->device == o->device);
+  DeviceGuard guard(e->device);
+  ORBFE_CUDA(cudaStreamSynchronize(e->stream));
+  if (e->owns_stream) cudaStreamDestroy(e->stream);
+  e->stream = o->stream;
+  e->owns_stream = false;
+  return ORBFE_OK;
 }
 
 int orbfe_extractor_sync(orbfe_extractor* h) {
@@ -324,7 +338,15 @@ int orbfe_extract_upload(orbfe_extractor* h, const uint8_t* images, size_t image
   const LevelGeom& L0 = e->geom.lv[0];
   const cudaMemcpyKind kind = images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
   uint8_t* dst = e->arena.pyr + L0.lvl_base;
-  if (batch == 1 || image_stride == (size_t)row_stride * e->height) {
+  const bool packed = image_stride == (size_t)row_stride * e->height || batch == 1;
+  if (!images_on_device && packed && row_stride == e->width && L0.pitch != e->width) {
+    // tightly packed host images: ONE linear H2D (full DMA rate; a 2-D copy with an odd width runs several times
+    // slower) into a staging buffer, then a 2-D device-to-device copy into the pitched level 0
+    const size_t bytes = (size_t)e->width * e->height * batch;
+    ORBFE_CUDA(cudaMemcpyAsync(e->arena.stage, images, bytes, cudaMemcpyHostToDevice, e->stream));
+    ORBFE_CUDA(cudaMemcpy2DAsync(dst, L0.pitch, e->arena.stage, e->width, e->width, (size_t)e->height * batch,
+                                 cudaMemcpyDeviceToDevice, e->stream));
+  } else if (packed) {
     // images are back to back: one 2-D copy of batch*height rows (level-major arena: image b at b*pitch*h)
     ORBFE_CUDA(cudaMemcpy2DAsync(dst, L0.pitch, images, row_stride, e->width, (size_t)e->height * batch, kind,
                                  e->stream));
@@ -413,13 +435,22 @@ int orbfe_extract_download(orbfe_extractor* h, int batch, orbfe_keypoint* keypoi
   const int ncopy = capacity < g.out_cap ? capacity : g.out_cap;
   ORBFE_CUDA(cudaMemcpyAsync(counts, a.out_count, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
   ORBFE_CUDA(cudaMemcpyAsync(e->h_flags, a.flags, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
-  if (ncopy > 0 && keypoints)
-    ORBFE_CUDA(cudaMemcpy2DAsync(keypoints, (size_t)capacity * sizeof(orbfe_keypoint), a.out_kp,
-                                 (size_t)g.out_cap * sizeof(orbfe_keypoint), (size_t)ncopy * sizeof(orbfe_keypoint),
-                                 batch, cudaMemcpyDeviceToHost, e->stream));
-  if (ncopy > 0 && descriptors)
-    ORBFE_CUDA(cudaMemcpy2DAsync(descriptors, (size_t)capacity * 32, a.out_desc, (size_t)g.out_cap * 32,
-                                 (size_t)ncopy * 32, batch, cudaMemcpyDeviceToHost, e->stream));
+  if (capacity == g.out_cap) {  // same slab layout on both sides: linear copies
+    if (keypoints)
+      ORBFE_CUDA(cudaMemcpyAsync(keypoints, a.out_kp, (size_t)batch * g.out_cap * sizeof(orbfe_keypoint),
+                                 cudaMemcpyDeviceToHost, e->stream));
+    if (descriptors)
+      ORBFE_CUDA(cudaMemcpyAsync(descriptors, a.out_desc, (size_t)batch * g.out_cap * 32, cudaMemcpyDeviceToHost,
+                                 e->stream));
+  } else {
+    if (ncopy > 0 && keypoints)
+      ORBFE_CUDA(cudaMemcpy2DAsync(keypoints, (size_t)capacity * sizeof(orbfe_keypoint), a.out_kp,
+                                   (size_t)g.out_cap * sizeof(orbfe_keypoint), (size_t)ncopy * sizeof(orbfe_keypoint),
+                                   batch, cudaMemcpyDeviceToHost, e->stream));
+    if (ncopy > 0 && descriptors)
+      ORBFE_CUDA(cudaMemcpy2DAsync(descriptors, (size_t)capacity * 32, a.out_desc, (size_t)g.out_cap * 32,
+                                   (size_t)ncopy * 32, batch, cudaMemcpyDeviceToHost, e->stream));
+  }
   ORBFE_CUDA(cudaStreamSynchronize(e->stream));
   for (int b = 0; b < batch; ++b) {
     if (e->h_flags[b]) { set_error("image %d: internal slab overflow (flags=%d)", b, e->h_flags[b]); return ORBFE_ERR_CAPACITY; }

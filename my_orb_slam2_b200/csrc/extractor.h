@@ -18,6 +18,7 @@ struct Extractor {
   ExtractorArena arena{};
   size_t pyr_bytes = 0;
   cudaStream_t stream = nullptr;
+  bool owns_stream = true;
   cudaEvent_t done = nullptr;   // recorded after the last queued work (cross-handle ordering for stereo)
   int32_t* h_flags = nullptr;   // pinned
   int64_t launches = 0;

@@ -99,29 +99,26 @@ __global__ void __launch_bounds__(FAST_T) fast_cells_kernel(const __grid_constan
   if (cw < 7 || ch < 7) return;  // cv::FAST finds nothing in such a sliver
 
   if (tid == 0) { n1 = 0; n2 = 0; n3 = 0; n_hi = 0; }
+  // i / cw and i / dw below: multiply by ceil(2^32 / d) (exact for i < 2^32 / d; here i < 4489)
+  const unsigned inv_cw = 0xFFFFFFFFu / (unsigned)cw + 1u;
   const uint8_t* img = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)y0 * L.pitch + x0;
   for (int i = tid; i < ch * cw; i += FAST_T) {
-    const int r = i / cw, c = i - r * cw;
+    const int r = (int)__umulhi((unsigned)i, inv_cw), c = i - r * cw;
     roi[r * RS + c] = __ldg(img + (size_t)r * L.pitch + c);
   }
-  for (int i = tid; i < (ROI_MAX * RS) / 4; i += FAST_T) reinterpret_cast<uint32_t*>(score)[i] = 0u;
+  for (int i = tid; i < ch * (RS / 4); i += FAST_T) reinterpret_cast<uint32_t*>(score)[i] = 0u;
   __syncthreads();
 
-#ifdef ORBFE_DEBUG_FAST
-  if (blockIdx.x == 0 && b == 0 && tid == 0) {
-    printf("DBG cell0 lvl %d x0 %d y0 %d cw %d ch %d pitch %d ini %d min %d wcell %d hcell %d ncols %d\n", lvl, x0, y0, cw, ch, L.pitch, g.ini_th, g.min_th, L.w_cell, L.h_cell, L.n_cols);
-    for (int r = 0; r < 8; ++r) { for (int c = 0; c < 12; ++c) printf("%3d ", roi[r * RS + c]); printf("\n"); }
-  }
-#endif
   const int t_lo = min(g.ini_th, g.min_th);
   const int dw = cw - 6, dh = ch - 6, npx = dw * dh;
+  const unsigned inv_dw = 0xFFFFFFFFu / (unsigned)dw + 1u;
   // stage 1: quick reject
   for (int base = 0; base < npx; base += FAST_T) {
     const int i = base + tid;
     bool keep = false;
     int pos = 0;
     if (i < npx) {
-      const int r = i / dw, c = i - r * dw;
+      const int r = (int)__umulhi((unsigned)i, inv_dw), c = i - r * dw;
       pos = (r + 3) * RS + (c + 3);
       const uint8_t* p = roi + pos;
       const int v = p[0], hi = v + t_lo, lo = v - t_lo;
@@ -200,7 +197,7 @@ __global__ void __launch_bounds__(FAST_T) fast_cells_kernel(const __grid_constan
   uint32_t* out = cand + (size_t)b * g.cand_total + L.cand_off;
   for (int i = tid; i < ne; i += FAST_T) {
     const int pos = list2[i];
-    const int r = pos / RS, c = pos - r * RS;
+    const int r = (int)__umulhi((unsigned)pos, 0xFFFFFFFFu / RS + 1u), c = pos - r * RS;
     if (ob + i < L.cand_cap) out[ob + i] = pack_cand(c + cj * L.w_cell, r + ci * L.h_cell, score[pos]);
     else atomicOr(&flags[b], FLAG_CAND_OVERFLOW);
   }

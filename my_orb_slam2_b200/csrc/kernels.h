@@ -11,6 +11,7 @@ namespace orbfe {
 struct ExtractorArena {
   uint8_t* pyr = nullptr;          // level-major: lv[l].lvl_base + b*lv[l].lvl_bytes
   uint8_t* blur = nullptr;         // blurred levels, same layout as pyr
+  uint8_t* stage = nullptr;        // [batch][h][w] landing buffer of linear H2D uploads
   XTab* xtab = nullptr;
   YTab* ytab = nullptr;
   uint32_t* cand = nullptr;        // [batch][cand_total]

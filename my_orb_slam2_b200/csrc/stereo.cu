@@ -23,7 +23,7 @@ int orbfe_stereo_match_run(orbfe_extractor* hl, orbfe_extractor* hr, int batch, 
   }
   ORBFE_ARG(mb > 0.f);
   DeviceGuard guard(l->device);
-  if (l != r) {  // order left's stream after right's queued work (the join at src/Frame.cc:91-92)
+  if (l != r && l->stream != r->stream) {  // order left's stream after right's queued work (the join at src/Frame.cc:91-92)
     ORBFE_CUDA(cudaEventRecord(r->done, r->stream));
     ORBFE_CUDA(cudaStreamWaitEvent(l->stream, r->done, 0));
   }

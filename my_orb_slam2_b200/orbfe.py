@@ -82,6 +82,7 @@ SYMBOLS = {
     "orbfe_extract_run": (_I, [_P, _I]),
     "orbfe_extract_download": (_I, [_P, _I, _P, _P, _I, _P]),
     "orbfe_extractor_sync": (_I, [_P]),
+    "orbfe_extractor_share_stream": (_I, [_P, _P]),
     "orbfe_extractor_stream": (_P, [_P]),
     "orbfe_extractor_launch_count": (C.c_int64, [_P]),
     "orbfe_extractor_set_profiling": (_I, [_P, _I]),
@@ -202,6 +203,9 @@ class Extractor:
 
     def sync(self):
         check(lib().orbfe_extractor_sync(self._h))
+
+    def share_stream(self, other):
+        check(lib().orbfe_extractor_share_stream(self._h, other._h))
 
     @property
     def stream(self):
