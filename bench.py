@@ -296,6 +296,8 @@ def run_gpu(args):
         L1.close()
         R1.close()
 
+    R.close()  # R borrows L's stream: release it first
+    L.close()
     if world > 1:
         dist.barrier()
     if rank != 0:

@@ -289,7 +289,8 @@ void orbfe_extractor_destroy(orbfe_extractor* h) {
   if (!h) return;
   Extractor* e = reinterpret_cast<Extractor*>(h);
   DeviceGuard guard(e->device);
-  cudaStreamSynchronize(e->stream);
+  // a borrowed stream (orbfe_extractor_share_stream) may already be gone: wait for the whole device instead
+  if (e->owns_stream) cudaStreamSynchronize(e->stream); else cudaDeviceSynchronize();
   free_arenas(e);
   if (e->done) cudaEventDestroy(e->done);
   if (e->owns_stream) cudaStreamDestroy(e->stream);
