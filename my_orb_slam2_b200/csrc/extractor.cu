@@ -104,7 +104,7 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
   g.ini_th = e->params.ini_th_fast < 0 ? 0 : (e->params.ini_th_fast > 255 ? 255 : e->params.ini_th_fast);
   g.min_th = e->params.min_th_fast < 0 ? 0 : (e->params.min_th_fast > 255 ? 255 : e->params.min_th_fast);
   unsigned long long pyr_off = 0;
-  int cells = 0, cand = 0, kept = 0, node_cap_max = 8, blur_tiles = 0;
+  int cells = 0, cand = 0, kept = 0, node_cap_max = 8, blur_tiles = 0, fast_strips = 0;
   for (int l = 0; l < g.nlevels; ++l) {
     LevelGeom& L = g.lv[l];
     L.scale = info.scale_factors[l];
@@ -133,6 +133,12 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
     cells += L.n_cols * L.n_rows;
     L.blur_tile_base = blur_tiles;
     blur_tiles += ((L.w + 127) / 128) * ((L.h + 127) / 128);
+    L.fast_strip_base = fast_strips;
+    L.fast_strips_x = 0;
+    if (L.n_cols > 0) {  // detection domain x in [19, w-19), y in [19, h-19); owned columns start at x = 16
+      L.fast_strips_x = (L.w - 2 * kMinBorder - 3 + kFastOwnCols - 1) / kFastOwnCols;
+      fast_strips += L.fast_strips_x * ((L.h - 2 * (kMinBorder + 3) + kFastOwnRows - 1) / kFastOwnRows);
+    }
     L.quota = info.features_per_level[l];
     L.n_ini = 1;
     L.h_x = 1.f;
@@ -167,6 +173,7 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
   }
   g.total_cells = cells;
   g.blur_tiles = blur_tiles;
+  g.fast_strips = fast_strips;
   g.cand_total = std::max(cand, 4);
   g.kept_total = std::max(kept, 4);
   g.out_cap = (int)align_up((size_t)kept + 8, 8);
@@ -194,6 +201,7 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
   ORBFE_CUDA(dalloc(&a.cand, B * g.cand_total));
   ORBFE_CUDA(dalloc(&a.node_of, B * g.cand_total));
   ORBFE_CUDA(dalloc(&a.cand_count, B * kMaxLevels));
+  ORBFE_CUDA(dalloc(&a.cell_hi, B * (size_t)std::max(g.total_cells, 1)));
   ORBFE_CUDA(dalloc(&a.kept, B * g.kept_total));
   ORBFE_CUDA(dalloc(&a.kept_count, B * kMaxLevels));
   ORBFE_CUDA(dalloc(&a.out_kp, B * g.out_cap));
@@ -222,7 +230,7 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
 static void free_arenas(Extractor* e) {
   ExtractorArena& a = e->arena;
   cudaFree(a.pyr); cudaFree(a.blur); cudaFree(a.stage); cudaFree(a.xtab); cudaFree(a.ytab); cudaFree(a.cand); cudaFree(a.node_of);
-  cudaFree(a.cand_count); cudaFree(a.kept); cudaFree(a.kept_count); cudaFree(a.out_kp); cudaFree(a.out_desc);
+  cudaFree(a.cand_count); cudaFree(a.cell_hi); cudaFree(a.kept); cudaFree(a.kept_count); cudaFree(a.out_kp); cudaFree(a.out_desc);
   cudaFree(a.out_count); cudaFree(a.flags); cudaFree(a.st_uright); cudaFree(a.st_depth); cudaFree(a.st_sad);
   cudaFree(a.st_count); cudaFree(a.st_band); cudaFree(a.st_bucket_start); cudaFree(a.st_bucket_items);
   if (e->h_flags) cudaFreeHost(e->h_flags);
@@ -372,7 +380,7 @@ int orbfe_extract_run(orbfe_extractor* h, int batch) {
   if (ev) cudaEventRecord(ev[0], e->stream);
   for (int l = 1; l < g.nlevels; ++l) launch_pyramid_level(g, a, l, batch, e->stream);  // ComputePyramid (:1075)
   if (ev) cudaEventRecord(ev[1], e->stream);
-  if (g.total_cells > 0) launch_fast_cells(g, a, batch, e->stream);                      // :776-850
+  launch_fast_cells(g, a, batch, e->stream);                      // :776-850
   if (ev) cudaEventRecord(ev[2], e->stream);
   launch_quadtree(g, a, batch, e->stream);                                               // :853
   if (ev) cudaEventRecord(ev[3], e->stream);
@@ -380,7 +388,7 @@ int orbfe_extract_run(orbfe_extractor* h, int batch) {
   if (ev) cudaEventRecord(ev[4], e->stream);
   launch_describe(g, a, batch, e->stream);                                               // :873-874, :1096-1126
   if (ev) { cudaEventRecord(ev[5], e->stream); ++e->prof_runs; }
-  e->launches += (g.nlevels - 1) + (g.total_cells > 0 ? 1 : 0) + 3;
+  e->launches += (g.nlevels - 1) + (g.fast_strips > 0 ? 1 : 0) + 3;
   e->last_batch = batch;
   ORBFE_CUDA(cudaGetLastError());
   return ORBFE_OK;

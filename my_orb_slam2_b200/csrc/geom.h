@@ -9,6 +9,8 @@ namespace orbfe {
 
 constexpr int kMinBorder = 16;   // EDGE_THRESHOLD-3 (src/ORBextractor.cc:785)
 constexpr int kMaxLevels = 16;
+constexpr int kFastOwnCols = 120;  // k_fast.cu: a strip computes 128 x 32 pixels and owns the inner 120 x 30
+constexpr int kFastOwnRows = 30;
 
 struct LevelGeom {
   int w, h, pitch;          // level image; pitch multiple of 128
@@ -17,6 +19,8 @@ struct LevelGeom {
   int w_cell, h_cell;       // (:798-799)
   int cell_base;            // id of this level's first cell within one image
   int blur_tile_base;       // id of this level's first 128x128 blur tile within one image
+  int fast_strip_base;      // id of this level's first FAST strip (k_fast.cu) within one image
+  int fast_strips_x;        // strips per strip row (0 => level has no cells)
   int quota;                // mnFeaturesPerLevel[level] (:435-446)
   int n_ini;                // quadtree roots (:543)
   float h_x;                // root width (:545)
@@ -35,6 +39,7 @@ struct PyrGeom {
   int nlevels;
   int total_cells;  // per image
   int blur_tiles;   // per image
+  int fast_strips;  // per image
   int cand_total;   // per image candidate capacity (sum over levels)
   int kept_total;   // per image kept capacity (sum over levels)
   int out_cap;      // per image output capacity (info.capacity)

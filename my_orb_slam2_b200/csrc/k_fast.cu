@@ -2,210 +2,329 @@
 // src/ORBextractor.cc:776-850): cv::FAST(cell ROI, iniThFAST, NMS) and, when a
 // cell returns nothing, cv::FAST(cell ROI, minThFAST, NMS) (:830-837).
 //
-// One CTA per 30-px cell (the reference's own unit: NMS never crosses a cell,
-// SURVEY.md A.3 / B.2).  The ROI (cell + 3 px FAST margin on each side) is staged
-// in shared memory.  The work is done in compacted stages so that warps stay
-// convergent:
-//   1. quick reject on the two opposite ring pairs (0,8) and (4,12): any 9-arc
-//      contains one pixel of each pair -> warp-ballot compaction into a list;
-//   2. corner strength m = max over the 16 arcs of min|diff| for listed pixels
-//      (sliding-window min/max by doubling, 4 steps), score = m-1 into a score
-//      tile; pixels with m > min(iniTh,minTh) go to a second list;
-//   3. strict 8-neighbour maximum test on that list (score tile is 0 outside
-//      the detection area, so suppression is cell-local as in the reference);
-//   4. threshold choice per cell: the set of strict local maxima does not
-//      depend on the threshold (a neighbour below the threshold is below the
-//      centre anyway), so FAST(t) = {maxima with score >= t}; emit the iniTh
-//      set if it is non-empty, else the minTh set.
-// Candidates are appended (one atomicAdd per CTA) to the level's list as
-// x | y<<12 | score<<24 with x,y relative to minBorder, as the reference stores
-// them (:841-846).  List order is not the reference's; the consumer
-// (k_quadtree.cu) breaks ties by the reference's order key computed from (x,y).
+// The corner score of a pixel does not depend on the cell it is in; only the
+// non-maximum suppression (cell-local, because cv::FAST runs on the cell ROI) and
+// the threshold choice do.  So detection is ONE dense,
+// streaming kernel over whole levels, and the per-cell threshold choice is a
+// filter in front of the quadtree (k_quadtree.cu):
+//
+//  fast_detect_kernel — a warp owns a strip of one level: it computes 128 columns
+//  x 32 rows and owns the inner 120 x 30 (1-px halo for the 3x3 suppression, padded
+//  to whole words).  Warps are independent (no CTA barrier).
+//   1. dense quick reject.  A lane owns one aligned 32-bit word (4 pixels) and
+//      walks down the rows with the last 7 centre words in registers.  Per row it
+//      loads three aligned words (coalesced 128 B per warp), forms the x-3 / x+3
+//      neighbours with funnel shifts and tests four pixels at once: any 9-arc of
+//      the 16-ring contains one pixel of each opposite pair (0,8) and (4,12), so a
+//      corner needs |p-v| > t on one of each pair — 4 x VABSDIFF4 + SWAR "byte >
+//      t".  Survivors (~14 % on textured images) stay a 128-bit register mask per
+//      lane; the rows are also copied into a shared-memory tile for step 2.
+//   2. exact corner strength, one lane per survivor (masks flattened into a
+//      per-warp list so the lanes are balanced): m = max over the 16 arcs of
+//      min|diff| = max(max_arc(min ring) - v, v - min_arc(max ring)); with
+//      x = p | (255-p)<<16 both halves are arc MINIMA, so 40 VIMNMX3.U16x2 do all
+//      32 arcs.  score = m-1 goes into a shared-memory score tile.
+//   3. strict 8-neighbour maximum on the score tile for the owned pixels with a
+//      score; a neighbour in another cell's detection window counts as 0.  The set
+//      of strict local maxima does not depend on the threshold (a neighbour below
+//      the threshold is below the centre anyway), so FAST(t) = {maxima with score
+//      >= t}: every maximum with score >= min(iniTh, minTh) is appended to the
+//      level's list and a per-cell flag records "has a maximum >= iniTh"; the
+//      consumer keeps the iniTh set of flagged cells and the minTh set of the
+//      others (:830-837).
+// Candidates are x | y<<12 | score<<24 with x,y relative to minBorder, as the
+// reference stores them (:841-846).  List order is not the reference's; the
+// consumer (k_quadtree.cu) breaks ties by the reference's order key computed
+// from (x,y).
 #include <cstdio>
 
 #include "kernels.h"
 
 namespace orbfe {
 
-constexpr int FAST_T = 128;
-constexpr int ROI_MAX = 66;  // w_cell <= 60 (+6)
-constexpr int RS = 68;       // smem row stride
-constexpr int LIST_MAX = 60 * 60;
+constexpr int FD_WARPS = 4;             // independent warps per CTA
+constexpr int FD_T = FD_WARPS * 32;
+constexpr int FD_ROWS = 32;             // computed rows per strip (kFastOwnRows owned)
+constexpr int FD_TROWS = FD_ROWS + 6;   // image tile rows (FAST ring: +-3)
+constexpr int FD_TS = 136;              // image tile stride in bytes: columns -4 .. 131 of the strip
+constexpr int FD_TW = FD_TS / 4;
+constexpr int FD_CAP = 1024;            // list entries per pass
 
-__device__ __forceinline__ int warp_push(bool pred, int* counter) {
-  const unsigned m = __ballot_sync(0xffffffffu, pred);
-  if (m == 0) return -1;
-  const int lane = threadIdx.x & 31;
-  const int leader = __ffs(m) - 1;
-  int base = 0;
-  if (lane == leader) base = atomicAdd(counter, __popc(m));
-  base = __shfl_sync(0xffffffffu, base, leader);
-  return pred ? base + __popc(m & ((1u << lane) - 1u)) : -1;
+struct FdSmem {
+  uint8_t img[FD_TROWS * FD_TS];
+  uint8_t score[FD_ROWS * 128];
+  uint16_t list[FD_CAP];
+};
+
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)),
+               "l"(gmem_src)
+               : "memory");
 }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
-// max over the 16 circular 9-arcs of max(min(d), min(-d)); 0 if negative
+// exact corner strength of the pixel at p in the image tile: max over the 16 circular 9-arcs of the
+// minimum of (ring - v) resp. (v - ring) over the arc, 0 if negative.  Unsigned 16x2 min/max only (no negations:
+// ptxas 12.9 drops the negation when max(a, -b) is fused into VIMNMX3 on sm_100a).
 __device__ __forceinline__ int corner_strength(const uint8_t* p) {
+  constexpr int S = FD_TS;
+  unsigned x[16];
+  x[0] = p[3 * S];       x[1] = p[3 * S + 1];   x[2] = p[2 * S + 2];    x[3] = p[S + 3];
+  x[4] = p[3];           x[5] = p[-S + 3];      x[6] = p[-2 * S + 2];   x[7] = p[-3 * S + 1];
+  x[8] = p[-3 * S];      x[9] = p[-3 * S - 1];  x[10] = p[-2 * S - 2];  x[11] = p[-S - 3];
+  x[12] = p[-3];         x[13] = p[S - 3];      x[14] = p[2 * S - 2];   x[15] = p[3 * S - 1];
   const int v = p[0];
-  int d[16];
-  d[0] = v - p[3 * RS];       d[1] = v - p[3 * RS + 1];   d[2] = v - p[2 * RS + 2];   d[3] = v - p[RS + 3];
-  d[4] = v - p[3];            d[5] = v - p[-RS + 3];      d[6] = v - p[-2 * RS + 2];  d[7] = v - p[-3 * RS + 1];
-  d[8] = v - p[-3 * RS];      d[9] = v - p[-3 * RS - 1];  d[10] = v - p[-2 * RS - 2]; d[11] = v - p[-RS - 3];
-  d[12] = v - p[-3];          d[13] = v - p[RS - 3];      d[14] = v - p[2 * RS - 2];  d[15] = v - p[3 * RS - 1];
-  // min over every 9-arc of d (darker ring) and of e = -d (brighter ring).  NB: written with two min chains on
-  // purpose: ptxas 12.9 drops the negation when max(a, -b) is fused into VIMNMX3 on sm_100a (measured).
-  int e[16];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) e[i] = -d[i];
-  int a1[16], b1[16], a2[16], b2[16];
+  for (int i = 0; i < 16; ++i) x[i] = (x[i] * 0x00010001u) ^ 0x00FF0000u;  // low half p, high half 255-p
+  unsigned a3[16], a9[16];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) { a1[i] = min(d[i], d[(i + 1) & 15]); b1[i] = min(e[i], e[(i + 1) & 15]); }
+  for (int i = 0; i < 16; ++i) a3[i] = __vimin3_u16x2(x[i], x[(i + 1) & 15], x[(i + 2) & 15]);
 #pragma unroll
-  for (int i = 0; i < 16; ++i) { a2[i] = min(a1[i], a1[(i + 2) & 15]); b2[i] = min(b1[i], b1[(i + 2) & 15]); }
-#pragma unroll
-  for (int i = 0; i < 16; ++i) { a1[i] = min(a2[i], a2[(i + 4) & 15]); b1[i] = min(b2[i], b2[(i + 4) & 15]); }
-  int best = 0;
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    best = max(best, min(a1[i], d[(i + 8) & 15]));
-    best = max(best, min(b1[i], e[(i + 8) & 15]));
-  }
-  return best;
+  for (int i = 0; i < 16; ++i) a9[i] = __vimin3_u16x2(a3[i], a3[(i + 3) & 15], a3[(i + 6) & 15]);
+  unsigned m0 = __vimax3_u16x2(a9[0], a9[1], a9[2]);
+  const unsigned m1 = __vimax3_u16x2(a9[3], a9[4], a9[5]);
+  const unsigned m2 = __vimax3_u16x2(a9[6], a9[7], a9[8]);
+  unsigned m3 = __vimax3_u16x2(a9[9], a9[10], a9[11]);
+  const unsigned m4 = __vimax3_u16x2(a9[12], a9[13], a9[14]);
+  m0 = __vimax3_u16x2(m0, m1, m2);
+  m3 = __vimax3_u16x2(m3, m4, a9[15]);
+  const unsigned mm = __vimax3_u16x2(m0, m3, m3);
+  const int bright = (int)(mm & 0xFFFFu) - v;  // max over arcs of (min ring) - v
+  const int dark = (int)(mm >> 16) - 255 + v;  // v - min over arcs of (max ring)
+  return max(max(bright, dark), 0);
 }
 
-__global__ void __launch_bounds__(FAST_T) fast_cells_kernel(const __grid_constant__ PyrGeom g,
-                                                            const uint8_t* __restrict__ pyr,
-                                                            uint32_t* __restrict__ cand,
-                                                            int32_t* __restrict__ cand_count,
-                                                            int32_t* __restrict__ flags) {
-  __shared__ __align__(16) uint8_t roi[ROI_MAX * RS];
-  __shared__ __align__(16) uint8_t score[ROI_MAX * RS];
-  __shared__ uint16_t list1[LIST_MAX];
-  __shared__ uint16_t list2[LIST_MAX];
-  __shared__ int n1, n2, n3, n_hi, out_base;
+// bit 7 of a byte is set iff that byte of x or of y is > t (K = (127 - t) * 0x01010101, t <= 127); other bits: garbage
+__device__ __forceinline__ unsigned swar_gt2(unsigned x, unsigned y, unsigned K) {
+  return ((x & 0x7F7F7F7Fu) + K) | x | ((y & 0x7F7F7F7Fu) + K) | y;
+}
+// bits 7,15,23,31 of m -> bits 28..31 (distinct partial products, no carries)
+__device__ __forceinline__ unsigned gather_bit7(unsigned m) { return (m & 0x80808080u) * 0x00204081u; }
 
-  const int tid = threadIdx.x;
+// nibble (r & 7) of acc[r >> 3] := bits 28..31 of nib  (r is a compile-time constant after unrolling)
+__device__ __forceinline__ void put_nibble(unsigned (&acc)[4], int r, unsigned nib) {
+  const int q = r & 7;
+  acc[r >> 3] |= (q == 7) ? (nib & 0xF0000000u) : ((nib >> (28 - 4 * q)) & (0xFu << (4 * q)));
+}
+
+// exclusive prefix over the lanes of the per-lane set-bit counts; returns the warp total
+__device__ __forceinline__ int mask_scan(const unsigned (&acc)[4], int lane, int* excl) {
+  const int cnt = __popc(acc[0]) + __popc(acc[1]) + __popc(acc[2]) + __popc(acc[3]);
+  int incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  *excl = incl - cnt;
+  return __shfl_sync(0xffffffffu, incl, 31);
+}
+
+// write the entries (row<<7 | column) whose flat index lies in [lo, lo+FD_CAP) into list[index - lo]
+__device__ __forceinline__ void flatten_window(const unsigned (&acc)[4], int lane, int excl, int lo, uint16_t* list) {
+  int off = excl - lo;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    unsigned a = acc[q];
+    while (a) {
+      const int bit = __ffs(a) - 1;
+      a &= a - 1;
+      if ((unsigned)off < (unsigned)FD_CAP) list[off] = (uint16_t)(((q * 8 + (bit >> 2)) << 7) | (lane * 4 + (bit & 3)));
+      ++off;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant__ PyrGeom g,
+                                                           const uint8_t* __restrict__ pyr,
+                                                           uint32_t* __restrict__ cand,
+                                                           int32_t* __restrict__ cand_count,
+                                                           uint8_t* __restrict__ cell_hi,
+                                                           int32_t* __restrict__ flags) {
+  __shared__ __align__(16) FdSmem s_all[FD_WARPS];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int item = blockIdx.x * FD_WARPS + wid;
+  if (item >= g.fast_strips) return;  // warps are independent: no CTA-wide barrier below
+  FdSmem& sm = s_all[wid];
   const int b = blockIdx.y;
-  int cell = blockIdx.x;
   int lvl = 0;
-  while (lvl + 1 < g.nlevels && cell >= g.lv[lvl + 1].cell_base) ++lvl;
+  while (lvl + 1 < g.nlevels && item >= g.lv[lvl + 1].fast_strip_base) ++lvl;
   const LevelGeom& L = g.lv[lvl];
-  cell -= L.cell_base;
-  if (L.n_cols <= 0 || cell >= L.n_cols * L.n_rows) return;
-  const int ci = cell / L.n_cols, cj = cell - ci * L.n_cols;
-  const int x0 = kMinBorder + cj * L.w_cell, y0 = kMinBorder + ci * L.h_cell;
-  if (y0 >= L.max_by - 3 || x0 >= L.max_bx - 6) return;  // :806, :815
-  const int cw = min(x0 + L.w_cell + 6, L.max_bx) - x0;
-  const int ch = min(y0 + L.h_cell + 6, L.max_by) - y0;
-  if (cw < 7 || ch < 7) return;  // cv::FAST finds nothing in such a sliver
-
-  if (tid == 0) { n1 = 0; n2 = 0; n3 = 0; n_hi = 0; }
-  // i / cw and i / dw below: multiply by ceil(2^32 / d) (exact for i < 2^32 / d; here i < 4489)
-  const unsigned inv_cw = 0xFFFFFFFFu / (unsigned)cw + 1u;
-  const uint8_t* img = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)y0 * L.pitch + x0;
-  for (int i = tid; i < ch * cw; i += FAST_T) {
-    const int r = (int)__umulhi((unsigned)i, inv_cw), c = i - r * cw;
-    roi[r * RS + c] = __ldg(img + (size_t)r * L.pitch + c);
-  }
-  for (int i = tid; i < ch * (RS / 4); i += FAST_T) reinterpret_cast<uint32_t*>(score)[i] = 0u;
-  __syncthreads();
-
+  item -= L.fast_strip_base;
+  const int sy = item / L.fast_strips_x, sx = item - sy * L.fast_strips_x;
+  const int w = L.w, h = L.h, pitch = L.pitch;
+  constexpr int kEdge = kMinBorder + 3;             // detection domain: kEdge <= x < w-kEdge, kEdge <= y < h-kEdge
+  const int cx0 = kMinBorder - 4 + kFastOwnCols * sx;  // first computed column (word aligned); owned = +4 .. +123
+  const int cy0 = kEdge - 1 + kFastOwnRows * sy;       // first computed row; owned = +1 .. +30
+  const int x_end = w - kEdge, y_end = h - kEdge;
+  const int pw = pitch >> 2;
+  const int xw = (cx0 >> 2) + lane;  // >= 3
+  const int x4 = xw * 4;
+  const int xwc = min(xw, pw - 1), xwm = min(xw - 1, pw - 1), xwp = min(xw + 1, pw - 1);  // clamped words are masked
+  const uint8_t* img = pyr + L.lvl_base + (size_t)b * L.lvl_bytes;
   const int t_lo = min(g.ini_th, g.min_th);
-  const int dw = cw - 6, dh = ch - 6, npx = dw * dh;
-  const unsigned inv_dw = 0xFFFFFFFFu / (unsigned)dw + 1u;
-  // stage 1: quick reject
-  for (int base = 0; base < npx; base += FAST_T) {
-    const int i = base + tid;
-    bool keep = false;
-    int pos = 0;
-    if (i < npx) {
-      const int r = (int)__umulhi((unsigned)i, inv_dw), c = i - r * dw;
-      pos = (r + 3) * RS + (c + 3);
-      const uint8_t* p = roi + pos;
-      const int v = p[0], hi = v + t_lo, lo = v - t_lo;
-      const int a = p[3 * RS], e = p[-3 * RS], f = p[3], h = p[-3];
-      const bool br = (a > hi || e > hi) && (f > hi || h > hi);
-      const bool dk = (a < lo || e < lo) && (f < lo || h < lo);
-      keep = br || dk;
+  const unsigned K = (unsigned)(127 - min(t_lo, 127)) * 0x01010101u;  // a weaker threshold only passes a superset
+  unsigned colmask = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (x4 + k >= kEdge && x4 + k < x_end) colmask |= 0x80u << (8 * k);
+  unsigned* tile_w = reinterpret_cast<unsigned*>(sm.img);
+  unsigned* score_w = reinterpret_cast<unsigned*>(sm.score);
+
+  // ---- 0. stage rows cy0-3 .. cy0+34, columns cx0-4 .. cx0+131 in shared memory (asynchronous copies: all 38 rows
+  // of a lane are in flight together; rows past the image are clamped and only feed masked pixels) ----
+  {
+    const bool edge = lane == 0 || lane == 31;
+    const int xe = lane == 0 ? xwm : xwp, te = lane == 0 ? 0 : FD_TW - 1;
+#pragma unroll
+    for (int j = 0; j < FD_TROWS; ++j) {
+      const unsigned* row = reinterpret_cast<const unsigned*>(img + (size_t)min(cy0 - 3 + j, h - 1) * pitch);
+      cp_async4(tile_w + j * FD_TW + lane + 1, row + xwc);
+      if (edge) cp_async4(tile_w + j * FD_TW + te, row + xe);
     }
-    const int slot = warp_push(keep, &n1);
-    if (slot >= 0) list1[slot] = (uint16_t)pos;
+    cp_async_wait_all();
+    __syncwarp();
   }
-  __syncthreads();
-  // stage 2: corner strength
-  const int c1 = n1;
-  for (int base = 0; base < c1; base += FAST_T) {
-    const int i = base + tid;
-    bool keep = false;
-    int pos = 0;
-    if (i < c1) {
-      pos = list1[i];
-      const int m = corner_strength(roi + pos);
-      if (m > t_lo) { keep = true; score[pos] = (uint8_t)(m - 1); }
+
+  // ---- 1. dense quick reject (branch-free) ----
+  unsigned c[7];   // centre words of the last 7 rows
+  unsigned hf[4];  // horizontal-pair flags of the last 4 rows
+  unsigned acc[4] = {0u, 0u, 0u, 0u};  // survivor bits: nibble (row & 7) of acc[row >> 3], bit = byte of the word
+#pragma unroll
+  for (int j = 0; j < FD_TROWS; ++j) {
+    const unsigned w1 = tile_w[j * FD_TW + lane + 1];
+    c[j % 7] = w1;
+    if (j >= 3 && j < FD_ROWS + 3) {
+      const unsigned w0 = tile_w[j * FD_TW + lane], w2 = tile_w[j * FD_TW + lane + 2];
+      const unsigned pl = __funnelshift_r(w0, w1, 8);   // pixels x-3
+      const unsigned pr = __funnelshift_r(w1, w2, 24);  // pixels x+3
+      hf[j % 4] = swar_gt2(__vabsdiffu4(w1, pl), __vabsdiffu4(w1, pr), K);
     }
-    const int slot = warp_push(keep, &n2);
-    if (slot >= 0) list2[slot] = (uint16_t)pos;
-  }
-  __syncthreads();
-  // stage 3: strict maximum over the 8 neighbours; survivors overwrite list1
-  const int c2 = n2;
-  for (int base = 0; base < c2; base += FAST_T) {
-    const int i = base + tid;
-    bool keep = false;
-    int pos = 0;
-    if (i < c2) {
-      pos = list2[i];
-      const uint8_t* s = score + pos;
-      const int c = s[0];
-      keep = c > s[-1] && c > s[1] && c > s[-RS - 1] && c > s[-RS] && c > s[-RS + 1] && c > s[RS - 1] && c > s[RS] &&
-             c > s[RS + 1];
-      if (keep && c >= g.ini_th) n_hi = 1;  // benign race: all writers store 1
+    if (j >= 6) {
+      const int r = j - 6, y = cy0 + r;
+      score_w[r * 32 + lane] = 0u;
+      const unsigned rm = (y >= kEdge && y < y_end) ? colmask : 0u;
+      const unsigned cc = c[(j - 3) % 7];
+      const unsigned vf = swar_gt2(__vabsdiffu4(cc, c[(j - 6) % 7]), __vabsdiffu4(cc, c[j % 7]), K);
+      put_nibble(acc, r, gather_bit7(vf & hf[(j - 3) % 4] & rm));
     }
-    const int slot = warp_push(keep, &n3);
-    if (slot >= 0) list1[slot] = (uint16_t)pos;
   }
-  __syncthreads();
-  // stage 4: threshold choice + emit
-  const int c3 = n3;
-  if (c3 == 0) return;
-  const int t_emit = n_hi ? g.ini_th : g.min_th;
-  __syncthreads();
-  if (tid == 0) n2 = 0;
-  __syncthreads();
-  for (int base = 0; base < c3; base += FAST_T) {
-    const int i = base + tid;
-    bool keep = false;
-    int pos = 0;
-    if (i < c3) {
-      pos = list1[i];
-      keep = (int)score[pos] >= t_emit;
-    }
-    const int slot = warp_push(keep, &n2);
-    if (slot >= 0) list2[slot] = (uint16_t)pos;
-  }
-  __syncthreads();
-  const int ne = n2;
-#ifdef ORBFE_DEBUG_FAST
-  if (blockIdx.x == 0 && b == 0 && tid == 0) {
-    printf("DBG n1 %d nc %d n3 %d n_hi %d ne %d\n", n1, c2, c3, n_hi, ne);
-    for (int i = 0; i < ne; ++i) printf("DBG emit pos %d -> x %d y %d score %d\n", list2[i], list2[i] % RS, list2[i] / RS, score[list2[i]]);
-  }
-#endif
-  if (ne == 0) return;
-  if (tid == 0) out_base = atomicAdd(&cand_count[b * kMaxLevels + lvl], ne);
-  __syncthreads();
-  const int ob = out_base;
+  int excl;
+  int total = mask_scan(acc, lane, &excl);
+  if (total == 0) return;  // uniform
+  __syncwarp();
+
+  const unsigned inv_w = 0xFFFFFFFFu / (unsigned)L.w_cell + 1u;  // n / d == umulhi(n, inv) for n < 2^32 / d
+  const unsigned inv_h = 0xFFFFFFFFu / (unsigned)L.h_cell + 1u;
   uint32_t* out = cand + (size_t)b * g.cand_total + L.cand_off;
-  for (int i = tid; i < ne; i += FAST_T) {
-    const int pos = list2[i];
-    const int r = (int)__umulhi((unsigned)pos, 0xFFFFFFFFu / RS + 1u), c = pos - r * RS;
-    if (ob + i < L.cand_cap) out[ob + i] = pack_cand(c + cj * L.w_cell, r + ci * L.h_cell, score[pos]);
-    else atomicOr(&flags[b], FLAG_CAND_OVERFLOW);
+  int32_t* out_n = cand_count + b * kMaxLevels + lvl;
+  uint8_t* hi = cell_hi + (size_t)b * g.total_cells + L.cell_base;
+  const unsigned lt = (1u << lane) - 1u;
+
+  // 3. cell-local 3x3 suppression of list[0..n) (owned pixels that have a score) + emit
+  auto suppress_emit = [&](int n) {
+    for (int base = 0; base < n; base += 32) {
+      const int i = base + lane;
+      bool keep = false;
+      int sc = 0, x = 0, y = 0, cell = 0;
+      if (i < n) {
+        const int e = sm.list[i];
+        const int r = e >> 7, cx = e & 127;
+        x = cx0 + cx;
+        y = cy0 + r;
+        const int cj = (int)__umulhi((unsigned)(x - kEdge), inv_w), ci = (int)__umulhi((unsigned)(y - kEdge), inv_h);
+        cell = ci * L.n_cols + cj;
+        // detection window of the pixel's cell (:803-818 minus FAST's 3-px margin)
+        const int wx0 = kEdge + cj * L.w_cell, wx1 = min(wx0 + L.w_cell, x_end);
+        const int wy0 = kEdge + ci * L.h_cell, wy1 = min(wy0 + L.h_cell, y_end);
+        const bool xl = x > wx0, xr = x + 1 < wx1, yu = y > wy0, yd = y + 1 < wy1;
+        const uint8_t* s = sm.score + r * 128 + cx;
+        sc = s[0];
+        // max over the neighbours inside the window (all 8 are inside the computed tile: owned pixels are inset)
+        int nb = max(xl ? (int)s[-1] : 0, xr ? (int)s[1] : 0);
+        const int u0 = s[-129], u1 = s[-128], u2 = s[-127], d0 = s[127], d1 = s[128], d2 = s[129];
+        const int un = max(u1, max(xl ? u0 : 0, xr ? u2 : 0)), dn = max(d1, max(xl ? d0 : 0, xr ? d2 : 0));
+        nb = max(nb, max(yu ? un : 0, yd ? dn : 0));
+        keep = sc > nb;
+      }
+      const unsigned mk = __ballot_sync(0xffffffffu, keep);
+      if (mk == 0u) continue;
+      int ob = 0;
+      if (lane == 0) ob = atomicAdd(out_n, __popc(mk));
+      ob = __shfl_sync(0xffffffffu, ob, 0);
+      if (keep) {
+        const int slot = ob + __popc(mk & lt);
+        if (slot < L.cand_cap) out[slot] = pack_cand(x - kMinBorder, y - kMinBorder, sc);
+        else atomicOr(&flags[b], FLAG_CAND_OVERFLOW);
+        if (sc >= g.ini_th) hi[cell] = 1;
+      }
+    }
+  };
+
+  if (total <= FD_CAP) {
+    // ---- 2. exact corner strength of the survivors -> score tile; owned corners compact in place ----
+    flatten_window(acc, lane, excl, 0, sm.list);
+    __syncwarp();
+    int nc = 0;
+    for (int base = 0; base < total; base += 32) {
+      const int i = base + lane;
+      bool corner = false;
+      int e = 0;
+      if (i < total) {
+        e = sm.list[i];
+        const int r = e >> 7, cx = e & 127;
+        const int m = corner_strength(sm.img + (r + 3) * FD_TS + cx + 4);
+        if (m > t_lo) {
+          sm.score[r * 128 + cx] = (uint8_t)(m - 1);
+          corner = m > 1 && r >= 1 && r <= kFastOwnRows && cx >= 4 && cx < 4 + kFastOwnCols;  // score 0 never wins
+        }
+      }
+      const unsigned mk = __ballot_sync(0xffffffffu, corner);
+      __syncwarp();  // this chunk has been read by every lane before slots <= base+31 are overwritten
+      if (corner) sm.list[nc + __popc(mk & lt)] = (uint16_t)e;
+      nc += __popc(mk);
+    }
+    __syncwarp();
+    suppress_emit(nc);
+    return;
+  }
+
+  // ---- dense strips (more survivors than the list holds): same steps in windows of FD_CAP entries ----
+  for (int lo = 0; lo < total; lo += FD_CAP) {
+    flatten_window(acc, lane, excl, lo, sm.list);
+    __syncwarp();
+    const int nwin = min(FD_CAP, total - lo);
+    for (int i = lane; i < nwin; i += 32) {
+      const int e = sm.list[i];
+      const int r = e >> 7, cx = e & 127;
+      const int m = corner_strength(sm.img + (r + 3) * FD_TS + cx + 4);
+      if (m > t_lo) sm.score[r * 128 + cx] = (uint8_t)(m - 1);
+    }
+    __syncwarp();
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) acc[q] = 0u;
+  if (lane >= 1 && lane <= 30) {  // owned columns 4 .. 123
+#pragma unroll
+    for (int r = 1; r <= kFastOwnRows; ++r) {
+      const unsigned v = score_w[r * 32 + lane];
+      put_nibble(acc, r, gather_bit7(((v & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | v));  // bytes != 0
+    }
+  }
+  total = mask_scan(acc, lane, &excl);
+  for (int lo = 0; lo < total; lo += FD_CAP) {
+    flatten_window(acc, lane, excl, lo, sm.list);
+    __syncwarp();
+    suppress_emit(min(FD_CAP, total - lo));
+    __syncwarp();
   }
 }
 
 void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
-  dim3 grid(g.total_cells, batch);
-  fast_cells_kernel<<<grid, FAST_T, 0, s>>>(g, a.pyr, a.cand, a.cand_count, a.flags);
+  if (g.fast_strips <= 0) return;
+  cudaMemsetAsync(a.cell_hi, 0, (size_t)batch * g.total_cells, s);
+  dim3 grid((g.fast_strips + FD_WARPS - 1) / FD_WARPS, batch);
+  fast_detect_kernel<<<grid, FD_T, 0, s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi, a.flags);
 }
 
 }  // namespace orbfe

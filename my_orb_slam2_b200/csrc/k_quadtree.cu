@@ -86,14 +86,13 @@ __device__ __forceinline__ int quadrant(const int4 bx, int x, int y) {
 }
 
 __global__ void __launch_bounds__(QT_T) quadtree_kernel(const __grid_constant__ PyrGeom g,
-                                                        const uint32_t* __restrict__ cand,
-                                                        uint16_t* __restrict__ node_of,
-                                                        const int32_t* __restrict__ cand_count,
+                                                        uint32_t* cand, const uint8_t* __restrict__ cell_hi,
+                                                        uint16_t* __restrict__ node_of, int32_t* cand_count,
                                                         uint32_t* __restrict__ kept, int32_t* __restrict__ kept_count,
                                                         int32_t* __restrict__ flags) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int wtmp[32];
-  __shared__ int s_misc[4];  // 0: first rank reaching N (phase 2), 1: children with count > 1
+  __shared__ int s_misc[4];  // 0: first rank reaching N (phase 2), 1: children with count > 1, 2: filtered candidates
 
   const int tid = threadIdx.x;
   const int lvl = blockIdx.x, b = blockIdx.y;
@@ -105,6 +104,38 @@ __global__ void __launch_bounds__(QT_T) quadtree_kernel(const __grid_constant__ 
   if (n <= 0 || L.n_cols <= 0) {
     if (tid == 0) kept_count[b * kMaxLevels + lvl] = 0;
     return;
+  }
+  uint32_t* ck = cand + (size_t)b * g.cand_total + L.cand_off;
+  // ---- the per-cell threshold choice (:830-837): k_fast.cu appended every cell-local maximum with score >=
+  // min(iniTh, minTh); a cell that has a maximum >= iniTh keeps only those, any other cell keeps those >= minTh.
+  // Compacted in place, chunk by chunk (a chunk is read completely before anything is written into it). ----
+  {
+    const uint8_t* hi = cell_hi + (size_t)b * g.total_cells + L.cell_base;
+    if (tid == 0) s_misc[2] = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += QT_T) {
+      const int k = base + tid;
+      uint32_t c = 0;
+      bool keep = false;
+      if (k < n) {
+        c = ck[k];
+        const int cell = ((cand_y(c) - 3) / L.h_cell) * L.n_cols + (cand_x(c) - 3) / L.w_cell;
+        keep = cand_score(c) >= (hi[cell] ? g.ini_th : g.min_th);
+      }
+      __syncthreads();
+      const unsigned mk = __ballot_sync(0xffffffffu, keep);
+      int slot = 0;
+      if ((tid & 31) == 0 && mk) slot = atomicAdd(&s_misc[2], __popc(mk));
+      slot = __shfl_sync(0xffffffffu, slot, 0) + __popc(mk & ((1u << (tid & 31)) - 1u));
+      if (keep) ck[slot] = c;
+    }
+    __syncthreads();
+    n = s_misc[2];
+    if (tid == 0) cand_count[b * kMaxLevels + lvl] = n;
+    if (n <= 0) {
+      if (tid == 0) kept_count[b * kMaxLevels + lvl] = 0;
+      return;
+    }
   }
   QtSmem sm;
   {
@@ -122,7 +153,6 @@ __global__ void __launch_bounds__(QT_T) quadtree_kernel(const __grid_constant__ 
     sm.elist = reinterpret_cast<int*>(p); p += (size_t)C * 4;
     sm.vis = reinterpret_cast<int*>(p);
   }
-  const uint32_t* ck = cand + (size_t)b * g.cand_total + L.cand_off;
   uint16_t* nk = node_of + (size_t)b * g.cand_total + L.cand_off;
 
   // ---- roots (:543-583) ----
@@ -311,7 +341,7 @@ int configure_kernels(const PyrGeom& g) {
 
 void launch_quadtree(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
   dim3 grid(g.nlevels, batch);
-  quadtree_kernel<<<grid, QT_T, quadtree_smem_bytes(g.max_node_cap), s>>>(g, a.cand, a.node_of, a.cand_count, a.kept,
+  quadtree_kernel<<<grid, QT_T, quadtree_smem_bytes(g.max_node_cap), s>>>(g, a.cand, a.cell_hi, a.node_of, a.cand_count, a.kept,
                                                                           a.kept_count, a.flags);
 }
 

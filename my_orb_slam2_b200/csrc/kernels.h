@@ -17,6 +17,7 @@ struct ExtractorArena {
   uint32_t* cand = nullptr;        // [batch][cand_total]
   uint16_t* node_of = nullptr;     // [batch][cand_total]
   int32_t* cand_count = nullptr;   // [batch][kMaxLevels]
+  uint8_t* cell_hi = nullptr;      // [batch][total_cells] cell has a FAST maximum with score >= iniThFAST
   uint32_t* kept = nullptr;        // [batch][kept_total]
   int32_t* kept_count = nullptr;   // [batch][kMaxLevels]
   orbfe_keypoint* out_kp = nullptr;  // [batch][out_cap]
@@ -38,7 +39,8 @@ enum : int { FLAG_CAND_OVERFLOW = 1, FLAG_NODE_OVERFLOW = 2, FLAG_OUT_OVERFLOW =
 
 // ComputePyramid (src/ORBextractor.cc:1129-1154): level `lvl` from level lvl-1 for `batch` images
 void launch_pyramid_level(const PyrGeom& g, const ExtractorArena& a, int lvl, int batch, cudaStream_t s);
-// cell loop of ComputeKeyPointsOctTree (:776-850): FAST + cell-local NMS + per-cell threshold fallback
+// cell loop of ComputeKeyPointsOctTree (:776-850): FAST + cell-local NMS; the per-cell threshold fallback is applied
+// by the quadtree kernel when it reads the candidates
 void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
 // DistributeOctTree (:539-765): one CTA per (level, image)
 void launch_quadtree(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
