@@ -48,7 +48,7 @@ constexpr int FD_ROWS = 32;             // computed rows per strip (kFastOwnRows
 constexpr int FD_TROWS = FD_ROWS + 6;   // image tile rows (FAST ring: +-3)
 constexpr int FD_TS = 136;              // image tile stride in bytes: columns -4 .. 131 of the strip
 constexpr int FD_TW = FD_TS / 4;
-constexpr int FD_CAP = 1024;            // list entries per pass
+constexpr int FD_CAP = 2048;            // list entries per pass (a strip with more survivors takes several passes)
 
 struct FdSmem {
   uint8_t img[FD_TROWS * FD_TS];
@@ -120,17 +120,21 @@ __device__ __forceinline__ int mask_scan(const unsigned (&acc)[4], int lane, int
   return __shfl_sync(0xffffffffu, incl, 31);
 }
 
-// write the entries (row<<7 | column) whose flat index lies in [lo, lo+FD_CAP) into list[index - lo]
+// write the entries (row<<7 | column) whose flat index lies in [lo, lo+FD_CAP) into list[index - lo]; WINDOWED=false
+// when the whole list fits (no range check).  Fully unrolled and predicated: no data-dependent loop.
+template <bool WINDOWED>
 __device__ __forceinline__ void flatten_window(const unsigned (&acc)[4], int lane, int excl, int lo, uint16_t* list) {
   int off = excl - lo;
+  const int col = lane * 4;
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    unsigned a = acc[q];
-    while (a) {
-      const int bit = __ffs(a) - 1;
-      a &= a - 1;
-      if ((unsigned)off < (unsigned)FD_CAP) list[off] = (uint16_t)(((q * 8 + (bit >> 2)) << 7) | (lane * 4 + (bit & 3)));
-      ++off;
+  for (int r = 0; r < FD_ROWS; ++r) {
+    const unsigned a = acc[r >> 3] >> (4 * (r & 7));
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (a & (1u << k)) {
+        if (!WINDOWED || (unsigned)off < (unsigned)FD_CAP) list[off] = (uint16_t)((r << 7) | (col + k));
+        ++off;
+      }
     }
   }
 }
@@ -141,7 +145,8 @@ __global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant
                                                            int32_t* __restrict__ cand_count,
                                                            uint8_t* __restrict__ cell_hi,
                                                            int32_t* __restrict__ flags) {
-  __shared__ __align__(16) FdSmem s_all[FD_WARPS];
+  extern __shared__ __align__(16) unsigned char fd_smem_raw[];
+  FdSmem* s_all = reinterpret_cast<FdSmem*>(fd_smem_raw);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   int item = blockIdx.x * FD_WARPS + wid;
   if (item >= g.fast_strips) return;  // warps are independent: no CTA-wide barrier below
@@ -263,7 +268,7 @@ __global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant
 
   if (total <= FD_CAP) {
     // ---- 2. exact corner strength of the survivors -> score tile; owned corners compact in place ----
-    flatten_window(acc, lane, excl, 0, sm.list);
+    flatten_window<false>(acc, lane, excl, 0, sm.list);
     __syncwarp();
     int nc = 0;
     for (int base = 0; base < total; base += 32) {
@@ -291,7 +296,7 @@ __global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant
 
   // ---- dense strips (more survivors than the list holds): same steps in windows of FD_CAP entries ----
   for (int lo = 0; lo < total; lo += FD_CAP) {
-    flatten_window(acc, lane, excl, lo, sm.list);
+    flatten_window<true>(acc, lane, excl, lo, sm.list);
     __syncwarp();
     const int nwin = min(FD_CAP, total - lo);
     for (int i = lane; i < nwin; i += 32) {
@@ -313,18 +318,23 @@ __global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant
   }
   total = mask_scan(acc, lane, &excl);
   for (int lo = 0; lo < total; lo += FD_CAP) {
-    flatten_window(acc, lane, excl, lo, sm.list);
+    flatten_window<true>(acc, lane, excl, lo, sm.list);
     __syncwarp();
     suppress_emit(min(FD_CAP, total - lo));
     __syncwarp();
   }
 }
 
+int configure_fast_kernel() {
+  return cudaFuncSetAttribute(fast_detect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)(FD_WARPS * sizeof(FdSmem))) == cudaSuccess ? 0 : -1;
+}
+
 void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
   if (g.fast_strips <= 0) return;
   cudaMemsetAsync(a.cell_hi, 0, (size_t)batch * g.total_cells, s);
   dim3 grid((g.fast_strips + FD_WARPS - 1) / FD_WARPS, batch);
-  fast_detect_kernel<<<grid, FD_T, 0, s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi, a.flags);
+  fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi, a.flags);
 }
 
 }  // namespace orbfe
