@@ -80,6 +80,12 @@ int orbfe_extract_run(orbfe_extractor* e, int batch);
 int orbfe_extract_download(orbfe_extractor* e, int batch, orbfe_keypoint* keypoints, uint8_t* descriptors,
                            int capacity, int32_t* counts);
 int orbfe_extractor_sync(orbfe_extractor* e);
+/* download without waiting: the copies are queued on the handle's stream (use pinned host memory so they overlap other
+ * streams' kernels); orbfe_extract_finish waits for them and performs the overflow / capacity checks of the
+ * synchronous call.  The host arrays must stay valid until then. */
+int orbfe_extract_download_async(orbfe_extractor* e, int batch, orbfe_keypoint* keypoints, uint8_t* descriptors,
+                                 int capacity, int32_t* counts);
+int orbfe_extract_finish(orbfe_extractor* e);
 /* Make `e` issue its work on `other`'s stream from now on (e.g. the left and right extractor of a stereo rig in
  * throughput mode: one in-order stream, no cross-stream events).  `other` must outlive `e`'s use of it. */
 int orbfe_extractor_share_stream(orbfe_extractor* e, orbfe_extractor* other);
@@ -131,6 +137,9 @@ int orbfe_stereo_match(orbfe_extractor* left, orbfe_extractor* right, int batch,
 int orbfe_stereo_match_run(orbfe_extractor* left, orbfe_extractor* right, int batch, float mbf, float mb);
 int orbfe_stereo_match_download(orbfe_extractor* left, int batch, float* u_right, float* depth, int capacity,
                                 int32_t* n_matched);
+/* ... without waiting (complete after orbfe_extractor_sync / orbfe_extract_finish on `left`). */
+int orbfe_stereo_match_download_async(orbfe_extractor* left, int batch, float* u_right, float* depth, int capacity,
+                                      int32_t* n_matched);
 
 /* ------------------------------------------------------------------ */
 /* ORBmatcher  (include/ORBmatcher.h:45-114, src/ORBmatcher.cc)        */

@@ -433,8 +433,8 @@ int orbfe_extractor_stage_times(orbfe_extractor* h, float* ms, int32_t* runs, in
   return ORBFE_OK;
 }
 
-int orbfe_extract_download(orbfe_extractor* h, int batch, orbfe_keypoint* keypoints, uint8_t* descriptors,
-                           int capacity, int32_t* counts) {
+int orbfe_extract_download_async(orbfe_extractor* h, int batch, orbfe_keypoint* keypoints, uint8_t* descriptors,
+                                 int capacity, int32_t* counts) {
   ORBFE_ARG(h && counts && capacity >= 0);
   Extractor* e = reinterpret_cast<Extractor*>(h);
   ORBFE_ARG(batch >= 1 && batch <= e->max_batch);
@@ -460,12 +460,34 @@ int orbfe_extract_download(orbfe_extractor* h, int batch, orbfe_keypoint* keypoi
       ORBFE_CUDA(cudaMemcpy2DAsync(descriptors, (size_t)capacity * 32, a.out_desc, (size_t)g.out_cap * 32,
                                    (size_t)ncopy * 32, batch, cudaMemcpyDeviceToHost, e->stream));
   }
+  e->pending_counts = counts;
+  e->pending_batch = batch;
+  e->pending_capacity = capacity;
+  return ORBFE_OK;
+}
+
+int orbfe_extract_finish(orbfe_extractor* h) {
+  ORBFE_ARG(h);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  DeviceGuard guard(e->device);
   ORBFE_CUDA(cudaStreamSynchronize(e->stream));
+  const int32_t* counts = e->pending_counts;
+  const int batch = e->pending_batch, capacity = e->pending_capacity;
+  e->pending_counts = nullptr;
+  e->pending_batch = 0;
+  if (!counts) return ORBFE_OK;
   for (int b = 0; b < batch; ++b) {
     if (e->h_flags[b]) { set_error("image %d: internal slab overflow (flags=%d)", b, e->h_flags[b]); return ORBFE_ERR_CAPACITY; }
     if (counts[b] > capacity) { set_error("image %d: %d keypoints > capacity %d", b, counts[b], capacity); return ORBFE_ERR_CAPACITY; }
   }
   return ORBFE_OK;
+}
+
+int orbfe_extract_download(orbfe_extractor* h, int batch, orbfe_keypoint* keypoints, uint8_t* descriptors,
+                           int capacity, int32_t* counts) {
+  const int rc = orbfe_extract_download_async(h, batch, keypoints, descriptors, capacity, counts);
+  if (rc != ORBFE_OK) return rc;
+  return orbfe_extract_finish(h);
 }
 
 int orbfe_extract_batch(orbfe_extractor* h, const uint8_t* images, size_t image_stride, int row_stride, int batch,

@@ -23,6 +23,9 @@ struct Extractor {
   int32_t* h_flags = nullptr;   // pinned
   int64_t launches = 0;
   int last_batch = 0;
+  // host side of an orbfe_extract_download_async not yet finished (counts are checked by orbfe_extract_finish)
+  const int32_t* pending_counts = nullptr;
+  int pending_batch = 0, pending_capacity = 0;
   // optional per-stage CUDA-event timing (bench.py roofline): ring of runs x (kStages+1) events
   static constexpr int kStages = 7;   // pyramid, fast, quadtree, blur, describe, stereo match, stereo median
   static constexpr int kProfRuns = 256;

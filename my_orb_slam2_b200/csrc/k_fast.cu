@@ -42,7 +42,7 @@
 
 namespace orbfe {
 
-constexpr int FD_WARPS = 4;             // independent warps per CTA
+constexpr int FD_WARPS = 2;             // independent warps per CTA (small CTAs: a slot frees as soon as 2 strips end)
 constexpr int FD_T = FD_WARPS * 32;
 constexpr int FD_ROWS = 32;             // computed rows per strip (kFastOwnRows owned)
 constexpr int FD_TROWS = FD_ROWS + 6;   // image tile rows (FAST ring: +-3)
@@ -226,25 +226,25 @@ __global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant
   uint8_t* hi = cell_hi + (size_t)b * g.total_cells + L.cell_base;
   const unsigned lt = (1u << lane) - 1u;
 
-  // 3. cell-local 3x3 suppression of list[0..n) (owned pixels that have a score) + emit
+  // 3. cell-local 3x3 suppression of list[0..n) (owned pixels that have a score); the maxima compact in place, then
+  // ONE atomicAdd reserves their slots in the level's candidate list
   auto suppress_emit = [&](int n) {
+    int nmax = 0;
     for (int base = 0; base < n; base += 32) {
       const int i = base + lane;
       bool keep = false;
-      int sc = 0, x = 0, y = 0, cell = 0;
+      int e = 0;
       if (i < n) {
-        const int e = sm.list[i];
+        e = sm.list[i];
         const int r = e >> 7, cx = e & 127;
-        x = cx0 + cx;
-        y = cy0 + r;
+        const int x = cx0 + cx, y = cy0 + r;
         const int cj = (int)__umulhi((unsigned)(x - kEdge), inv_w), ci = (int)__umulhi((unsigned)(y - kEdge), inv_h);
-        cell = ci * L.n_cols + cj;
         // detection window of the pixel's cell (:803-818 minus FAST's 3-px margin)
         const int wx0 = kEdge + cj * L.w_cell, wx1 = min(wx0 + L.w_cell, x_end);
         const int wy0 = kEdge + ci * L.h_cell, wy1 = min(wy0 + L.h_cell, y_end);
         const bool xl = x > wx0, xr = x + 1 < wx1, yu = y > wy0, yd = y + 1 < wy1;
         const uint8_t* s = sm.score + r * 128 + cx;
-        sc = s[0];
+        const int sc = s[0];
         // max over the neighbours inside the window (all 8 are inside the computed tile: owned pixels are inset)
         int nb = max(xl ? (int)s[-1] : 0, xr ? (int)s[1] : 0);
         const int u0 = s[-129], u1 = s[-128], u2 = s[-127], d0 = s[127], d1 = s[128], d2 = s[129];
@@ -253,15 +253,25 @@ __global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant
         keep = sc > nb;
       }
       const unsigned mk = __ballot_sync(0xffffffffu, keep);
-      if (mk == 0u) continue;
-      int ob = 0;
-      if (lane == 0) ob = atomicAdd(out_n, __popc(mk));
-      ob = __shfl_sync(0xffffffffu, ob, 0);
-      if (keep) {
-        const int slot = ob + __popc(mk & lt);
-        if (slot < L.cand_cap) out[slot] = pack_cand(x - kMinBorder, y - kMinBorder, sc);
-        else atomicOr(&flags[b], FLAG_CAND_OVERFLOW);
-        if (sc >= g.ini_th) hi[cell] = 1;
+      __syncwarp();  // this chunk has been read by every lane before slots <= base+31 are overwritten
+      if (keep) sm.list[nmax + __popc(mk & lt)] = (uint16_t)e;
+      nmax += __popc(mk);
+    }
+    if (nmax == 0) return;
+    __syncwarp();
+    int ob = 0;
+    if (lane == 0) ob = atomicAdd(out_n, nmax);
+    ob = __shfl_sync(0xffffffffu, ob, 0);
+    for (int i = lane; i < nmax; i += 32) {
+      const int e = sm.list[i];
+      const int r = e >> 7, cx = e & 127;
+      const int x = cx0 + cx, y = cy0 + r;
+      const int sc = sm.score[r * 128 + cx];
+      if (ob + i < L.cand_cap) out[ob + i] = pack_cand(x - kMinBorder, y - kMinBorder, sc);
+      else atomicOr(&flags[b], FLAG_CAND_OVERFLOW);
+      if (sc >= g.ini_th) {
+        const int cj = (int)__umulhi((unsigned)(x - kEdge), inv_w), ci = (int)__umulhi((unsigned)(y - kEdge), inv_h);
+        hi[ci * L.n_cols + cj] = 1;
       }
     }
   };

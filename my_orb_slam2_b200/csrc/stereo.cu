@@ -36,8 +36,8 @@ int orbfe_stereo_match_run(orbfe_extractor* hl, orbfe_extractor* hr, int batch, 
   return ORBFE_OK;
 }
 
-int orbfe_stereo_match_download(orbfe_extractor* hl, int batch, float* u_right, float* depth, int capacity,
-                                int32_t* n_matched) {
+int orbfe_stereo_match_download_async(orbfe_extractor* hl, int batch, float* u_right, float* depth, int capacity,
+                                      int32_t* n_matched) {
   ORBFE_ARG(hl && capacity >= 0);
   Extractor* l = reinterpret_cast<Extractor*>(hl);
   ORBFE_ARG(batch >= 1 && batch <= l->max_batch);
@@ -52,6 +52,15 @@ int orbfe_stereo_match_download(orbfe_extractor* hl, int batch, float* u_right, 
                                  batch, cudaMemcpyDeviceToHost, l->stream));
   if (n_matched)
     ORBFE_CUDA(cudaMemcpyAsync(n_matched, l->arena.st_count, (size_t)batch * 4, cudaMemcpyDeviceToHost, l->stream));
+  return ORBFE_OK;
+}
+
+int orbfe_stereo_match_download(orbfe_extractor* hl, int batch, float* u_right, float* depth, int capacity,
+                                int32_t* n_matched) {
+  const int rc = orbfe_stereo_match_download_async(hl, batch, u_right, depth, capacity, n_matched);
+  if (rc != ORBFE_OK) return rc;
+  Extractor* l = reinterpret_cast<Extractor*>(hl);
+  DeviceGuard guard(l->device);
   ORBFE_CUDA(cudaStreamSynchronize(l->stream));
   return ORBFE_OK;
 }

@@ -82,6 +82,9 @@ SYMBOLS = {
     "orbfe_extract_run": (_I, [_P, _I]),
     "orbfe_extract_download": (_I, [_P, _I, _P, _P, _I, _P]),
     "orbfe_extractor_sync": (_I, [_P]),
+    "orbfe_extract_download_async": (_I, [_P, _I, _P, _P, _I, _P]),
+    "orbfe_extract_finish": (_I, [_P]),
+    "orbfe_stereo_match_download_async": (_I, [_P, _I, _P, _P, _I, _P]),
     "orbfe_extractor_share_stream": (_I, [_P, _P]),
     "orbfe_extractor_stream": (_P, [_P]),
     "orbfe_extractor_launch_count": (C.c_int64, [_P]),
