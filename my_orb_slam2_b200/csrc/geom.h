@@ -9,8 +9,8 @@ namespace orbfe {
 
 constexpr int kMinBorder = 16;   // EDGE_THRESHOLD-3 (src/ORBextractor.cc:785)
 constexpr int kMaxLevels = 16;
-constexpr int kFastOwnCols = 120;  // k_fast.cu: a strip computes 128 x 32 pixels and owns the inner 120 x 30
-constexpr int kFastOwnRows = 30;
+constexpr int kFastOwnCols = 120;  // k_fast.cu: a strip computes 128 x (rows+2) pixels and owns the inner 120 x rows
+constexpr int kFastOwnRows = 14;
 
 struct LevelGeom {
   int w, h, pitch;          // level image; pitch multiple of 128

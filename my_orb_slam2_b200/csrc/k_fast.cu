@@ -44,11 +44,13 @@ namespace orbfe {
 
 constexpr int FD_WARPS = 2;             // independent warps per CTA (small CTAs: a slot frees as soon as 2 strips end)
 constexpr int FD_T = FD_WARPS * 32;
-constexpr int FD_ROWS = 32;             // computed rows per strip (kFastOwnRows owned)
+constexpr int FD_ROWS = kFastOwnRows + 2;  // computed rows per strip (multiple of 8)
+constexpr int FD_ACC = FD_ROWS / 8;     // 32-bit survivor masks per lane (8 rows x 4 pixels each)
+static_assert(FD_ROWS % 8 == 0 && FD_ROWS <= 32, "strip rows");
 constexpr int FD_TROWS = FD_ROWS + 6;   // image tile rows (FAST ring: +-3)
 constexpr int FD_TS = 136;              // image tile stride in bytes: columns -4 .. 131 of the strip
 constexpr int FD_TW = FD_TS / 4;
-constexpr int FD_CAP = 2048;            // list entries per pass (a strip with more survivors takes several passes)
+constexpr int FD_CAP = FD_ROWS * 64;            // list entries per pass (a strip with more survivors takes several passes)
 
 struct FdSmem {
   uint8_t img[FD_TROWS * FD_TS];
@@ -102,14 +104,16 @@ __device__ __forceinline__ unsigned swar_gt2(unsigned x, unsigned y, unsigned K)
 __device__ __forceinline__ unsigned gather_bit7(unsigned m) { return (m & 0x80808080u) * 0x00204081u; }
 
 // nibble (r & 7) of acc[r >> 3] := bits 28..31 of nib  (r is a compile-time constant after unrolling)
-__device__ __forceinline__ void put_nibble(unsigned (&acc)[4], int r, unsigned nib) {
+__device__ __forceinline__ void put_nibble(unsigned (&acc)[FD_ACC], int r, unsigned nib) {
   const int q = r & 7;
   acc[r >> 3] |= (q == 7) ? (nib & 0xF0000000u) : ((nib >> (28 - 4 * q)) & (0xFu << (4 * q)));
 }
 
 // exclusive prefix over the lanes of the per-lane set-bit counts; returns the warp total
-__device__ __forceinline__ int mask_scan(const unsigned (&acc)[4], int lane, int* excl) {
-  const int cnt = __popc(acc[0]) + __popc(acc[1]) + __popc(acc[2]) + __popc(acc[3]);
+__device__ __forceinline__ int mask_scan(const unsigned (&acc)[FD_ACC], int lane, int* excl) {
+  int cnt = 0;
+#pragma unroll
+  for (int q = 0; q < FD_ACC; ++q) cnt += __popc(acc[q]);
   int incl = cnt;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -123,7 +127,7 @@ __device__ __forceinline__ int mask_scan(const unsigned (&acc)[4], int lane, int
 // write the entries (row<<7 | column) whose flat index lies in [lo, lo+FD_CAP) into list[index - lo]; WINDOWED=false
 // when the whole list fits (no range check).  Fully unrolled and predicated: no data-dependent loop.
 template <bool WINDOWED>
-__device__ __forceinline__ void flatten_window(const unsigned (&acc)[4], int lane, int excl, int lo, uint16_t* list) {
+__device__ __forceinline__ void flatten_window(const unsigned (&acc)[FD_ACC], int lane, int excl, int lo, uint16_t* list) {
   int off = excl - lo;
   const int col = lane * 4;
 #pragma unroll
@@ -139,7 +143,7 @@ __device__ __forceinline__ void flatten_window(const unsigned (&acc)[4], int lan
   }
 }
 
-__global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant__ PyrGeom g,
+__global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_constant__ PyrGeom g,
                                                            const uint8_t* __restrict__ pyr,
                                                            uint32_t* __restrict__ cand,
                                                            int32_t* __restrict__ cand_count,
@@ -194,7 +198,9 @@ __global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant
   // ---- 1. dense quick reject (branch-free) ----
   unsigned c[7];   // centre words of the last 7 rows
   unsigned hf[4];  // horizontal-pair flags of the last 4 rows
-  unsigned acc[4] = {0u, 0u, 0u, 0u};  // survivor bits: nibble (row & 7) of acc[row >> 3], bit = byte of the word
+  unsigned acc[FD_ACC];  // survivor bits: nibble (row & 7) of acc[row >> 3], bit = byte of the word
+#pragma unroll
+  for (int q = 0; q < FD_ACC; ++q) acc[q] = 0u;
 #pragma unroll
   for (int j = 0; j < FD_TROWS; ++j) {
     const unsigned w1 = tile_w[j * FD_TW + lane + 1];
@@ -318,7 +324,7 @@ __global__ void __launch_bounds__(FD_T) fast_detect_kernel(const __grid_constant
     __syncwarp();
   }
 #pragma unroll
-  for (int q = 0; q < 4; ++q) acc[q] = 0u;
+  for (int q = 0; q < FD_ACC; ++q) acc[q] = 0u;
   if (lane >= 1 && lane <= 30) {  // owned columns 4 .. 123
 #pragma unroll
     for (int r = 1; r <= kFastOwnRows; ++r) {
