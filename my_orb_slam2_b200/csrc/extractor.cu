@@ -169,6 +169,17 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
       L.xtab_off = (int)xt.size();
       L.ytab_off = (int)yt.size();
       build_resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, L.w, L.h, xt, yt);
+      // k_pyramid.cu's word-based kernel needs the taps of pixels x4..x4+3 at bytes <= 8 of (sx0(x4) & ~3), and b >= 0
+      L.resize_fast = 1;
+      for (int x4 = 0; x4 < L.w; x4 += 4) {
+        const int ws = xt[L.xtab_off + x4].sx0 & ~3;
+        for (int k = 0; k < 4 && x4 + k < L.w; ++k) {
+          const XTab& t = xt[L.xtab_off + x4 + k];
+          if (t.sx0 - ws > 7 || t.sx0 - ws < 0 || (t.a1 != 0 && t.sx1 != t.sx0 + 1) || t.a0 < 0 || t.a1 < 0) L.resize_fast = 0;
+        }
+      }
+      for (int y = 0; y < L.h; ++y)
+        if (yt[L.ytab_off + y].b0 < 0 || yt[L.ytab_off + y].b1 < 0) L.resize_fast = 0;
     }
   }
   g.total_cells = cells;

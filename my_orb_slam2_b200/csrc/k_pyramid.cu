@@ -2,15 +2,23 @@
 //
 // Level l is cv::resize(level l-1, INTER_LINEAR) in OpenCV's 11-bit fixed point
 // (SURVEY.md A.1); the 19 px copyMakeBorder frame is not materialised (A.5).
-// HBM-bound integer stencil: each thread produces 4 horizontally adjacent
-// destination pixels (one uchar4 store); the two source rows it needs are read
-// through the read-only path.  Coefficients come from per-level tables built on
-// the host exactly as OpenCV builds them.
+// Coefficients come from per-level tables built on the host exactly as OpenCV
+// builds them.
+//
+// pyramid_level_kernel (the normal path, scale < ~1.3): a thread produces 4
+// adjacent destination pixels x 8 destination rows.  The horizontal pass of a
+// source row is 3 aligned word loads (the 4 pixels' taps lie within 9 bytes of
+// an aligned address), and per pixel one funnel shift that brings its two taps
+// into the low bytes + one DP2A with the packed (a0, a1) weights; it is computed
+// once per source row and reused by the destination rows that share it (the
+// vertical pass walks down the column: consecutive rows share a source row).
+// The vertical pass is two IMAD.HI per pixel.  One 32-bit store per 4 pixels.
+// pyramid_level_generic_kernel: byte loads through the tables, any scale factor.
 #include "kernels.h"
 
 namespace orbfe {
 
-__global__ void __launch_bounds__(256) pyramid_level_kernel(const __grid_constant__ PyrGeom g, uint8_t* __restrict__ pyr,
+__global__ void __launch_bounds__(256) pyramid_level_generic_kernel(const __grid_constant__ PyrGeom g, uint8_t* __restrict__ pyr,
                                                             const XTab* __restrict__ xtab,
                                                             const YTab* __restrict__ ytab, int lvl) {
   const LevelGeom& D = g.lv[lvl];
@@ -45,11 +53,95 @@ __global__ void __launch_bounds__(256) pyramid_level_kernel(const __grid_constan
   }
 }
 
+constexpr int PY_ROWS = 8;   // destination rows per thread
+constexpr int PY_WARPS = 4;  // warps per CTA, stacked vertically: a CTA covers 128 x 32 destination pixels
+
+__global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __grid_constant__ PyrGeom g,
+                                                                      uint8_t* __restrict__ pyr,
+                                                                      const XTab* __restrict__ xtab,
+                                                                      const YTab* __restrict__ ytab, int lvl) {
+  const LevelGeom& D = g.lv[lvl];
+  const LevelGeom& S = g.lv[lvl - 1];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int x4 = (blockIdx.x * 32 + lane) * 4;
+  const int y0 = (blockIdx.y * PY_WARPS + wid) * PY_ROWS;
+  const int b = blockIdx.z;
+  if (x4 >= D.w || y0 >= D.h) return;
+  const uint8_t* src = pyr + S.lvl_base + (size_t)b * S.lvl_bytes;
+  uint8_t* dst = pyr + D.lvl_base + (size_t)b * D.lvl_bytes;
+  // per-pixel taps: bytes o, o+1 of the 12-byte window at ws (o <= 7, checked on the host: LevelGeom::resize_fast)
+  const XTab* xt = xtab + D.xtab_off;
+  const int ws = __ldg(&xt[x4].sx0) & ~3;
+  unsigned a01[4];
+  int sh[4];
+  bool hiw[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int xi = min(x4 + k, D.w - 1);  // pixels past the row end are computed and dropped
+    const int o = __ldg(&xt[xi].sx0) - ws;
+    a01[k] = __ldg(reinterpret_cast<const unsigned*>(&xt[xi].a0));  // a0 | a1 << 16
+    hiw[k] = o >= 4;
+    sh[k] = (o & 3) * 8;
+  }
+  auto hrow = [&](int sy, unsigned (&h)[4]) {
+    const unsigned* p = reinterpret_cast<const unsigned*>(src + (size_t)sy * S.pitch + ws);
+    const unsigned w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const unsigned taps = __funnelshift_r(hiw[k] ? w1 : w0, hiw[k] ? w2 : w1, sh[k]);  // bytes: S[sx0], S[sx0+1], ..
+      h[k] = __dp2a_lo(a01[k], taps, 0u) >> 4;                                           // (S0*a0 + S1*a1) >> 4
+    }
+  };
+  int cur0 = -1, cur1 = -1;
+  unsigned h0[4] = {0u, 0u, 0u, 0u}, h1[4] = {0u, 0u, 0u, 0u};
+  const YTab* yt = ytab + D.ytab_off;
+#pragma unroll 1
+  for (int r = 0; r < PY_ROWS; ++r) {
+    const int y = y0 + r;
+    if (y >= D.h) break;
+    const int sy0 = __ldg(&yt[y].sy0), sy1 = __ldg(&yt[y].sy1);
+    const unsigned b01 = __ldg(reinterpret_cast<const unsigned*>(&yt[y].b0));
+    // all conditions below are warp-uniform (they depend on y only)
+    if (sy0 != cur0) {
+      if (sy0 == cur1) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) h0[k] = h1[k];
+      } else {
+        hrow(sy0, h0);
+      }
+      cur0 = sy0;
+    }
+    if (sy1 != cur1) {
+      if (sy1 == cur0) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) h1[k] = h0[k];
+      } else {
+        hrow(sy1, h1);
+      }
+      cur1 = sy1;
+    }
+    const unsigned b0s = b01 << 16, b1s = b01 & 0xFFFF0000u;  // b << 16: umulhi(b << 16, h) == (b * h) >> 16
+    unsigned out = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const unsigned v = (__umulhi(b0s, h0[k]) + __umulhi(b1s, h1[k]) + 2u) >> 2;
+      out |= v << (8 * k);
+    }
+    uint8_t* d = dst + (size_t)y * D.pitch + x4;
+    *reinterpret_cast<unsigned*>(d) = out;  // pitch is a multiple of 128: the padding bytes may be written
+  }
+}
+
 void launch_pyramid_level(const PyrGeom& g, const ExtractorArena& a, int lvl, int batch, cudaStream_t s) {
   const LevelGeom& D = g.lv[lvl];
+  if (D.resize_fast) {
+    dim3 grid((D.w + 127) / 128, (D.h + PY_ROWS * PY_WARPS - 1) / (PY_ROWS * PY_WARPS), batch);
+    pyramid_level_kernel<<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+    return;
+  }
   dim3 block(32, 8);
   dim3 grid((D.w + 127) / 128, (D.h + 7) / 8, batch);
-  pyramid_level_kernel<<<grid, block, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+  pyramid_level_generic_kernel<<<grid, block, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
 }
 
 }  // namespace orbfe

@@ -90,7 +90,9 @@ def test_stress_images(fe, oracle, kind):
 def test_other_parameters(fe, oracle):
     # monocular initialisation extractor: 2 x nFeatures (src/Tracking.cc:141-142); fewer levels; other thresholds
     img = synth.synth_image(640, 480, 21)
-    for params in [(2000, 1.2, 8, 20, 7), (500, 1.5, 4, 30, 10), (1000, 1.2, 8, 12, 12)]:
+    # scale 1.5 and 2.0 take the generic resize kernel, 1.2 and 1.1 the word-based one (k_pyramid.cu)
+    for params in [(2000, 1.2, 8, 20, 7), (500, 1.5, 4, 30, 10), (1000, 1.2, 8, 12, 12), (800, 2.0, 3, 20, 7),
+                   (1000, 1.1, 10, 20, 7)]:
         okp, odesc = oracle.Extractor(*params).extract(img)
         kp, desc = fe.ORBextractor(*params)(img)
         _assert_same(kp, desc, okp, odesc)
