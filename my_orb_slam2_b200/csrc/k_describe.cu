@@ -1,9 +1,11 @@
-// k_describe.cu — everything after DistributeOctTree for one kept keypoint, one warp per keypoint:
+// k_describe.cu — everything after DistributeOctTree for the kept keypoints.  A CTA takes 32 output rows; the
+// per-pixel parts run one warp per keypoint, the scalar parts (level lookup, atan2, sin/cos, keypoint record) one
+// THREAD per keypoint so that their instruction stream is paid once per 32 keypoints, not once per keypoint:
 //   * the fix-up of src/ORBextractor.cc:859-870 (pt += minBorder, octave, size);
 //   * computeOrientation -> IC_Angle (:472-479, :77-104): m10/m01 over the radius-15 disc of the UN-blurred level
 //     (lane u = column of the disc, loop over its 31 rows), warp-shuffle reduction, cv::fastAtan2 polynomial;
 //   * computeOrbDescriptor (:108-147) on the blurred level (k_blur.cu): lane i builds descriptor byte i
-//     (8 tests = 16 gathers), its 32 pattern bytes read with two coalesced 16-byte loads;
+//     (8 tests = 16 gathers) from its 32 fp32 pattern values (loaded once per warp, coalesced float4);
 //   * the rescale by mvScaleFactor[level] and the level-order concatenation of operator() (:1117-1125).
 // Kept keypoints are >= 19 px from every level edge (FAST margin 3 + minBorder 16), the disc has radius 15 and the
 // rotated pattern reaches <= 18 px, so no access leaves the level image.
@@ -15,14 +17,38 @@
 namespace orbfe {
 
 constexpr int DESC_WARPS = 8;
+constexpr int DESC_KP = 32;  // keypoints per CTA (4 per warp)
 
-// 256 test pairs x (x0,y0,x1,y1) as int8.  In GLOBAL memory, not __constant__: lane i reads ITS 32 bytes (two
-// coalesced 16-byte loads); a lane-indexed read of constant memory would be serialised 32 ways.
-__device__ __align__(16) int8_t d_pattern[1024] = {
+// 256 test pairs x (x0,y0,x1,y1) as fp32 (the reference converts the int pattern to float in the rotation,
+// src/ORBextractor.cc:123-131), transposed so that the 32 lanes of a warp read consecutive float4: element
+// [q][lane] holds values 4q..4q+3 of lane's 32 values (= tests 8*lane .. 8*lane+7).
+struct PatternT { float4 v[8][32]; };
+static PatternT make_pattern() {
+  static const int p[1024] = {
 #include "../../include/orb_pattern_31.inc"
-};
-// end of each row of the radius-15 disc (umax, :454-469)
+  };
+  PatternT t;
+  for (int lane = 0; lane < 32; ++lane)
+    for (int q = 0; q < 8; ++q) {
+      const int* s = p + lane * 32 + q * 4;
+      t.v[q][lane] = make_float4((float)s[0], (float)s[1], (float)s[2], (float)s[3]);
+    }
+  return t;
+}
+__device__ PatternT d_pattern_t;
+// end of each row of the radius-15 disc (umax, :454-469); the disc is symmetric: |u| <= umax[|v|] <=> |v| <= umax[|u|]
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+
+int upload_pattern() {
+  const PatternT t = make_pattern();
+  return cudaMemcpyToSymbol(d_pattern_t, &t, sizeof(t)) == cudaSuccess ? 0 : -1;
+}
+
+struct KpSlot {
+  int kx, ky, lvl, score;  // level coordinates (minBorder added, :865-866); lvl < 0: no keypoint in this slot
+  int m01, m10;
+  float ca, sb;            // cos, sin of the orientation
+};
 
 __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_constant__ PyrGeom g,
                                                                    const uint8_t* __restrict__ pyr,
@@ -33,95 +59,131 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
                                                                    uint8_t* __restrict__ out_desc,
                                                                    int32_t* __restrict__ out_count,
                                                                    int32_t* __restrict__ flags) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ KpSlot slot[DESC_KP];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
-  const int oi = blockIdx.x * DESC_WARPS + warp;  // output row of this keypoint
-  // level of this output row: levels are concatenated in order 0..L-1 (:1096-1126)
-  const int32_t* kc = kept_count + b * kMaxLevels;
-  int lvl = 0, first = 0;
-  {
-    int acc = 0;
-    bool found = false;
+  const int oi0 = blockIdx.x * DESC_KP;  // first output row of this CTA
+
+  // ---- 0. one thread per keypoint: which level does output row oi belong to (levels are concatenated in order
+  // 0..L-1, :1096-1126), and its kept record ----
+  if (tid < DESC_KP) {
+    const int oi = oi0 + tid;
+    const int32_t* kc = kept_count + b * kMaxLevels;
+    int lvl = -1, first = 0, acc = 0;
     for (int l = 0; l < g.nlevels; ++l) {
       const int c = kc[l];
-      if (!found && oi < acc + c) { lvl = l; first = acc; found = true; }
+      if (lvl < 0 && oi < acc + c) { lvl = l; first = acc; }
       acc += c;
     }
-    if (oi == 0 && lane == 0) {
+    if (oi == 0) {
       out_count[b] = min(acc, g.out_cap);
       if (acc > g.out_cap) atomicOr(&flags[b], FLAG_OUT_OVERFLOW);
     }
-    if (!found || oi >= g.out_cap) return;
+    if (oi >= g.out_cap) lvl = -1;
+    KpSlot k;
+    k.lvl = lvl;
+    k.kx = k.ky = k.score = k.m01 = k.m10 = 0;
+    k.ca = k.sb = 0.f;
+    if (lvl >= 0) {
+      const uint32_t c = kept[(size_t)b * g.kept_total + g.lv[lvl].kept_off + (oi - first)];
+      k.kx = cand_x(c) + kMinBorder;  // :865-866
+      k.ky = cand_y(c) + kMinBorder;
+      k.score = cand_score(c);
+    }
+    slot[tid] = k;
   }
-  const LevelGeom& L = g.lv[lvl];
-  const uint32_t c = kept[(size_t)b * g.kept_total + L.kept_off + (oi - first)];
-  const int kx = cand_x(c) + kMinBorder, ky = cand_y(c) + kMinBorder;  // :865-866
-  const size_t lvl_off = L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)ky * L.pitch + kx;
+  __syncthreads();
+  if (slot[0].lvl < 0) return;  // output rows are dense: an empty first slot means an empty CTA
 
-  // ---- IC_Angle (:77-104) ----
-  int m01 = 0, m10 = 0;
+  // ---- 1. IC_Angle moments (:77-104), one warp per keypoint: lane = column u of the radius-15 disc ----
   {
-    const uint8_t* center = pyr + lvl_off;
     const int u = lane - 15;
     const int au = u < 0 ? -u : u;
-    if (lane < 31) {
+    const int vlim = lane < 31 ? c_umax[au] : -1;  // rows |v| <= vlim belong to column u
+#pragma unroll 1
+    for (int i = warp; i < DESC_KP; i += DESC_WARPS) {
+      const KpSlot k = slot[i];
+      if (k.lvl < 0) break;
+      const LevelGeom& L = g.lv[k.lvl];
+      const int pitch = L.pitch;
+      const uint8_t* center = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)k.ky * pitch + k.kx + u;
+      int sum = 0, m01 = 0;
 #pragma unroll
       for (int v = -15; v <= 15; ++v) {
         const int av = v < 0 ? -v : v;
-        if (au <= c_umax[av]) {
-          const int val = __ldg(center + v * L.pitch + u);
-          m10 += u * val;
+        if (av <= vlim) {
+          const int val = __ldg(center + v * pitch);
+          sum += val;
           m01 += v * val;
         }
       }
-    }
+      int m10 = u * sum;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-      m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+      for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+      }
+      if (lane == 0) { slot[i].m01 = m01; slot[i].m10 = m10; }
     }
   }
-  const float angle = orb_fast_atan2_deg((float)m01, (float)m10);  // :103
+  __syncthreads();
 
-  // ---- computeOrbDescriptor (:108-147): lane -> descriptor byte ----
-  float ca, sb;
-  orb_sincos_deg(angle, &ca, &sb);  // a = cos, b = sin (:112-113, documented deviation 3)
-  const uint8_t* center = blur + lvl_off;
-  const int step = L.pitch;
-  int val = 0;
-  const uint4 p_lo = __ldg(reinterpret_cast<const uint4*>(d_pattern) + 2 * lane);
-  const uint4 p_hi = __ldg(reinterpret_cast<const uint4*>(d_pattern) + 2 * lane + 1);
-  const unsigned pw[8] = {p_lo.x, p_lo.y, p_lo.z, p_lo.w, p_hi.x, p_hi.y, p_hi.z, p_hi.w};
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const unsigned q = pw[j];  // bytes: x0, y0, x1, y1 of test 8*lane + j
-    const float x0 = (float)(int8_t)(q & 0xFF), y0 = (float)(int8_t)((q >> 8) & 0xFF);
-    const float x1 = (float)(int8_t)((q >> 16) & 0xFF), y1 = (float)(int8_t)(q >> 24);
-    const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));
-    const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
-    const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
-    const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-    const int t0 = __ldg(center + r0 * step + c0), t1 = __ldg(center + r1 * step + c1);
-    val |= (t0 < t1) << j;
+  // ---- 2. one thread per keypoint: angle (cv::fastAtan2, :103), its cos / sin (:112-113, documented deviation 3),
+  // and the keypoint record with the rescale of operator() (:1117-1125) ----
+  if (tid < DESC_KP && slot[tid].lvl >= 0) {
+    const KpSlot k = slot[tid];
+    const LevelGeom& L = g.lv[k.lvl];
+    const float angle = orb_fast_atan2_deg((float)k.m01, (float)k.m10);
+    float ca, sb;
+    orb_sincos_deg(angle, &ca, &sb);
+    slot[tid].ca = ca;
+    slot[tid].sb = sb;
+    orbfe_keypoint o;
+    o.x = (float)k.kx;
+    o.y = (float)k.ky;
+    if (k.lvl != 0) { o.x = __fmul_rn(o.x, L.scale); o.y = __fmul_rn(o.y, L.scale); }
+    o.size = L.kp_size;
+    o.angle = angle;
+    o.response = (float)k.score;
+    o.octave = k.lvl;
+    o.class_id = -1;
+    out_kp[(size_t)b * g.out_cap + oi0 + tid] = o;
   }
-  out_desc[((size_t)b * g.out_cap + oi) * 32 + lane] = (uint8_t)val;
+  __syncthreads();
 
-  if (lane == 0) {
-    orbfe_keypoint k;
-    k.x = (float)kx;
-    k.y = (float)ky;
-    if (lvl != 0) { k.x = __fmul_rn(k.x, L.scale); k.y = __fmul_rn(k.y, L.scale); }  // :1117-1123
-    k.size = L.kp_size;
-    k.angle = angle;
-    k.response = (float)cand_score(c);
-    k.octave = lvl;
-    k.class_id = -1;
-    out_kp[(size_t)b * g.out_cap + oi] = k;
+  // ---- 3. computeOrbDescriptor (:108-147) on the blurred level: lane -> descriptor byte (8 tests = 16 gathers);
+  // the lane's 32 pattern values stay in registers for the warp's 4 keypoints ----
+  float pat[32];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const float4 t = d_pattern_t.v[q][lane];
+    pat[4 * q] = t.x; pat[4 * q + 1] = t.y; pat[4 * q + 2] = t.z; pat[4 * q + 3] = t.w;
+  }
+#pragma unroll 1
+  for (int i = warp; i < DESC_KP; i += DESC_WARPS) {
+    const KpSlot k = slot[i];
+    if (k.lvl < 0) break;
+    const LevelGeom& L = g.lv[k.lvl];
+    const int step = L.pitch;
+    const uint8_t* center = blur + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)k.ky * step + k.kx;
+    const float ca = k.ca, sb = k.sb;
+    int val = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float x0 = pat[4 * j], y0 = pat[4 * j + 1], x1 = pat[4 * j + 2], y1 = pat[4 * j + 3];
+      const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));
+      const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
+      const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
+      const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
+      const int t0 = __ldg(center + (r0 * step + c0)), t1 = __ldg(center + (r1 * step + c1));
+      val |= (t0 < t1) << j;
+    }
+    out_desc[((size_t)b * g.out_cap + oi0 + i) * 32 + lane] = (uint8_t)val;
   }
 }
 
 void launch_describe(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
-  dim3 grid((g.out_cap + DESC_WARPS - 1) / DESC_WARPS, batch);
+  dim3 grid((g.out_cap + DESC_KP - 1) / DESC_KP, batch);
   describe_kernel<<<grid, DESC_WARPS * 32, 0, s>>>(g, a.pyr, a.blur, a.kept, a.kept_count, a.out_kp, a.out_desc,
                                                    a.out_count, a.flags);
 }

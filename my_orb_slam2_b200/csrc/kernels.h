@@ -45,6 +45,7 @@ void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cud
 // DistributeOctTree (:539-765): one CTA per (level, image)
 void launch_quadtree(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
 size_t quadtree_smem_bytes(int node_cap);
+int upload_pattern();          // k_describe.cu: rBRIEF pattern -> device (once per device); 0 on success
 int configure_fast_kernel();  // opt in to > 48 KB dynamic shared memory; 0 on success
 // GaussianBlur(7x7, sigma 2) of every level (:1107-1108), one launch
 void launch_blur_levels(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
