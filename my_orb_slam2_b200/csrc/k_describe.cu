@@ -106,16 +106,21 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
       if (k.lvl < 0) break;
       const LevelGeom& L = g.lv[k.lvl];
       const int pitch = L.pitch;
-      const uint8_t* center = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)k.ky * pitch + k.kx + u;
+      // row pointer, bumped by the pitch (opaque to the compiler: otherwise it rebuilds pyr + offset for every row)
+      const uint8_t* p = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)((k.ky - 15) * pitch + k.kx + u);
+      asm volatile("" : "+l"(p));
+      const size_t pitch64 = (size_t)pitch;
       int sum = 0, m01 = 0;
 #pragma unroll
       for (int v = -15; v <= 15; ++v) {
         const int av = v < 0 ? -v : v;
         if (av <= vlim) {
-          const int val = __ldg(center + v * pitch);
+          const int val = __ldg(p);
           sum += val;
           m01 += v * val;
         }
+        p += pitch64;
+        asm volatile("" : "+l"(p));  // keep the bump a 64-bit add (not p0 + v * pitch recomputed per row)
       }
       int m10 = u * sum;
 #pragma unroll
@@ -165,7 +170,10 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
     if (k.lvl < 0) break;
     const LevelGeom& L = g.lv[k.lvl];
     const int step = L.pitch;
-    const uint8_t* center = blur + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)k.ky * step + k.kx;
+    // 32-bit offsets: the rotated pattern reaches <= 18 px and the keypoint is >= 19 px inside the level
+    const uint8_t* base = blur + L.lvl_base + (size_t)b * L.lvl_bytes;
+    asm volatile("" : "+l"(base));
+    const int ctr = k.ky * step + k.kx;
     const float ca = k.ca, sb = k.sb;
     int val = 0;
 #pragma unroll
@@ -175,7 +183,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
       const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
       const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
       const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-      const int t0 = __ldg(center + (r0 * step + c0)), t1 = __ldg(center + (r1 * step + c1));
+      const int t0 = __ldg(base + (unsigned)(r0 * step + (c0 + ctr)));
+      const int t1 = __ldg(base + (unsigned)(r1 * step + (c1 + ctr)));
       val |= (t0 < t1) << j;
     }
     out_desc[((size_t)b * g.out_cap + oi0 + i) * 32 + lane] = (uint8_t)val;
