@@ -17,6 +17,7 @@
 namespace orbfe {
 
 constexpr int BL_TX = 32, BL_TY = 4, BL_ROWS = 32;  // CTA covers 128 x 128 pixels
+constexpr int BL_PF = 3;                            // rows of loads in flight per thread
 
 __device__ __forceinline__ int reflect101i(int p, int len) {
   if (p < 0) p = -p;
@@ -46,52 +47,86 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
   const unsigned K_LO = 0x38302212u;  // 18,34,48,56 (byte 0 first)
   const unsigned K_HI = 0x00122230u;  // 48,34,18,0
 
-  unsigned win[7][4];
+  const int rows = min(BL_ROWS, h - y0);  // warp-uniform
+  if (slow) {
+    // right edge of the level (the last one or two words of a row): byte-wise loads with column reflection, rolled loop
+    unsigned win[7][4];
 #pragma unroll
-  for (int i = 0; i < 7; ++i)
+    for (int i = 0; i < 7; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) win[i][j] = 0;
-
-  const int rows = min(BL_ROWS, h - y0);
+      for (int j = 0; j < 4; ++j) win[i][j] = 0;
 #pragma unroll 1
-  for (int r = 0; r < rows + 6; ++r) {
-    const int y = reflect101i(y0 + r - 3, h);
-    const uint8_t* row = src + (size_t)y * pitch;
-    unsigned w0, w1, w2;
-    if (!slow) {
-      w1 = __ldg(reinterpret_cast<const unsigned*>(row + x4));
-      w2 = __ldg(reinterpret_cast<const unsigned*>(row + x4 + 4));
-      w0 = left ? __byte_perm(w1, 0, 0x1230) : __ldg(reinterpret_cast<const unsigned*>(row + x4 - 4));
-    } else {
+    for (int r = 0; r < rows + 6; ++r) {
+      const int y = reflect101i(y0 + r - 3, h);
+      const uint8_t* row = src + (size_t)y * pitch;
       unsigned t[3] = {0, 0, 0};
 #pragma unroll
       for (int i = 0; i < 12; ++i) {
         const int c = reflect101i(x4 - 4 + i, w);
         t[i >> 2] |= (unsigned)__ldg(row + c) << (8 * (i & 3));
       }
-      w0 = t[0]; w1 = t[1]; w2 = t[2];
-    }
-    // horizontal sums of the 4 pixels: taps are bytes j+1 .. j+7 of (w0,w1,w2)
-    unsigned hs[4];
-    hs[0] = __dp4a(__funnelshift_r(w0, w1, 8), K_LO, __dp4a(__funnelshift_r(w1, w2, 8), K_HI, 0u));
-    hs[1] = __dp4a(__funnelshift_r(w0, w1, 16), K_LO, __dp4a(__funnelshift_r(w1, w2, 16), K_HI, 0u));
-    hs[2] = __dp4a(__funnelshift_r(w0, w1, 24), K_LO, __dp4a(__funnelshift_r(w1, w2, 24), K_HI, 0u));
-    hs[3] = __dp4a(w1, K_LO, __dp4a(w2, K_HI, 0u));
+      const unsigned w0 = t[0], w1 = t[1], w2 = t[2];
+      unsigned hs[4];
+      hs[0] = __dp4a(__funnelshift_r(w0, w1, 8), K_LO, __dp4a(__funnelshift_r(w1, w2, 8), K_HI, 0u));
+      hs[1] = __dp4a(__funnelshift_r(w0, w1, 16), K_LO, __dp4a(__funnelshift_r(w1, w2, 16), K_HI, 0u));
+      hs[2] = __dp4a(__funnelshift_r(w0, w1, 24), K_LO, __dp4a(__funnelshift_r(w1, w2, 24), K_HI, 0u));
+      hs[3] = __dp4a(w1, K_LO, __dp4a(w2, K_HI, 0u));
 #pragma unroll
-    for (int i = 0; i < 6; ++i)
+      for (int i = 0; i < 6; ++i)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) win[i][j] = win[i + 1][j];
+        for (int j = 0; j < 4; ++j) win[i][j] = win[i + 1][j];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) win[6][j] = hs[j];
-    if (r >= 6) {
-      unsigned out = 0;
+      for (int j = 0; j < 4; ++j) win[6][j] = hs[j];
+      if (r >= 6) {
+        unsigned out = 0;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const unsigned v = 18u * (win[0][j] + win[6][j]) + 34u * (win[1][j] + win[5][j]) +
-                           48u * (win[2][j] + win[4][j]) + 56u * win[3][j];
-        out |= ((v + 32768u) >> 16) << (8 * j);
+        for (int j = 0; j < 4; ++j) {
+          const unsigned v = 18u * (win[0][j] + win[6][j]) + 34u * (win[1][j] + win[5][j]) +
+                             48u * (win[2][j] + win[4][j]) + 56u * win[3][j];
+          out |= ((v + 32768u) >> 16) << (8 * j);
+        }
+        *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * pitch + x4) = out;
       }
-      *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * pitch + x4) = out;
+    }
+    return;
+  }
+  // win[r % 7] holds the horizontal sums of loaded row r: with the row loop fully unrolled the window is renamed, not
+  // moved (a rolled loop spends a quarter of its instructions on register moves); the words of row r + BL_PF are
+  // requested before row r is processed so that several rows of loads are in flight per thread
+  unsigned win[7][4];
+  unsigned pf[BL_PF][3];
+  const int xl = left ? x4 : x4 - 4;  // at the left edge w0 is rebuilt from w1 (reflection of columns -1..-3)
+  auto load_row = [&](int r, unsigned (&q)[3]) {
+    const int y = reflect101i(y0 + r - 3, h);
+    const uint8_t* row = src + (size_t)y * pitch;
+    q[0] = __ldg(reinterpret_cast<const unsigned*>(row + xl));
+    q[1] = __ldg(reinterpret_cast<const unsigned*>(row + x4));
+    q[2] = __ldg(reinterpret_cast<const unsigned*>(row + x4 + 4));
+  };
+#pragma unroll
+  for (int r = 0; r < BL_PF; ++r) load_row(min(r, rows + 5), pf[r]);
+#pragma unroll
+  for (int r = 0; r < BL_ROWS + 6; ++r) {
+    if (r < rows + 6) {
+      const unsigned w1 = pf[r % BL_PF][1], w2 = pf[r % BL_PF][2];
+      const unsigned w0 = left ? __byte_perm(w1, 0, 0x1230) : pf[r % BL_PF][0];
+      load_row(min(r + BL_PF, rows + 5), pf[r % BL_PF]);
+      // horizontal sums of the 4 pixels: taps are bytes j+1 .. j+7 of (w0,w1,w2)
+      unsigned* hs = win[r % 7];
+      hs[0] = __dp4a(__funnelshift_r(w0, w1, 8), K_LO, __dp4a(__funnelshift_r(w1, w2, 8), K_HI, 0u));
+      hs[1] = __dp4a(__funnelshift_r(w0, w1, 16), K_LO, __dp4a(__funnelshift_r(w1, w2, 16), K_HI, 0u));
+      hs[2] = __dp4a(__funnelshift_r(w0, w1, 24), K_LO, __dp4a(__funnelshift_r(w1, w2, 24), K_HI, 0u));
+      hs[3] = __dp4a(w1, K_LO, __dp4a(w2, K_HI, 0u));
+      if (r >= 6) {
+        unsigned out = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const unsigned v = 18u * (win[(r + 1) % 7][j] + win[r % 7][j]) + 34u * (win[(r + 2) % 7][j] + win[(r + 6) % 7][j]) +
+                             48u * (win[(r + 3) % 7][j] + win[(r + 5) % 7][j]) + 56u * win[(r + 4) % 7][j];
+          out |= ((v + 32768u) >> 16) << (8 * j);
+        }
+        *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * pitch + x4) = out;
+      }
     }
   }
 }

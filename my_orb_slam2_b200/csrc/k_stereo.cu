@@ -22,7 +22,7 @@
 
 namespace orbfe {
 
-constexpr int ST_WARPS = 8;
+constexpr int ST_WARPS = 4;
 constexpr int ST_BROWS = 8;       // image rows per bucket of the row table
 constexpr int ST_MAXB = 1024;     // buckets per image (rows <= 8192)
 constexpr int TH_HIGH = ORBFE_TH_HIGH, TH_LOW = ORBFE_TH_LOW;
@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(512) stereo_bucket_kernel(const __grid_constan
                                                             const orbfe_keypoint* __restrict__ kpR,
                                                             const int32_t* __restrict__ cntR, int4* __restrict__ band,
                                                             int32_t* __restrict__ bucket_start,
-                                                            int32_t* __restrict__ bucket_items, int items_per_kp) {
+                                                            int4* __restrict__ bucket_items, int items_per_kp) {
   __shared__ int s_cnt[ST_MAXB + 1];
   __shared__ int s_wtmp[32];
   const int b = blockIdx.x, tid = threadIdx.x;
@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(512) stereo_bucket_kernel(const __grid_constan
   const orbfe_keypoint* kr = kpR + (size_t)b * g.out_cap;
   int4* bands = band + (size_t)b * g.out_cap;
   int32_t* bstart = bucket_start + (size_t)b * (nb + 1);
-  int32_t* bitems = bucket_items + (size_t)b * g.out_cap * items_per_kp;
+  int4* bitems = bucket_items + (size_t)b * g.out_cap * items_per_kp;
   for (int i = tid; i <= nb; i += 512) s_cnt[i] = 0;
   __syncthreads();
   for (int i = tid; i < nR; i += 512) {
@@ -85,16 +85,16 @@ __global__ void __launch_bounds__(512) stereo_bucket_kernel(const __grid_constan
     const int lo = max(bd.x, 0) / ST_BROWS, hi = min(bd.y, n_rows - 1) / ST_BROWS;
     for (int q = lo; q <= hi; ++q) {
       const int slot = atomicAdd(&s_cnt[q], 1);
-      if (slot < cap_items) bitems[slot] = i;
+      if (slot < cap_items) bitems[slot] = make_int4(bd.x, bd.y, bd.z, bd.w | (i << 8));  // band inline: no second lookup
     }
   }
 }
 
-__global__ void __launch_bounds__(ST_WARPS * 32) stereo_match_kernel(
+__global__ void __launch_bounds__(ST_WARPS * 32, 8) stereo_match_kernel(
     const __grid_constant__ PyrGeom g, const uint8_t* __restrict__ pyrL, const uint8_t* __restrict__ pyrR,
     const orbfe_keypoint* __restrict__ kpL, const uint8_t* __restrict__ descL, const int32_t* __restrict__ cntL,
     const orbfe_keypoint* __restrict__ kpR, const uint8_t* __restrict__ descR, const int4* __restrict__ band,
-    const int32_t* __restrict__ bucket_start, const int32_t* __restrict__ bucket_items, int items_per_kp,
+    const int32_t* __restrict__ bucket_start, const int4* __restrict__ bucket_items, int items_per_kp,
     float mbf, float mb, float* __restrict__ u_right, float* __restrict__ depth, int32_t* __restrict__ sad_out) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = blockIdx.y;
@@ -117,18 +117,43 @@ __global__ void __launch_bounds__(ST_WARPS * 32) stereo_match_kernel(
   if (searchable) {
     const int nb = (n_rows + ST_BROWS - 1) / ST_BROWS;
     const int32_t* bstart = bucket_start + (size_t)b * (nb + 1);
-    const int32_t* bitems = bucket_items + (size_t)b * g.out_cap * items_per_kp;
-    const int4* bands = band + (size_t)b * g.out_cap;
+    const int4* bitems = bucket_items + (size_t)b * g.out_cap * items_per_kp;
     const int bk = rowi / ST_BROWS;
     const int beg = bstart[bk], end = bstart[bk + 1];
-    for (int p = beg + lane; p < end; p += 32) {
-      const int iR = bitems[p];
-      const int4 bd = __ldg(bands + iR);  // minr, maxr, x bits, octave
-      const float uR = __int_as_float(bd.z);
-      if (rowi >= bd.x && rowi <= bd.y && bd.w >= levelL - 1 && bd.w <= levelL + 1 && uR >= minU && uR <= maxU) {
-        const uint4* dp = reinterpret_cast<const uint4*>(descR + ((size_t)b * g.out_cap + iR) * 32);
-        const unsigned dist = (unsigned)hamming256(d0, d1, __ldg(dp), __ldg(dp + 1));
-        best = min(best, (dist << 16) | (unsigned)iR);
+    const uint8_t* dR = descR + (size_t)b * g.out_cap * 32;
+    // 4 items per lane in flight: the item loads of a 128-item chunk are issued together, then the descriptor loads
+    for (int base = beg; base < end; base += 128) {
+      int4 bd[4];
+      bool cand[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int p = base + lane + 32 * u;
+        bd[u] = p < end ? __ldg(bitems + p) : make_int4(1, 0, 0, 0);  // minr > maxr: never a candidate
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float uR = __int_as_float(bd[u].z);
+        const int oct = bd[u].w & 0xFF;
+        cand[u] = rowi >= bd[u].x && rowi <= bd[u].y && oct >= levelL - 1 && oct <= levelL + 1 && uR >= minU && uR <= maxU;
+      }
+#pragma unroll
+      for (int h = 0; h < 4; h += 2) {  // descriptor loads two at a time (register budget)
+        uint4 r0[2], r1[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (cand[h + u]) {
+            const uint4* dp = reinterpret_cast<const uint4*>(dR + (size_t)(bd[h + u].w >> 8) * 32);
+            r0[u] = __ldg(dp);
+            r1[u] = __ldg(dp + 1);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (cand[h + u]) {
+            const unsigned dist = (unsigned)hamming256(d0, d1, r0[u], r1[u]);
+            best = min(best, (dist << 16) | (unsigned)(bd[h + u].w >> 8));
+          }
+        }
       }
     }
   }

@@ -31,7 +31,7 @@ struct ExtractorArena {
   int32_t* st_count = nullptr;  // [batch]
   int4* st_band = nullptr;             // [batch][out_cap] right keypoint: minr, maxr, x bits, octave
   int32_t* st_bucket_start = nullptr;  // [batch][rows/8 + 2]
-  int32_t* st_bucket_items = nullptr;  // [batch][out_cap * st_items_per_kp]
+  int4* st_bucket_items = nullptr;     // [batch][out_cap * st_items_per_kp] band + right keypoint index per bucket entry
   int st_items_per_kp = 0;
 };
 
