@@ -162,6 +162,79 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def matcher_extras(torch, dist, orbfe, rank, world, local, kp_frame, desc_frame, quick):
+    """BASELINE.json configs 4 and 5 (reported next to the headline, not the headline): brute-force Hamming
+    8192 x 1,048,576 (map sharded over the ranks, one NCCL all-gather of the per-shard top-2, CUDA merge) as a fraction of
+    the MEASURED popc-pipe peak, and the two SearchByProjection overloads through the C ABI with host views."""
+    from my_orb_slam2_b200 import frontend, sharding
+    dev = torch.device("cuda", local)
+    m = orbfe.Matcher(device=local)
+    out = {}
+    popc_peak = m.popc_peak()
+    nq, nm = 8192, (1 << 20) if not quick else (1 << 17)
+    q, mp = synth.bruteforce_case(nq, nm, 4096, seed=1)
+    start, cnt = sharding.map_shard(nm, rank, world)
+    d_q = torch.from_numpy(q).to(dev)
+    d_m = torch.from_numpy(mp[start:start + cnt].copy()).to(dev)
+    sb = sharding.ShardedBruteForce(m, dev)
+    for _ in range(3):
+        sb.run(d_q, d_m, start)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    e0.record()
+    for _ in range(reps):
+        best, second = sb.run(d_q, d_m, start)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    pairs = float(nq) * nm
+    out["bruteforce_hamming"] = {
+        "workload": "configs[4]: %d queries x %d map descriptors, map sharded over %d GPU(s)" % (nq, nm, world),
+        "ms": ms, "pairs_per_s": pairs / (ms * 1e-3), "algorithmic_popc32_per_s": 8.0 * pairs / (ms * 1e-3),
+        "popc_peak_per_gpu_measured": popc_peak, "frac_of_popc_peak": 8.0 * pairs / (ms * 1e-3) / (popc_peak * world),
+        "note": "the kernel spends 5 POPC per pair (carry-save compression of the 8 XOR words), so the algorithmic "
+                "rate (8 popc32 per pair) may exceed the POPC pipe's own peak",
+        "first_best_key": int(best[0].item()) & 0xFFFFFFFFFFFFFFFF,
+    }
+    if rank == 0:
+        # config 4: SearchByProjection (map overload, then last-frame overload) through the C ABI, host views
+        bounds = (0.0, 0.0, float(W), float(H))
+        frame = synth.frame_arrays(kp_frame, desc_frame, bounds, seed=0)
+        mps = synth.map_points_case(frame, 20000, 1500, seed=0, bf=float(MBF))
+        fv = frontend.frame_view(frame["keys_un"], frame["u_right"], frame["desc"], frame["mp_obs"], frame["bounds"],
+                                 frame["scale_factors"])
+        mv = frontend.mappoints_view(mps["proj_x"], mps["proj_y"], mps["proj_xr"], mps["level"], mps["view_cos"],
+                                     mps["in_view"], mps["obs"], mps["desc"])
+        ts = []
+        for i in range(13):
+            t0 = time.perf_counter()
+            assigned, n = m.search_by_projection_map(fv, mv, 1.0, 0.8)
+            ts.append(time.perf_counter() - t0)
+        out["search_by_projection_map"] = {"workload": "configs[3]: %d features vs 20000 map points, th=1, nnratio=0.8, "
+                                           "host views in, assignments out" % len(kp_frame),
+                                           "ms_p50": 1e3 * float(np.median(ts[3:])), "matches": int(n)}
+        last, cam = synth.last_frame_case(frame, seed=0)
+        lv = frontend.lastframe_view(last["valid"], last["world_pos"], last["obs"], last["desc"], last["octave"],
+                                     last["angle"], last["tcw"])
+        cv = frontend.camera_pose(cam["tcw"], cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["mbf"], cam["mb"])
+        ts = []
+        for i in range(13):
+            t0 = time.perf_counter()
+            assigned, n = m.search_by_projection_last(fv, cv, lv, 7.0, False, True)
+            ts.append(time.perf_counter() - t0)
+        out["search_by_projection_last"] = {"workload": "configs[3]: last-frame overload, th=7, rotation histogram on",
+                                            "ms_p50": 1e3 * float(np.median(ts[3:])), "matches": int(n)}
+    m.close()
+    return out
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -341,6 +414,13 @@ def run_gpu(args):
         L1.close()
         R1.close()
 
+    # ---- configs 3 / 4: the matchers (extra keys; every rank takes part in the sharded brute force) ----
+    extras = None
+    if not args.no_matchers:
+        n0 = int(rigs[0].cntL[0])
+        kp0 = rigs[0].kpL[0].numpy()[:n0].copy().view(orbfe.KEYPOINT_DTYPE).reshape(-1)
+        ds0 = rigs[0].dsL[0].numpy()[:n0].copy()
+        extras = matcher_extras(torch, dist, orbfe, rank, world, local, kp0, ds0, args.quick_matchers)
     for g in rigs:
         g.close()
     if world > 1:
@@ -412,6 +492,7 @@ def run_gpu(args):
                      "extract_frac": (b_extract * 2 * B * args.steps / (ms_dev * 1e-3) / 1e9) / peak_gbs},
         "stages_ms_per_launch": per_launch,
         "cpu_baseline": cpu,
+        "matchers": extras,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -428,6 +509,8 @@ def main():
     ap.add_argument("--latency-frames", type=int, default=200)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-matchers", action="store_true", help="skip the configs 3/4 matcher figures")
+    ap.add_argument("--quick-matchers", action="store_true", help="128 k map descriptors instead of 1 M")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -190,6 +190,9 @@ int orbfe_hamming_bruteforce_device(orbfe_matcher* m, const uint8_t* d_query, in
 int orbfe_hamming_merge_device(orbfe_matcher* m, const uint64_t* d_best_all, const uint64_t* d_second_all,
                                int shards, int nq, uint64_t* d_best, uint64_t* d_second);
 int orbfe_matcher_sync(orbfe_matcher* m);
+/* Measured 32-bit POPC results per second of the matcher's device (register-only probe kernel): the roofline
+ * denominator of the Hamming kernels ("measure it"). */
+int orbfe_measure_popc_peak(orbfe_matcher* m, double* popc32_per_second);
 
 #ifdef __cplusplus
 }

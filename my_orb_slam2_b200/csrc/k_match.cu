@@ -19,6 +19,66 @@ constexpr int BF_T = 128;        // threads per CTA
 constexpr int BF_QPT = 4;        // queries per thread
 constexpr int BF_TILE = 256;     // map descriptors per shared-memory tile (8 KB)
 
+// popcount of 256 bits with 5 POPC instead of 8: three carry-save adders (2 LOP3 each: sum = a^b^c, carry = majority)
+// compress the 8 words into two "ones" words and three "twos" words.  POPC issues at 16 lanes/clk/SM, LOP3 at 64, so
+// trading 3 POPC for 6 LOP3 moves the brute-force loop from the POPC pipe towards a POPC/ALU balance.
+__device__ __forceinline__ uint32_t hamming256_csa(uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3, uint32_t x4,
+                                                   uint32_t x5, uint32_t x6, uint32_t x7) {
+  const uint32_t l1 = x0 ^ x1 ^ x2, h1 = (x0 & x1) | (x2 & (x0 | x1));
+  const uint32_t l2 = x3 ^ x4 ^ x5, h2 = (x3 & x4) | (x5 & (x3 | x4));
+  const uint32_t l3 = l1 ^ l2 ^ x6, h3 = (l1 & l2) | (x6 & (l1 | l2));
+  return __popc(l3) + __popc(x7) + 2u * (__popc(h1) + __popc(h2) + __popc(h3));
+}
+
+// register-only POPC throughput probe (the roofline denominator of the Hamming kernels): every thread runs
+// iters x 8 independent popc chains; out keeps the compiler honest
+__global__ void __launch_bounds__(256) popc_peak_kernel(int iters, uint32_t seed, uint32_t* __restrict__ out) {
+  uint32_t v[8], acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { v[i] = seed * (threadIdx.x + 1u) + i * 0x9E3779B9u; acc[i] = 0; }
+#pragma unroll 1
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      acc[i] += __popc(v[i]);
+      v[i] ^= acc[i] << 3;  // data dependence so the popc cannot be hoisted; LOP3/SHF go to the ALU pipe
+    }
+  }
+  uint32_t s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += acc[i];
+  if (s == 0xFFFFFFFFu) out[0] = s;
+}
+
+double measure_popc_peak(cudaStream_t s) {
+  uint32_t* d = nullptr;
+  if (cudaMalloc(&d, 4) != cudaSuccess) return 0.0;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  int sms = 148;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int iters = 8192, blocks = sms * 8;
+  popc_peak_kernel<<<blocks, 256, 0, s>>>(64, 1u, d);  // warm-up
+  double best = 0.0;
+  for (int rep = 0; rep < 3; ++rep) {
+    cudaEventRecord(e0, s);
+    popc_peak_kernel<<<blocks, 256, 0, s>>>(iters, 12345u + rep, d);
+    cudaEventRecord(e1, s);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double rate = (double)blocks * 256.0 * iters * 8.0 / (ms * 1e-3);
+    if (rate > best) best = rate;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  return best;
+}
+
 __global__ void descriptor_distance_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
                                            int32_t* __restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -62,9 +122,8 @@ __global__ void __launch_bounds__(BF_T) hamming_bruteforce_kernel(const uint4* _
       const uint4 lo = tile[2 * j], hi = tile[2 * j + 1];
 #pragma unroll
       for (int k = 0; k < BF_QPT; ++k) {
-        const uint32_t d = __popc(q[k][0] ^ lo.x) + __popc(q[k][1] ^ lo.y) + __popc(q[k][2] ^ lo.z) +
-                           __popc(q[k][3] ^ lo.w) + __popc(q[k][4] ^ hi.x) + __popc(q[k][5] ^ hi.y) +
-                           __popc(q[k][6] ^ hi.z) + __popc(q[k][7] ^ hi.w);
+        const uint32_t d = hamming256_csa(q[k][0] ^ lo.x, q[k][1] ^ lo.y, q[k][2] ^ lo.z, q[k][3] ^ lo.w,
+                                          q[k][4] ^ hi.x, q[k][5] ^ hi.y, q[k][6] ^ hi.z, q[k][7] ^ hi.w);
         const uint32_t key = (d << 20) + (jbase + (uint32_t)j);
         b2[k] = min(b2[k], max(b1[k], key));
         b1[k] = min(b1[k], key);

@@ -198,6 +198,16 @@ int orbfe_hamming_merge_device(orbfe_matcher* h, const uint64_t* d_best_all, con
   return ORBFE_OK;
 }
 
+int orbfe_measure_popc_peak(orbfe_matcher* h, double* popc32_per_second) {
+  ORBFE_ARG(h && popc32_per_second);
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  *popc32_per_second = measure_popc_peak(m->stream);
+  ORBFE_CUDA(cudaGetLastError());
+  return *popc32_per_second > 0.0 ? ORBFE_OK : ORBFE_ERR_CUDA;
+}
+
 int orbfe_hamming_bruteforce_device(orbfe_matcher* h, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm,
                                     int64_t index_base, uint64_t* d_best, uint64_t* d_second) {
   ORBFE_ARG(h && d_query && d_best && d_second && nq >= 1 && nm >= 0);

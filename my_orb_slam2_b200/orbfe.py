@@ -112,6 +112,7 @@ SYMBOLS = {
     "orbfe_hamming_bruteforce_device": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_merge_device": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "orbfe_matcher_sync": (_I, [_P]),
+    "orbfe_measure_popc_peak": (_I, [_P, C.POINTER(C.c_double)]),
 }
 
 _lib = None
@@ -324,6 +325,11 @@ class Matcher:
                                                    int(only_stereo), int(check_ori), _p(pairs), len(pairs),
                                                    C.byref(n)))
         return pairs[:n.value].copy()
+
+    def popc_peak(self):
+        v = C.c_double()
+        check(lib().orbfe_measure_popc_peak(self._h, C.byref(v)))
+        return v.value
 
     def hamming_bruteforce(self, query, mapd, index_base=0):
         query, mapd = _u8(query).reshape(-1, 32), _u8(mapd).reshape(-1, 32)

@@ -128,3 +128,35 @@ def test_empty_inputs(fe):
     fv, mv = views(fe, frame=frame, mps=mps)
     got, n = mt.search_by_projection_map(fv, mv, 1.0, 0.8)
     assert n == 0 and len(got) == 0
+
+
+def test_bruteforce_sharded_single_process(oracle):
+    """The multi-GPU path of config 5 on one GPU: per-shard CUDA top-2 with global index bases + the CUDA merge kernel
+    (the NCCL all-gather in between is exercised by bench.py --gpus N; its layout by tests/test_sharding_gloo.py)."""
+    import torch
+    from my_orb_slam2_b200 import orbfe, sharding
+    nq, nm, world = 300, 7000, 3
+    q, m = synth.bruteforce_case(nq, nm, 150, seed=5)
+    m[nm - 1] = m[2]
+    q[1] = m[2]  # a tie across shards: the lower global index must win
+    mt = orbfe.Matcher()
+    dev = torch.device("cuda", 0)
+    d_q = torch.from_numpy(q).to(dev)
+    base = 12345
+    bests, seconds = [], []
+    sb = sharding.ShardedBruteForce(mt, dev)
+    for r in range(world):
+        start, cnt = sharding.map_shard(nm, r, world)
+        d_m = torch.from_numpy(m[start:start + cnt].copy()).to(dev)
+        b, s = sb.run(d_q, d_m, base + start)  # world == 1 (no process group): the local top-2
+        bests.append(b)
+        seconds.append(s)
+    ba, sa = torch.stack(bests).contiguous(), torch.stack(seconds).contiguous()
+    gb, gs = torch.empty_like(bests[0]), torch.empty_like(bests[0])
+    torch.cuda.synchronize()
+    mt.hamming_merge_device(ba.data_ptr(), sa.data_ptr(), world, nq, gb.data_ptr(), gs.data_ptr())
+    mt.sync()
+    ob, os_ = oracle.hamming_bruteforce(q, m, base)
+    assert np.array_equal(gb.cpu().numpy().view(np.uint64), ob)
+    assert np.array_equal(gs.cpu().numpy().view(np.uint64), os_)
+    assert mt.popc_peak() > 1e11
