@@ -164,7 +164,8 @@ int orbfe_search_by_projection_map(orbfe_matcher* m, const orbfe_frame_view* fra
                                    int32_t* n_matches);
 
 /* ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)
- * (src/ORBmatcher.cc:1392-1538) incl. the rotation histogram (:1499-1535). */
+ * (src/ORBmatcher.cc:1392-1538) incl. the rotation histogram (:1499-1535).  assigned[f] = row of `last` written into
+ * Cur.mvpMapPoints[f]; -1 = untouched; -2 = assigned and then reset to NULL by the rotation histogram (:1527). */
 int orbfe_search_by_projection_last(orbfe_matcher* m, const orbfe_frame_view* cur, const orbfe_camera_pose* cam,
                                     const orbfe_lastframe_view* last, float th, int mono, int check_ori,
                                     int32_t* assigned, int32_t* n_matches);

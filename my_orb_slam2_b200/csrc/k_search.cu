@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(1024) resolve_kernel(const DevFrame f, int row
       const int res = sc.result[i];
       if (res >= 0) {
         const int bin = rot_bin(row_angle[i], f.keys[res].angle);
-        if (bin != s_ind[0] && bin != s_ind[1] && bin != s_ind[2]) { sc.assigned[res] = -1; ++removed; }  // :1516-1535
+        if (bin != s_ind[0] && bin != s_ind[1] && bin != s_ind[2]) { sc.assigned[res] = -2; ++removed; }  // :1516-1535: set to NULL
       }
     }
     if (removed) atomicSub(&s_nmatch, removed);

@@ -173,7 +173,8 @@ class ORBmatcher:
         """Two reference overloads share this name:
         (Frame&, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:46)  -> other is a mappoints_view
         (Frame& Cur, const Frame& Last, th, bMono) (:1392)             -> other is a lastframe_view, cam required.
-        Returns (assigned, nmatches): assigned[f] is the row written into F.mvpMapPoints[f] (-1 = untouched)."""
+        Returns (assigned, nmatches): assigned[f] is the row written into F.mvpMapPoints[f] (-1 = untouched, -2 = reset to NULL by the
+        rotation histogram of the last-frame overload)."""
         m = self._matcher(self.device)
         if isinstance(other.struct, orbfe.MapPointsView):
             return m.search_by_projection_map(F, other, th, self.mfNNratio)

@@ -197,7 +197,7 @@ int orc_search_by_projection_last(const orbfe_frame_view* cur, const orbfe_camer
     orc::three_maxima(rotHist, ORBFE_HISTO_LENGTH, ind1, ind2, ind3);
     for (int b = 0; b < ORBFE_HISTO_LENGTH; ++b) {
       if (b == ind1 || b == ind2 || b == ind3) continue;
-      for (int f : rotHist[b]) { assigned[f] = -1; --nmatches; }
+      for (int f : rotHist[b]) { assigned[f] = -2; --nmatches; }  // :1527 mvpMapPoints[f] = NULL (not 'untouched')
     }
   }
   delete grid;

@@ -59,3 +59,11 @@ def test_product_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cc")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "pyoracle" not in txt and "orb_oracle" not in txt and "oracle/" not in txt, f
+
+
+def test_compat_matcher_compiles_without_gpu():
+    """compat/ORBmatcher.cc (the reference's signatures over the C ABI) compiles and links against liborbfe.so."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call(["make", "-C", os.path.join(root, "compat")])
+    assert os.path.exists(os.path.join(root, "compat", "_build", "test_compat_matcher"))

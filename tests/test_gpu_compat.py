@@ -40,3 +40,97 @@ def test_cpp_dropin_matches_oracle(oracle, tmp_path):
     assert nl == len(okl) and nr == len(okr) and nm == on
     assert np.array_equal(kp, okl) and np.array_equal(desc, odl)
     assert np.array_equal(ur, our) and np.array_equal(dp, odp)
+
+
+# ---- drop-in ORBmatcher (compat/ORBmatcher.cc): the reference's C++ signatures on mock Frame / KeyFrame / MapPoint
+# objects (compat/slam_min.h), results as the reference's callers observe them, against the oracle ----
+def _exe():
+    exe = os.path.join(ROOT, "compat", "_build", "test_compat_matcher")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "compat")])
+    return exe
+
+
+def _dump(d, **arrays):
+    os.makedirs(d, exist_ok=True)
+    for k, v in arrays.items():
+        np.ascontiguousarray(v).tofile(os.path.join(d, k + ".bin"))
+
+
+def _dump_frame(d, frame):
+    _dump(d, keys_un=frame["keys_un"], u_right=frame["u_right"].astype(np.float32), desc=frame["desc"],
+          mp_obs=frame["mp_obs"].astype(np.int32), scale_factors=frame["scale_factors"].astype(np.float32),
+          bounds=np.array(frame["bounds"], np.float32))
+
+
+@pytest.fixture(scope="module")
+def kitti_frame(oracle):
+    from cases import extract_with_oracle
+    _, _, _, (kp, desc) = extract_with_oracle(oracle, "kitti", 0)
+    w, h = synth.SHAPES["kitti"]
+    return synth.frame_arrays(kp, desc, (0.0, 0.0, float(w), float(h)), seed=0)
+
+
+def test_cpp_matcher_search_by_projection_map(oracle, kitti_frame, tmp_path):
+    from cases import views
+    frame = kitti_frame
+    mps = synth.map_points_case(frame, 20000, 1500, seed=0)
+    d = str(tmp_path)
+    _dump_frame(d, frame)
+    _dump(d, proj_x=mps["proj_x"], proj_y=mps["proj_y"], proj_xr=mps["proj_xr"], view_cos=mps["view_cos"],
+          level=mps["level"].astype(np.int32), obs=mps["obs"].astype(np.int32), in_view=mps["in_view"],
+          mp_desc=mps["desc"], params=np.array([1.0, 0.8], np.float32))
+    subprocess.check_call([_exe(), "map", d])
+    res = np.fromfile(os.path.join(d, "result.bin"), np.int32)
+    fv, mv = views(oracle, frame=frame, mps=mps)
+    want, n = oracle.search_by_projection_map(fv, mv, 1.0, 0.8)
+    assert res[-1] == n and n > 500
+    assert np.array_equal(res[:-1], want)
+
+
+def test_cpp_matcher_search_by_projection_last(oracle, kitti_frame, tmp_path):
+    from cases import views
+    frame = kitti_frame
+    last, cam = synth.last_frame_case(frame, seed=7)
+    d = str(tmp_path)
+    _dump_frame(d, frame)
+    camv = np.concatenate([np.asarray(cam["tcw"], np.float32).reshape(12),
+                           np.array([cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["mbf"], cam["mb"]], np.float32)])
+    _dump(d, cam=camv, valid=last["valid"], last_desc=last["desc"], world_pos=last["world_pos"].astype(np.float32),
+          angle=last["angle"].astype(np.float32), last_tcw=np.asarray(last["tcw"], np.float32).reshape(12),
+          obs=last["obs"].astype(np.int32), octave=last["octave"].astype(np.int32),
+          params=np.array([7.0, 0.0, 1.0], np.float32))
+    subprocess.check_call([_exe(), "last", d])
+    res = np.fromfile(os.path.join(d, "result.bin"), np.int32)
+    fv, lv, cv = views(oracle, frame=frame, last=last, cam=cam)
+    want, n = oracle.search_by_projection_last(fv, cv, lv, 7.0, False, True)
+    assert res[-1] == n and n > 300
+    # -2 (assigned, then reset to NULL by the rotation histogram) is only observable where a map point existed before
+    want_obs = np.where((want == -2) & (frame["mp_obs"] < 0), -1, want)
+    assert np.array_equal(res[:-1], want_obs)
+
+
+def test_cpp_matcher_triangulation_and_distance(oracle, kitti_frame, tmp_path):
+    from cases import views
+    k1, k2, F12, ep = synth.keyframe_pair_case(kitti_frame["keys_un"], kitti_frame["desc"], seed=3)
+    d = str(tmp_path)
+    for sub, k in (("kf1", k1), ("kf2", k2)):
+        _dump(os.path.join(d, sub), keys_un=k["keys_un"], u_right=k["u_right"], desc=k["desc"], has_mp=k["has_mp"],
+              node_ids=k["node_ids"].astype(np.uint32), node_offsets=k["node_offsets"].astype(np.int32),
+              node_features=k["node_features"].astype(np.int32), scale_factors=k["scale_factors"].astype(np.float32),
+              level_sigma2=k["level_sigma2"].astype(np.float32))
+    _dump(d, geom=np.concatenate([F12.reshape(9), np.array([ep[0], ep[1], 0.0, 0.0], np.float32)]).astype(np.float32))
+    subprocess.check_call([_exe(), "tri", d])
+    res = np.fromfile(os.path.join(d, "result.bin"), np.int32)
+    want = oracle.search_for_triangulation(views(oracle, kf=k1), views(oracle, kf=k2), F12, float(ep[0]), float(ep[1]),
+                                           False, False)
+    assert res[0] == len(want) and len(want) > 50
+    assert np.array_equal(res[1:].reshape(-1, 2), want)
+    # DescriptorDistance
+    rng = np.random.default_rng(5)
+    a = rng.integers(0, 256, (64, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (64, 32), dtype=np.uint8)
+    _dump(d, a=a, b=b)
+    subprocess.check_call([_exe(), "dist", d])
+    got = np.fromfile(os.path.join(d, "result.bin"), np.int32)
+    assert np.array_equal(got, np.unpackbits(a ^ b, axis=1).sum(1))
