@@ -5,6 +5,7 @@
 // geometry tables runs in the sm_100a kernels of k_*.cu.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -299,6 +300,7 @@ int orbfe_extractor_create(const orbfe_extractor_params* params, int width, int 
   }
   if (rc == ORBFE_OK && cudaEventCreateWithFlags(&e->done, cudaEventDisableTiming) != cudaSuccess) rc = ORBFE_ERR_CUDA;
   if (rc == ORBFE_OK) rc = configure_kernels(e->geom);
+  { const char* ng = getenv("ORBFE_NO_GRAPHS"); e->use_graph = !(ng && ng[0] == '1'); }
   if (rc != ORBFE_OK) { free_arenas(e); if (e->stream) cudaStreamDestroy(e->stream); delete e; return rc; }
   *out = reinterpret_cast<orbfe_extractor*>(e);
   return ORBFE_OK;
@@ -311,6 +313,8 @@ void orbfe_extractor_destroy(orbfe_extractor* h) {
   // a borrowed stream (orbfe_extractor_share_stream) may already be gone: wait for the whole device instead
   if (e->owns_stream) cudaStreamSynchronize(e->stream); else cudaDeviceSynchronize();
   free_arenas(e);
+  if (e->run_graph) cudaGraphExecDestroy(e->run_graph);
+  if (e->stereo_graph) cudaGraphExecDestroy(e->stereo_graph);
   if (e->done) cudaEventDestroy(e->done);
   if (e->owns_stream) cudaStreamDestroy(e->stream);
   delete e;
@@ -378,27 +382,50 @@ int orbfe_extract_upload(orbfe_extractor* h, const uint8_t* images, size_t image
   return ORBFE_OK;
 }
 
-int orbfe_extract_run(orbfe_extractor* h, int batch) {
-  ORBFE_ARG(h);
-  Extractor* e = reinterpret_cast<Extractor*>(h);
-  ORBFE_ARG(batch >= 1 && batch <= e->max_batch);
-  DeviceGuard guard(e->device);
+// the kernel schedule of operator() (:1065-1127) for `batch` images on e->stream
+static void issue_extract(Extractor* e, int batch, cudaEvent_t* ev) {
   const PyrGeom& g = e->geom;
   const ExtractorArena& a = e->arena;
-  ORBFE_CUDA(cudaMemsetAsync(a.cand_count, 0, (size_t)batch * kMaxLevels * sizeof(int32_t), e->stream));
-  ORBFE_CUDA(cudaMemsetAsync(a.flags, 0, (size_t)batch * sizeof(int32_t), e->stream));
-  cudaEvent_t* ev = (e->profiling && e->prof_runs < Extractor::kProfRuns) ? e->prof_ev + 6 * e->prof_runs : nullptr;
+  cudaMemsetAsync(a.cand_count, 0, (size_t)batch * kMaxLevels * sizeof(int32_t), e->stream);
+  cudaMemsetAsync(a.flags, 0, (size_t)batch * sizeof(int32_t), e->stream);
   if (ev) cudaEventRecord(ev[0], e->stream);
   for (int l = 1; l < g.nlevels; ++l) launch_pyramid_level(g, a, l, batch, e->stream);  // ComputePyramid (:1075)
   if (ev) cudaEventRecord(ev[1], e->stream);
-  launch_fast_cells(g, a, batch, e->stream);                      // :776-850
+  launch_fast_cells(g, a, batch, e->stream);                                             // :776-850
   if (ev) cudaEventRecord(ev[2], e->stream);
   launch_quadtree(g, a, batch, e->stream);                                               // :853
   if (ev) cudaEventRecord(ev[3], e->stream);
   launch_blur_levels(g, a, batch, e->stream);                                            // :1107-1108
   if (ev) cudaEventRecord(ev[4], e->stream);
   launch_describe(g, a, batch, e->stream);                                               // :873-874, :1096-1126
-  if (ev) { cudaEventRecord(ev[5], e->stream); ++e->prof_runs; }
+  if (ev) cudaEventRecord(ev[5], e->stream);
+}
+
+int orbfe_extract_run(orbfe_extractor* h, int batch) {
+  ORBFE_ARG(h);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  ORBFE_ARG(batch >= 1 && batch <= e->max_batch);
+  DeviceGuard guard(e->device);
+  const PyrGeom& g = e->geom;
+  cudaEvent_t* ev = (e->profiling && e->prof_runs < Extractor::kProfRuns) ? e->prof_ev + 6 * e->prof_runs : nullptr;
+  if (ev || !e->use_graph) {
+    issue_extract(e, batch, ev);
+    if (ev) ++e->prof_runs;
+  } else {
+    // one cudaGraphLaunch instead of 3 memsets + 11 kernel launches: what matters for single-frame latency, where
+    // the kernels are a few microseconds each.  Captured once per batch size, on the calling thread only.
+    if (!e->run_graph || e->run_graph_batch != batch) {
+      if (e->run_graph) { cudaGraphExecDestroy(e->run_graph); e->run_graph = nullptr; }
+      cudaGraph_t graph = nullptr;
+      ORBFE_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+      issue_extract(e, batch, nullptr);
+      ORBFE_CUDA(cudaStreamEndCapture(e->stream, &graph));
+      ORBFE_CUDA(cudaGraphInstantiate(&e->run_graph, graph, 0));
+      cudaGraphDestroy(graph);
+      e->run_graph_batch = batch;
+    }
+    ORBFE_CUDA(cudaGraphLaunch(e->run_graph, e->stream));
+  }
   e->launches += (g.nlevels - 1) + (g.fast_strips > 0 ? 1 : 0) + 3;
   e->last_batch = batch;
   ORBFE_CUDA(cudaGetLastError());

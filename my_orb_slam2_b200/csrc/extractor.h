@@ -23,6 +23,14 @@ struct Extractor {
   int32_t* h_flags = nullptr;   // pinned
   int64_t launches = 0;
   int last_batch = 0;
+  // orbfe_extract_run as one CUDA graph (captured lazily per batch size; ORBFE_NO_GRAPHS=1 disables)
+  bool use_graph = true;
+  cudaGraphExec_t run_graph = nullptr;
+  int run_graph_batch = 0;
+  cudaGraphExec_t stereo_graph = nullptr;  // orbfe_stereo_match_run with this handle as `left`
+  int stereo_graph_batch = 0;
+  const void* stereo_graph_right = nullptr;
+  float stereo_graph_mbf = 0.f, stereo_graph_mb = 0.f;
   // host side of an orbfe_extract_download_async not yet finished (counts are checked by orbfe_extract_finish)
   const int32_t* pending_counts = nullptr;
   int pending_batch = 0, pending_capacity = 0;

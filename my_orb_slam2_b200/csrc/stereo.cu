@@ -30,7 +30,26 @@ int orbfe_stereo_match_run(orbfe_extractor* hl, orbfe_extractor* hr, int batch, 
   cudaEvent_t* ev = nullptr;
   if (l->profiling && l->prof_ev && l->prof_stereo_runs < Extractor::kProfRuns)
     ev = l->prof_ev + 6 * Extractor::kProfRuns + 3 * l->prof_stereo_runs++;
-  launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream, ev);
+  if (ev || !l->use_graph) {
+    launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream, ev);
+  } else {
+    // the three stereo kernels as one graph launch (keyed by everything baked into the kernel parameters)
+    if (!l->stereo_graph || l->stereo_graph_batch != batch || l->stereo_graph_right != r || l->stereo_graph_mbf != mbf ||
+        l->stereo_graph_mb != mb) {
+      if (l->stereo_graph) { cudaGraphExecDestroy(l->stereo_graph); l->stereo_graph = nullptr; }
+      cudaGraph_t graph = nullptr;
+      ORBFE_CUDA(cudaStreamBeginCapture(l->stream, cudaStreamCaptureModeThreadLocal));
+      launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream, nullptr);
+      ORBFE_CUDA(cudaStreamEndCapture(l->stream, &graph));
+      ORBFE_CUDA(cudaGraphInstantiate(&l->stereo_graph, graph, 0));
+      cudaGraphDestroy(graph);
+      l->stereo_graph_batch = batch;
+      l->stereo_graph_right = r;
+      l->stereo_graph_mbf = mbf;
+      l->stereo_graph_mb = mb;
+    }
+    ORBFE_CUDA(cudaGraphLaunch(l->stereo_graph, l->stream));
+  }
   l->launches += kLaunchesPerStereo;
   ORBFE_CUDA(cudaGetLastError());
   return ORBFE_OK;
