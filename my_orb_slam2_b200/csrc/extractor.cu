@@ -105,7 +105,7 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
   g.ini_th = e->params.ini_th_fast < 0 ? 0 : (e->params.ini_th_fast > 255 ? 255 : e->params.ini_th_fast);
   g.min_th = e->params.min_th_fast < 0 ? 0 : (e->params.min_th_fast > 255 ? 255 : e->params.min_th_fast);
   unsigned long long pyr_off = 0;
-  int cells = 0, cand = 0, kept = 0, node_cap_max = 8, blur_tiles = 0, fast_strips = 0;
+  int cells = 0, cand = 0, kept = 0, node_cap_max = 8, blur_tiles = 0, blur_tiles_small = 0, fast_strips = 0;
   for (int l = 0; l < g.nlevels; ++l) {
     LevelGeom& L = g.lv[l];
     L.scale = info.scale_factors[l];
@@ -134,6 +134,8 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
     cells += L.n_cols * L.n_rows;
     L.blur_tile_base = blur_tiles;
     blur_tiles += ((L.w + 127) / 128) * ((L.h + 127) / 128);
+    L.blur_tile_base_small = blur_tiles_small;
+    blur_tiles_small += ((L.w + 127) / 128) * ((L.h + 31) / 32);
     L.fast_strip_base = fast_strips;
     L.fast_strips_x = 0;
     if (L.n_cols > 0) {  // detection domain x in [19, w-19), y in [19, h-19); owned columns start at x = 16
@@ -185,6 +187,7 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
   }
   g.total_cells = cells;
   g.blur_tiles = blur_tiles;
+  g.blur_tiles_small = blur_tiles_small;
   g.fast_strips = fast_strips;
   g.cand_total = std::max(cand, 4);
   g.kept_total = std::max(kept, 4);

@@ -19,6 +19,7 @@ struct LevelGeom {
   int w_cell, h_cell;       // (:798-799)
   int cell_base;            // id of this level's first cell within one image
   int blur_tile_base;       // id of this level's first 128x128 blur tile within one image
+  int blur_tile_base_small; // ... first 128x32 blur tile (launches that would not fill the GPU with 128x128 tiles)
   int fast_strip_base;      // id of this level's first FAST strip (k_fast.cu) within one image
   int fast_strips_x;        // strips per strip row (0 => level has no cells)
   int quota;                // mnFeaturesPerLevel[level] (:435-446)
@@ -40,6 +41,7 @@ struct PyrGeom {
   int nlevels;
   int total_cells;  // per image
   int blur_tiles;   // per image
+  int blur_tiles_small;
   int fast_strips;  // per image
   int cand_total;   // per image candidate capacity (sum over levels)
   int kept_total;   // per image kept capacity (sum over levels)

@@ -16,7 +16,7 @@
 
 namespace orbfe {
 
-constexpr int BL_TX = 32, BL_TY = 4, BL_ROWS = 32;  // CTA covers 128 x 128 pixels
+constexpr int BL_TX = 32, BL_TY = 4;  // CTA covers 128 x (4 * BL_ROWS) pixels; BL_ROWS = 32 (throughput) or 8 (few images)
 constexpr int BL_PF = 3;                            // rows of loads in flight per thread
 
 __device__ __forceinline__ int reflect101i(int p, int len) {
@@ -25,14 +25,16 @@ __device__ __forceinline__ int reflect101i(int p, int len) {
   return p;
 }
 
+template <int BL_ROWS>
 __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid_constant__ PyrGeom g,
                                                                     const uint8_t* __restrict__ pyr,
                                                                     uint8_t* __restrict__ blur) {
   int tile = blockIdx.x;
   int lvl = 0;
-  while (lvl + 1 < g.nlevels && tile >= g.lv[lvl + 1].blur_tile_base) ++lvl;
+  constexpr bool kTall = BL_ROWS == 32;
+  while (lvl + 1 < g.nlevels && tile >= (kTall ? g.lv[lvl + 1].blur_tile_base : g.lv[lvl + 1].blur_tile_base_small)) ++lvl;
   const LevelGeom& L = g.lv[lvl];
-  tile -= L.blur_tile_base;
+  tile -= kTall ? L.blur_tile_base : L.blur_tile_base_small;
   const int tiles_x = (L.w + 127) / 128;
   const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
   const int b = blockIdx.y;
@@ -132,9 +134,12 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
 }
 
 void launch_blur_levels(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
-  dim3 grid(g.blur_tiles, batch);
   dim3 block(BL_TX, BL_TY);
-  blur_levels_kernel<<<grid, block, 0, s>>>(g, a.pyr, a.blur);
+  if ((long long)g.blur_tiles * batch >= 2 * 148 * 4) {
+    blur_levels_kernel<32><<<dim3(g.blur_tiles, batch), block, 0, s>>>(g, a.pyr, a.blur);
+  } else {  // few images: 128 x 32 tiles (4x more CTAs, 8-row strips per thread)
+    blur_levels_kernel<8><<<dim3(g.blur_tiles_small, batch), block, 0, s>>>(g, a.pyr, a.blur);
+  }
 }
 
 }  // namespace orbfe

@@ -53,9 +53,11 @@ __global__ void __launch_bounds__(256) pyramid_level_generic_kernel(const __grid
   }
 }
 
-constexpr int PY_ROWS = 8;   // destination rows per thread
-constexpr int PY_WARPS = 4;  // warps per CTA, stacked vertically: a CTA covers 128 x 32 destination pixels
+constexpr int PY_WARPS = 4;  // warps per CTA, stacked vertically: a CTA covers 128 x (4 * PY_ROWS) destination pixels
+// PY_ROWS = destination rows per thread: 8 in throughput mode (source rows are reused by the rows that share them), 2
+// when the launch would not fill the GPU (single frames: shorter dependent chains per thread, 4x more CTAs)
 
+template <int PY_ROWS>
 __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __grid_constant__ PyrGeom g,
                                                                       uint8_t* __restrict__ pyr,
                                                                       const XTab* __restrict__ xtab,
@@ -135,8 +137,14 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
 void launch_pyramid_level(const PyrGeom& g, const ExtractorArena& a, int lvl, int batch, cudaStream_t s) {
   const LevelGeom& D = g.lv[lvl];
   if (D.resize_fast) {
-    dim3 grid((D.w + 127) / 128, (D.h + PY_ROWS * PY_WARPS - 1) / (PY_ROWS * PY_WARPS), batch);
-    pyramid_level_kernel<<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+    const int cols = (D.w + 127) / 128;
+    if ((long long)cols * ((D.h + 31) / 32) * batch >= 2 * 148 * 4) {
+      dim3 grid(cols, (D.h + 8 * PY_WARPS - 1) / (8 * PY_WARPS), batch);
+      pyramid_level_kernel<8><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+    } else {
+      dim3 grid(cols, (D.h + 2 * PY_WARPS - 1) / (2 * PY_WARPS), batch);
+      pyramid_level_kernel<2><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+    }
     return;
   }
   dim3 block(32, 8);
