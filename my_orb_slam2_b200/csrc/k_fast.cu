@@ -77,7 +77,7 @@ __device__ __forceinline__ int corner_strength(const uint8_t* p) {
   x[12] = p[-3];         x[13] = p[S - 3];      x[14] = p[2 * S - 2];   x[15] = p[3 * S - 1];
   const int v = p[0];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) x[i] = (x[i] * 0x00010001u) ^ 0x00FF0000u;  // low half p, high half 255-p
+  for (int i = 0; i < 16; ++i) x[i] = x[i] * 0xFFFF0001u + 0x00FF0000u;  // low half p, high half 255-p; one IMAD (FMA pipe)
   unsigned a3[16], a9[16];
 #pragma unroll
   for (int i = 0; i < 16; ++i) a3[i] = __vimin3_u16x2(x[i], x[(i + 1) & 15], x[(i + 2) & 15]);
