@@ -469,6 +469,15 @@ def run_gpu(args):
     dom = max(("pyramid", "fast", "quadtree", "blur", "describe"), key=lambda k: per_launch[k])
     achieved = alg[dom] * B / (per_launch[dom] * 1e-3) / 1e9 if per_launch[dom] > 0 else 0.0
     b_extract = W * H + lp + kp_per_img * 60  # compulsory bytes of the whole extraction per image
+    # DRAM traffic of the dominant kernel from the committed `ncu --set full` capture (profiles/, per launch of 64 images)
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        kname = {"fast": "fast_detect_kernel", "blur": "void blur_levels_kernel<32>", "describe": "describe_kernel",
+                 "pyramid": "void pyramid_level_kernel<8>", "quadtree": "quadtree_kernel"}[dom]
+        traffic = tj[kname]["dram_bytes_per_launch"] * B / tj[kname]["images"]
+    except Exception:
+        pass
     frames = B * args.steps * world
     value = frames / (ms_dev * 1e-3)
     line = {
@@ -487,7 +496,11 @@ def run_gpu(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
-                     "frac": achieved / peak_gbs, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src,
+                     "timed": "per-stage CUDA events on the handle's stream, %d steps run right after the timed region with "
+                              "the two handles serialised (the timed region overlaps their streams)" % args.steps,
+                     "bound_note": "every extraction kernel is bound by integer instruction issue (ALU pipe), not HBM: "
+                                   "see profiles/r1_kernels_full.md (issue slots busy, pipe utilisation)",
                      "algorithmic_bytes_per_launch": alg[dom] * B,
                      "extract_frac": (b_extract * 2 * B * args.steps / (ms_dev * 1e-3) / 1e9) / peak_gbs},
         "stages_ms_per_launch": per_launch,
