@@ -156,24 +156,42 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
   }
   __syncthreads();
 
-  // ---- 3. computeOrbDescriptor (:108-147) on the blurred level: lane -> descriptor byte (8 tests = 16 gathers);
-  // the lane's 32 pattern values stay in registers for the warp's 4 keypoints ----
+  // ---- 3. computeOrbDescriptor (:108-147) on the blurred level: lane -> descriptor byte (8 tests = 16 gathers).
+  // The 37 x 37 patch the rotated pattern can reach is first copied into shared memory with coalesced word loads
+  // (3 rows per warp instruction): a gather of 32 scattered bytes then costs ~3 bank-conflict wavefronts instead of
+  // ~20 L1 sectors — the gathers, not the arithmetic, bound this kernel.  The lane's 32 pattern values stay in
+  // registers for the warp's 4 keypoints. ----
+  constexpr int PW = 10;  // words per patch row: 37 bytes at any alignment fit 40 (3 rows = 30 lanes per load)
+  __shared__ unsigned patch_all[DESC_WARPS][37 * PW];
+  unsigned* patch = patch_all[warp];
+  const uint8_t* patch_b = reinterpret_cast<const uint8_t*>(patch);
   float pat[32];
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
     const float4 t = d_pattern_t.v[q][lane];
     pat[4 * q] = t.x; pat[4 * q + 1] = t.y; pat[4 * q + 2] = t.z; pat[4 * q + 3] = t.w;
   }
+  const int prow = lane / PW, pcol = lane - prow * PW;  // lanes 0..29: (row within a group of 3, word); lanes 30, 31 idle
 #pragma unroll 1
   for (int i = warp; i < DESC_KP; i += DESC_WARPS) {
     const KpSlot k = slot[i];
     if (k.lvl < 0) break;
     const LevelGeom& L = g.lv[k.lvl];
     const int step = L.pitch;
-    // 32-bit offsets: the rotated pattern reaches <= 18 px and the keypoint is >= 19 px inside the level
-    const uint8_t* base = blur + L.lvl_base + (size_t)b * L.lvl_bytes;
+    // rows ky-18 .. ky+18, bytes from the aligned address at or below kx-18 (the keypoint is >= 19 px inside the level)
+    const int x_al = (k.kx - 18) & ~3;
+    const uint8_t* base = blur + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)(k.ky - 18) * step + x_al;
     asm volatile("" : "+l"(base));
-    const int ctr = k.ky * step + k.kx;
+    __syncwarp();  // the previous keypoint's gathers are done
+    if (prow < 3) {
+#pragma unroll
+      for (int r0 = 0; r0 < 39; r0 += 3) {
+        const int r = r0 + prow;
+        if (r < 37) patch[r * PW + pcol] = __ldg(reinterpret_cast<const unsigned*>(base + (size_t)r * step) + pcol);
+      }
+    }
+    __syncwarp();
+    const int ctr = 18 * (PW * 4) + (k.kx - x_al);  // byte offset of the keypoint in the patch
     const float ca = k.ca, sb = k.sb;
     int val = 0;
 #pragma unroll
@@ -183,8 +201,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
       const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
       const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
       const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-      const int t0 = __ldg(base + (unsigned)(r0 * step + (c0 + ctr)));
-      const int t1 = __ldg(base + (unsigned)(r1 * step + (c1 + ctr)));
+      const int t0 = patch_b[r0 * (PW * 4) + (c0 + ctr)];
+      const int t1 = patch_b[r1 * (PW * 4) + (c1 + ctr)];
       val |= (t0 < t1) << j;
     }
     out_desc[((size_t)b * g.out_cap + oi0 + i) * 32 + lane] = (uint8_t)val;
