@@ -10,6 +10,8 @@
  *    evaluated in double with a fixed range reduction + fixed polynomial and
  *    rounded to float, instead of libm cosf/sinf whose bits are machine
  *    dependent.
+ *  - orb_log_f32        : logf for MapPoint::PredictScale (src/MapPoint.cc:406-444),
+ *    same construction.
  */
 #ifndef ORB_MATH_SHARED_H_
 #define ORB_MATH_SHARED_H_
@@ -23,6 +25,7 @@
 #define ORB_DMUL(a, b) __dmul_rn((a), (b))
 #define ORB_DADD(a, b) __dadd_rn((a), (b))
 #define ORB_DSUB(a, b) __dsub_rn((a), (b))
+#define ORB_DDIV(a, b) __ddiv_rn((a), (b))
 #else
 #if defined(__CUDACC__)
 #define ORB_HD __host__ __device__ inline
@@ -36,6 +39,7 @@
 #define ORB_DMUL(a, b) ((double)(a) * (double)(b))
 #define ORB_DADD(a, b) ((double)(a) + (double)(b))
 #define ORB_DSUB(a, b) ((double)(a) - (double)(b))
+#define ORB_DDIV(a, b) ((double)(a) / (double)(b))
 #endif
 
 /* cv::fastAtan2(y, x) in degrees, fp32, no FMA. */
@@ -112,6 +116,65 @@ ORB_HD void orb_sincos_deg(float angle_deg, float* cos_out, float* sin_out) {
   if (x < 0.0) sn = -sn;
   *cos_out = (float)cs;
   *sin_out = (float)sn;
+}
+
+/* Natural logarithm of a positive finite float, rounded to float: the value
+ * MapPoint::PredictScale needs (`log(ratio)` with a float argument is logf,
+ * src/MapPoint.cc:414,437).  Evaluated in double (x = m*2^e, m in
+ * [sqrt(1/2), sqrt(2)); log m = 2 atanh((m-1)/(m+1)), series to s^10;
+ * |error| < 1e-16 relative), so the float result is the correctly rounded one
+ * except with probability ~1e-8 and — the point — has the same bits on host
+ * and device.  x <= 0, inf and nan are not handled (callers gate them). */
+ORB_HD float orb_log_f32(float xf) {
+  double x = (double)xf;
+  long long bits;
+#if defined(__CUDA_ARCH__)
+  bits = __double_as_longlong(x);
+#else
+  __builtin_memcpy(&bits, &x, 8);
+#endif
+  int e = (int)((bits >> 52) & 0x7FF) - 1023;
+  long long mb = (bits & 0x000FFFFFFFFFFFFFLL) | 0x3FF0000000000000LL;
+  double m;
+#if defined(__CUDA_ARCH__)
+  m = __longlong_as_double(mb);
+#else
+  __builtin_memcpy(&m, &mb, 8);
+#endif
+  if (m > 1.41421356237309514547) { m = ORB_DMUL(m, 0.5); e += 1; }
+  const double f = ORB_DDIV(ORB_DSUB(m, 1.0), ORB_DADD(m, 1.0));
+  const double s = ORB_DMUL(f, f);
+  double p = 1.0 / 21.0;
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0 / 19.0);
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0 / 17.0);
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0 / 15.0);
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0 / 13.0);
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0 / 11.0);
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0 / 9.0);
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0 / 7.0);
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0 / 5.0);
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0 / 3.0);
+  p = ORB_DADD(ORB_DMUL(p, s), 1.0);
+  const double r = ORB_DMUL(ORB_DMUL(2.0, f), p);
+  const double ed = (double)e;
+  const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
+  return (float)ORB_DADD(ORB_DMUL(ed, LN2_HI), ORB_DADD(r, ORB_DMUL(ed, LN2_LO)));
+}
+
+/* MapPoint::PredictScale (src/MapPoint.cc:406-444): ratio = mfMaxDistance / dist,
+ * nScale = ceil(log(ratio) / mfLogScaleFactor) clamped to [0, nlevels-1].  The clamp
+ * is applied in float so that inf / nan / huge values convert identically on
+ * host and device (ratio <= 0 or nan -> 0). */
+ORB_HD int orb_predict_scale(float max_distance, float current_dist, float log_scale_factor, int nlevels) {
+  const float ratio = ORB_FDIV(max_distance, current_dist);
+  if (!(ratio > 0.f)) return 0;
+  if (ratio > 3.0e38f) return nlevels - 1;
+  const float q = ORB_FDIV(orb_log_f32(ratio), log_scale_factor);
+  if (!(q > -1.f)) return 0;               /* ceil(q) <= -1, or nan */
+  if (q > (float)(nlevels - 1)) return nlevels - 1;
+  const int t = (int)q;                    /* trunc; q in (-1, nlevels-1] */
+  const int c = ((float)t < q) ? t + 1 : t;
+  return c < 0 ? 0 : c;
 }
 
 #endif /* ORB_MATH_SHARED_H_ */

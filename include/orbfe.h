@@ -176,6 +176,57 @@ int orbfe_search_for_triangulation(orbfe_matcher* m, const orbfe_keyframe_view* 
                                    const orbfe_keyframe_view* kf2, const float* F12, float ex, float ey,
                                    int only_stereo, int check_ori, int32_t* pairs, int cap, int32_t* n_pairs);
 
+/* ---- the seven other ORBmatcher members ---- */
+
+/* ORBmatcher::SearchByBoW, both overloads.  Feature vectors in CSR form as for
+ * SearchForTriangulation; every feature index must appear in at most one node
+ * (DBoW2 FeatureVector invariant).  has_mp = "map point present and not bad".
+ *  kf_kf = 0: SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches) (src/ORBmatcher.cc:182-319); kf1 = pKF,
+ *             kf2 = F (its has_mp is not read); matches[f], f < kf2->n, = index of the pKF feature whose map point
+ *             is written to vpMapPointMatches[f], -1 = NULL.
+ *  kf_kf = 1: SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) (:563-696); matches[idx1], idx1 < kf1->n, = idx2 with
+ *             vpMatches12[idx1] = vpMapPoints2[idx2], -1 = NULL.
+ * *n_matches = return value. */
+int orbfe_search_by_bow(orbfe_matcher* m, const orbfe_keyframe_view* kf1, const orbfe_keyframe_view* kf2, int kf_kf,
+                        float nnratio, int check_ori, int32_t* matches, int32_t* n_matches);
+
+/* ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:446-561).  prev_matched = vbPrevMatched as n1 x 2 floats,
+ * updated in place (:556-558); matches12 = vnMatches12. */
+int orbfe_search_for_initialization(orbfe_matcher* m, const orbfe_frame_view* f1, const orbfe_frame_view* f2,
+                                    float* prev_matched, int window, float nnratio, int check_ori,
+                                    int32_t* matches12, int32_t* n_matches);
+
+/* ORBmatcher::SearchByProjection(Frame& Cur, KeyFrame* pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1540-1667).
+ * pts = pKF->GetMapPointMatches() (valid = present, not bad, not in sAlreadyFound; angle = pKF->mvKeysUn[i].angle);
+ * cur->mp_obs[f] >= 0 means Cur.mvpMapPoints[f] != NULL.  assigned[f] = row of pts written to Cur.mvpMapPoints[f],
+ * -1 = untouched, -2 = written and reset to NULL by the rotation check (:1659). */
+int orbfe_search_by_projection_reloc(orbfe_matcher* m, const orbfe_frame_view* cur, const orbfe_projection* pr,
+                                     const orbfe_points3d_view* pts, float th, int orb_dist, int check_ori,
+                                     int32_t* assigned, int32_t* n_matches);
+
+/* ORBmatcher::SearchByProjection(KeyFrame* pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:321-434).
+ * kf->mp_obs[f] >= 0 means vpMatched[f] != NULL on entry; valid = !isBad() && not in spAlreadyFound.
+ * assigned[f] = row written to vpMatched[f], -1 = untouched. */
+int orbfe_search_by_projection_sim3(orbfe_matcher* m, const orbfe_frame_view* kf, const orbfe_projection* pr,
+                                    const orbfe_points3d_view* pts, int th, int32_t* assigned, int32_t* n_matches);
+
+/* The SEARCH of ORBmatcher::Fuse, both overloads (src/ORBmatcher.cc:879-1029 with pr->is_sim3 = 0, has_ow = 1;
+ * :1033-1156 with is_sim3 = 1): best_idx[i] = bestIdx of point i when bestDist <= TH_LOW, else -1.  The search of a
+ * point reads nothing that earlier points write; the map surgery that follows it (Replace / AddObservation /
+ * AddMapPoint / vpReplacePoint, :1008-1023, :1140-1150) is the caller's, walking best_idx in order.
+ * valid = pMP && !isBad() && !IsInKeyFrame(pKF) (resp. not in pKF->GetMapPoints()).  inv_level_sigma2 =
+ * pKF->mvInvLevelSigma2 (first overload only). */
+int orbfe_fuse(orbfe_matcher* m, const orbfe_frame_view* kf, const orbfe_projection* pr,
+               const orbfe_points3d_view* pts, float th, const float* inv_level_sigma2, int32_t* best_idx,
+               int32_t* n_fused);
+
+/* ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1158-1382).  p1 / p2 = GetMapPointMatches() of the keyframes
+ * (m == n; valid = present, not bad, not vbAlreadyMatched).  match12[i1] = idx2 of the mutually agreeing pairs
+ * (vpMatches12[i1] = vpMapPoints2[idx2]), -1 otherwise.  *n_found = return value. */
+int orbfe_search_by_sim3(orbfe_matcher* m, const orbfe_frame_view* kf1, const orbfe_frame_view* kf2,
+                         const orbfe_points3d_view* p1, const orbfe_points3d_view* p2, const orbfe_sim3_pair* s,
+                         float th, int32_t* match12, int32_t* n_found);
+
 /* Brute-force Hamming (BASELINE.json config 5): per query the two smallest
  * keys (dist << 32 | index_base + j) over the map shard (index_base + nm <= 2^32); ties -> lowest index.
  * Host arrays in/out. */

@@ -126,6 +126,43 @@ typedef struct orbfe_keyframe_view {
   const float* level_sigma2;     /* mvLevelSigma2 */
 } orbfe_keyframe_view;
 
+/* Map points given by their 3-D position, as the projection searches that do
+ * NOT go through Frame::isInFrustum read them (src/ORBmatcher.cc:321-434,
+ * 879-1156, 1158-1382, 1540-1667; accessors src/MapPoint.cc:394-444). */
+typedef struct orbfe_points3d_view {
+  int32_t m;
+  const uint8_t* valid;      /* row takes part: pMP!=NULL && !isBad() && not in the
+                                method's own skip set (sAlreadyFound, IsInKeyFrame,
+                                vbAlreadyMatched) */
+  const float* world_pos;    /* GetWorldPos(), m x 3 */
+  const float* normal;       /* GetNormal(), m x 3; NULL where the method does not read it */
+  const float* max_distance; /* mfMaxDistance (GetMaxDistanceInvariance() = 1.2f * it) */
+  const float* min_distance; /* mfMinDistance (GetMinDistanceInvariance() = 0.8f * it) */
+  const uint8_t* desc;       /* GetDescriptor(), m x 32 */
+  const float* angle;        /* relocalisation overload only: pKF->mvKeysUn[i].angle */
+} orbfe_points3d_view;
+
+/* Pose + calibration of the frame / keyframe the points are projected into. */
+typedef struct orbfe_projection {
+  float tcw[12];           /* rows 0..2 of Tcw (3x4 row-major), or of the Sim3 Scw when
+                              is_sim3 (decomposed as src/ORBmatcher.cc:329-334) */
+  int32_t is_sim3;
+  int32_t has_ow;          /* 1: ow[] is KeyFrame::GetCameraCenter() (Fuse, :890);
+                              0: Ow = -Rcw^T tcw is derived from tcw (:334, :1046, :1546) */
+  float ow[3];
+  float fx, fy, cx, cy, bf;
+  float log_scale_factor;  /* mfLogScaleFactor of the target (MapPoint::PredictScale) */
+} orbfe_projection;
+
+/* Everything ORBmatcher::SearchBySim3 reads besides the two keyframes' features
+ * and map points (src/ORBmatcher.cc:1158-1177). */
+typedef struct orbfe_sim3_pair {
+  float t1w[12], t2w[12];  /* pKF1 / pKF2 pose rows 0..2 */
+  float s12, r12[9], t12[3];
+  float fx, fy, cx, cy;    /* pKF1's intrinsics, used for BOTH directions (:1161-1164) */
+  float log_scale_factor1, log_scale_factor2;
+} orbfe_sim3_pair;
+
 #ifdef __cplusplus
 }
 #endif

@@ -16,62 +16,9 @@
 //      rows above it cannot lower "exists claimer < i"), and in practice after 2-4
 //      iterations; the loop stops when B does not change.  First-wins ties are kept by
 //      walking the candidate list in traversal order with strict '<'.
-#include <climits>
-
-#include "match_kernels.h"
+#include "search_common.cuh"
 
 namespace orbfe {
-
-constexpr int GRID_COLS = ORBFE_GRID_COLS, GRID_ROWS = ORBFE_GRID_ROWS, GRID_CELLS = GRID_COLS * GRID_ROWS;
-constexpr int TH_HIGH = ORBFE_TH_HIGH, TH_LOW = ORBFE_TH_LOW, HISTO = ORBFE_HISTO_LENGTH;
-
-__device__ __forceinline__ int hamming32(const uint8_t* a, const uint8_t* b) {
-  const uint4* pa = reinterpret_cast<const uint4*>(a);
-  const uint4* pb = reinterpret_cast<const uint4*>(b);
-  const uint4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
-  return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-         __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
-}
-
-// exclusive scan of a[0..n) in place by one CTA of 1024 threads; returns the total
-__device__ int cta_excl_scan(int32_t* a, int n, int* wtmp) {
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, T = blockDim.x;
-  const int per = (n + T - 1) / T;
-  const int beg = min(tid * per, n), end = min(beg + per, n);
-  int s = 0;
-  for (int i = beg; i < end; ++i) s += a[i];
-  int v = s;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int t = __shfl_up_sync(0xffffffffu, v, o);
-    if (lane >= o) v += t;
-  }
-  if (lane == 31) wtmp[wid] = v;
-  __syncthreads();
-  if (wid == 0) {
-    int w = lane < (T >> 5) ? wtmp[lane] : 0;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, w, o);
-      if (lane >= o) w += t;
-    }
-    wtmp[lane] = w;
-  }
-  __syncthreads();
-  int run = (wid > 0 ? wtmp[wid - 1] : 0) + v - s;
-  const int total = wtmp[(T >> 5) - 1];
-  for (int i = beg; i < end; ++i) { const int t = a[i]; a[i] = run; run += t; }
-  __syncthreads();
-  return total;
-}
-
-// ---- Frame::AssignFeaturesToGrid + PosInGrid (src/Frame.cc:243-258, :407-417) ----
-__device__ __forceinline__ int pos_in_grid(const DevFrame& f, const orbfe_keypoint& kp) {
-  const int px = (int)roundf(__fmul_rn(__fsub_rn(kp.x, f.min_x), f.inv_w));
-  const int py = (int)roundf(__fmul_rn(__fsub_rn(kp.y, f.min_y), f.inv_h));
-  if (px < 0 || px >= GRID_COLS || py < 0 || py >= GRID_ROWS) return -1;
-  return px * GRID_ROWS + py;  // mGrid[x][y]
-}
 
 __global__ void __launch_bounds__(1024) build_grid_kernel(const DevFrame f) {
   __shared__ int32_t cnt[GRID_CELLS + 1];
@@ -104,38 +51,6 @@ __global__ void __launch_bounds__(1024) build_grid_kernel(const DevFrame f) {
       f.cell_items[j + 1] = v;
     }
   }
-}
-
-// Frame::GetFeaturesInArea (src/Frame.cc:351-405) as a visitor; fn(idx) is called in the reference's order
-template <typename Fn>
-__device__ __forceinline__ void features_in_area(const DevFrame& f, float x, float y, float r, int min_level,
-                                                 int max_level, Fn fn) {
-  const int min_cx = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, f.min_x), r), f.inv_w)));
-  if (min_cx >= GRID_COLS) return;
-  const int max_cx = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, f.min_x), r), f.inv_w)));
-  if (max_cx < 0) return;
-  const int min_cy = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, f.min_y), r), f.inv_h)));
-  if (min_cy >= GRID_ROWS) return;
-  const int max_cy = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, f.min_y), r), f.inv_h)));
-  if (max_cy < 0) return;
-  const bool check_levels = (min_level > 0) || (max_level >= 0);
-  for (int ix = min_cx; ix <= max_cx; ++ix) {
-    const int b = f.cell_start[ix * GRID_ROWS + min_cy], e = f.cell_start[ix * GRID_ROWS + max_cy + 1];
-    for (int p = b; p < e; ++p) {  // cells iy = min_cy..max_cy of column ix are contiguous in the CSR
-      const int idx = f.cell_items[p];
-      const orbfe_keypoint kp = f.keys[idx];
-      if (check_levels) {
-        if (kp.octave < min_level) continue;
-        if (max_level >= 0 && kp.octave > max_level) continue;
-      }
-      const float dx = __fsub_rn(kp.x, x), dy = __fsub_rn(kp.y, y);
-      if (fabsf(dx) < r && fabsf(dy) < r) fn(idx, kp.octave);
-    }
-  }
-}
-
-__device__ __forceinline__ uint32_t pack_sc(int idx, int dist, int oct) {
-  return (uint32_t)idx | ((uint32_t)dist << 16) | ((uint32_t)oct << 25);
 }
 
 // ---- SearchByProjection(Frame&, const vector<MapPoint*>&, th): candidates (src/ORBmatcher.cc:46-118) ----
@@ -240,34 +155,10 @@ __global__ void __launch_bounds__(1024) scan_counts_kernel(int32_t* counts, int 
   if (threadIdx.x == 0) { counts[rows] = carry; *total = carry; }
 }
 
-// ---- rotation histogram helpers (:1499-1509, :1669-1710) ----
-__device__ __forceinline__ int rot_bin(float a1, float a2) {
-  const float factor = 1.0f / HISTO;
-  float rot = __fsub_rn(a1, a2);
-  if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-  int bin = (int)roundf(__fmul_rn(rot, factor));
-  if (bin == HISTO) bin = 0;
-  return bin;
-}
-
-// ORBmatcher::ComputeThreeMaxima on the bin sizes
-__device__ void three_maxima(const int* histo, int& ind1, int& ind2, int& ind3) {
-  int max1 = 0, max2 = 0, max3 = 0;
-  ind1 = ind2 = ind3 = -1;
-  for (int i = 0; i < HISTO; ++i) {
-    const int s = histo[i];
-    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
-    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
-    else if (s > max3) { max3 = s; ind3 = i; }
-  }
-  if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
-  else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
-}
-
 // ---- ordered claim resolution + rotation histogram; one CTA ----
 __global__ void __launch_bounds__(1024) resolve_kernel(const DevFrame f, int rows, const int32_t* __restrict__ row_obs,
                                                        const float* __restrict__ row_angle, int mode, float nnratio,
-                                                       int check_ori, SearchScratch sc) {
+                                                       int check_ori, int accept_th, SearchScratch sc) {
   __shared__ int s_changed, s_nmatch, s_ind[3];
   __shared__ int s_hist[HISTO];
   const int tid = threadIdx.x, T = blockDim.x;
@@ -290,7 +181,7 @@ __global__ void __launch_bounds__(1024) resolve_kernel(const DevFrame f, int row
         else if (dist < best2) { lvl2 = oct; best2 = dist; }
       }
       int res = -1;
-      if (best <= TH_HIGH) {
+      if (best <= accept_th) {
         if (mode == 0) {
           if (!(lvl == lvl2 && (float)best > __fmul_rn(nnratio, (float)best2))) res = best_idx;  // :121-124
         } else {
@@ -298,7 +189,7 @@ __global__ void __launch_bounds__(1024) resolve_kernel(const DevFrame f, int row
         }
       }
       sc.result[i] = res;
-      if (res >= 0 && row_obs[i] > 0) atomicMin(&b_new[res], i);
+      if (res >= 0 && (row_obs == nullptr || row_obs[i] > 0)) atomicMin(&b_new[res], i);
     }
     __syncthreads();
     int diff = 0;
@@ -467,8 +358,8 @@ void launch_scan_counts(int32_t* counts, int rows, int32_t* total, cudaStream_t 
 }
 
 void launch_resolve(const DevFrame& f, int rows, const int32_t* row_obs, const float* row_angle, int mode,
-                    float nnratio, int check_ori, const SearchScratch& sc, cudaStream_t s) {
-  resolve_kernel<<<1, 1024, 0, s>>>(f, rows, row_obs, row_angle, mode, nnratio, check_ori, sc);
+                    float nnratio, int check_ori, int accept_th, const SearchScratch& sc, cudaStream_t s) {
+  resolve_kernel<<<1, 1024, 0, s>>>(f, rows, row_obs, row_angle, mode, nnratio, check_ori, accept_th, sc);
 }
 
 void launch_triangulation(const DevKeyFrame& k1, const DevKeyFrame& k2, const float* F12, float ex, float ey,

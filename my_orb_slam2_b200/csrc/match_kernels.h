@@ -84,14 +84,55 @@ void launch_sbp_map_candidates(const DevFrame& f, const DevMapPoints& mp, float 
 void launch_sbp_last_candidates(const DevFrame& f, const DevLastFrame& lf, const orbfe_camera_pose& cam, float th,
                                 int mono, const SearchScratch& sc, int fill, cudaStream_t s);
 void launch_scan_counts(int32_t* counts, int rows, int32_t* total, cudaStream_t s);
-// ordered claim resolution + rotation histogram; mode 0 = map overload (ratio test), 1 = last frame
+// ordered claim resolution + rotation histogram; mode 0 = map overload (ratio test), 1 = best only
+// (last frame / relocalisation / Sim3 overloads).  row_obs == nullptr: every row's claim blocks later rows.
+// accept_th: bestDist <= accept_th (TH_HIGH, TH_LOW or the caller's ORBdist).
 void launch_resolve(const DevFrame& f, int rows, const int32_t* row_obs, const float* row_angle, int mode,
-                    float nnratio, int check_ori, const SearchScratch& sc, cudaStream_t s);
+                    float nnratio, int check_ori, int accept_th, const SearchScratch& sc, cudaStream_t s);
 // SearchForTriangulation
 float host_tlc_z(const float* tcw_cur, const float* tcw_last);
 void launch_triangulation(const DevKeyFrame& k1, const DevKeyFrame& k2, const float* F12 /*device, 9*/, float ex,
                           float ey, int only_stereo, int check_ori, int32_t* matches12 /*[k1.n]*/,
                           int32_t* flags /*[k1.n+1]*/, int32_t* pairs, int cap, int32_t* n_pairs, int total_entries,
                           cudaStream_t s);
+
+// ---- k_search2.cu: the seven other ORBmatcher members ----
+struct DevPoints {  // device mirror of orbfe_points3d_view
+  int m;
+  const uint8_t* valid;
+  const float *world_pos, *normal, *max_d, *min_d, *angle;
+  const uint8_t* desc;
+};
+
+// Rcw / tcw / Ow of the target (already decomposed when the caller passed a Sim3) and, for SearchBySim3, the second
+// transform applied after the first (p3Dc2 = sR21*(R1w*X + t1w) + t21, src/ORBmatcher.cc:1215-1216).
+struct DevProjection {
+  float R[9], t[3], Ow[3];
+  float R2[9], t2[3];
+  float fx, fy, cx, cy, bf, log_sf;
+};
+
+enum ProjMode {
+  PM_RELOC = 0,      // SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist)   :1540-1667
+  PM_SIM3 = 1,       // SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th)          :321-434
+  PM_FUSE = 2,       // Fuse(KeyFrame*, vpMapPoints, th)                                     :879-1029
+  PM_FUSE_SIM3 = 3,  // Fuse(KeyFrame*, Scw, vpPoints, th, vpReplacePoint)                   :1033-1156
+  PM_BYSIM3 = 4      // one direction of SearchBySim3                                        :1204-1361
+};
+
+void launch_proj_candidates(int mode, const DevFrame& f, const DevPoints& p, const DevProjection& P, float th,
+                            const SearchScratch& sc, int fill, cudaStream_t s);
+void launch_proj_best(int mode, const DevFrame& f, const DevPoints& p, const DevProjection& P, float th,
+                      const float* inv_sigma2, int accept_th, int32_t* best_idx, int32_t* n_found, cudaStream_t s);
+void launch_sim3_agree(const int32_t* m1, int n1, const int32_t* m2, int n2, int32_t* out12, int32_t* n_found,
+                       cudaStream_t s);
+// SearchByBoW: claimed2 [k2.n] zeroed, matches [n_out] = -1 on entry
+void launch_bow(const DevKeyFrame& k1, const DevKeyFrame& k2, int kf_kf, float nnratio, int check_ori,
+                int32_t* claimed2, int32_t* matches, int n_out, int32_t* n_matches, cudaStream_t s);
+void launch_init_candidates(const DevFrame& f2, const orbfe_keypoint* keys1, const uint8_t* desc1, int n1,
+                            const float* prev, float window, const SearchScratch& sc, int fill, cudaStream_t s);
+int launch_init_resolve(const DevFrame& f2, const orbfe_keypoint* keys1, int n1, float nnratio, int check_ori,
+                        const SearchScratch& sc, int32_t* m12, int32_t* m21, float* prev, int32_t* n_matches,
+                        cudaStream_t s);
 
 }  // namespace orbfe

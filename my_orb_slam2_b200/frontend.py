@@ -149,6 +149,30 @@ def keyframe_view(keys_un, u_right, desc, has_mp, node_ids, node_offsets, node_f
     return _View(s, a)
 
 
+def points3d_view(valid, world_pos, normal, max_distance, min_distance, desc, angle=None):
+    """Map points given by position (include/orbfe_types.h: orbfe_points3d_view)."""
+    a = [np.ascontiguousarray(valid, np.uint8), np.ascontiguousarray(world_pos, np.float32),
+         None if normal is None else np.ascontiguousarray(normal, np.float32),
+         np.ascontiguousarray(max_distance, np.float32), np.ascontiguousarray(min_distance, np.float32),
+         np.ascontiguousarray(desc, np.uint8), None if angle is None else np.ascontiguousarray(angle, np.float32)]
+    s = orbfe.Points3DView(len(a[0]), *[None if x is None else _p(x) for x in a])
+    return _View(s, a)
+
+
+def _f(vals, n):
+    return (C.c_float * n)(*[float(x) for x in np.asarray(vals, np.float32).reshape(-1)[:n]])
+
+
+def projection(tcw, fx, fy, cx, cy, bf, log_scale_factor, is_sim3=False, ow=None):
+    """Pose (or Sim3) + calibration of the projection target (orbfe_projection)."""
+    return orbfe.Projection(_f(tcw, 12), int(is_sim3), int(ow is not None), _f(ow if ow is not None else [0, 0, 0], 3),
+                            fx, fy, cx, cy, bf, log_scale_factor)
+
+
+def sim3_pair(t1w, t2w, s12, r12, t12, fx, fy, cx, cy, log_sf1, log_sf2):
+    return orbfe.Sim3Pair(_f(t1w, 12), _f(t2w, 12), s12, _f(r12, 9), _f(t12, 3), fx, fy, cx, cy, log_sf1, log_sf2)
+
+
 class ORBmatcher:
     """ORBmatcher(nnratio=0.6, checkOri=true) (include/ORBmatcher.h:45; src/ORBmatcher.cc:40-42)."""
 
@@ -184,6 +208,34 @@ class ORBmatcher:
         """(KeyFrame*, KeyFrame*, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:702); returns the pair list."""
         return self._matcher(self.device).search_for_triangulation(kf1, kf2, F12, float(epipole[0]), float(epipole[1]),
                                                                    bOnlyStereo, self.mbCheckOrientation)
+
+    def SearchByBoW(self, kf, other, kf_kf=False):
+        """(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:182) when kf_kf is False -> matches[f] = index of
+        the keyframe feature whose map point lands in vpMapPointMatches[f]; (KeyFrame*, KeyFrame*, vpMatches12) (:563)
+        when True -> matches[idx1] = idx2.  Returns (matches, nmatches)."""
+        return self._matcher(self.device).search_by_bow(kf, other, kf_kf, self.mfNNratio, self.mbCheckOrientation)
+
+    def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
+        """(Frame&, Frame&, vbPrevMatched, vnMatches12, windowSize) (:446); returns (vnMatches12, vbPrevMatched', n)."""
+        return self._matcher(self.device).search_for_initialization(F1, F2, vbPrevMatched, windowSize, self.mfNNratio,
+                                                                    self.mbCheckOrientation)
+
+    def SearchByProjectionReloc(self, Cur, proj, pts, th, ORBdist):
+        """(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (:1540); returns (assigned, nmatches)."""
+        return self._matcher(self.device).search_by_projection_reloc(Cur, proj, pts, th, ORBdist,
+                                                                     self.mbCheckOrientation)
+
+    def SearchByProjectionSim3(self, kf, proj, pts, th):
+        """(KeyFrame*, Scw, vpPoints, vpMatched, th) (:321); returns (assigned, nmatches)."""
+        return self._matcher(self.device).search_by_projection_sim3(kf, proj, pts, th)
+
+    def Fuse(self, kf, proj, pts, th=3.0, inv_level_sigma2=None):
+        """The search of both Fuse overloads (:879, :1033); returns (best_idx per point, nFused)."""
+        return self._matcher(self.device).fuse(kf, proj, pts, th, inv_level_sigma2)
+
+    def SearchBySim3(self, kf1, kf2, p1, p2, pair, th):
+        """(KeyFrame*, KeyFrame*, vpMatches12, s12, R12, t12, th) (:1158); returns (match12, nFound)."""
+        return self._matcher(self.device).search_by_sim3(kf1, kf2, p1, p2, pair, th)
 
 
 class Frame:

@@ -65,6 +65,24 @@ class KeyFrameView(C.Structure):
                 ("scale_factors", C.c_void_p), ("level_sigma2", C.c_void_p)]
 
 
+class Points3DView(C.Structure):
+    _fields_ = [("m", C.c_int32), ("valid", C.c_void_p), ("world_pos", C.c_void_p), ("normal", C.c_void_p),
+                ("max_distance", C.c_void_p), ("min_distance", C.c_void_p), ("desc", C.c_void_p),
+                ("angle", C.c_void_p)]
+
+
+class Projection(C.Structure):
+    _fields_ = [("tcw", C.c_float * 12), ("is_sim3", C.c_int32), ("has_ow", C.c_int32), ("ow", C.c_float * 3),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("bf", C.c_float),
+                ("log_scale_factor", C.c_float)]
+
+
+class Sim3Pair(C.Structure):
+    _fields_ = [("t1w", C.c_float * 12), ("t2w", C.c_float * 12), ("s12", C.c_float), ("r12", C.c_float * 9),
+                ("t12", C.c_float * 3), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("log_scale_factor1", C.c_float), ("log_scale_factor2", C.c_float)]
+
+
 # every symbol include/orbfe.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
 _I = C.c_int
@@ -108,6 +126,15 @@ SYMBOLS = {
                                              C.POINTER(LastFrameView), _F, _I, _I, _P, _P]),
     "orbfe_search_for_triangulation": (_I, [_P, C.POINTER(KeyFrameView), C.POINTER(KeyFrameView), _P, _F, _F, _I, _I,
                                             _P, _I, _P]),
+    "orbfe_search_by_bow": (_I, [_P, C.POINTER(KeyFrameView), C.POINTER(KeyFrameView), _I, _F, _I, _P, _P]),
+    "orbfe_search_for_initialization": (_I, [_P, C.POINTER(FrameView), C.POINTER(FrameView), _P, _I, _F, _I, _P, _P]),
+    "orbfe_search_by_projection_reloc": (_I, [_P, C.POINTER(FrameView), C.POINTER(Projection),
+                                              C.POINTER(Points3DView), _F, _I, _I, _P, _P]),
+    "orbfe_search_by_projection_sim3": (_I, [_P, C.POINTER(FrameView), C.POINTER(Projection),
+                                             C.POINTER(Points3DView), _I, _P, _P]),
+    "orbfe_fuse": (_I, [_P, C.POINTER(FrameView), C.POINTER(Projection), C.POINTER(Points3DView), _F, _P, _P, _P]),
+    "orbfe_search_by_sim3": (_I, [_P, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(Points3DView),
+                                  C.POINTER(Points3DView), C.POINTER(Sim3Pair), _F, _P, _P]),
     "orbfe_hamming_bruteforce": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_bruteforce_device": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_merge_device": (_I, [_P, _P, _P, _I, _I, _P, _P]),
@@ -325,6 +352,52 @@ class Matcher:
                                                    int(only_stereo), int(check_ori), _p(pairs), len(pairs),
                                                    C.byref(n)))
         return pairs[:n.value].copy()
+
+    def search_by_bow(self, kf1, kf2, kf_kf, nnratio, check_ori):
+        n_out = kf1.struct.n if kf_kf else kf2.struct.n
+        matches = np.empty(max(n_out, 1), np.int32)
+        n = C.c_int32()
+        check(lib().orbfe_search_by_bow(self._h, C.byref(kf1.struct), C.byref(kf2.struct), int(kf_kf), nnratio,
+                                        int(check_ori), _p(matches), C.byref(n)))
+        return matches[:n_out], n.value
+
+    def search_for_initialization(self, f1, f2, prev_matched, window, nnratio, check_ori):
+        prev = np.array(prev_matched, np.float32).reshape(-1, 2).copy()
+        assert len(prev) == f1.struct.n
+        m12 = np.empty(max(f1.struct.n, 1), np.int32)
+        n = C.c_int32()
+        check(lib().orbfe_search_for_initialization(self._h, C.byref(f1.struct), C.byref(f2.struct), _p(prev),
+                                                    int(window), nnratio, int(check_ori), _p(m12), C.byref(n)))
+        return m12[:f1.struct.n], prev, n.value
+
+    def search_by_projection_reloc(self, cur, proj, pts, th, orb_dist, check_ori):
+        assigned = np.empty(max(cur.struct.n, 1), np.int32)
+        n = C.c_int32()
+        check(lib().orbfe_search_by_projection_reloc(self._h, C.byref(cur.struct), C.byref(proj), C.byref(pts.struct),
+                                                     th, int(orb_dist), int(check_ori), _p(assigned), C.byref(n)))
+        return assigned[:cur.struct.n], n.value
+
+    def search_by_projection_sim3(self, kf, proj, pts, th):
+        assigned = np.empty(max(kf.struct.n, 1), np.int32)
+        n = C.c_int32()
+        check(lib().orbfe_search_by_projection_sim3(self._h, C.byref(kf.struct), C.byref(proj), C.byref(pts.struct),
+                                                    int(th), _p(assigned), C.byref(n)))
+        return assigned[:kf.struct.n], n.value
+
+    def fuse(self, kf, proj, pts, th, inv_level_sigma2=None):
+        best = np.empty(max(pts.struct.m, 1), np.int32)
+        n = C.c_int32()
+        sig = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+        check(lib().orbfe_fuse(self._h, C.byref(kf.struct), C.byref(proj), C.byref(pts.struct), th,
+                               None if sig is None else _p(sig), _p(best), C.byref(n)))
+        return best[:pts.struct.m], n.value
+
+    def search_by_sim3(self, kf1, kf2, p1, p2, pair, th):
+        m12 = np.empty(max(p1.struct.m, 1), np.int32)
+        n = C.c_int32()
+        check(lib().orbfe_search_by_sim3(self._h, C.byref(kf1.struct), C.byref(kf2.struct), C.byref(p1.struct),
+                                         C.byref(p2.struct), C.byref(pair), th, _p(m12), C.byref(n)))
+        return m12[:p1.struct.m], n.value
 
     def popc_peak(self):
         v = C.c_double()

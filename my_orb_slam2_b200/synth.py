@@ -246,3 +246,168 @@ def bruteforce_case(nq=8192, nm=1 << 20, n_planted=4096, seed=1):
             planted[r, bpos >> 3] ^= np.uint8(1 << (bpos & 7))
     m[mi] = planted
     return q, m
+
+
+# --------------------------------------------------------------------------------------------------------
+# Workloads of the seven other ORBmatcher members
+# --------------------------------------------------------------------------------------------------------
+KITTI_CAM = dict(fx=718.856, fy=718.856, cx=607.1928, cy=185.2157, bf=386.1448)
+
+
+def _small_pose(rng, rot=0.01, trans=0.1):
+    """A pose close to identity: rotation about y by `rot` rad, small translation."""
+    R = np.array([[np.cos(rot), 0, np.sin(rot)], [0, 1, 0], [-np.sin(rot), 0, np.cos(rot)]])
+    t = rng.uniform(-trans, trans, 3)
+    return R, t
+
+
+def points3d_case(frame, seed=0, cam=KITTI_CAM, n_extra=400, noise_px=2.0, sim3_scale=None, nlevels=8, sf=1.2,
+                  dup_frac=0.15):
+    """Map points given by 3-D position that re-project near the features of `frame` (relocalisation / Sim3 /
+    Fuse overloads): point i < n comes from feature i (back-projected at a random depth, descriptor = the
+    feature's with flipped bits, scale-invariance range centred on the feature's octave), a `dup_frac` of the points
+    are second copies aimed at the same feature (so rows compete), and n_extra distractors are random.
+    Returns (points dict, projection dict)."""
+    rng = np.random.default_rng([seed, 21])
+    kps, desc = frame["keys_un"], frame["desc"]
+    n = len(kps)
+    src = np.concatenate([np.arange(n), rng.integers(0, n, int(n * dup_frac))])
+    m_true = len(src)
+    R, t = _small_pose(rng)
+    z = rng.uniform(4, 60, m_true)
+    u = kps["x"][src] + rng.normal(0, noise_px, m_true)
+    v = kps["y"][src] + rng.normal(0, noise_px, m_true)
+    pc = np.stack([(u - cam["cx"]) / cam["fx"] * z, (v - cam["cy"]) / cam["fy"] * z, z], 1)
+    pw = (pc - t) @ R
+    ow = -R.T @ t
+    d3 = np.linalg.norm(pw - ow, axis=1)
+    lvl = np.clip(kps["octave"][src] + rng.integers(0, 2, m_true), 0, nlevels - 1)
+    max_d = d3 * (sf ** lvl) * rng.uniform(0.93, 1.0, m_true)  # PredictScale lands on lvl (or lvl-1 near the edge)
+    min_d = max_d / (sf ** (nlevels - 1))
+    normal = (pw - ow) / d3[:, None]
+    normal += rng.normal(0, 0.15, normal.shape)
+    wide = rng.random(m_true) < 0.08
+    normal[wide] = rng.normal(0, 1, (wide.sum(), 3))  # some fail the 60-degree gate
+    normal /= np.linalg.norm(normal, axis=1, keepdims=True)
+    d = flip_bits(desc[src], 0.06, rng)
+    ang = (kps["angle"][src] + 15.0 + rng.normal(0, 4.0, m_true)) % 360.0
+    wild = rng.random(m_true) < 0.1
+    ang[wild] = rng.uniform(0, 360, wild.sum())
+    # distractors: random positions in front of the camera, random descriptors
+    ze = rng.uniform(2, 80, n_extra)
+    min_x, min_y, max_x, max_y = frame["bounds"]
+    ue, ve = rng.uniform(min_x - 50, max_x + 50, n_extra), rng.uniform(min_y - 50, max_y + 50, n_extra)
+    pce = np.stack([(ue - cam["cx"]) / cam["fx"] * ze, (ve - cam["cy"]) / cam["fy"] * ze, ze], 1)
+    behind = rng.random(n_extra) < 0.1
+    pce[behind, 2] *= -1.0  # negative depth
+    pwe = (pce - t) @ R
+    d3e = np.linalg.norm(pwe - ow, axis=1)
+    max_de = d3e * rng.uniform(0.5, 4.0, n_extra)
+    order = rng.permutation(m_true + n_extra)
+    pts = dict(
+        valid=(rng.random(m_true + n_extra) < 0.9).astype(np.uint8)[order],
+        world_pos=np.concatenate([pw, pwe]).astype(np.float32)[order],
+        normal=np.concatenate([normal, (pwe - ow) / d3e[:, None]]).astype(np.float32)[order],
+        max_distance=np.concatenate([max_d, max_de]).astype(np.float32)[order],
+        min_distance=np.concatenate([min_d, max_de / (sf ** (nlevels - 1))]).astype(np.float32)[order],
+        desc=np.concatenate([d, rng.integers(0, 256, (n_extra, 32), dtype=np.uint8)])[order],
+        angle=np.concatenate([ang, rng.uniform(0, 360, n_extra)]).astype(np.float32)[order])
+    T = np.hstack([R, t[:, None]])
+    if sim3_scale is not None:
+        T = T * sim3_scale  # Scw = [s R | s t]
+    proj = dict(tcw=T.astype(np.float32), fx=cam["fx"], fy=cam["fy"], cx=cam["cx"], cy=cam["cy"], bf=cam["bf"],
+                log_scale_factor=float(np.log(np.float32(sf)).astype(np.float32)), is_sim3=sim3_scale is not None,
+                ow=None)
+    return pts, proj
+
+
+def bow_case(kps, desc, seed=0, n_nodes=100, mp_frac=0.75):
+    """Two feature sets with DBoW2-style feature vectors for SearchByBoW: the pair of keyframe_pair_case with a
+    map-point density fit for tracking (most keyframe features carry a map point)."""
+    k1, k2, _, _ = keyframe_pair_case(kps, desc, seed, n_nodes)
+    r = np.random.default_rng([seed, 22])
+    k1["has_mp"] = (r.random(len(k1["keys_un"])) < mp_frac).astype(np.uint8)
+    k2["has_mp"] = (r.random(len(k2["keys_un"])) < mp_frac).astype(np.uint8)
+    keys2 = k2["keys_un"].copy()
+    wild = r.random(len(keys2)) < 0.08  # some matches must fail the rotation-consistency check
+    keys2["angle"][wild] = r.uniform(0, 360, wild.sum()).astype(np.float32)
+    k2["keys_un"] = keys2
+    return k1, k2
+
+
+def initialization_case(kps, desc, bounds, seed=0, shift=12.0, nlevels=8):
+    """Two monocular frames for SearchForInitialization: F2 = F1 moved by a few pixels, other feature order, a
+    fraction of near-duplicate descriptors so that later rows steal earlier rows' matches."""
+    rng = np.random.default_rng([seed, 23])
+    n = len(kps)
+    k2 = kps.copy()
+    k2["x"] = kps["x"] + shift + rng.normal(0, 3.0, n).astype(np.float32)
+    k2["y"] = kps["y"] + rng.normal(0, 3.0, n).astype(np.float32)
+    k2["angle"] = (kps["angle"] + rng.normal(0, 3.0, n)) % 360.0
+    wild = rng.random(n) < 0.08
+    k2["angle"][wild] = rng.uniform(0, 360, wild.sum())
+    d2 = flip_bits(desc, 0.04, rng)
+    perm = rng.permutation(n)
+    k2, d2 = k2[perm], d2[perm]
+    d1 = desc.copy()
+    twins = rng.permutation(n)[: n // 5]  # rows that look like another row's best match
+    d1[twins] = flip_bits(desc[np.roll(twins, 1)], 0.03, rng)
+    k1 = kps.copy()
+    k1["x"][twins] = kps["x"][np.roll(twins, 1)] + rng.normal(0, 4.0, len(twins)).astype(np.float32)
+    k1["y"][twins] = kps["y"][np.roll(twins, 1)] + rng.normal(0, 4.0, len(twins)).astype(np.float32)
+    none = np.full(n, -1.0, np.float32)
+    f1 = dict(keys_un=k1, u_right=none, desc=d1, mp_obs=np.full(n, -1, np.int32), bounds=bounds,
+              scale_factors=scale_factors(nlevels))
+    f2 = dict(keys_un=k2, u_right=none, desc=d2, mp_obs=np.full(n, -1, np.int32), bounds=bounds,
+              scale_factors=scale_factors(nlevels))
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)  # vbPrevMatched starts as F1's keypoints
+    return f1, f2, prev
+
+
+def sim3_pair_case(frame, seed=0, cam=KITTI_CAM, nlevels=8, sf=1.2, s12=1.03):
+    """Two keyframes seeing the same points for SearchBySim3: KF1 = `frame`; KF2 sees every point of KF1 from another
+    pose (features in another order, descriptors with flipped bits); one map point per feature on both sides."""
+    rng = np.random.default_rng([seed, 24])
+    kps, desc = frame["keys_un"], frame["desc"]
+    n = len(kps)
+    min_x, min_y, max_x, max_y = frame["bounds"]
+    R1, t1 = _small_pose(rng, 0.0, 0.05)
+    R2, t2 = _small_pose(rng, 0.02, 0.3)
+    z = rng.uniform(6, 50, n)
+    pc1 = np.stack([(kps["x"] - cam["cx"]) / cam["fx"] * z, (kps["y"] - cam["cy"]) / cam["fy"] * z, z], 1)
+    pw = (pc1 - t1) @ R1
+    pc2 = pw @ R2.T + t2
+    u2 = cam["fx"] * pc2[:, 0] / pc2[:, 2] + cam["cx"] + rng.normal(0, 1.0, n)
+    v2 = cam["fy"] * pc2[:, 1] / pc2[:, 2] + cam["cy"] + rng.normal(0, 1.0, n)
+    k2 = kps.copy()
+    k2["x"], k2["y"] = u2.astype(np.float32), v2.astype(np.float32)
+    out = (u2 < min_x) | (u2 >= max_x) | (v2 < min_y) | (v2 >= max_y)
+    k2["x"][out] = rng.uniform(min_x, max_x - 1, out.sum())
+    k2["y"][out] = rng.uniform(min_y, max_y - 1, out.sum())
+    d2 = flip_bits(desc, 0.05, rng)
+    d2[out] = rng.integers(0, 256, (out.sum(), 32), dtype=np.uint8)
+    perm = rng.permutation(n)
+    k2, d2 = k2[perm], d2[perm]
+    pw2 = (pw + rng.normal(0, 0.02, pw.shape))[perm]  # KF2's own map points sit (almost) on KF1's
+    lvl = kps["octave"]
+
+    def pts(world, centre, levels, s):
+        r = np.random.default_rng([seed, s])
+        d3 = np.linalg.norm(world - centre, axis=1)
+        max_d = d3 * (sf ** levels) * r.uniform(0.93, 1.0, len(world))
+        return dict(valid=(r.random(len(world)) < 0.85).astype(np.uint8), world_pos=world.astype(np.float32),
+                    normal=None, max_distance=max_d.astype(np.float32),
+                    min_distance=(max_d / sf ** (nlevels - 1)).astype(np.float32),
+                    desc=flip_bits(desc if s == 25 else d2, 0.03, r), angle=None)
+
+    p1 = pts(pw, -R1.T @ t1, lvl, 25)
+    p2 = pts(pw2, -R2.T @ t2, lvl[perm], 26)
+    f2 = dict(frame, keys_un=k2, desc=d2, u_right=np.full(n, -1.0, np.float32), mp_obs=np.full(n, -1, np.int32))
+    # camera 1 from camera 2 with a scale drift: Xc1 = s12 R12 Xc2 + t12
+    R12 = R1 @ R2.T
+    t12 = t1 - R12 @ t2
+    lsf = float(np.log(np.float32(sf)).astype(np.float32))
+    pair = dict(t1w=np.hstack([R1, t1[:, None]]).astype(np.float32), t2w=np.hstack([R2, t2[:, None]]).astype(np.float32),
+                s12=float(s12), r12=R12.astype(np.float32), t12=t12.astype(np.float32), fx=cam["fx"], fy=cam["fy"],
+                cx=cam["cx"], cy=cam["cy"], log_sf1=lsf, log_sf2=lsf)
+    return dict(frame, mp_obs=np.full(n, -1, np.int32)), f2, p1, p2, pair

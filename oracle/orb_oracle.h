@@ -78,6 +78,24 @@ int orc_search_for_triangulation(const orbfe_keyframe_view* kf1, const orbfe_key
 void orc_hamming_bruteforce(const uint8_t* query, int nq, const uint8_t* map, int nm, int64_t index_base,
                             uint64_t* best, uint64_t* second);
 
+/* ---- the seven other ORBmatcher members (orb_matcher2.cc) ---- */
+int orc_search_by_bow(const orbfe_keyframe_view* k1, const orbfe_keyframe_view* k2, int kf_kf, float nnratio,
+                      int check_ori, int32_t* matches);
+int orc_search_for_initialization(const orbfe_frame_view* F1, const orbfe_frame_view* F2, float* prev_matched,
+                                  int window, float nnratio, int check_ori, int32_t* matches12);
+int orc_search_by_projection_reloc(const orbfe_frame_view* cur, const orbfe_projection* pr,
+                                   const orbfe_points3d_view* pts, float th, int orb_dist, int check_ori,
+                                   int32_t* assigned);
+int orc_search_by_projection_sim3(const orbfe_frame_view* kf, const orbfe_projection* pr,
+                                  const orbfe_points3d_view* pts, int th, int32_t* assigned);
+int orc_fuse(const orbfe_frame_view* kf, const orbfe_projection* pr, const orbfe_points3d_view* pts, float th,
+             const float* inv_level_sigma2, int32_t* best_idx);
+int orc_search_by_sim3(const orbfe_frame_view* kf1, const orbfe_frame_view* kf2, const orbfe_points3d_view* p1,
+                       const orbfe_points3d_view* p2, const orbfe_sim3_pair* s, float th, int32_t* match12);
+/* shared arithmetic probes (include/orb_math_shared.h) for the known-answer tests */
+float orc_log_f32(float x);
+int orc_predict_scale(float max_distance, float dist, float log_scale_factor, int nlevels);
+
 #ifdef __cplusplus
 }
 #endif

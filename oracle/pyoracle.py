@@ -58,6 +58,24 @@ class CameraPose(C.Structure):
                 ("mbf", C.c_float), ("mb", C.c_float)]
 
 
+class Points3DView(C.Structure):
+    _fields_ = [("m", C.c_int32), ("valid", C.c_void_p), ("world_pos", C.c_void_p), ("normal", C.c_void_p),
+                ("max_distance", C.c_void_p), ("min_distance", C.c_void_p), ("desc", C.c_void_p),
+                ("angle", C.c_void_p)]
+
+
+class Projection(C.Structure):
+    _fields_ = [("tcw", C.c_float * 12), ("is_sim3", C.c_int32), ("has_ow", C.c_int32), ("ow", C.c_float * 3),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("bf", C.c_float),
+                ("log_scale_factor", C.c_float)]
+
+
+class Sim3Pair(C.Structure):
+    _fields_ = [("t1w", C.c_float * 12), ("t2w", C.c_float * 12), ("s12", C.c_float), ("r12", C.c_float * 9),
+                ("t12", C.c_float * 3), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("log_scale_factor1", C.c_float), ("log_scale_factor2", C.c_float)]
+
+
 class KeyFrameView(C.Structure):
     _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("u_right", C.c_void_p), ("desc", C.c_void_p),
                 ("has_mp", C.c_void_p), ("n_nodes", C.c_int32), ("node_ids", C.c_void_p),
@@ -109,6 +127,21 @@ def lib():
                                                     C.POINTER(LastFrameView), C.c_float, C.c_int, C.c_int, C.c_void_p]
         L.orc_search_for_triangulation.argtypes = [C.POINTER(KeyFrameView), C.POINTER(KeyFrameView), C.c_void_p,
                                                    C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_search_by_bow.argtypes = [C.POINTER(KeyFrameView), C.POINTER(KeyFrameView), C.c_int, C.c_float, C.c_int,
+                                        C.c_void_p]
+        L.orc_search_for_initialization.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.c_void_p, C.c_int,
+                                                    C.c_float, C.c_int, C.c_void_p]
+        L.orc_search_by_projection_reloc.argtypes = [C.POINTER(FrameView), C.POINTER(Projection),
+                                                     C.POINTER(Points3DView), C.c_float, C.c_int, C.c_int, C.c_void_p]
+        L.orc_search_by_projection_sim3.argtypes = [C.POINTER(FrameView), C.POINTER(Projection),
+                                                    C.POINTER(Points3DView), C.c_int, C.c_void_p]
+        L.orc_fuse.argtypes = [C.POINTER(FrameView), C.POINTER(Projection), C.POINTER(Points3DView), C.c_float,
+                               C.c_void_p, C.c_void_p]
+        L.orc_search_by_sim3.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(Points3DView),
+                                         C.POINTER(Points3DView), C.POINTER(Sim3Pair), C.c_float, C.c_void_p]
+        L.orc_log_f32.restype = C.c_float
+        L.orc_log_f32.argtypes = [C.c_float]
+        L.orc_predict_scale.argtypes = [C.c_float, C.c_float, C.c_float, C.c_int]
         L.orc_hamming_bruteforce.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_void_p,
                                              C.c_void_p]
         _lib = L
@@ -348,3 +381,78 @@ def hamming_bruteforce(query, mapd, index_base=0):
     second = np.empty(len(query), np.uint64)
     lib().orc_hamming_bruteforce(_p(query), len(query), _p(mapd), len(mapd), index_base, _p(best), _p(second))
     return best, second
+
+
+# ---------------------------------------------------------------- the seven other matcher members
+def make_points3d_view(valid, world_pos, normal, max_distance, min_distance, desc, angle=None, cls=Points3DView):
+    arrs = [np.ascontiguousarray(valid, np.uint8), np.ascontiguousarray(world_pos, np.float32),
+            None if normal is None else np.ascontiguousarray(normal, np.float32),
+            np.ascontiguousarray(max_distance, np.float32), np.ascontiguousarray(min_distance, np.float32), _u8(desc),
+            None if angle is None else np.ascontiguousarray(angle, np.float32)]
+    v = cls(len(arrs[0]), *[None if a is None else _p(a).value for a in arrs])
+    return _Keep(v, arrs)
+
+
+def _fl(vals, n):
+    return (C.c_float * n)(*[float(x) for x in np.asarray(vals, np.float32).reshape(-1)[:n]])
+
+
+def make_projection(tcw, fx, fy, cx, cy, bf, log_scale_factor, is_sim3=False, ow=None):
+    return Projection(_fl(tcw, 12), int(is_sim3), int(ow is not None), _fl(ow if ow is not None else [0, 0, 0], 3), fx,
+                      fy, cx, cy, bf, log_scale_factor)
+
+
+def make_sim3_pair(t1w, t2w, s12, r12, t12, fx, fy, cx, cy, log_sf1, log_sf2):
+    return Sim3Pair(_fl(t1w, 12), _fl(t2w, 12), s12, _fl(r12, 9), _fl(t12, 3), fx, fy, cx, cy, log_sf1, log_sf2)
+
+
+def search_by_bow(kf1, kf2, kf_kf, nnratio, check_ori):
+    n_out = kf1.struct.n if kf_kf else kf2.struct.n
+    matches = np.empty(max(n_out, 1), np.int32)
+    n = lib().orc_search_by_bow(C.byref(kf1.struct), C.byref(kf2.struct), int(kf_kf), C.c_float(nnratio),
+                                int(check_ori), _p(matches))
+    return matches[:n_out], n
+
+
+def search_for_initialization(f1, f2, prev_matched, window, nnratio, check_ori):
+    prev = np.array(prev_matched, np.float32).reshape(-1, 2).copy()
+    m12 = np.empty(max(f1.struct.n, 1), np.int32)
+    n = lib().orc_search_for_initialization(C.byref(f1.struct), C.byref(f2.struct), _p(prev), int(window),
+                                            C.c_float(nnratio), int(check_ori), _p(m12))
+    return m12[:f1.struct.n], prev, n
+
+
+def search_by_projection_reloc(cur, proj, pts, th, orb_dist, check_ori):
+    assigned = np.empty(max(cur.struct.n, 1), np.int32)
+    n = lib().orc_search_by_projection_reloc(C.byref(cur.struct), C.byref(proj), C.byref(pts.struct), C.c_float(th),
+                                             int(orb_dist), int(check_ori), _p(assigned))
+    return assigned[:cur.struct.n], n
+
+
+def search_by_projection_sim3(kf, proj, pts, th):
+    assigned = np.empty(max(kf.struct.n, 1), np.int32)
+    n = lib().orc_search_by_projection_sim3(C.byref(kf.struct), C.byref(proj), C.byref(pts.struct), int(th),
+                                            _p(assigned))
+    return assigned[:kf.struct.n], n
+
+
+def fuse(kf, proj, pts, th, inv_level_sigma2=None):
+    best = np.empty(max(pts.struct.m, 1), np.int32)
+    sig = np.zeros(16, np.float32) if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+    n = lib().orc_fuse(C.byref(kf.struct), C.byref(proj), C.byref(pts.struct), C.c_float(th), _p(sig), _p(best))
+    return best[:pts.struct.m], n
+
+
+def search_by_sim3(kf1, kf2, p1, p2, pair, th):
+    m12 = np.empty(max(p1.struct.m, 1), np.int32)
+    n = lib().orc_search_by_sim3(C.byref(kf1.struct), C.byref(kf2.struct), C.byref(p1.struct), C.byref(p2.struct),
+                                 C.byref(pair), C.c_float(th), _p(m12))
+    return m12[:p1.struct.m], n
+
+
+def log_f32(x):
+    return float(lib().orc_log_f32(C.c_float(x)))
+
+
+def predict_scale(max_distance, dist, log_sf, nlevels):
+    return int(lib().orc_predict_scale(C.c_float(max_distance), C.c_float(dist), C.c_float(log_sf), int(nlevels)))

@@ -19,6 +19,23 @@ def extract_with_oracle(oracle, shape="kitti", seed=0, pair=False, small=None):
     return params, img, ex, ex.extract(img)
 
 
+def points_view(mod, p):
+    f = mod.make_points3d_view if hasattr(mod, "make_frame_view") else mod.points3d_view
+    return f(p["valid"], p["world_pos"], p["normal"], p["max_distance"], p["min_distance"], p["desc"], p["angle"])
+
+
+def projection(mod, pr, ow=None, is_sim3=None):
+    f = mod.make_projection if hasattr(mod, "make_frame_view") else mod.projection
+    return f(pr["tcw"], pr["fx"], pr["fy"], pr["cx"], pr["cy"], pr["bf"], pr["log_scale_factor"],
+             pr["is_sim3"] if is_sim3 is None else is_sim3, ow if ow is not None else pr["ow"])
+
+
+def sim3_pair(mod, s):
+    f = mod.make_sim3_pair if hasattr(mod, "make_frame_view") else mod.sim3_pair
+    return f(s["t1w"], s["t2w"], s["s12"], s["r12"], s["t12"], s["fx"], s["fy"], s["cx"], s["cy"], s["log_sf1"],
+             s["log_sf2"])
+
+
 def views(mod, frame=None, mps=None, last=None, cam=None, kf=None):
     """Build views with either oracle.pyoracle (make_*_view) or my_orb_slam2_b200.frontend (*_view)."""
     is_oracle = hasattr(mod, "make_frame_view")
