@@ -1,8 +1,6 @@
-// ORBmatcher.h — drop-in replacement of the reference's include/ORBmatcher.h:45-114 for the four members that run
-// on the GPU: DescriptorDistance, SearchByProjection(Frame&, MapPoints),
-// SearchByProjection(Frame&, const Frame&) and SearchForTriangulation.  Same namespace, class name, signatures and
-// constants.  The other seven members are SURVEY.md 8(f)-1 ("next"); they are declared so that callers compile, and
-// are to be linked from the reference's own translation unit until their GPU versions exist.
+// ORBmatcher.h — drop-in replacement of the reference's include/ORBmatcher.h:45-114.  Same namespace, class name,
+// signatures and constants; all eleven members are defined in compat/ORBmatcher.cc on top of liborbfe.so (SURVEY.md
+// 8(a) rows a10-a13 and 8(f)-1), so the reference's src/ORBmatcher.cc drops out of the build.
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
 
@@ -34,7 +32,7 @@ class ORBmatcher {
   int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,
                              std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo);
 
-  // SURVEY.md 8(f)-1, not GPU-backed yet: definitions stay in the reference's src/ORBmatcher.cc
+  // SURVEY.md 8(f)-1 (src/ORBmatcher.cc:1540, :321, :182, :563, :446, :1158, :879, :1033)
   int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th,
                          const int ORBdist);
   int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints,

@@ -136,8 +136,9 @@ typedef struct orbfe_points3d_view {
                                 vbAlreadyMatched) */
   const float* world_pos;    /* GetWorldPos(), m x 3 */
   const float* normal;       /* GetNormal(), m x 3; NULL where the method does not read it */
-  const float* max_distance; /* mfMaxDistance (GetMaxDistanceInvariance() = 1.2f * it) */
-  const float* min_distance; /* mfMinDistance (GetMinDistanceInvariance() = 0.8f * it) */
+  const float* max_dist_inv; /* GetMaxDistanceInvariance() (= 1.2f * mfMaxDistance) */
+  const float* min_dist_inv; /* GetMinDistanceInvariance() (= 0.8f * mfMinDistance) */
+  const float* max_distance; /* mfMaxDistance, the numerator of MapPoint::PredictScale */
   const uint8_t* desc;       /* GetDescriptor(), m x 32 */
   const float* angle;        /* relocalisation overload only: pKF->mvKeysUn[i].angle */
 } orbfe_points3d_view;

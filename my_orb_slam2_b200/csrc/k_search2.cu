@@ -60,7 +60,7 @@ __device__ bool project_point(int mode, const DevFrame& f, const DevPoints& p, c
     if (!(q.u >= f.min_x && q.u < f.max_x && q.v >= f.min_y && q.v < f.max_y)) return false;  // KeyFrame::IsInImage
   }
   q.ur = __fsub_rn(q.u, __fmul_rn(P.bf, invz));
-  const float max_d = __fmul_rn(1.2f, p.max_d[i]), min_d = __fmul_rn(0.8f, p.min_d[i]);
+  const float max_d = p.max_inv[i], min_d = p.min_inv[i];  // Get{Max,Min}DistanceInvariance()
   float dist;
   if (mode == PM_BYSIM3) {
     dist = norm3(pc[0], pc[1], pc[2]);  // :1235

@@ -100,7 +100,7 @@ void launch_triangulation(const DevKeyFrame& k1, const DevKeyFrame& k2, const fl
 struct DevPoints {  // device mirror of orbfe_points3d_view
   int m;
   const uint8_t* valid;
-  const float *world_pos, *normal, *max_d, *min_d, *angle;
+  const float *world_pos, *normal, *max_inv, *min_inv, *max_d, *angle;
   const uint8_t* desc;
 };
 

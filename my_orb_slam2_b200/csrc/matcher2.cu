@@ -41,7 +41,7 @@ static void decompose_pose(const orbfe_projection* pr, DevProjection* P) {
 
 static int check_points(const orbfe_points3d_view* p, bool need_normal, bool need_angle) {
   ORBFE_ARG(p && p->m >= 0);
-  ORBFE_ARG(p->m == 0 || (p->valid && p->world_pos && p->max_distance && p->min_distance && p->desc));
+  ORBFE_ARG(p->m == 0 || (p->valid && p->world_pos && p->max_dist_inv && p->min_dist_inv && p->max_distance && p->desc));
   ORBFE_ARG(p->m == 0 || !need_normal || p->normal);
   ORBFE_ARG(p->m == 0 || !need_angle || p->angle);
   return ORBFE_OK;
@@ -49,7 +49,7 @@ static int check_points(const orbfe_points3d_view* p, bool need_normal, bool nee
 
 static size_t points_bytes(const orbfe_points3d_view* p) {
   const size_t m = (size_t)p->m;
-  return padded(m) + 2 * padded(m * 12) + 3 * padded(m * 4) + padded(m * 32);
+  return padded(m) + 2 * padded(m * 12) + 4 * padded(m * 4) + padded(m * 32);
 }
 
 static void put_points(Matcher* m, const orbfe_points3d_view* p, DevPoints* d) {
@@ -58,8 +58,9 @@ static void put_points(Matcher* m, const orbfe_points3d_view* p, DevPoints* d) {
   d->valid = arena_put(m, p->valid, n);
   d->world_pos = arena_put(m, p->world_pos, n * 3);
   d->normal = p->normal ? arena_put(m, p->normal, n * 3) : nullptr;
+  d->max_inv = arena_put(m, p->max_dist_inv, n);
+  d->min_inv = arena_put(m, p->min_dist_inv, n);
   d->max_d = arena_put(m, p->max_distance, n);
-  d->min_d = arena_put(m, p->min_distance, n);
   d->angle = p->angle ? arena_put(m, p->angle, n) : nullptr;
   d->desc = arena_put(m, p->desc, n * 32);
 }

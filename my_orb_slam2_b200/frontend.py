@@ -150,10 +150,13 @@ def keyframe_view(keys_un, u_right, desc, has_mp, node_ids, node_offsets, node_f
 
 
 def points3d_view(valid, world_pos, normal, max_distance, min_distance, desc, angle=None):
-    """Map points given by position (include/orbfe_types.h: orbfe_points3d_view)."""
+    """Map points given by position (include/orbfe_types.h: orbfe_points3d_view).  max_distance / min_distance are
+    MapPoint::mfMaxDistance / mfMinDistance; the two Get*DistanceInvariance() values are derived as MapPoint.cc:394-404
+    does (1.2f * max, 0.8f * min in fp32)."""
+    max_distance = np.ascontiguousarray(max_distance, np.float32)
     a = [np.ascontiguousarray(valid, np.uint8), np.ascontiguousarray(world_pos, np.float32),
          None if normal is None else np.ascontiguousarray(normal, np.float32),
-         np.ascontiguousarray(max_distance, np.float32), np.ascontiguousarray(min_distance, np.float32),
+         np.float32(1.2) * max_distance, np.float32(0.8) * np.ascontiguousarray(min_distance, np.float32), max_distance,
          np.ascontiguousarray(desc, np.uint8), None if angle is None else np.ascontiguousarray(angle, np.float32)]
     s = orbfe.Points3DView(len(a[0]), *[None if x is None else _p(x) for x in a])
     return _View(s, a)

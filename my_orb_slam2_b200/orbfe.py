@@ -67,7 +67,8 @@ class KeyFrameView(C.Structure):
 
 class Points3DView(C.Structure):
     _fields_ = [("m", C.c_int32), ("valid", C.c_void_p), ("world_pos", C.c_void_p), ("normal", C.c_void_p),
-                ("max_distance", C.c_void_p), ("min_distance", C.c_void_p), ("desc", C.c_void_p),
+                ("max_dist_inv", C.c_void_p), ("min_dist_inv", C.c_void_p), ("max_distance", C.c_void_p),
+                ("desc", C.c_void_p),
                 ("angle", C.c_void_p)]
 
 

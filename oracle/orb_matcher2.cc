@@ -222,8 +222,8 @@ int orc_search_by_projection_reloc(const orbfe_frame_view* cur, const orbfe_proj
     if (v < cur->min_y || v > cur->max_y) continue;
     const float PO[3] = {X[0] - P.Ow[0], X[1] - P.Ow[1], X[2] - P.Ow[2]};
     const float dist3D = orc::norm3(PO);
-    const float maxDistance = 1.2f * pts->max_distance[i];  // MapPoint.cc:394-404
-    const float minDistance = 0.8f * pts->min_distance[i];
+    const float maxDistance = pts->max_dist_inv[i];  // GetMaxDistanceInvariance(), MapPoint.cc:394-404
+    const float minDistance = pts->min_dist_inv[i];
     if (dist3D < minDistance || dist3D > maxDistance) continue;
     const int lvl = orb_predict_scale(pts->max_distance[i], dist3D, pr->log_scale_factor, cur->nlevels);
     const float radius = th * cur->scale_factors[lvl];
@@ -277,7 +277,7 @@ int orc_search_by_projection_sim3(const orbfe_frame_view* kf, const orbfe_projec
     const float x = pc[0] * invz, y = pc[1] * invz;
     const float u = pr->fx * x + pr->cx, v = pr->fy * y + pr->cy;
     if (!orc::in_image(kf, u, v)) continue;
-    const float maxDistance = 1.2f * pts->max_distance[iMP], minDistance = 0.8f * pts->min_distance[iMP];
+    const float maxDistance = pts->max_dist_inv[iMP], minDistance = pts->min_dist_inv[iMP];
     const float PO[3] = {X[0] - P.Ow[0], X[1] - P.Ow[1], X[2] - P.Ow[2]};
     const float dist = orc::norm3(PO);
     if (dist < minDistance || dist > maxDistance) continue;
@@ -327,7 +327,7 @@ int orc_fuse(const orbfe_frame_view* kf, const orbfe_projection* pr, const orbfe
     const float u = pr->fx * x + pr->cx, v = pr->fy * y + pr->cy;
     if (!orc::in_image(kf, u, v)) continue;
     const float ur = u - pr->bf * invz;
-    const float maxDistance = 1.2f * pts->max_distance[i], minDistance = 0.8f * pts->min_distance[i];
+    const float maxDistance = pts->max_dist_inv[i], minDistance = pts->min_dist_inv[i];
     const float PO[3] = {X[0] - P.Ow[0], X[1] - P.Ow[1], X[2] - P.Ow[2]};
     const float dist3D = orc::norm3(PO);
     if (dist3D < minDistance || dist3D > maxDistance) continue;
@@ -398,7 +398,7 @@ int orc_search_by_sim3(const orbfe_frame_view* kf1, const orbfe_frame_view* kf2,
       const float x = pb[0] * invz, y = pb[1] * invz;
       const float u = s->fx * x + s->cx, v = s->fy * y + s->cy;
       if (!orc::in_image(target, u, v)) continue;
-      const float maxDistance = 1.2f * pts->max_distance[i], minDistance = 0.8f * pts->min_distance[i];
+      const float maxDistance = pts->max_dist_inv[i], minDistance = pts->min_dist_inv[i];
       const float dist3D = orc::norm3(pb);
       if (dist3D < minDistance || dist3D > maxDistance) continue;
       const int lvl = orb_predict_scale(pts->max_distance[i], dist3D, log_sf, target->nlevels);

@@ -60,7 +60,8 @@ class CameraPose(C.Structure):
 
 class Points3DView(C.Structure):
     _fields_ = [("m", C.c_int32), ("valid", C.c_void_p), ("world_pos", C.c_void_p), ("normal", C.c_void_p),
-                ("max_distance", C.c_void_p), ("min_distance", C.c_void_p), ("desc", C.c_void_p),
+                ("max_dist_inv", C.c_void_p), ("min_dist_inv", C.c_void_p), ("max_distance", C.c_void_p),
+                ("desc", C.c_void_p),
                 ("angle", C.c_void_p)]
 
 
@@ -385,9 +386,11 @@ def hamming_bruteforce(query, mapd, index_base=0):
 
 # ---------------------------------------------------------------- the seven other matcher members
 def make_points3d_view(valid, world_pos, normal, max_distance, min_distance, desc, angle=None, cls=Points3DView):
+    max_distance = np.ascontiguousarray(max_distance, np.float32)
     arrs = [np.ascontiguousarray(valid, np.uint8), np.ascontiguousarray(world_pos, np.float32),
             None if normal is None else np.ascontiguousarray(normal, np.float32),
-            np.ascontiguousarray(max_distance, np.float32), np.ascontiguousarray(min_distance, np.float32), _u8(desc),
+            np.float32(1.2) * max_distance, np.float32(0.8) * np.ascontiguousarray(min_distance, np.float32),
+            max_distance, _u8(desc),
             None if angle is None else np.ascontiguousarray(angle, np.float32)]
     v = cls(len(arrs[0]), *[None if a is None else _p(a).value for a in arrs])
     return _Keep(v, arrs)

@@ -134,3 +134,145 @@ def test_cpp_matcher_triangulation_and_distance(oracle, kitti_frame, tmp_path):
     subprocess.check_call([_exe(), "dist", d])
     got = np.fromfile(os.path.join(d, "result.bin"), np.int32)
     assert np.array_equal(got, np.unpackbits(a ^ b, axis=1).sum(1))
+
+
+# ---- the seven members of SURVEY.md 8(f)-1 through the C++ drop-in ----
+def _dump_kf(d, k):
+    _dump(d, keys_un=k["keys_un"], u_right=k["u_right"], desc=k["desc"], has_mp=k["has_mp"],
+          node_ids=k["node_ids"].astype(np.uint32), node_offsets=k["node_offsets"].astype(np.int32),
+          node_features=k["node_features"].astype(np.int32), scale_factors=k["scale_factors"].astype(np.float32),
+          level_sigma2=k["level_sigma2"].astype(np.float32))
+
+
+def _dump_points(d, p):
+    _dump(d, valid=p["valid"], world_pos=p["world_pos"], max_distance=p["max_distance"],
+          min_distance=p["min_distance"], pt_desc=p["desc"])
+    if p["normal"] is not None:
+        _dump(d, normal=p["normal"])
+    else:
+        _dump(d, normal=np.zeros(0, np.float32))
+    if p["angle"] is not None:
+        _dump(d, pt_angle=p["angle"])
+
+
+def _dump_proj(d, pr):
+    _dump(d, proj=np.concatenate([np.asarray(pr["tcw"], np.float32).reshape(12),
+                                  np.array([pr["fx"], pr["fy"], pr["cx"], pr["cy"], pr["bf"], pr["log_scale_factor"]],
+                                           np.float32)]))
+
+
+def _run(mode, d):
+    subprocess.check_call([_exe(), mode, d])
+    res = np.fromfile(os.path.join(d, "result.bin"), np.int32)
+    return res[:-1], int(res[-1])
+
+
+@pytest.mark.parametrize("kf_kf", [0, 1])
+def test_cpp_matcher_search_by_bow(oracle, kitti_frame, tmp_path, kf_kf):
+    from cases import views
+    k1, k2 = synth.bow_case(kitti_frame["keys_un"], kitti_frame["desc"], seed=5)
+    d = str(tmp_path)
+    _dump_kf(os.path.join(d, "kf1"), k1)
+    _dump_kf(os.path.join(d, "kf2"), k2)
+    _dump(d, params=np.array([0.7, 1.0], np.float32))
+    got, n = _run("bow%d" % kf_kf, d)
+    want, wn = oracle.search_by_bow(views(oracle, kf=k1), views(oracle, kf=k2), kf_kf, 0.7, True)
+    assert n == wn and wn > 300 and np.array_equal(got, want)
+
+
+def test_cpp_matcher_search_for_initialization(oracle, kitti_frame, tmp_path):
+    from cases import views
+    f1, f2, prev = synth.initialization_case(kitti_frame["keys_un"], kitti_frame["desc"], kitti_frame["bounds"], seed=5)
+    d = str(tmp_path)
+    _dump_frame(os.path.join(d, "f1"), f1)
+    _dump_frame(os.path.join(d, "f2"), f2)
+    _dump(d, prev=prev, params=np.array([100, 0.9, 1.0], np.float32))
+    got, n = _run("init", d)
+    wm, wp, wn = oracle.search_for_initialization(views(oracle, frame=f1), views(oracle, frame=f2), prev, 100, 0.9, True)
+    assert n == wn and wn > 100 and np.array_equal(got, wm)
+    assert np.array_equal(np.fromfile(os.path.join(d, "prev_out.bin"), np.float32).reshape(-1, 2), wp)
+
+
+def test_cpp_matcher_projection_overloads(oracle, kitti_frame, tmp_path):
+    from cases import points_view, projection, views
+    frame = dict(kitti_frame, mp_obs=synth.frame_arrays(kitti_frame["keys_un"], kitti_frame["desc"],
+                                                        kitti_frame["bounds"], seed=3, taken_frac=0.15)["mp_obs"])
+    # relocalisation overload
+    pts, pr = synth.points3d_case(frame, seed=5)
+    d = str(tmp_path / "reloc")
+    _dump_frame(d, frame)
+    _dump_points(d, pts)
+    _dump_proj(d, pr)
+    _dump(d, params=np.array([10.0, 100.0, 1.0], np.float32))
+    got, n = _run("reloc", d)
+    want, wn = oracle.search_by_projection_reloc(views(oracle, frame=frame), projection(oracle, pr),
+                                                 points_view(oracle, pts), 10.0, 100, True)
+    assert n == wn and wn > 500 and np.array_equal(got, np.where(want == -2, -1, want))
+    # Sim3 overload
+    pts, pr = synth.points3d_case(frame, seed=6, sim3_scale=1.05)
+    d = str(tmp_path / "sim3")
+    _dump_frame(d, frame)
+    _dump_points(d, pts)
+    _dump_proj(d, pr)
+    _dump(d, params=np.array([10.0], np.float32))
+    got, n = _run("sim3proj", d)
+    want, wn = oracle.search_by_projection_sim3(views(oracle, frame=frame), projection(oracle, pr),
+                                                points_view(oracle, pts), 10)
+    assert n == wn and wn > 500 and np.array_equal(got, want)
+
+
+def _fuse_observable(got, want):
+    """What the keyframe / map points show after Fuse equals the oracle's bestIdx per row, except for a row that meets
+    a slot whose point an earlier row already replaced (counted in nFused, no visible effect: src/ORBmatcher.cc:1011)."""
+    seen = set()
+    for g, w in zip(got, want):
+        if g != w and not (g == -1 and w in seen):
+            return False
+        if w >= 0:
+            seen.add(int(w))
+    return True
+
+
+def test_cpp_matcher_fuse(oracle, kitti_frame, tmp_path):
+    from cases import points_view, projection, views
+    frame = dict(kitti_frame, mp_obs=synth.frame_arrays(kitti_frame["keys_un"], kitti_frame["desc"],
+                                                        kitti_frame["bounds"], seed=4, taken_frac=0.5)["mp_obs"])
+    pts, pr = synth.points3d_case(frame, seed=7)
+    ow = (-pr["tcw"][:, :3].T @ pr["tcw"][:, 3]).astype(np.float32)
+    d = str(tmp_path / "fuse")
+    _dump_frame(d, frame)
+    _dump_points(d, pts)
+    _dump_proj(d, pr)
+    _dump(d, params=np.array([3.0], np.float32), ow=ow)
+    got, n = _run("fuse", d)
+    sig = (np.float32(1.0) / (frame["scale_factors"] * frame["scale_factors"])).astype(np.float32)
+    want, wn = oracle.fuse(views(oracle, frame=frame), projection(oracle, pr, ow=ow), points_view(oracle, pts), 3.0, sig)
+    assert n == wn and wn > 300 and _fuse_observable(got, want)
+    assert (got >= 0).sum() > 0.9 * wn
+    pts, pr = synth.points3d_case(frame, seed=8, sim3_scale=0.97)
+    d = str(tmp_path / "fusesim3")
+    _dump_frame(d, frame)
+    _dump_points(d, pts)
+    _dump_proj(d, pr)
+    _dump(d, params=np.array([4.0], np.float32))
+    got, n = _run("fusesim3", d)
+    want, wn = oracle.fuse(views(oracle, frame=frame), projection(oracle, pr), points_view(oracle, pts), 4.0, None)
+    assert n == wn and wn > 300 and np.array_equal(got, want)
+
+
+def test_cpp_matcher_search_by_sim3(oracle, kitti_frame, tmp_path):
+    from cases import points_view, sim3_pair, views
+    f1, f2, p1, p2, pair = synth.sim3_pair_case(kitti_frame, seed=5)
+    d = str(tmp_path)
+    _dump_frame(os.path.join(d, "f1"), f1)
+    _dump_frame(os.path.join(d, "f2"), f2)
+    _dump_points(os.path.join(d, "p1"), p1)
+    _dump_points(os.path.join(d, "p2"), p2)
+    g = np.concatenate([pair["t1w"].reshape(12), pair["t2w"].reshape(12), [pair["s12"]], pair["r12"].reshape(9),
+                        pair["t12"].reshape(3), [pair["fx"], pair["fy"], pair["cx"], pair["cy"], pair["log_sf1"],
+                                                 pair["log_sf2"]]]).astype(np.float32)
+    _dump(d, pair=g, params=np.array([7.5], np.float32))
+    got, n = _run("bysim3", d)
+    want, wn = oracle.search_by_sim3(views(oracle, frame=f1), views(oracle, frame=f2), points_view(oracle, p1),
+                                     points_view(oracle, p2), sim3_pair(oracle, pair), 7.5)
+    assert n == wn and wn > 300 and np.array_equal(got, want)
