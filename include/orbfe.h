@@ -246,6 +246,40 @@ int orbfe_matcher_sync(orbfe_matcher* m);
  * denominator of the Hamming kernels ("measure it"). */
 int orbfe_measure_popc_peak(orbfe_matcher* m, double* popc32_per_second);
 
+/* ------------------------------------------------------------------ */
+/* DBoW2 vocabulary transform                        */
+/* Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1127-1262, called from */
+/* Frame::ComputeBoW (src/Frame.cc:420-427) and KeyFrame::ComputeBoW   */
+/* (src/KeyFrame.cc:59-68)                                             */
+/* ------------------------------------------------------------------ */
+typedef struct orbfe_vocabulary orbfe_vocabulary;
+/* The tree as arrays: node 0 is the root; node i > 0 has parent[i] < i, a 32-byte descriptor, a weight and the
+ * "is a word" flag of its text line; word ids count the flagged nodes in order (TemplatedVocabulary.h:1385-1418).
+ * scoring / weighting are DBoW2's enums (ScoringType 0..5, WeightingType 0..3). */
+int orbfe_vocabulary_create(int device, int k, int L, int scoring, int weighting, int n_nodes, const int32_t* parent,
+                            const uint8_t* is_leaf, const uint8_t* desc, const double* weight,
+                            orbfe_vocabulary** out);
+/* TemplatedVocabulary::loadFromTextFile (TemplatedVocabulary.h:1338-1424), e.g. Vocabulary/ORBvoc.txt. */
+int orbfe_vocabulary_load_text(int device, const char* path, orbfe_vocabulary** out);
+void orbfe_vocabulary_destroy(orbfe_vocabulary* v);
+/* info6 = k, L, scoring, weighting, nodes, words */
+int orbfe_vocabulary_info(const orbfe_vocabulary* v, int32_t* info6);
+/* transform(features, BowVector&, FeatureVector&, levelsup): desc = n x 32 host bytes.  BowVector: ascending
+ * (bow_ids[j], bow_vals[j]), j < *n_bow.  FeatureVector in CSR form (the layout orbfe_keyframe_view takes):
+ * fv_nodes[j] ascending, features of node j = fv_features[fv_offsets[j] .. fv_offsets[j+1]) in ascending feature
+ * index; fv_offsets has fv_cap + 1 entries, fv_features n.  Capacities of n always suffice.  word_of / node_of /
+ * weight_of (optional, n entries) = the single-feature transform (:1216-1262).  Thread safe per handle. */
+int orbfe_vocabulary_transform(orbfe_vocabulary* v, const uint8_t* desc, int n, int levelsup, uint32_t* bow_ids,
+                               double* bow_vals, int bow_cap, int32_t* n_bow, uint32_t* fv_nodes, int32_t* fv_offsets,
+                               int32_t* fv_features, int fv_cap, int32_t* n_fv, uint32_t* word_of, uint32_t* node_of,
+                               double* weight_of);
+/* Same on device-resident descriptors (orbfe_extractor_device_results of a finished run, same device): ComputeBoW
+ * without a host trip of the descriptors.  Outputs are host arrays. */
+int orbfe_vocabulary_transform_device(orbfe_vocabulary* v, const uint8_t* d_desc, int n, int levelsup,
+                                      uint32_t* bow_ids, double* bow_vals, int bow_cap, int32_t* n_bow,
+                                      uint32_t* fv_nodes, int32_t* fv_offsets, int32_t* fv_features, int fv_cap,
+                                      int32_t* n_fv);
+
 #ifdef __cplusplus
 }
 #endif

@@ -135,4 +135,22 @@ int launch_init_resolve(const DevFrame& f2, const orbfe_keypoint* keys1, int n1,
                         const SearchScratch& sc, int32_t* m12, int32_t* m21, float* prev, int32_t* n_matches,
                         cudaStream_t s);
 
+// ---- k_bow.cu: DBoW2 vocabulary transform ----
+// The tree of TemplatedVocabulary (m_nodes) as device arrays: children of node i are child_list[child_start[i] ..
+// child_start[i+1]) in the reference's push_back order; a node without children is a leaf (Node::isLeaf()).
+struct DevVocab {
+  int n_nodes;
+  const int32_t* child_start;  // [n_nodes + 1]
+  const int32_t* child_list;   // [n_nodes - 1]
+  const uint8_t* desc;         // [n_nodes][32]
+  const uint32_t* word_id;     // [n_nodes]
+  const double* weight;        // [n_nodes]
+};
+void launch_bow_descend(const DevVocab& v, const uint8_t* desc, int n, int nid_level, uint32_t* word_of,
+                        uint32_t* node_of, double* weight_of, cudaStream_t s);
+int bow_build_capacity();
+int launch_bow_build(int n, const uint32_t* word_of, const uint32_t* node_of, const double* weight_of, int weighting,
+                     int must, int l1, uint32_t* bow_ids, double* bow_vals, uint32_t* fv_nodes, int32_t* fv_offsets,
+                     int32_t* fv_features, int32_t* out_counts, cudaStream_t s);
+
 }  // namespace orbfe

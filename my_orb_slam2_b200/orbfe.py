@@ -136,6 +136,12 @@ SYMBOLS = {
     "orbfe_fuse": (_I, [_P, C.POINTER(FrameView), C.POINTER(Projection), C.POINTER(Points3DView), _F, _P, _P, _P]),
     "orbfe_search_by_sim3": (_I, [_P, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(Points3DView),
                                   C.POINTER(Points3DView), C.POINTER(Sim3Pair), _F, _P, _P]),
+    "orbfe_vocabulary_create": (_I, [_I, _I, _I, _I, _I, _I, _P, _P, _P, _P, C.POINTER(_P)]),
+    "orbfe_vocabulary_load_text": (_I, [_I, C.c_char_p, C.POINTER(_P)]),
+    "orbfe_vocabulary_destroy": (None, [_P]),
+    "orbfe_vocabulary_info": (_I, [_P, _P]),
+    "orbfe_vocabulary_transform": (_I, [_P, _P, _I, _I, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P, _P, _P]),
+    "orbfe_vocabulary_transform_device": (_I, [_P, _P, _I, _I, _P, _P, _I, _P, _P, _P, _P, _I, _P]),
     "orbfe_hamming_bruteforce": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_bruteforce_device": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_merge_device": (_I, [_P, _P, _P, _I, _I, _P, _P]),
@@ -419,3 +425,65 @@ class Matcher:
 
     def hamming_merge_device(self, d_best_all, d_second_all, shards, nq, d_best, d_second):
         check(lib().orbfe_hamming_merge_device(self._h, d_best_all, d_second_all, shards, nq, d_best, d_second))
+
+
+class Vocabulary:
+    """DBoW2 vocabulary tree on the device (orbfe_vocabulary_*): ORBVocabulary::loadFromTextFile / transform."""
+
+    def __init__(self, handle, device):
+        self._h, self.device = handle, device
+        info = np.zeros(6, np.int32)
+        check(lib().orbfe_vocabulary_info(self._h, _p(info)))
+        self.k, self.L, self.scoring, self.weighting, self.n_nodes, self.n_words = [int(x) for x in info]
+
+    @classmethod
+    def from_arrays(cls, k, L, scoring, weighting, parent, is_leaf, desc, weight, device=0):
+        parent = np.ascontiguousarray(parent, np.int32)
+        is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = _u8(desc).reshape(-1, 32)
+        weight = np.ascontiguousarray(weight, np.float64)
+        h = C.c_void_p()
+        check(lib().orbfe_vocabulary_create(device, k, L, scoring, weighting, len(parent), _p(parent), _p(is_leaf),
+                                            _p(desc), _p(weight), C.byref(h)))
+        return cls(h, device)
+
+    @classmethod
+    def load_text(cls, path, device=0):
+        h = C.c_void_p()
+        check(lib().orbfe_vocabulary_load_text(device, os.fsencode(path), C.byref(h)))
+        return cls(h, device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbfe_vocabulary_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def transform(self, desc, levelsup, device_ptr=None, n=None):
+        """Returns (bow_ids, bow_vals, fv_nodes, fv_offsets, fv_features, word_of, node_of, weight_of); with
+        device_ptr (an int address of n x 32 device bytes) the per-feature arrays are None."""
+        if device_ptr is None:
+            desc = _u8(desc).reshape(-1, 32)
+            n = len(desc)
+        cap = max(n, 1)
+        bow_ids, bow_vals = np.empty(cap, np.uint32), np.empty(cap, np.float64)
+        fv_nodes, fv_off, fv_feat = np.empty(cap, np.uint32), np.zeros(cap + 1, np.int32), np.empty(cap, np.int32)
+        nb, nf = C.c_int32(), C.c_int32()
+        if device_ptr is None:
+            word, node, wt = np.empty(cap, np.uint32), np.empty(cap, np.uint32), np.empty(cap, np.float64)
+            check(lib().orbfe_vocabulary_transform(self._h, _p(desc), n, levelsup, _p(bow_ids), _p(bow_vals), cap,
+                                                   C.byref(nb), _p(fv_nodes), _p(fv_off), _p(fv_feat), cap, C.byref(nf),
+                                                   _p(word), _p(node), _p(wt)))
+            per = (word[:n], node[:n], wt[:n])
+        else:
+            check(lib().orbfe_vocabulary_transform_device(self._h, device_ptr, n, levelsup, _p(bow_ids), _p(bow_vals),
+                                                          cap, C.byref(nb), _p(fv_nodes), _p(fv_off), _p(fv_feat), cap,
+                                                          C.byref(nf)))
+            per = (None, None, None)
+        nb, nf = nb.value, nf.value
+        return (bow_ids[:nb], bow_vals[:nb], fv_nodes[:nf], fv_off[:nf + 1], fv_feat[:fv_off[nf]]) + per

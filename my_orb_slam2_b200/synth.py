@@ -411,3 +411,59 @@ def sim3_pair_case(frame, seed=0, cam=KITTI_CAM, nlevels=8, sf=1.2, s12=1.03):
                 s12=float(s12), r12=R12.astype(np.float32), t12=t12.astype(np.float32), fx=cam["fx"], fy=cam["fy"],
                 cx=cam["cx"], cy=cam["cy"], log_sf1=lsf, log_sf2=lsf)
     return dict(frame, mp_obs=np.full(n, -1, np.int32)), f2, p1, p2, pair
+
+
+# --------------------------------------------------------------------------------------------------------
+# DBoW2 vocabulary: Vocabulary/ORBvoc.txt is not in the reference tree, so a random tree
+# --------------------------------------------------------------------------------------------------------
+def vocabulary_case(k=10, L=4, seed=0, prune=0.03, stop_frac=0.05, dup_frac=0.02):
+    """A random k-ary tree of depth L in the order a DBoW2 text file lists it (parents before children): child
+    descriptors are the parent's with ~20 % of the bits flipped (so the descent is meaningful), a few inner nodes are
+    pruned into early leaves, a few words are stopped (weight 0) and a few siblings share a descriptor (ties).
+    Returns dict(parent, is_leaf, desc, weight, k, L) with node 0 = root."""
+    rng = np.random.default_rng([seed, 31])
+    parent, depth, desc = [0], [0], [np.zeros(32, np.uint8)]
+    frontier = [0]
+    for level in range(1, L + 1):
+        nxt = []
+        for pnode in frontier:
+            base = desc[pnode] if pnode else rng.integers(0, 256, 32, dtype=np.uint8)
+            kids = flip_bits(np.repeat(base[None], k, 0), 0.5 if pnode == 0 else 0.2, rng)
+            if rng.random() < dup_frac * 5:
+                kids[int(rng.integers(1, k))] = kids[0]  # equal distance: the first child must win
+            for c in range(k):
+                parent.append(pnode)
+                depth.append(level)
+                desc.append(kids[c])
+                if level < L and rng.random() >= prune:
+                    nxt.append(len(parent) - 1)
+        frontier = nxt
+    n = len(parent)
+    parent = np.array(parent, np.int32)
+    has_child = np.zeros(n, bool)
+    has_child[parent[1:]] = True
+    is_leaf = (~has_child).astype(np.uint8)
+    is_leaf[0] = 0
+    weight = np.where(is_leaf > 0, rng.uniform(0.5, 9.0, n), 0.0)
+    weight[(rng.random(n) < stop_frac) & (is_leaf > 0)] = 0.0
+    return dict(parent=parent, is_leaf=is_leaf, desc=np.stack(desc), weight=weight.astype(np.float64), k=k, L=L)
+
+
+def vocabulary_text(voc, scoring=0, weighting=0):
+    """The text form TemplatedVocabulary::saveToTextFile writes / loadFromTextFile reads."""
+    lines = ["%d %d  %d %d" % (voc["k"], voc["L"], scoring, weighting)]
+    for i in range(1, len(voc["parent"])):
+        lines.append("%d %d %s %s" % (voc["parent"][i], voc["is_leaf"][i], " ".join(str(int(b)) for b in voc["desc"][i]),
+                                      repr(float(voc["weight"][i]))))
+    return "\n".join(lines) + "\n"
+
+
+def descriptors_near_words(voc, n, seed=0, flip=0.08):
+    """n descriptors drawn near random leaves of the vocabulary (plus 10 % uniform ones)."""
+    rng = np.random.default_rng([seed, 32])
+    leaves = np.flatnonzero(voc["is_leaf"] > 0)
+    pick = leaves[rng.integers(0, len(leaves), n)]
+    d = flip_bits(voc["desc"][pick], flip, rng)
+    uni = rng.random(n) < 0.1
+    d[uni] = rng.integers(0, 256, (int(uni.sum()), 32), dtype=np.uint8)
+    return d

@@ -96,6 +96,19 @@ int orc_search_by_sim3(const orbfe_frame_view* kf1, const orbfe_frame_view* kf2,
 float orc_log_f32(float x);
 int orc_predict_scale(float max_distance, float dist, float log_scale_factor, int nlevels);
 
+/* ---- DBoW2 vocabulary transform (orb_bow.cc) ---- */
+typedef struct orc_vocabulary orc_vocabulary;
+orc_vocabulary* orc_vocabulary_create(int k, int L, int scoring, int weighting, int n_nodes, const int32_t* parent,
+                                      const uint8_t* is_leaf, const uint8_t* desc, const double* weight);
+orc_vocabulary* orc_vocabulary_load_text(const char* path);
+void orc_vocabulary_destroy(orc_vocabulary* v);
+void orc_vocabulary_info(const orc_vocabulary* v, int* k, int* L, int* scoring, int* weighting, int* n_nodes,
+                         int* n_words);
+int orc_vocabulary_transform(const orc_vocabulary* v, const uint8_t* desc, int n, int levelsup, uint32_t* bow_ids,
+                             double* bow_vals, int bow_cap, int32_t* n_bow, uint32_t* fv_nodes, int32_t* fv_offsets,
+                             int32_t* fv_features, int fv_cap, int32_t* n_fv, uint32_t* word_of, uint32_t* node_of,
+                             double* weight_of);
+
 #ifdef __cplusplus
 }
 #endif

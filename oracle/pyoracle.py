@@ -143,6 +143,15 @@ def lib():
         L.orc_log_f32.restype = C.c_float
         L.orc_log_f32.argtypes = [C.c_float]
         L.orc_predict_scale.argtypes = [C.c_float, C.c_float, C.c_float, C.c_int]
+        L.orc_vocabulary_create.restype = C.c_void_p
+        L.orc_vocabulary_create.argtypes = [C.c_int] * 5 + [C.c_void_p] * 4
+        L.orc_vocabulary_load_text.restype = C.c_void_p
+        L.orc_vocabulary_load_text.argtypes = [C.c_char_p]
+        L.orc_vocabulary_destroy.argtypes = [C.c_void_p]
+        L.orc_vocabulary_info.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 6
+        L.orc_vocabulary_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                               C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_hamming_bruteforce.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_void_p,
                                              C.c_void_p]
         _lib = L
@@ -459,3 +468,50 @@ def log_f32(x):
 
 def predict_scale(max_distance, dist, log_sf, nlevels):
     return int(lib().orc_predict_scale(C.c_float(max_distance), C.c_float(dist), C.c_float(log_sf), int(nlevels)))
+
+
+# ---------------------------------------------------------------- DBoW2 vocabulary transform
+class Vocabulary:
+    """CPU oracle of the DBoW2 vocabulary tree (TemplatedVocabulary.h:1127-1262, :1338-1424)."""
+
+    def __init__(self, handle):
+        if not handle:
+            raise ValueError("bad vocabulary")
+        self._h = handle
+        v = [C.c_int() for _ in range(6)]
+        lib().orc_vocabulary_info(self._h, *[C.byref(x) for x in v])
+        self.k, self.L, self.scoring, self.weighting, self.n_nodes, self.n_words = [x.value for x in v]
+
+    @classmethod
+    def from_arrays(cls, k, L, scoring, weighting, parent, is_leaf, desc, weight):
+        parent = np.ascontiguousarray(parent, np.int32)
+        is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = _u8(desc)
+        weight = np.ascontiguousarray(weight, np.float64)
+        return cls(lib().orc_vocabulary_create(k, L, scoring, weighting, len(parent), _p(parent), _p(is_leaf),
+                                               _p(desc), _p(weight)))
+
+    @classmethod
+    def load_text(cls, path):
+        return cls(lib().orc_vocabulary_load_text(os.fsencode(path)))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_vocabulary_destroy(self._h)
+            self._h = None
+
+    def transform(self, desc, levelsup):
+        desc = _u8(desc).reshape(-1, 32)
+        n = len(desc)
+        cap = max(n, 1)
+        bow_ids, bow_vals = np.empty(cap, np.uint32), np.empty(cap, np.float64)
+        fv_nodes, fv_off, fv_feat = np.empty(cap, np.uint32), np.zeros(cap + 1, np.int32), np.empty(cap, np.int32)
+        word, node, wt = np.empty(cap, np.uint32), np.empty(cap, np.uint32), np.empty(cap, np.float64)
+        nb, nf = C.c_int32(), C.c_int32()
+        rc = lib().orc_vocabulary_transform(self._h, _p(desc), n, levelsup, _p(bow_ids), _p(bow_vals), cap, C.byref(nb),
+                                            _p(fv_nodes), _p(fv_off), _p(fv_feat), cap, C.byref(nf), _p(word), _p(node),
+                                            _p(wt))
+        assert rc == 0
+        nb, nf = nb.value, nf.value
+        return (bow_ids[:nb], bow_vals[:nb], fv_nodes[:nf], fv_off[:nf + 1], fv_feat[:fv_off[nf]], word[:n], node[:n],
+                wt[:n])
