@@ -12,7 +12,10 @@
 
 namespace DBoW2 {
 typedef unsigned int NodeId;
+typedef unsigned int WordId;
+typedef double WordValue;
 typedef std::map<NodeId, std::vector<unsigned int> > FeatureVector;  // Thirdparty/DBoW2/DBoW2/FeatureVector.h
+typedef std::map<WordId, WordValue> BowVector;                        // Thirdparty/DBoW2/DBoW2/BowVector.h
 }  // namespace DBoW2
 
 namespace ORB_SLAM2 {

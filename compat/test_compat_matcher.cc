@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 
+#include "ORBVocabulary.h"
 #include "ORBmatcher.h"
 
 using namespace ORB_SLAM2;
@@ -423,6 +424,32 @@ int main(int argc, char** argv) {
     std::vector<int32_t> out;
     for (int i = 0; i < k1.N; ++i) out.push_back(index_in(p2, vm[i]));
     out.push_back(n);
+    write_i32(dir, "result", out);
+  } else if (mode == "voc") {
+    ORBVocabulary voc;
+    if (!voc.loadFromTextFile(dir + "/voc.txt")) return 3;
+    std::vector<uint8_t> d = rd<uint8_t>(dir, "desc");
+    std::vector<float> par = rd<float>(dir, "params");  // levelsup
+    std::vector<cv::Mat> feats;
+    for (size_t i = 0; i + 32 <= d.size(); i += 32) feats.push_back(desc_row(d, (int)(i / 32)));
+    DBoW2::BowVector v;
+    DBoW2::FeatureVector fv;
+    voc.transform(feats, v, fv, (int)par[0]);
+    std::vector<int32_t> out;
+    out.push_back((int32_t)voc.size());
+    out.push_back((int32_t)v.size());
+    FILE* f = std::fopen((dir + "/bow_vals.bin").c_str(), "wb");
+    for (DBoW2::BowVector::const_iterator it = v.begin(); it != v.end(); ++it) {
+      out.push_back((int32_t)it->first);
+      std::fwrite(&it->second, 8, 1, f);
+    }
+    std::fclose(f);
+    out.push_back((int32_t)fv.size());
+    for (DBoW2::FeatureVector::const_iterator it = fv.begin(); it != fv.end(); ++it) {
+      out.push_back((int32_t)it->first);
+      out.push_back((int32_t)it->second.size());
+      for (size_t k = 0; k < it->second.size(); ++k) out.push_back((int32_t)it->second[k]);
+    }
     write_i32(dir, "result", out);
   } else {
     return 2;

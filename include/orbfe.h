@@ -227,6 +227,18 @@ int orbfe_search_by_sim3(orbfe_matcher* m, const orbfe_frame_view* kf1, const or
                          const orbfe_points3d_view* p1, const orbfe_points3d_view* p2, const orbfe_sim3_pair* s,
                          float th, int32_t* match12, int32_t* n_found);
 
+/* Tracking::SearchLocalPoints (src/Tracking.cc:1258-1284) in one call: Frame::isInFrustum
+ * (src/Frame.cc:285-349) for every local map point on the device, then SearchByProjection(Frame&, vpMapPoints, th)
+ * (src/ORBmatcher.cc:46-132) on the device-resident mTrackProj* fields.  pts->valid = the point is visited by the
+ * loop (mnLastFrameSeen != frame id, !isBad()); obs = Observations() per point; pr = mTcw / calibration / mbf /
+ * mfLogScaleFactor of the frame (has_ow = 0: mOw = -mRcw^T mtcw as Frame::UpdatePoseMatrices).  Outputs: assigned /
+ * n_matches as orbfe_search_by_projection_map; per point in_view = isInFrustum() (the caller's IncreaseVisible) and,
+ * where not NULL, mTrackProjX / mTrackProjY / mTrackProjXR / mnTrackScaleLevel / mTrackViewCos. */
+int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* frame, const orbfe_projection* pr,
+                              const orbfe_points3d_view* pts, const int32_t* obs, float viewing_cos_limit, float th,
+                              float nnratio, int32_t* assigned, int32_t* n_matches, uint8_t* in_view, float* proj_x,
+                              float* proj_y, float* proj_xr, int32_t* level, float* view_cos);
+
 /* Brute-force Hamming (BASELINE.json config 5): per query the two smallest
  * keys (dist << 32 | index_base + j) over the map shard (index_base + nm <= 2^32); ties -> lowest index.
  * Host arrays in/out. */

@@ -350,6 +350,54 @@ __global__ void __launch_bounds__(1024) init_resolve_kernel(const DevFrame f2, c
   if (tid == 0) *n_matches = s_n;
 }
 
+
+// ------------------------------------------------------------------------------------------------ isInFrustum
+// Frame::isInFrustum (src/Frame.cc:285-349) over the local map (Tracking::SearchLocalPoints, src/Tracking.cc:1258-1273):
+// fills the mbTrackInView / mTrackProj* fields that SearchByProjection(Frame&, vector<MapPoint*>&, th) reads, on the
+// device, so the projection search starts without a host pass over the map.
+__global__ void frustum_kernel(const DevFrame f, const DevPoints p, const DevProjection P, float cos_limit,
+                               uint8_t* __restrict__ in_view, float* __restrict__ proj_x, float* __restrict__ proj_y,
+                               float* __restrict__ proj_xr, int32_t* __restrict__ level, float* __restrict__ view_cos) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.m) return;
+  uint8_t ok = 0;
+  float u = 0.f, v = 0.f, ur = 0.f, vc = 0.f;
+  int lvl = 0;
+  if (p.valid[i]) {
+    const float X0 = p.world_pos[3 * i], X1 = p.world_pos[3 * i + 1], X2 = p.world_pos[3 * i + 2];
+    float pc[3];
+    rigid3(P.R, P.t, X0, X1, X2, pc);
+    if (!(pc[2] < 0.0f)) {
+      const float invz = __fdiv_rn(1.0f, pc[2]);
+      u = __fadd_rn(__fmul_rn(__fmul_rn(P.fx, pc[0]), invz), P.cx);
+      v = __fadd_rn(__fmul_rn(__fmul_rn(P.fy, pc[1]), invz), P.cy);
+      if (!(u < f.min_x || u > f.max_x) && !(v < f.min_y || v > f.max_y)) {
+        const float po0 = __fsub_rn(X0, P.Ow[0]), po1 = __fsub_rn(X1, P.Ow[1]), po2 = __fsub_rn(X2, P.Ow[2]);
+        const float dist = norm3(po0, po1, po2);
+        if (!(dist < p.min_inv[i] || dist > p.max_inv[i])) {
+          const double dot = __dadd_rn(__dadd_rn(__dmul_rn((double)po0, (double)p.normal[3 * i]),
+                                                 __dmul_rn((double)po1, (double)p.normal[3 * i + 1])),
+                                       __dmul_rn((double)po2, (double)p.normal[3 * i + 2]));
+          vc = (float)__ddiv_rn(dot, (double)dist);  // const float viewCos = PO.dot(Pn)/dist
+          if (!(vc < cos_limit)) {
+            lvl = orb_predict_scale(p.max_d[i], dist, P.log_sf, f.nlevels);
+            ur = __fsub_rn(u, __fmul_rn(P.bf, invz));
+            ok = 1;
+          }
+        }
+      }
+    }
+  }
+  in_view[i] = ok;  // the reference leaves the fields of rejected points stale; here they read 0
+  proj_x[i] = ok ? u : 0.f; proj_y[i] = ok ? v : 0.f; proj_xr[i] = ur; level[i] = lvl; view_cos[i] = ok ? vc : 0.f;
+}
+
+void launch_frustum(const DevFrame& f, const DevPoints& p, const DevProjection& P, float cos_limit, uint8_t* in_view,
+                    float* proj_x, float* proj_y, float* proj_xr, int32_t* level, float* view_cos, cudaStream_t s) {
+  if (p.m > 0)
+    frustum_kernel<<<(p.m + 127) / 128, 128, 0, s>>>(f, p, P, cos_limit, in_view, proj_x, proj_y, proj_xr, level, view_cos);
+}
+
 // ------------------------------------------------------------------------------------------------ launchers
 void launch_proj_candidates(int mode, const DevFrame& f, const DevPoints& p, const DevProjection& P, float th,
                             const SearchScratch& sc, int fill, cudaStream_t s) {

@@ -124,6 +124,8 @@ void launch_proj_candidates(int mode, const DevFrame& f, const DevPoints& p, con
                             const SearchScratch& sc, int fill, cudaStream_t s);
 void launch_proj_best(int mode, const DevFrame& f, const DevPoints& p, const DevProjection& P, float th,
                       const float* inv_sigma2, int accept_th, int32_t* best_idx, int32_t* n_found, cudaStream_t s);
+void launch_frustum(const DevFrame& f, const DevPoints& p, const DevProjection& P, float cos_limit, uint8_t* in_view,
+                    float* proj_x, float* proj_y, float* proj_xr, int32_t* level, float* view_cos, cudaStream_t s);
 void launch_sim3_agree(const int32_t* m1, int n1, const int32_t* m2, int n2, int32_t* out12, int32_t* n_found,
                        cudaStream_t s);
 // SearchByBoW: claimed2 [k2.n] zeroed, matches [n_out] = -1 on entry

@@ -131,6 +131,73 @@ int orbfe_search_by_projection_sim3(orbfe_matcher* h, const orbfe_frame_view* kf
   return projection_claims(h, PM_SIM3, kf, pr, pts, (float)th, ORBFE_TH_LOW, 0, assigned, n_matches);
 }
 
+int orbfe_search_local_points(orbfe_matcher* h, const orbfe_frame_view* frame, const orbfe_projection* pr,
+                              const orbfe_points3d_view* pts, const int32_t* obs, float viewing_cos_limit, float th,
+                              float nnratio, int32_t* assigned, int32_t* n_matches, uint8_t* in_view, float* proj_x,
+                              float* proj_y, float* proj_xr, int32_t* level, float* view_cos) {
+  ORBFE_ARG(h && pr);
+  int rc = check_frame(frame);
+  if (rc != ORBFE_OK) return rc;
+  rc = check_points(pts, true, false);
+  if (rc != ORBFE_OK) return rc;
+  ORBFE_ARG(frame->n == 0 || assigned);
+  ORBFE_ARG(pts->m == 0 || (obs && in_view));
+  if (n_matches) *n_matches = 0;
+  for (int i = 0; i < frame->n; ++i) assigned[i] = -1;
+  if (pts->m == 0) return ORBFE_OK;
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  const size_t M = (size_t)pts->m;
+  rc = arena_reserve(m, frame_bytes(frame) + points_bytes(pts) + 7 * padded(M * 4) + scratch_bytes(pts->m, frame->n));
+  if (rc != ORBFE_OK) return rc;
+  DevFrame f;
+  put_frame(m, frame, &f);
+  DevPoints d;
+  put_points(m, pts, &d);
+  const int32_t* d_obs = arena_put(m, obs, M);
+  DevProjection P;
+  decompose_pose(pr, &P);
+  const size_t up = m->off;
+  uint8_t* d_in = arena_alloc<uint8_t>(m, M);
+  float* d_px = arena_alloc<float>(m, M);
+  float* d_py = arena_alloc<float>(m, M);
+  float* d_pxr = arena_alloc<float>(m, M);
+  int32_t* d_lvl = arena_alloc<int32_t>(m, M);
+  float* d_vc = arena_alloc<float>(m, M);
+  SearchScratch sc;
+  alloc_scratch(m, pts->m, std::max(frame->n, 1), &f, &sc);
+  ORBFE_CUDA(cudaMemcpyAsync(m->d_buf, m->h_buf, up, cudaMemcpyHostToDevice, m->stream));
+  launch_frustum(f, d, P, viewing_cos_limit, d_in, d_px, d_py, d_pxr, d_lvl, d_vc, m->stream);
+  m->launches += 1;
+  int result = ORBFE_OK;
+  if (frame->n > 0) {
+    DevMapPoints mp;  // the fields the map overload reads, now device-resident
+    mp.m = pts->m;
+    mp.proj_x = d_px; mp.proj_y = d_py; mp.proj_xr = d_pxr; mp.view_cos = d_vc;
+    mp.level = d_lvl; mp.obs = d_obs; mp.in_view = d_in; mp.desc = d.desc;
+    launch_build_grid(f, m->stream);
+    launch_sbp_map_candidates(f, mp, th, sc, 0, m->stream);
+    m->launches += 2;
+    struct Ctx { Matcher* m; DevFrame* f; DevMapPoints* d; float th; SearchScratch* sc; } ctx = {m, &f, &mp, th, &sc};
+    auto fill = [](void* p, int fl) {
+      Ctx* c = static_cast<Ctx*>(p);
+      launch_sbp_map_candidates(*c->f, *c->d, c->th, *c->sc, fl, c->m->stream);
+    };
+    result = finish_projection(m, f, pts->m, d_obs, nullptr, 0, nnratio, 0, ORBFE_TH_HIGH, sc, fill, &ctx, assigned,
+                               n_matches);
+    if (result != ORBFE_OK) return result;
+  }
+  ORBFE_CUDA(cudaMemcpyAsync(in_view, d_in, M, cudaMemcpyDeviceToHost, m->stream));
+  if (proj_x) ORBFE_CUDA(cudaMemcpyAsync(proj_x, d_px, M * 4, cudaMemcpyDeviceToHost, m->stream));
+  if (proj_y) ORBFE_CUDA(cudaMemcpyAsync(proj_y, d_py, M * 4, cudaMemcpyDeviceToHost, m->stream));
+  if (proj_xr) ORBFE_CUDA(cudaMemcpyAsync(proj_xr, d_pxr, M * 4, cudaMemcpyDeviceToHost, m->stream));
+  if (level) ORBFE_CUDA(cudaMemcpyAsync(level, d_lvl, M * 4, cudaMemcpyDeviceToHost, m->stream));
+  if (view_cos) ORBFE_CUDA(cudaMemcpyAsync(view_cos, d_vc, M * 4, cudaMemcpyDeviceToHost, m->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  ORBFE_CUDA(cudaGetLastError());
+  return ORBFE_OK;
+}
+
 int orbfe_fuse(orbfe_matcher* h, const orbfe_frame_view* kf, const orbfe_projection* pr,
                const orbfe_points3d_view* pts, float th, const float* inv_level_sigma2, int32_t* best_idx,
                int32_t* n_fused) {

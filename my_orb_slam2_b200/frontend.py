@@ -232,6 +232,11 @@ class ORBmatcher:
         """(KeyFrame*, Scw, vpPoints, vpMatched, th) (:321); returns (assigned, nmatches)."""
         return self._matcher(self.device).search_by_projection_sim3(kf, proj, pts, th)
 
+    def SearchLocalPoints(self, F, proj, pts, obs, th=1.0, viewingCosLimit=0.5):
+        """Tracking::SearchLocalPoints (src/Tracking.cc:1258-1284): Frame::isInFrustum over the local map fused with
+        SearchByProjection(Frame&, vpMapPoints, th); returns (assigned, nmatches, per-point track fields)."""
+        return self._matcher(self.device).search_local_points(F, proj, pts, obs, viewingCosLimit, th, self.mfNNratio)
+
     def Fuse(self, kf, proj, pts, th=3.0, inv_level_sigma2=None):
         """The search of both Fuse overloads (:879, :1033); returns (best_idx per point, nFused)."""
         return self._matcher(self.device).fuse(kf, proj, pts, th, inv_level_sigma2)

@@ -133,6 +133,8 @@ SYMBOLS = {
                                               C.POINTER(Points3DView), _F, _I, _I, _P, _P]),
     "orbfe_search_by_projection_sim3": (_I, [_P, C.POINTER(FrameView), C.POINTER(Projection),
                                              C.POINTER(Points3DView), _I, _P, _P]),
+    "orbfe_search_local_points": (_I, [_P, C.POINTER(FrameView), C.POINTER(Projection), C.POINTER(Points3DView), _P,
+                                       _F, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P]),
     "orbfe_fuse": (_I, [_P, C.POINTER(FrameView), C.POINTER(Projection), C.POINTER(Points3DView), _F, _P, _P, _P]),
     "orbfe_search_by_sim3": (_I, [_P, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(Points3DView),
                                   C.POINTER(Points3DView), C.POINTER(Sim3Pair), _F, _P, _P]),
@@ -390,6 +392,21 @@ class Matcher:
         check(lib().orbfe_search_by_projection_sim3(self._h, C.byref(kf.struct), C.byref(proj), C.byref(pts.struct),
                                                     int(th), _p(assigned), C.byref(n)))
         return assigned[:kf.struct.n], n.value
+
+    def search_local_points(self, frame, proj, pts, obs, cos_limit, th, nnratio):
+        """Returns (assigned, nmatches, dict(in_view, proj_x, proj_y, proj_xr, level, view_cos))."""
+        m = pts.struct.m
+        obs = np.ascontiguousarray(obs, np.int32)
+        assigned = np.empty(max(frame.struct.n, 1), np.int32)
+        out = dict(in_view=np.zeros(max(m, 1), np.uint8), proj_x=np.zeros(max(m, 1), np.float32),
+                   proj_y=np.zeros(max(m, 1), np.float32), proj_xr=np.zeros(max(m, 1), np.float32),
+                   level=np.zeros(max(m, 1), np.int32), view_cos=np.zeros(max(m, 1), np.float32))
+        n = C.c_int32()
+        check(lib().orbfe_search_local_points(self._h, C.byref(frame.struct), C.byref(proj), C.byref(pts.struct),
+                                              _p(obs), cos_limit, th, nnratio, _p(assigned), C.byref(n),
+                                              _p(out["in_view"]), _p(out["proj_x"]), _p(out["proj_y"]),
+                                              _p(out["proj_xr"]), _p(out["level"]), _p(out["view_cos"])))
+        return assigned[:frame.struct.n], n.value, {k: v[:m] for k, v in out.items()}
 
     def fuse(self, kf, proj, pts, th, inv_level_sigma2=None):
         best = np.empty(max(pts.struct.m, 1), np.int32)

@@ -429,6 +429,43 @@ int orc_search_by_sim3(const orbfe_frame_view* kf1, const orbfe_frame_view* kf2,
   return nFound;
 }
 
+// ---- Tracking::SearchLocalPoints (src/Tracking.cc:1258-1284): Frame::isInFrustum (src/Frame.cc:285-349) per local
+// map point, then SearchByProjection(Frame&, vpMapPoints, th) on the fields it filled.
+int orc_search_local_points(const orbfe_frame_view* F, const orbfe_projection* pr, const orbfe_points3d_view* pts,
+                            const int32_t* obs, float viewingCosLimit, float th, float nnratio, int32_t* assigned,
+                            uint8_t* in_view, float* proj_x, float* proj_y, float* proj_xr, int32_t* level,
+                            float* view_cos) {
+  const orc::Pose P = orc::decompose(pr);
+  for (int i = 0; i < pts->m; ++i) {
+    in_view[i] = 0;  // pMP->mbTrackInView = false
+    proj_x[i] = proj_y[i] = proj_xr[i] = view_cos[i] = 0.f;
+    level[i] = 0;
+    if (!pts->valid[i]) continue;
+    const float* X = pts->world_pos + 3 * i;
+    float Pc[3];
+    orc::rigid(P.R, P.t, X, Pc);
+    if (Pc[2] < 0.0f) continue;
+    const float invz = 1.0f / Pc[2];
+    const float u = pr->fx * Pc[0] * invz + pr->cx;
+    const float v = pr->fy * Pc[1] * invz + pr->cy;
+    if (u < F->min_x || u > F->max_x) continue;
+    if (v < F->min_y || v > F->max_y) continue;
+    const float PO[3] = {X[0] - P.Ow[0], X[1] - P.Ow[1], X[2] - P.Ow[2]};
+    const float dist = orc::norm3(PO);
+    if (dist < pts->min_dist_inv[i] || dist > pts->max_dist_inv[i]) continue;
+    const float viewCos = (float)(orc::dot3(PO, pts->normal + 3 * i) / (double)dist);
+    if (viewCos < viewingCosLimit) continue;
+    proj_x[i] = u; proj_y[i] = v; view_cos[i] = viewCos;
+    level[i] = orb_predict_scale(pts->max_distance[i], dist, pr->log_scale_factor, F->nlevels);
+    proj_xr[i] = u - pr->bf * invz;
+    in_view[i] = 1;
+  }
+  orbfe_mappoints_view mv;
+  mv.m = pts->m; mv.proj_x = proj_x; mv.proj_y = proj_y; mv.proj_xr = proj_xr; mv.level = level;
+  mv.view_cos = view_cos; mv.in_view = in_view; mv.obs = obs; mv.desc = pts->desc;
+  return orc_search_by_projection_map(F, &mv, th, nnratio, assigned);
+}
+
 float orc_log_f32(float x) { return orb_log_f32(x); }
 int orc_predict_scale(float max_distance, float dist, float log_scale_factor, int nlevels) {
   return orb_predict_scale(max_distance, dist, log_scale_factor, nlevels);

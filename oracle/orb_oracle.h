@@ -92,6 +92,10 @@ int orc_fuse(const orbfe_frame_view* kf, const orbfe_projection* pr, const orbfe
              const float* inv_level_sigma2, int32_t* best_idx);
 int orc_search_by_sim3(const orbfe_frame_view* kf1, const orbfe_frame_view* kf2, const orbfe_points3d_view* p1,
                        const orbfe_points3d_view* p2, const orbfe_sim3_pair* s, float th, int32_t* match12);
+int orc_search_local_points(const orbfe_frame_view* F, const orbfe_projection* pr, const orbfe_points3d_view* pts,
+                            const int32_t* obs, float viewingCosLimit, float th, float nnratio, int32_t* assigned,
+                            uint8_t* in_view, float* proj_x, float* proj_y, float* proj_xr, int32_t* level,
+                            float* view_cos);
 /* shared arithmetic probes (include/orb_math_shared.h) for the known-answer tests */
 float orc_log_f32(float x);
 int orc_predict_scale(float max_distance, float dist, float log_scale_factor, int nlevels);

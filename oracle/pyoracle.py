@@ -152,6 +152,8 @@ def lib():
         L.orc_vocabulary_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                                C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_search_local_points.argtypes = [C.POINTER(FrameView), C.POINTER(Projection), C.POINTER(Points3DView),
+                                              C.c_void_p, C.c_float, C.c_float, C.c_float] + [C.c_void_p] * 7
         L.orc_hamming_bruteforce.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_void_p,
                                              C.c_void_p]
         _lib = L
@@ -460,6 +462,19 @@ def search_by_sim3(kf1, kf2, p1, p2, pair, th):
     n = lib().orc_search_by_sim3(C.byref(kf1.struct), C.byref(kf2.struct), C.byref(p1.struct), C.byref(p2.struct),
                                  C.byref(pair), C.c_float(th), _p(m12))
     return m12[:p1.struct.m], n
+
+
+def search_local_points(frame, proj, pts, obs, cos_limit, th, nnratio):
+    m = pts.struct.m
+    obs = np.ascontiguousarray(obs, np.int32)
+    assigned = np.empty(max(frame.struct.n, 1), np.int32)
+    out = dict(in_view=np.zeros(max(m, 1), np.uint8), proj_x=np.zeros(max(m, 1), np.float32),
+               proj_y=np.zeros(max(m, 1), np.float32), proj_xr=np.zeros(max(m, 1), np.float32),
+               level=np.zeros(max(m, 1), np.int32), view_cos=np.zeros(max(m, 1), np.float32))
+    n = lib().orc_search_local_points(C.byref(frame.struct), C.byref(proj), C.byref(pts.struct), _p(obs), cos_limit, th,
+                                      nnratio, _p(assigned), _p(out["in_view"]), _p(out["proj_x"]), _p(out["proj_y"]),
+                                      _p(out["proj_xr"]), _p(out["level"]), _p(out["view_cos"]))
+    return assigned[:frame.struct.n], n, {k: v[:m] for k, v in out.items()}
 
 
 def log_f32(x):

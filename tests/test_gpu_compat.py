@@ -276,3 +276,29 @@ def test_cpp_matcher_search_by_sim3(oracle, kitti_frame, tmp_path):
     want, wn = oracle.search_by_sim3(views(oracle, frame=f1), views(oracle, frame=f2), points_view(oracle, p1),
                                      points_view(oracle, p2), sim3_pair(oracle, pair), 7.5)
     assert n == wn and wn > 300 and np.array_equal(got, want)
+
+
+def test_cpp_vocabulary(oracle, tmp_path):
+    """compat/ORBVocabulary.h: loadFromTextFile + transform into DBoW2's std::map containers."""
+    voc = synth.vocabulary_case(10, 4, seed=2)
+    d = str(tmp_path)
+    os.makedirs(d, exist_ok=True)
+    with open(os.path.join(d, "voc.txt"), "w") as f:
+        f.write(synth.vocabulary_text(voc, 0, 0))
+    desc = synth.descriptors_near_words(voc, 1800, seed=4)
+    _dump(d, desc=desc, params=np.array([4.0], np.float32))
+    subprocess.check_call([_exe(), "voc", d])
+    res = np.fromfile(os.path.join(d, "result.bin"), np.int32)
+    vals = np.fromfile(os.path.join(d, "bow_vals.bin"), np.float64)
+    ov = oracle.Vocabulary.from_arrays(10, 4, 0, 0, voc["parent"], voc["is_leaf"], voc["desc"], voc["weight"])
+    ids, wvals, fvn, fvo, fvf, _, _, _ = ov.transform(desc, 4)
+    assert res[0] == ov.n_words and res[1] == len(ids) and len(ids) > 300
+    assert np.array_equal(res[2:2 + len(ids)], ids.astype(np.int32)) and np.array_equal(vals, wvals)
+    p = 2 + len(ids)
+    assert res[p] == len(fvn)
+    p += 1
+    for j, nd in enumerate(fvn):
+        cnt = fvo[j + 1] - fvo[j]
+        assert res[p] == nd and res[p + 1] == cnt and np.array_equal(res[p + 2:p + 2 + cnt], fvf[fvo[j]:fvo[j + 1]])
+        p += 2 + cnt
+    assert p == len(res)

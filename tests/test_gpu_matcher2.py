@@ -124,3 +124,21 @@ def test_empty_inputs(fe, feats):
     got, gn = fe.ORBmatcher(0.6, True).Fuse(views(fe, frame=frame), projection(fe, pr), points_view(fe, none), 3.0,
                                            np.ones(8, np.float32))
     assert gn == 0 and len(got) == 0
+
+
+@pytest.mark.parametrize("seed,th,n_extra", [(0, 1.0, 400), (1, 3.0, 400), (2, 5.0, 18000), (3, 1.0, 0)])
+def test_search_local_points(fe, oracle, feats, seed, th, n_extra):
+    """Frame::isInFrustum over the local map fused with SearchByProjection (SURVEY.md 8(f)-3)."""
+    kp, desc = feats
+    frame = synth.frame_arrays(kp, desc, BOUNDS, seed=seed, taken_frac=0.1)
+    pts, pr = synth.points3d_case(frame, seed=seed, n_extra=n_extra, noise_px=1.0)
+    obs = np.random.default_rng(seed).integers(0, 9, len(pts["valid"])).astype(np.int32)
+    wa, wn, wf = oracle.search_local_points(views(oracle, frame=frame), projection(oracle, pr), points_view(oracle, pts),
+                                            obs, 0.5, th, 0.8)
+    ga, gn, gf = fe.ORBmatcher(0.8, True).SearchLocalPoints(views(fe, frame=frame), projection(fe, pr),
+                                                           points_view(fe, pts), obs, th)
+    assert gn == wn and np.array_equal(ga, wa) and wn > 300
+    for k in wf:
+        assert np.array_equal(gf[k].view(np.uint32) if gf[k].dtype == np.float32 else gf[k],
+                              wf[k].view(np.uint32) if wf[k].dtype == np.float32 else wf[k]), k
+    assert 0.3 < wf["in_view"].mean() < 0.98
