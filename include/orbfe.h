@@ -239,6 +239,14 @@ int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* frame, c
                               float nnratio, int32_t* assigned, int32_t* n_matches, uint8_t* in_view, float* proj_x,
                               float* proj_y, float* proj_xr, int32_t* level, float* view_cos);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:252-318), batched over the map points a new keyframe
+ * touches.  Point p observes desc[offsets[p] .. offsets[p+1]) (32 bytes each, in the iteration order
+ * of its mObservations with bad keyframes left out); best_idx[p] = index WITHIN the point's list of the descriptor
+ * with the least median Hamming distance to the rest (first one on ties), -1 for an empty list (the reference then
+ * keeps the old descriptor); best_desc (optional, n_points x 32) = that descriptor, zeros for -1. */
+int orbfe_compute_distinctive_descriptors(orbfe_matcher* m, const uint8_t* desc, const int32_t* offsets, int n_points,
+                                          int32_t* best_idx, uint8_t* best_desc);
+
 /* Brute-force Hamming (BASELINE.json config 5): per query the two smallest
  * keys (dist << 32 | index_base + j) over the map shard (index_base + nm <= 2^32); ties -> lowest index.
  * Host arrays in/out. */

@@ -11,6 +11,8 @@
 //     branch-free with 3 min/max (ties -> lowest index falls out of the packing);
 //   * per (query, map slice) partial top-2 go to a small workspace and a second kernel
 //     merges slices (and, multi-GPU, shards) as 64-bit keys dist<<32 | global index.
+#include <climits>
+
 #include "match_kernels.h"
 
 namespace orbfe {
@@ -189,6 +191,75 @@ void launch_hamming_bruteforce(const uint8_t* query, int nq, const uint8_t* map,
 void launch_hamming_merge(const unsigned long long* best_all, const unsigned long long* second_all, int parts, int nq,
                           unsigned long long* best, unsigned long long* second, cudaStream_t s) {
   hamming_merge_kernel<<<(nq + 255) / 256, 256, 0, s>>>(best_all, second_all, parts, nq, best, second);
+}
+
+
+// ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:252-318), batched over map points:
+// one warp per point; for every observation i the median of its Hamming distances to all observations of the point
+// (self included, element floor(0.5*(N-1)) of the sorted row, :303-305) is found by a 9-step bisection on the value
+// range [0, 256] with warp-wide counts; the first observation with the least median wins (:307-311).
+__device__ __forceinline__ int hamming_regs(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
+  return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+         __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__global__ void __launch_bounds__(256) distinctive_kernel(const uint8_t* __restrict__ desc,
+                                                          const int32_t* __restrict__ offsets, int n_points,
+                                                          int32_t* __restrict__ best_idx,
+                                                          uint8_t* __restrict__ best_desc) {
+  const int lane = threadIdx.x & 31;
+  const int p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (p >= n_points) return;
+  const int beg = offsets[p], N = offsets[p + 1] - beg;
+  if (N <= 0) {
+    if (lane == 0) best_idx[p] = -1;  // "if(vDescriptors.empty()) return;": the descriptor stays as it was
+    return;
+  }
+  const uint4* D = reinterpret_cast<const uint4*>(desc + (size_t)beg * 32);
+  const int k = (int)(0.5 * (double)(N - 1));  // vDists[0.5*(N-1)]
+  int best_median = INT_MAX, best_i = 0;
+  if (N <= 32) {  // one observation per lane: the row of distances lives in registers
+    uint4 m0 = make_uint4(0, 0, 0, 0), m1 = m0;
+    if (lane < N) { m0 = __ldg(D + 2 * lane); m1 = __ldg(D + 2 * lane + 1); }
+    for (int i = 0; i < N; ++i) {
+      uint4 a0, a1;
+      a0.x = __shfl_sync(0xffffffffu, m0.x, i); a0.y = __shfl_sync(0xffffffffu, m0.y, i);
+      a0.z = __shfl_sync(0xffffffffu, m0.z, i); a0.w = __shfl_sync(0xffffffffu, m0.w, i);
+      a1.x = __shfl_sync(0xffffffffu, m1.x, i); a1.y = __shfl_sync(0xffffffffu, m1.y, i);
+      a1.z = __shfl_sync(0xffffffffu, m1.z, i); a1.w = __shfl_sync(0xffffffffu, m1.w, i);
+      const int d = lane < N ? hamming_regs(a0, a1, m0, m1) : 1 << 20;
+      int lo = 0, hi = 256;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const int c = __popc(__ballot_sync(0xffffffffu, d <= mid));
+        if (c >= k + 1) hi = mid; else lo = mid + 1;
+      }
+      if (lo < best_median) { best_median = lo; best_i = i; }
+    }
+  } else {  // long observation lists: distances are recomputed inside the bisection
+    for (int i = 0; i < N; ++i) {
+      const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
+      int lo = 0, hi = 256;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        int c = 0;
+        for (int j = lane; j < N; j += 32) c += hamming_regs(a0, a1, __ldg(D + 2 * j), __ldg(D + 2 * j + 1)) <= mid;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        if (c >= k + 1) hi = mid; else lo = mid + 1;
+      }
+      if (lo < best_median) { best_median = lo; best_i = i; }
+    }
+  }
+  if (lane == 0) best_idx[p] = best_i;
+  if (best_desc && lane < 8)
+    reinterpret_cast<uint32_t*>(best_desc + (size_t)p * 32)[lane] =
+        reinterpret_cast<const uint32_t*>(desc + (size_t)(beg + best_i) * 32)[lane];
+}
+
+void launch_distinctive(const uint8_t* desc, const int32_t* offsets, int n_points, int32_t* best_idx,
+                        uint8_t* best_desc, cudaStream_t s) {
+  if (n_points > 0) distinctive_kernel<<<(n_points + 7) / 8, 256, 0, s>>>(desc, offsets, n_points, best_idx, best_desc);
 }
 
 }  // namespace orbfe

@@ -18,6 +18,9 @@ void launch_hamming_bruteforce(const uint8_t* query, int nq, const uint8_t* map,
 void launch_hamming_merge(const unsigned long long* best_all, const unsigned long long* second_all, int parts, int nq,
                           unsigned long long* best, unsigned long long* second, cudaStream_t s);
 
+void launch_distinctive(const uint8_t* desc, const int32_t* offsets, int n_points, int32_t* best_idx,
+                        uint8_t* best_desc, cudaStream_t s);
+
 // ---- k_search.cu ----
 // Device mirror of orbfe_frame_view + the 64x48 grid of Frame::AssignFeaturesToGrid (src/Frame.cc:243-258) in CSR form.
 struct DevFrame {

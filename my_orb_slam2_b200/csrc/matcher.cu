@@ -74,6 +74,35 @@ int orbfe_descriptor_distance(orbfe_matcher* h, const uint8_t* a, const uint8_t*
   return ORBFE_OK;
 }
 
+int orbfe_compute_distinctive_descriptors(orbfe_matcher* h, const uint8_t* desc, const int32_t* offsets, int n_points,
+                                          int32_t* best_idx, uint8_t* best_desc) {
+  ORBFE_ARG(h && n_points >= 0);
+  if (n_points == 0) return ORBFE_OK;
+  ORBFE_ARG(offsets && best_idx && offsets[0] == 0);
+  for (int p = 0; p < n_points; ++p) ORBFE_ARG(offsets[p + 1] >= offsets[p]);
+  const size_t total = (size_t)offsets[n_points];
+  ORBFE_ARG(total == 0 || desc);
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  const size_t P = (size_t)n_points;
+  int rc = arena_reserve(m, padded(total * 32) + padded((P + 1) * 4) + padded(P * 4) + padded(P * 32));
+  if (rc != ORBFE_OK) return rc;
+  const uint8_t* dd = arena_put(m, desc, total * 32);
+  const int32_t* doff = arena_put(m, offsets, P + 1);
+  const size_t up = m->off;
+  int32_t* dbest = arena_alloc<int32_t>(m, P);
+  uint8_t* dbd = best_desc ? arena_alloc<uint8_t>(m, P * 32) : nullptr;
+  ORBFE_CUDA(cudaMemcpyAsync(m->d_buf, m->h_buf, up, cudaMemcpyHostToDevice, m->stream));
+  if (dbd) ORBFE_CUDA(cudaMemsetAsync(dbd, 0, P * 32, m->stream));
+  launch_distinctive(dd, doff, n_points, dbest, dbd, m->stream);
+  m->launches += 1;
+  ORBFE_CUDA(cudaMemcpyAsync(best_idx, dbest, P * 4, cudaMemcpyDeviceToHost, m->stream));
+  if (dbd) ORBFE_CUDA(cudaMemcpyAsync(best_desc, dbd, P * 32, cudaMemcpyDeviceToHost, m->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  ORBFE_CUDA(cudaGetLastError());
+  return ORBFE_OK;
+}
+
 int orbfe_hamming_merge_device(orbfe_matcher* h, const uint64_t* d_best_all, const uint64_t* d_second_all, int shards,
                                int nq, uint64_t* d_best, uint64_t* d_second) {
   ORBFE_ARG(h && d_best_all && d_second_all && d_best && d_second && shards >= 1 && nq >= 1);

@@ -135,6 +135,7 @@ SYMBOLS = {
                                              C.POINTER(Points3DView), _I, _P, _P]),
     "orbfe_search_local_points": (_I, [_P, C.POINTER(FrameView), C.POINTER(Projection), C.POINTER(Points3DView), _P,
                                        _F, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "orbfe_compute_distinctive_descriptors": (_I, [_P, _P, _P, _I, _P, _P]),
     "orbfe_fuse": (_I, [_P, C.POINTER(FrameView), C.POINTER(Projection), C.POINTER(Points3DView), _F, _P, _P, _P]),
     "orbfe_search_by_sim3": (_I, [_P, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(Points3DView),
                                   C.POINTER(Points3DView), C.POINTER(Sim3Pair), _F, _P, _P]),
@@ -422,6 +423,15 @@ class Matcher:
         check(lib().orbfe_search_by_sim3(self._h, C.byref(kf1.struct), C.byref(kf2.struct), C.byref(p1.struct),
                                          C.byref(p2.struct), C.byref(pair), th, _p(m12), C.byref(n)))
         return m12[:p1.struct.m], n.value
+
+    def compute_distinctive_descriptors(self, desc, offsets):
+        desc = _u8(desc).reshape(-1, 32)
+        offsets = np.ascontiguousarray(offsets, np.int32)
+        n = len(offsets) - 1
+        best = np.empty(max(n, 1), np.int32)
+        bd = np.zeros((max(n, 1), 32), np.uint8)
+        check(lib().orbfe_compute_distinctive_descriptors(self._h, _p(desc), _p(offsets), n, _p(best), _p(bd)))
+        return best[:n], bd[:n]
 
     def popc_peak(self):
         v = C.c_double()

@@ -467,3 +467,18 @@ def descriptors_near_words(voc, n, seed=0, flip=0.08):
     uni = rng.random(n) < 0.1
     d[uni] = rng.integers(0, 256, (int(uni.sum()), 32), dtype=np.uint8)
     return d
+
+
+def observations_case(n_points=5000, seed=0, max_obs=40, long_lists=3):
+    """Descriptor lists of map points for ComputeDistinctiveDescriptors: every point has 0..max_obs noisy copies of a
+    prototype (a few outliers included), and `long_lists` points carry several hundred observations."""
+    rng = np.random.default_rng([seed, 41])
+    counts = rng.integers(0, max_obs + 1, n_points)
+    counts[rng.random(n_points) < 0.3] = rng.integers(1, 5, int((rng.random(n_points) < 0.3).sum() or 1))[0]
+    counts[:long_lists] = rng.integers(100, 400, long_lists)
+    offsets = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    proto = rng.integers(0, 256, (n_points, 32), dtype=np.uint8)
+    desc = flip_bits(np.repeat(proto, counts, axis=0), 0.07, rng)
+    out = rng.random(len(desc)) < 0.05
+    desc[out] = rng.integers(0, 256, (int(out.sum()), 32), dtype=np.uint8)
+    return desc, offsets

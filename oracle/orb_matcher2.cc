@@ -466,6 +466,34 @@ int orc_search_local_points(const orbfe_frame_view* F, const orbfe_projection* p
   return orc_search_by_projection_map(F, &mv, th, nnratio, assigned);
 }
 
+// ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:252-318) for a batch of points (CSR of descriptors)
+void orc_compute_distinctive_descriptors(const uint8_t* desc, const int32_t* offsets, int n_points, int32_t* best_idx,
+                                         uint8_t* best_desc) {
+  for (int p = 0; p < n_points; ++p) {
+    const int beg = offsets[p], N = offsets[p + 1] - beg;
+    if (best_desc) std::memset(best_desc + (size_t)p * 32, 0, 32);
+    if (N <= 0) { best_idx[p] = -1; continue; }
+    std::vector<std::vector<float>> Distances(N, std::vector<float>(N));
+    for (int i = 0; i < N; ++i) {
+      Distances[i][i] = 0;
+      for (int j = i + 1; j < N; ++j) {
+        const int distij = orc::descriptor_distance(desc + (size_t)(beg + i) * 32, desc + (size_t)(beg + j) * 32);
+        Distances[i][j] = distij;
+        Distances[j][i] = distij;
+      }
+    }
+    int BestMedian = INT_MAX, BestIdx = 0;
+    for (int i = 0; i < N; ++i) {
+      std::vector<int> vDists(Distances[i].begin(), Distances[i].end());
+      std::sort(vDists.begin(), vDists.end());
+      const int median = vDists[(size_t)(0.5 * (N - 1))];
+      if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+    }
+    best_idx[p] = BestIdx;
+    if (best_desc) std::memcpy(best_desc + (size_t)p * 32, desc + (size_t)(beg + BestIdx) * 32, 32);
+  }
+}
+
 float orc_log_f32(float x) { return orb_log_f32(x); }
 int orc_predict_scale(float max_distance, float dist, float log_scale_factor, int nlevels) {
   return orb_predict_scale(max_distance, dist, log_scale_factor, nlevels);

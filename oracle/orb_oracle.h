@@ -96,6 +96,8 @@ int orc_search_local_points(const orbfe_frame_view* F, const orbfe_projection* p
                             const int32_t* obs, float viewingCosLimit, float th, float nnratio, int32_t* assigned,
                             uint8_t* in_view, float* proj_x, float* proj_y, float* proj_xr, int32_t* level,
                             float* view_cos);
+void orc_compute_distinctive_descriptors(const uint8_t* desc, const int32_t* offsets, int n_points, int32_t* best_idx,
+                                         uint8_t* best_desc);
 /* shared arithmetic probes (include/orb_math_shared.h) for the known-answer tests */
 float orc_log_f32(float x);
 int orc_predict_scale(float max_distance, float dist, float log_scale_factor, int nlevels);

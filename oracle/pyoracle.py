@@ -154,6 +154,8 @@ def lib():
                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_search_local_points.argtypes = [C.POINTER(FrameView), C.POINTER(Projection), C.POINTER(Points3DView),
                                               C.c_void_p, C.c_float, C.c_float, C.c_float] + [C.c_void_p] * 7
+        L.orc_compute_distinctive_descriptors.restype = None
+        L.orc_compute_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_hamming_bruteforce.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_void_p,
                                              C.c_void_p]
         _lib = L
@@ -475,6 +477,16 @@ def search_local_points(frame, proj, pts, obs, cos_limit, th, nnratio):
                                       nnratio, _p(assigned), _p(out["in_view"]), _p(out["proj_x"]), _p(out["proj_y"]),
                                       _p(out["proj_xr"]), _p(out["level"]), _p(out["view_cos"]))
     return assigned[:frame.struct.n], n, {k: v[:m] for k, v in out.items()}
+
+
+def compute_distinctive_descriptors(desc, offsets):
+    desc = _u8(desc).reshape(-1, 32)
+    offsets = np.ascontiguousarray(offsets, np.int32)
+    n = len(offsets) - 1
+    best = np.empty(max(n, 1), np.int32)
+    bd = np.zeros((max(n, 1), 32), np.uint8)
+    lib().orc_compute_distinctive_descriptors(_p(desc), _p(offsets), n, _p(best), _p(bd))
+    return best[:n], bd[:n]
 
 
 def log_f32(x):

@@ -142,3 +142,15 @@ def test_search_local_points(fe, oracle, feats, seed, th, n_extra):
         assert np.array_equal(gf[k].view(np.uint32) if gf[k].dtype == np.float32 else gf[k],
                               wf[k].view(np.uint32) if wf[k].dtype == np.float32 else wf[k]), k
     assert 0.3 < wf["in_view"].mean() < 0.98
+
+
+@pytest.mark.parametrize("n_points,seed", [(1, 0), (5000, 1), (300, 2)])
+def test_compute_distinctive_descriptors(oracle, n_points, seed):
+    """MapPoint::ComputeDistinctiveDescriptors batched over map points (SURVEY.md 8(f)-4)."""
+    from my_orb_slam2_b200 import orbfe
+    desc, offsets = synth.observations_case(n_points, seed, long_lists=min(3, n_points))
+    wb, wd = oracle.compute_distinctive_descriptors(desc, offsets)
+    gb, gd = orbfe.Matcher().compute_distinctive_descriptors(desc, offsets)
+    assert np.array_equal(gb, wb) and np.array_equal(gd, wd)
+    if n_points > 100:
+        assert (wb == -1).sum() > 0 and (wb > 0).sum() > n_points // 4
