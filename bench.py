@@ -231,6 +231,76 @@ def matcher_extras(torch, dist, orbfe, rank, world, local, kp_frame, desc_frame,
             ts.append(time.perf_counter() - t0)
         out["search_by_projection_last"] = {"workload": "configs[3]: last-frame overload, th=7, rotation histogram on",
                                             "ms_p50": 1e3 * float(np.median(ts[3:])), "matches": int(n)}
+        # each entry point through the C ABI with host views (p50 of 10), the CPU oracle beside it
+        from oracle import pyoracle as orc
+
+        def p50(fn, reps=13, skip=3):
+            ts = []
+            for _ in range(reps):
+                t0 = time.perf_counter()
+                r = fn()
+                ts.append(time.perf_counter() - t0)
+            return 1e3 * float(np.median(ts[skip:])), r
+
+        def both(name, workload, gpu_fn, cpu_fn, count):
+            g_ms, g = p50(gpu_fn)
+            c_ms, c = p50(cpu_fn, reps=3, skip=0)
+            out[name] = {"workload": workload, "ms_p50": g_ms, "cpu_oracle_ms": c_ms, "matches": int(count(g)),
+                         "equal_to_oracle": bool(count(g) == count(c))}
+
+        def ov(kind, d):
+            if kind == "frame":
+                return orc.make_frame_view(d["keys_un"], d["u_right"], d["desc"], d["mp_obs"], d["bounds"], d["scale_factors"])
+            if kind == "kf":
+                return orc.make_keyframe_view(d["keys_un"], d["u_right"], d["desc"], d["has_mp"], d["node_ids"],
+                                              d["node_offsets"], d["node_features"], d["scale_factors"], d["level_sigma2"])
+            return orc.make_points3d_view(d["valid"], d["world_pos"], d["normal"], d["max_distance"], d["min_distance"],
+                                          d["desc"], d["angle"])
+
+        def gv(kind, d):
+            if kind == "frame":
+                return frontend.frame_view(d["keys_un"], d["u_right"], d["desc"], d["mp_obs"], d["bounds"], d["scale_factors"])
+            if kind == "kf":
+                return frontend.keyframe_view(d["keys_un"], d["u_right"], d["desc"], d["has_mp"], d["node_ids"],
+                                              d["node_offsets"], d["node_features"], d["scale_factors"], d["level_sigma2"])
+            return frontend.points3d_view(d["valid"], d["world_pos"], d["normal"], d["max_distance"], d["min_distance"],
+                                          d["desc"], d["angle"])
+
+        def proj(mod, pr, ow=None):
+            f = orc.make_projection if mod is orc else frontend.projection
+            return f(pr["tcw"], pr["fx"], pr["fy"], pr["cx"], pr["cy"], pr["bf"], pr["log_scale_factor"], pr["is_sim3"],
+                     ow if ow is not None else pr["ow"])
+
+        k1, k2 = synth.bow_case(kp_frame, desc_frame, seed=0)
+        g1, g2, o1, o2 = gv("kf", k1), gv("kf", k2), ov("kf", k1), ov("kf", k2)
+        both("search_by_bow", "SearchByBoW(KeyFrame, Frame): %d features, 100 nodes, nnratio 0.7" % len(kp_frame),
+             lambda: m.search_by_bow(g1, g2, 0, 0.7, True), lambda: orc.search_by_bow(o1, o2, 0, 0.7, True), lambda r: r[1])
+        pts, pr = synth.points3d_case(frame, seed=0, n_extra=18000)
+        obs = np.random.default_rng(0).integers(0, 9, len(pts["valid"])).astype(np.int32)
+        gp, op, gf, of = gv("pts", pts), ov("pts", pts), gv("frame", frame), ov("frame", frame)
+        both("search_local_points", "Tracking::SearchLocalPoints: isInFrustum over %d map points fused with "
+             "SearchByProjection, th=1" % len(obs),
+             lambda: m.search_local_points(gf, proj(frontend, pr), gp, obs, 0.5, 1.0, 0.8),
+             lambda: orc.search_local_points(of, proj(orc, pr), op, obs, 0.5, 1.0, 0.8), lambda r: r[1])
+        both("search_by_projection_reloc", "relocalisation overload, th=10, ORBdist=100, rotation histogram on",
+             lambda: m.search_by_projection_reloc(gf, proj(frontend, pr), gp, 10.0, 100, True),
+             lambda: orc.search_by_projection_reloc(of, proj(orc, pr), op, 10.0, 100, True), lambda r: r[1])
+        ow = (-pr["tcw"][:, :3].T @ pr["tcw"][:, 3]).astype(np.float32)
+        sig = (np.float32(1.0) / (frame["scale_factors"] * frame["scale_factors"])).astype(np.float32)
+        both("fuse", "Fuse(KeyFrame, %d map points, th=3): the search" % len(obs),
+             lambda: m.fuse(gf, proj(frontend, pr, ow), gp, 3.0, sig), lambda: orc.fuse(of, proj(orc, pr, ow), op, 3.0, sig),
+             lambda r: r[1])
+        voc = synth.vocabulary_case(10, 5, seed=0)
+        gvoc = orbfe.Vocabulary.from_arrays(10, 5, 0, 0, voc["parent"], voc["is_leaf"], voc["desc"], voc["weight"], device=local)
+        ovoc = orc.Vocabulary.from_arrays(10, 5, 0, 0, voc["parent"], voc["is_leaf"], voc["desc"], voc["weight"])
+        both("bow_transform", "DBoW2 transform: %d descriptors through a k=10, L=5 tree (%d nodes), levelsup 3" %
+             (len(desc_frame), len(voc["parent"])), lambda: gvoc.transform(desc_frame, 3), lambda: ovoc.transform(desc_frame, 3),
+             lambda r: len(r[0]))
+        gvoc.close()
+        dd, doff = synth.observations_case(5000, seed=0)
+        both("compute_distinctive_descriptors", "5000 map points, %d observations" % len(dd),
+             lambda: m.compute_distinctive_descriptors(dd, doff), lambda: orc.compute_distinctive_descriptors(dd, doff),
+             lambda r: int((r[0] >= 0).sum()))
     m.close()
     return out
 

@@ -122,6 +122,23 @@ int orbfe_extractor_debug_candidates(orbfe_extractor* e, int image_index, int le
 int orbfe_extractor_debug_level_keypoints(orbfe_extractor* e, int image_index, int level, int cap, int32_t* xs,
                                           int32_t* ys, int32_t* scores, int32_t* n_out);
 
+/* ---- input side of the pipeline on the device ---- */
+/* cv::cvtColor(im, im, CV_{RGB,BGR}2GRAY / CV_{RGBA,BGRA}2GRAY) as Tracking::GrabImage* does before the Frame is
+ * built (src/Tracking.cc:189-214, :231-244, :259-272), fused into the upload: pixels = batch interleaved 8-bit
+ * images of the handle's size with `channels` (3 or 4) bytes per pixel, rgb != 0 when the first byte is red (mbRGB).
+ * Replaces orbfe_extract_upload; follow with orbfe_extract_run. */
+int orbfe_extract_upload_color(orbfe_extractor* e, const uint8_t* pixels, size_t image_stride, int row_stride,
+                               int channels, int rgb, int batch);
+/* cv::remap(im, imRect, M1, M2, cv::INTER_LINEAR) of the EuRoC stereo example (Examples/Stereo/stereo_euroc.cc:97-98,
+ * :136-137): install the two CV_32F maps of cv::initUndistortRectifyMap once (width x height floats each, the
+ * handle's size; they index a src_width x src_height camera image) ... */
+int orbfe_extractor_set_rectify_maps(orbfe_extractor* e, const float* map_x, const float* map_y, int src_width,
+                                     int src_height);
+/* ... then upload raw (distorted) 8-bit gray frames; rectification runs on the device straight into level 0
+ * (constant border 0, OpenCV's 1/32-pixel fixed-point bilinear).  Replaces orbfe_extract_upload. */
+int orbfe_extract_upload_distorted(orbfe_extractor* e, const uint8_t* pixels, size_t image_stride, int row_stride,
+                                   int batch);
+
 /* ------------------------------------------------------------------ */
 /* Frame::ComputeStereoMatches  (src/Frame.cc:496-686)                 */
 /* ------------------------------------------------------------------ */

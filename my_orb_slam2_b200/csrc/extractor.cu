@@ -316,6 +316,9 @@ void orbfe_extractor_destroy(orbfe_extractor* h) {
   // a borrowed stream (orbfe_extractor_share_stream) may already be gone: wait for the whole device instead
   if (e->owns_stream) cudaStreamSynchronize(e->stream); else cudaDeviceSynchronize();
   free_arenas(e);
+  if (e->d_raw) cudaFree(e->d_raw);
+  if (e->d_map_x) cudaFree(e->d_map_x);
+  if (e->d_map_y) cudaFree(e->d_map_y);
   if (e->run_graph) cudaGraphExecDestroy(e->run_graph);
   if (e->stereo_graph) cudaGraphExecDestroy(e->stereo_graph);
   if (e->done) cudaEventDestroy(e->done);
@@ -382,6 +385,78 @@ int orbfe_extract_upload(orbfe_extractor* h, const uint8_t* images, size_t image
       ORBFE_CUDA(cudaMemcpy2DAsync(dst + (size_t)b * L0.lvl_bytes, L0.pitch, images + (size_t)b * image_stride,
                                    row_stride, e->width, e->height, kind, e->stream));
   }
+  return ORBFE_OK;
+}
+
+static int ensure_raw(Extractor* e, size_t bytes) {
+  if (bytes <= e->raw_cap) return ORBFE_OK;
+  if (e->d_raw) cudaFree(e->d_raw);
+  e->d_raw = nullptr; e->raw_cap = 0;
+  ORBFE_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->d_raw), bytes));
+  e->raw_cap = bytes;
+  return ORBFE_OK;
+}
+
+int orbfe_extract_upload_color(orbfe_extractor* h, const uint8_t* pixels, size_t image_stride, int row_stride,
+                               int channels, int rgb, int batch) {
+  ORBFE_ARG(h && pixels);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  ORBFE_ARG(channels == 3 || channels == 4);
+  ORBFE_ARG(batch >= 1 && batch <= e->max_batch && row_stride >= e->width * channels);
+  if (batch == 1) image_stride = (size_t)row_stride * e->height;
+  ORBFE_ARG(image_stride >= (size_t)row_stride * e->height);
+  DeviceGuard guard(e->device);
+  const size_t bytes = image_stride * (size_t)(batch - 1) + (size_t)row_stride * e->height;
+  int rc = ensure_raw(e, bytes);
+  if (rc != ORBFE_OK) return rc;
+  ORBFE_CUDA(cudaMemcpyAsync(e->d_raw, pixels, bytes, cudaMemcpyHostToDevice, e->stream));
+  const LevelGeom& L0 = e->geom.lv[0];
+  launch_gray(e->d_raw, image_stride, row_stride, channels, rgb, e->arena.pyr + L0.lvl_base, L0.pitch, L0.lvl_bytes,
+              e->width, e->height, batch, e->stream);
+  e->launches += 1;
+  ORBFE_CUDA(cudaGetLastError());
+  return ORBFE_OK;
+}
+
+int orbfe_extractor_set_rectify_maps(orbfe_extractor* h, const float* map_x, const float* map_y, int src_width,
+                                     int src_height) {
+  ORBFE_ARG(h && map_x && map_y && src_width >= 1 && src_height >= 1 && src_width <= 32767 && src_height <= 32767);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  DeviceGuard guard(e->device);
+  const size_t n = (size_t)e->width * e->height;
+  if (!e->d_map_x) {
+    ORBFE_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->d_map_x), n * sizeof(float)));
+    ORBFE_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->d_map_y), n * sizeof(float)));
+  }
+  ORBFE_CUDA(cudaMemcpyAsync(e->d_map_x, map_x, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+  ORBFE_CUDA(cudaMemcpyAsync(e->d_map_y, map_y, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+  ORBFE_CUDA(cudaStreamSynchronize(e->stream));
+  e->src_w = src_width;
+  e->src_h = src_height;
+  return ORBFE_OK;
+}
+
+int orbfe_extract_upload_distorted(orbfe_extractor* h, const uint8_t* pixels, size_t image_stride, int row_stride,
+                                   int batch) {
+  ORBFE_ARG(h && pixels);
+  Extractor* e = reinterpret_cast<Extractor*>(h);
+  if (!e->d_map_x) {
+    set_error("orbfe_extract_upload_distorted: no rectification maps (call orbfe_extractor_set_rectify_maps first)");
+    return ORBFE_ERR_ARG;
+  }
+  ORBFE_ARG(batch >= 1 && batch <= e->max_batch && row_stride >= e->src_w);
+  if (batch == 1) image_stride = (size_t)row_stride * e->src_h;
+  ORBFE_ARG(image_stride >= (size_t)row_stride * e->src_h);
+  DeviceGuard guard(e->device);
+  const size_t bytes = image_stride * (size_t)(batch - 1) + (size_t)row_stride * e->src_h;
+  int rc = ensure_raw(e, bytes);
+  if (rc != ORBFE_OK) return rc;
+  ORBFE_CUDA(cudaMemcpyAsync(e->d_raw, pixels, bytes, cudaMemcpyHostToDevice, e->stream));
+  const LevelGeom& L0 = e->geom.lv[0];
+  launch_remap(e->d_raw, image_stride, row_stride, e->src_w, e->src_h, e->d_map_x, e->d_map_y,
+               e->arena.pyr + L0.lvl_base, L0.pitch, L0.lvl_bytes, e->width, e->height, batch, e->stream);
+  e->launches += 1;
+  ORBFE_CUDA(cudaGetLastError());
   return ORBFE_OK;
 }
 

@@ -34,6 +34,12 @@ struct Extractor {
   // host side of an orbfe_extract_download_async not yet finished (counts are checked by orbfe_extract_finish)
   const int32_t* pending_counts = nullptr;
   int pending_batch = 0, pending_capacity = 0;
+  // input side (k_input.cu): raw-frame staging and the rectification maps of orbfe_extractor_set_rectify_maps
+  uint8_t* d_raw = nullptr;
+  size_t raw_cap = 0;
+  float* d_map_x = nullptr;
+  float* d_map_y = nullptr;
+  int src_w = 0, src_h = 0;
   // optional per-stage CUDA-event timing (bench.py roofline): ring of runs x (kStages+1) events
   static constexpr int kStages = 7;   // pyramid, fast, quadtree, blur, describe, stereo match, stereo median
   static constexpr int kProfRuns = 256;

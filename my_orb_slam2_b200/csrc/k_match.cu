@@ -236,19 +236,39 @@ __global__ void __launch_bounds__(256) distinctive_kernel(const uint8_t* __restr
       }
       if (lo < best_median) { best_median = lo; best_i = i; }
     }
-  } else {  // long observation lists: distances are recomputed inside the bisection
+  } else {  // long observation lists: a 257-bin histogram of the row in shared memory, k-th element by a warp scan
+    __shared__ int s_hist[8][288];
+    int* hist = s_hist[threadIdx.x >> 5];
     for (int i = 0; i < N; ++i) {
-      const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
-      int lo = 0, hi = 256;
-      while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        int c = 0;
-        for (int j = lane; j < N; j += 32) c += hamming_regs(a0, a1, __ldg(D + 2 * j), __ldg(D + 2 * j + 1)) <= mid;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-        if (c >= k + 1) hi = mid; else lo = mid + 1;
+      for (int b = 0; b < 9; ++b) hist[lane * 9 + b] = 0;
+      __syncwarp();
+      const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
+      for (int j = lane; j < N; j += 32) atomicAdd(&hist[hamming_regs(a0, a1, __ldg(D + 2 * j), __ldg(D + 2 * j + 1))], 1);
+      __syncwarp();
+      int mine = 0;
+#pragma unroll
+      for (int b = 0; b < 9; ++b) mine += hist[lane * 9 + b];
+      int incl = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
       }
-      if (lo < best_median) { best_median = lo; best_i = i; }
+      const int excl = incl - mine;
+      int median = -1;
+      if (excl <= k && k < incl) {  // exactly one lane owns the k-th smallest
+        int run = excl;
+#pragma unroll
+        for (int b = 0; b < 9; ++b) {
+          run += hist[lane * 9 + b];
+          if (median < 0 && k < run) median = lane * 9 + b;
+        }
+      }
+      const unsigned owner = __ballot_sync(0xffffffffu, median >= 0);
+      median = __shfl_sync(0xffffffffu, median, __ffs(owner) - 1);
+      if (median < best_median) { best_median = median; best_i = i; }
+      __syncwarp();
     }
   }
   if (lane == 0) best_idx[p] = best_i;

@@ -59,4 +59,10 @@ constexpr int kLaunchesPerExtract(int nlevels) { return (nlevels - 1) + 3; }
 constexpr int kLaunchesPerStereo = 3;
 int stereo_items_per_kp(const PyrGeom& g);
 
+// ---- k_input.cu: cvtColor *2GRAY and remap INTER_LINEAR straight into level 0 ----
+void launch_gray(const uint8_t* src, size_t image_stride, int row_stride, int channels, int rgb, uint8_t* dst, int pitch,
+                 size_t dst_image, int w, int h, int batch, cudaStream_t s);
+void launch_remap(const uint8_t* src, size_t image_stride, int row_stride, int sw, int sh, const float* mapx,
+                  const float* mapy, uint8_t* dst, int pitch, size_t dst_image, int w, int h, int batch, cudaStream_t s);
+
 }  // namespace orbfe

@@ -99,6 +99,9 @@ SYMBOLS = {
     "orbfe_extract_batch": (_I, [_P, _P, C.c_size_t, _I, _I, _P, _P, _I, _P]),
     "orbfe_extract_upload": (_I, [_P, _P, C.c_size_t, _I, _I, _I]),
     "orbfe_extract_run": (_I, [_P, _I]),
+    "orbfe_extract_upload_color": (_I, [_P, _P, C.c_size_t, _I, _I, _I, _I]),
+    "orbfe_extractor_set_rectify_maps": (_I, [_P, _P, _P, _I, _I]),
+    "orbfe_extract_upload_distorted": (_I, [_P, _P, C.c_size_t, _I, _I]),
     "orbfe_extract_download": (_I, [_P, _I, _P, _P, _I, _P]),
     "orbfe_extractor_sync": (_I, [_P]),
     "orbfe_extract_download_async": (_I, [_P, _I, _P, _P, _I, _P]),
@@ -235,6 +238,29 @@ class Extractor:
     def upload(self, images_ptr, batch, image_stride=None, row_stride=None, on_device=False):
         check(lib().orbfe_extract_upload(self._h, images_ptr, image_stride or self.width * self.height,
                                          row_stride or self.width, batch, int(on_device)))
+
+    def upload_color(self, images, rgb=True):
+        """cvtColor(*2GRAY) fused into the upload: images = [batch, H, W, 3|4] uint8 (Tracking::GrabImage*)."""
+        images = _u8(images)
+        b, h, w, ch = images.shape
+        if (w, h) != (self.width, self.height):
+            raise ValueError("image size %dx%d != handle size %dx%d" % (w, h, self.width, self.height))
+        check(lib().orbfe_extract_upload_color(self._h, _p(images), h * w * ch, w * ch, ch, int(rgb), b))
+        self.sync()  # the host array may go away
+
+    def set_rectify_maps(self, map_x, map_y, src_width, src_height):
+        map_x = np.ascontiguousarray(map_x, np.float32)
+        map_y = np.ascontiguousarray(map_y, np.float32)
+        if map_x.shape != (self.height, self.width) or map_y.shape != map_x.shape:
+            raise ValueError("maps must be %d x %d" % (self.height, self.width))
+        check(lib().orbfe_extractor_set_rectify_maps(self._h, _p(map_x), _p(map_y), src_width, src_height))
+
+    def upload_distorted(self, images):
+        """cv::remap(INTER_LINEAR) fused into the upload: images = [batch, srcH, srcW] uint8 raw camera frames."""
+        images = _u8(images)
+        b, h, w = images.shape
+        check(lib().orbfe_extract_upload_distorted(self._h, _p(images), h * w, w, b))
+        self.sync()
 
     def run(self, batch):
         check(lib().orbfe_extract_run(self._h, batch))

@@ -20,6 +20,9 @@ struct FastPoint {
 
 void resize_linear_u8(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride);
 void gaussian_blur7_u8(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride);
+void cvt_gray_u8(const uint8_t* src, int w, int h, int sstride, int channels, bool rgb, uint8_t* dst, int dstride);
+void remap_linear_u8(const uint8_t* src, int sw, int sh, int sstride, const float* mapx, const float* mapy, int dw, int dh,
+                     uint8_t* dst, int dstride);
 int fast_corner_strength(const uint8_t* p, int stride);
 int fast9_16(const uint8_t* roi, int cols, int rows, int stride, int threshold, bool nms, std::vector<FastPoint>& out);
 

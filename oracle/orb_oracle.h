@@ -37,6 +37,10 @@ int orc_fast9_16(const uint8_t* roi, int cols, int rows, int stride, int thresho
 float orc_fast_atan2(float y, float x);
 void orc_sincos_deg(float angle_deg, int use_libm, float* c, float* s);
 int orc_descriptor_distance(const uint8_t* a, const uint8_t* b);
+/* input side: cv::cvtColor *2GRAY and cv::remap INTER_LINEAR with CV_32F maps */
+void orc_cvt_gray_u8(const uint8_t* src, int w, int h, int sstride, int channels, int rgb, uint8_t* dst, int dstride);
+void orc_remap_linear_u8(const uint8_t* src, int sw, int sh, int sstride, const float* mapx, const float* mapy, int dw,
+                         int dh, uint8_t* dst, int dstride);
 float orc_ic_angle(const uint8_t* img, int stride, int x, int y);
 void orc_orb_descriptor(const uint8_t* blurred, int stride, int x, int y, float angle_deg, int use_libm, uint8_t* desc32);
 

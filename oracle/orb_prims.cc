@@ -200,6 +200,45 @@ int fast9_16(const uint8_t* roi, int cols, int rows, int stride, int threshold, 
   return (int)out.size();
 }
 
+
+// ---- input side of the pipeline ----
+// cv::cvtColor(src, dst, CV_{RGB,BGR,RGBA,BGRA}2GRAY) on 8-bit pixels (src/Tracking.cc:189-214): OpenCV 4.x fixed
+// point, 15 fractional bits: (R*9798 + G*19235 + B*3735 + 2^14) >> 15 (verified against cv2 4.13 on all (R,G) and
+// every third B).
+void cvt_gray_u8(const uint8_t* src, int w, int h, int sstride, int channels, bool rgb, uint8_t* dst, int dstride) {
+  for (int y = 0; y < h; ++y) {
+    const uint8_t* s = src + (size_t)y * sstride;
+    uint8_t* d = dst + (size_t)y * dstride;
+    for (int x = 0; x < w; ++x, s += channels) {
+      const int r = rgb ? s[0] : s[2], g = s[1], b = rgb ? s[2] : s[0];
+      d[x] = (uint8_t)((r * 9798 + g * 19235 + b * 3735 + (1 << 14)) >> 15);
+    }
+  }
+}
+
+// cv::remap(src, dst, map1, map2, INTER_LINEAR) with CV_32FC1 maps, BORDER_CONSTANT 0, 8-bit single channel
+// (Examples/Stereo/stereo_euroc.cc:136-137): coordinates go to 1/32 pixel with cvRound(map * 32) (fp32 product, round
+// half to even), the four taps are weighted with the 15-bit integer table (32-ay)(32-ax)*32 ... and the sum is rounded
+// with + 2^14 >> 15; taps outside the source read 0.
+void remap_linear_u8(const uint8_t* src, int sw, int sh, int sstride, const float* mapx, const float* mapy, int dw, int dh,
+                     uint8_t* dst, int dstride) {
+  for (int y = 0; y < dh; ++y)
+    for (int x = 0; x < dw; ++x) {
+      const int sx = round_half_even(mapx[(size_t)y * dw + x] * 32.0f);
+      const int sy = round_half_even(mapy[(size_t)y * dw + x] * 32.0f);
+      int ix = sx >> 5, iy = sy >> 5;
+      ix = ix < -32768 ? -32768 : (ix > 32767 ? 32767 : ix);  // saturate_cast<short>
+      iy = iy < -32768 ? -32768 : (iy > 32767 ? 32767 : iy);
+      const int ax = sx & 31, ay = sy & 31;
+      auto px = [&](int yy, int xx) -> int {
+        return (xx >= 0 && xx < sw && yy >= 0 && yy < sh) ? src[(size_t)yy * sstride + xx] : 0;
+      };
+      const int v = px(iy, ix) * ((32 - ay) * (32 - ax) * 32) + px(iy, ix + 1) * ((32 - ay) * ax * 32) +
+                    px(iy + 1, ix) * (ay * (32 - ax) * 32) + px(iy + 1, ix + 1) * (ay * ax * 32);
+      dst[(size_t)y * dstride + x] = (uint8_t)((v + (1 << 14)) >> 15);
+    }
+}
+
 }  // namespace orc
 
 // ---------------------------------------------------------------------------
@@ -231,5 +270,14 @@ int orc_fast9_16(const uint8_t* roi, int cols, int rows, int stride, int thresho
 float orc_fast_atan2(float y, float x) { return orb_fast_atan2_deg(y, x); }
 
 int orc_descriptor_distance(const uint8_t* a, const uint8_t* b) { return orc::descriptor_distance(a, b); }
+
+void orc_cvt_gray_u8(const uint8_t* src, int w, int h, int sstride, int channels, int rgb, uint8_t* dst, int dstride) {
+  orc::cvt_gray_u8(src, w, h, sstride, channels, rgb != 0, dst, dstride);
+}
+
+void orc_remap_linear_u8(const uint8_t* src, int sw, int sh, int sstride, const float* mapx, const float* mapy, int dw,
+                         int dh, uint8_t* dst, int dstride) {
+  orc::remap_linear_u8(src, sw, sh, sstride, mapx, mapy, dw, dh, dst, dstride);
+}
 
 }  // extern "C"

@@ -156,6 +156,11 @@ def lib():
                                               C.c_void_p, C.c_float, C.c_float, C.c_float] + [C.c_void_p] * 7
         L.orc_compute_distinctive_descriptors.restype = None
         L.orc_compute_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_cvt_gray_u8.restype = None
+        L.orc_cvt_gray_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_remap_linear_u8.restype = None
+        L.orc_remap_linear_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                          C.c_void_p, C.c_int]
         L.orc_hamming_bruteforce.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_void_p,
                                              C.c_void_p]
         _lib = L
@@ -487,6 +492,26 @@ def compute_distinctive_descriptors(desc, offsets):
     bd = np.zeros((max(n, 1), 32), np.uint8)
     lib().orc_compute_distinctive_descriptors(_p(desc), _p(offsets), n, _p(best), _p(bd))
     return best[:n], bd[:n]
+
+
+def cvt_gray(img, rgb=True):
+    """cv::cvtColor(img, CV_{RGB,BGR}[A]2GRAY) on an H x W x {3,4} uint8 image."""
+    img = _u8(img)
+    h, w, ch = img.shape
+    out = np.empty((h, w), np.uint8)
+    lib().orc_cvt_gray_u8(_p(img), w, h, w * ch, ch, int(rgb), _p(out), w)
+    return out
+
+
+def remap_linear(src, mapx, mapy):
+    """cv::remap(src, mapx, mapy, INTER_LINEAR) with CV_32F maps, constant border 0."""
+    src = _u8(src)
+    mapx = np.ascontiguousarray(mapx, np.float32)
+    mapy = np.ascontiguousarray(mapy, np.float32)
+    out = np.empty(mapx.shape, np.uint8)
+    lib().orc_remap_linear_u8(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(mapx), _p(mapy), mapx.shape[1],
+                              mapx.shape[0], _p(out), mapx.shape[1])
+    return out
 
 
 def log_f32(x):

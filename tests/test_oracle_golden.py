@@ -96,3 +96,15 @@ def test_hamming_bruteforce_ties_lowest_index(oracle):
     m[2, 0] = 1
     best, second = oracle.hamming_bruteforce(q, m, index_base=100)
     assert int(best[0]) == (0 << 32) | 103 and int(second[0]) == (0 << 32) | 104
+
+
+def test_input_side_matches_cv2_fixture(oracle, golden_dir):
+    """cvtColor *2GRAY and remap INTER_LINEAR against cv2 4.13 outputs (tests/golden/gen_golden_input.py)."""
+    import os
+    g = np.load(os.path.join(golden_dir, "input_side.npz"))
+    for name, rgb in (("rgb", True), ("bgr", False), ("rgba", True), ("bgra", False)):
+        assert np.array_equal(oracle.cvt_gray(g["color_" + name], rgb), g["gray_" + name]), name
+    for i in range(2):
+        got = oracle.remap_linear(g["remap_src_%d" % i], g["remap_mx_%d" % i], g["remap_my_%d" % i])
+        assert np.array_equal(got, g["remap_dst_%d" % i]), i
+    assert (g["remap_dst_1"][:10] == 0).mean() > 0.1  # the constant border was exercised
