@@ -95,25 +95,32 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
   // win[r % 7] holds the horizontal sums of loaded row r: with the row loop fully unrolled the window is renamed, not
   // moved (a rolled loop spends a quarter of its instructions on register moves); the words of row r + BL_PF are
   // requested before row r is processed so that several rows of loads are in flight per thread
-  unsigned win[7][4];
-  unsigned pf[BL_PF][3];
   const int xl = left ? x4 : x4 - 4;  // at the left edge w0 is rebuilt from w1 (reflection of columns -1..-3)
-  auto load_row = [&](int r, unsigned (&q)[3]) {
-    const int y = reflect101i(y0 + r - 3, h);
-    const uint8_t* row = src + (size_t)y * pitch;
-    q[0] = __ldg(reinterpret_cast<const unsigned*>(row + xl));
-    q[1] = __ldg(reinterpret_cast<const unsigned*>(row + x4));
-    q[2] = __ldg(reinterpret_cast<const unsigned*>(row + x4 + 4));
-  };
+  if (y0 >= 3 && y0 + BL_ROWS + 3 <= h) {
+    // strip with all its 6 halo rows inside the level (warp-uniform): no row reflection, no row-count tests, the
+    // source and destination rows are reached by bumping two pointers
+    unsigned win[7][4];
+    unsigned pf[BL_PF][3];
+    const uint8_t* rp = src + (size_t)(y0 - 3) * pitch + x4;
+    uint8_t* wp = dst + (size_t)y0 * pitch + x4;
+    const int dl = xl - x4;  // 0 or -4
 #pragma unroll
-  for (int r = 0; r < BL_PF; ++r) load_row(min(r, rows + 5), pf[r]);
+    for (int r = 0; r < BL_PF; ++r) {
+      pf[r][0] = __ldg(reinterpret_cast<const unsigned*>(rp + dl));
+      pf[r][1] = __ldg(reinterpret_cast<const unsigned*>(rp));
+      pf[r][2] = __ldg(reinterpret_cast<const unsigned*>(rp + 4));
+      rp += pitch;
+    }
 #pragma unroll
-  for (int r = 0; r < BL_ROWS + 6; ++r) {
-    if (r < rows + 6) {
+    for (int r = 0; r < BL_ROWS + 6; ++r) {
       const unsigned w1 = pf[r % BL_PF][1], w2 = pf[r % BL_PF][2];
       const unsigned w0 = left ? __byte_perm(w1, 0, 0x1230) : pf[r % BL_PF][0];
-      load_row(min(r + BL_PF, rows + 5), pf[r % BL_PF]);
-      // horizontal sums of the 4 pixels: taps are bytes j+1 .. j+7 of (w0,w1,w2)
+      if (r + BL_PF < BL_ROWS + 6) {
+        pf[r % BL_PF][0] = __ldg(reinterpret_cast<const unsigned*>(rp + dl));
+        pf[r % BL_PF][1] = __ldg(reinterpret_cast<const unsigned*>(rp));
+        pf[r % BL_PF][2] = __ldg(reinterpret_cast<const unsigned*>(rp + 4));
+        rp += pitch;
+      }
       unsigned* hs = win[r % 7];
       hs[0] = __dp4a(__funnelshift_r(w0, w1, 8), K_LO, __dp4a(__funnelshift_r(w1, w2, 8), K_HI, 0u));
       hs[1] = __dp4a(__funnelshift_r(w0, w1, 16), K_LO, __dp4a(__funnelshift_r(w1, w2, 16), K_HI, 0u));
@@ -127,8 +134,56 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
                              48u * (win[(r + 3) % 7][j] + win[(r + 5) % 7][j]) + 56u * win[(r + 4) % 7][j];
           out |= ((v + 32768u) >> 16) << (8 * j);
         }
+        *reinterpret_cast<unsigned*>(wp) = out;
+        wp += pitch;
+      }
+    }
+    return;
+  }
+  // strips touching the top or bottom of the level: row reflection and a row count, window moved instead of renamed
+  // (rolled loop: these are the minority of strips and a second unrolled body would double the kernel's code size)
+  {
+    unsigned win[7][4];
+#pragma unroll
+    for (int i = 0; i < 7; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) win[i][j] = 0;
+    unsigned q[3], nq[3];
+    auto load_row = [&](int r, unsigned (&o)[3]) {
+      const int y = reflect101i(y0 + r - 3, h);
+      const uint8_t* row = src + (size_t)y * pitch;
+      o[0] = __ldg(reinterpret_cast<const unsigned*>(row + xl));
+      o[1] = __ldg(reinterpret_cast<const unsigned*>(row + x4));
+      o[2] = __ldg(reinterpret_cast<const unsigned*>(row + x4 + 4));
+    };
+    load_row(0, q);
+#pragma unroll 2
+    for (int r = 0; r < rows + 6; ++r) {
+      load_row(min(r + 1, rows + 5), nq);
+      const unsigned w1 = q[1], w2 = q[2];
+      const unsigned w0 = left ? __byte_perm(w1, 0, 0x1230) : q[0];
+      unsigned hs[4];
+      hs[0] = __dp4a(__funnelshift_r(w0, w1, 8), K_LO, __dp4a(__funnelshift_r(w1, w2, 8), K_HI, 0u));
+      hs[1] = __dp4a(__funnelshift_r(w0, w1, 16), K_LO, __dp4a(__funnelshift_r(w1, w2, 16), K_HI, 0u));
+      hs[2] = __dp4a(__funnelshift_r(w0, w1, 24), K_LO, __dp4a(__funnelshift_r(w1, w2, 24), K_HI, 0u));
+      hs[3] = __dp4a(w1, K_LO, __dp4a(w2, K_HI, 0u));
+#pragma unroll
+      for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) win[i][j] = win[i + 1][j];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) win[6][j] = hs[j];
+      if (r >= 6) {
+        unsigned out = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const unsigned v = 18u * (win[0][j] + win[6][j]) + 34u * (win[1][j] + win[5][j]) +
+                             48u * (win[2][j] + win[4][j]) + 56u * win[3][j];
+          out |= ((v + 32768u) >> 16) << (8 * j);
+        }
         *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * pitch + x4) = out;
       }
+      q[0] = nq[0]; q[1] = nq[1]; q[2] = nq[2];
     }
   }
 }
