@@ -1,0 +1,19 @@
+#!/bin/bash
+# Capture the ncu evidence of a round on the GPU box (run under gpurun, ONE GPU):   bash tools/capture_profiles.sh r1
+# 1. the bench must exit 0 without ncu first; 2. launch list of the same command (gpu__time_duration only);
+# 3. one `--set full` capture per hot kernel over one device-resident step of 64 KITTI stereo pairs.
+# Afterwards, here:  python tools/make_profiles.py r1   (summaries into profiles/, tracked).
+set -u
+TAG=${1:-r1}
+OUT=gpurun_out
+mkdir -p $OUT
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-matchers --latency-frames 2"
+$CMD > $OUT/plain_$TAG.log 2>&1 || { echo "bench failed without ncu"; tail -5 $OUT/plain_$TAG.log; exit 1; }
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_bench_launches.csv $CMD > $OUT/ncu_bench.log 2>&1
+python tools/one_step.py 64 1 > $OUT/plain_step_$TAG.log 2>&1 || { echo "one_step failed without ncu"; exit 1; }
+for K in pyramid_level fast_detect quadtree blur_levels describe stereo_match; do
+  ncu --set full --clock-control none --import-source on -k regex:${K} -c 1 -f -o $OUT/prof_${K}_${TAG}f \
+      python tools/one_step.py 64 1 > $OUT/ncu_${K}.log 2>&1
+  echo "$K rc=$?"
+done
+ls -la $OUT/*_${TAG}f.ncu-rep
