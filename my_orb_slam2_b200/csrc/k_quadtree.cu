@@ -95,7 +95,9 @@ __global__ void __launch_bounds__(QT_T) quadtree_kernel(const __grid_constant__ 
   __shared__ int s_misc[4];  // 0: first rank reaching N (phase 2), 1: children with count > 1, 2: filtered candidates
 
   const int tid = threadIdx.x;
-  const int lvl = blockIdx.x, b = blockIdx.y;
+  // level-major CTA order (x = image is the fast index): the long level-0 CTAs of ALL images start in the first wave
+  // and the short upper levels fill the slots they free; image-major order made two full-length waves
+  const int lvl = blockIdx.y, b = blockIdx.x;
   const LevelGeom& L = g.lv[lvl];
   const int C = g.max_node_cap;
   const int N = L.quota;
@@ -342,7 +344,7 @@ int configure_kernels(const PyrGeom& g) {
 }
 
 void launch_quadtree(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
-  dim3 grid(g.nlevels, batch);
+  dim3 grid(batch, g.nlevels);
   quadtree_kernel<<<grid, QT_T, quadtree_smem_bytes(g.max_node_cap), s>>>(g, a.cand, a.cell_hi, a.node_of, a.cand_count, a.kept,
                                                                           a.kept_count, a.flags);
 }
