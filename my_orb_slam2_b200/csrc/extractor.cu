@@ -89,6 +89,7 @@ static void build_resize_tables(int sw, int sh, int dw, int dh, std::vector<XTab
     int sy = (int)floorf(fy);
     fy -= sy;
     YTab t;
+    t.pad = 0;
     t.b0 = (short)cv_round((1.f - fy) * 2048.f);
     t.b1 = (short)cv_round(fy * 2048.f);
     t.sy0 = sy < 0 ? 0 : (sy > sh - 1 ? sh - 1 : sy);

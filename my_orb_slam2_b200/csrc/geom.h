@@ -53,7 +53,7 @@ struct PyrGeom {
 
 // resize tables (cv::resize INTER_LINEAR)
 struct XTab { int sx0, sx1; short a0, a1; };          // per destination column
-struct YTab { int sy0, sy1; short b0, b1; };          // per destination row
+struct __align__(16) YTab { int sy0, sy1; short b0, b1; int pad; };  // per destination row; one 16-byte load
 
 // candidate / kept keypoint record: x | y<<12 | score<<24, x,y relative to minBorder
 __host__ __device__ inline uint32_t pack_cand(int x, int y, int score) {

@@ -69,40 +69,42 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
   const int y0 = (blockIdx.y * PY_WARPS + wid) * PY_ROWS;
   const int b = blockIdx.z;
   if (x4 >= D.w || y0 >= D.h) return;
-  const uint8_t* src = pyr + S.lvl_base + (size_t)b * S.lvl_bytes;
-  uint8_t* dst = pyr + D.lvl_base + (size_t)b * D.lvl_bytes;
-  // per-pixel taps: bytes o, o+1 of the 12-byte window at ws (o <= 7, checked on the host: LevelGeom::resize_fast)
+  // per-pixel taps: bytes o, o+1 of the 12-byte window at ws (o <= 7, checked on the host: LevelGeom::resize_fast).
+  // Two byte permutes bring them into the low half-word: PRMT(w0, w1, selA) takes byte o and (o < 7) byte o+1 of the
+  // first two words, PRMT(t, w2, selB) replaces byte 1 by the first byte of the third word when o == 7.
   const XTab* xt = xtab + D.xtab_off;
   const int ws = __ldg(&xt[x4].sx0) & ~3;
-  unsigned a01[4];
-  int sh[4];
-  bool hiw[4];
+  unsigned a01[4], selA[4], selB[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     const int xi = min(x4 + k, D.w - 1);  // pixels past the row end are computed and dropped
     const int o = __ldg(&xt[xi].sx0) - ws;
     a01[k] = __ldg(reinterpret_cast<const unsigned*>(&xt[xi].a0));  // a0 | a1 << 16
-    hiw[k] = o >= 4;
-    sh[k] = (o & 3) * 8;
+    selA[k] = (unsigned)o | ((unsigned)min(o + 1, 7) << 4);
+    selB[k] = o == 7 ? 0x40u : 0x10u;
   }
+  const unsigned spitch = (unsigned)S.pitch, dpitch = (unsigned)D.pitch;
+  const uint8_t* sbase = pyr + S.lvl_base + (size_t)b * S.lvl_bytes + ws;
+  uint8_t* dp = pyr + D.lvl_base + (size_t)b * D.lvl_bytes + (size_t)y0 * dpitch + x4;
+  asm volatile("" : "+l"(sbase));  // keep the row base in a register pair: rebuilt per source row otherwise
   auto hrow = [&](int sy, unsigned (&h)[4]) {
-    const unsigned* p = reinterpret_cast<const unsigned*>(src + (size_t)sy * S.pitch + ws);
+    const unsigned* p = reinterpret_cast<const unsigned*>(sbase + (size_t)((unsigned)sy * spitch));
     const unsigned w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const unsigned taps = __funnelshift_r(hiw[k] ? w1 : w0, hiw[k] ? w2 : w1, sh[k]);  // bytes: S[sx0], S[sx0+1], ..
-      h[k] = __dp2a_lo(a01[k], taps, 0u) >> 4;                                           // (S0*a0 + S1*a1) >> 4
+      const unsigned taps = __byte_perm(__byte_perm(w0, w1, selA[k]), w2, selB[k]);  // bytes: S[sx0], S[sx0+1]
+      h[k] = __dp2a_lo(a01[k], taps, 0u) >> 4;                                       // (S0*a0 + S1*a1) >> 4
     }
   };
   int cur0 = -1, cur1 = -1;
   unsigned h0[4] = {0u, 0u, 0u, 0u}, h1[4] = {0u, 0u, 0u, 0u};
-  const YTab* yt = ytab + D.ytab_off;
+  const int4* yt = reinterpret_cast<const int4*>(ytab + D.ytab_off + y0);
+  const int rows = min(PY_ROWS, D.h - y0);
 #pragma unroll 1
-  for (int r = 0; r < PY_ROWS; ++r) {
-    const int y = y0 + r;
-    if (y >= D.h) break;
-    const int sy0 = __ldg(&yt[y].sy0), sy1 = __ldg(&yt[y].sy1);
-    const unsigned b01 = __ldg(reinterpret_cast<const unsigned*>(&yt[y].b0));
+  for (int r = 0; r < rows; ++r) {
+    const int4 t = __ldg(yt + r);  // sy0, sy1, b0 | b1 << 16, pad
+    const int sy0 = t.x, sy1 = t.y;
+    const unsigned b01 = (unsigned)t.z;
     // all conditions below are warp-uniform (they depend on y only)
     if (sy0 != cur0) {
       if (sy0 == cur1) {
@@ -129,8 +131,8 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
       const unsigned v = (__umulhi(b0s, h0[k]) + __umulhi(b1s, h1[k]) + 2u) >> 2;
       out |= v << (8 * k);
     }
-    uint8_t* d = dst + (size_t)y * D.pitch + x4;
-    *reinterpret_cast<unsigned*>(d) = out;  // pitch is a multiple of 128: the padding bytes may be written
+    *reinterpret_cast<unsigned*>(dp) = out;  // pitch is a multiple of 128: the padding bytes may be written
+    dp += dpitch;
   }
 }
 
