@@ -541,11 +541,22 @@ def run_gpu(args):
     b_extract = W * H + lp + kp_per_img * 60  # compulsory bytes of the whole extraction per image
     # DRAM traffic of the dominant kernel from the committed `ncu --set full` capture (profiles/, per launch of 64 images)
     traffic = None
+    issue = None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
         kname = {"fast": "fast_detect_kernel", "blur": "void blur_levels_kernel<32>", "describe": "describe_kernel",
                  "pyramid": "void pyramid_level_kernel<8>", "quadtree": "quadtree_kernel"}[dom]
         traffic = tj[kname]["dram_bytes_per_launch"] * B / tj[kname]["images"]
+        # the bound that applies (north_star: "fraction of the HBM or integer-pipe roofline"): warp instructions of
+        # the kernel (deterministic for these inputs; counted by ncu, committed in profiles/) / LIVE launch time,
+        # against one warp instruction per SM sub-partition per clock
+        winst = tj[kname].get("warp_inst_per_launch")
+        if winst and per_launch[dom] > 0:
+            a_i = winst * B / tj[kname]["images"] / (per_launch[dom] * 1e-3) / 1e12
+            p_i = 148 * 4 * float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0) * 1e6 / 1e12
+            issue = {"bound": "issue", "achieved": a_i, "peak": p_i, "unit": "T warp-inst/s", "frac": a_i / p_i,
+                     "peak_source": "148 SMs x 4 schedulers x SM clock under load (1 warp instruction / scheduler / clk)",
+                     "warp_inst_per_launch": winst * B / tj[kname]["images"]}
     except Exception:
         pass
     frames = B * args.steps * world
@@ -571,7 +582,7 @@ def run_gpu(args):
                               "the two handles serialised (the timed region overlaps their streams)" % args.steps,
                      "bound_note": "every extraction kernel is bound by integer instruction issue (ALU pipe), not HBM: "
                                    "see profiles/r1_kernels_full.md (issue slots busy, pipe utilisation)",
-                     "algorithmic_bytes_per_launch": alg[dom] * B,
+                     "algorithmic_bytes_per_launch": alg[dom] * B, "issue": issue,
                      "extract_frac": (b_extract * 2 * B * args.steps / (ms_dev * 1e-3) / 1e9) / peak_gbs},
         "stages_ms_per_launch": per_launch,
         "cpu_baseline": cpu,

@@ -184,6 +184,17 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
       }
       for (int y = 0; y < L.h; ++y)
         if (yt[L.ytab_off + y].b0 < 0 || yt[L.ytab_off + y].b1 < 0) L.resize_fast = 0;
+      // the staged variant copies, per 128x32 destination tile, 16-byte chunks [c0, c0 + 16*n) of source rows
+      // sy0(first) .. sy1(last): n <= 12 chunks inside the source pitch and <= 44 rows (k_pyramid.cu PT_CHUNKS, PT_ROWS)
+      L.resize_tile = L.resize_fast;
+      for (int xc = 0; xc < L.w && L.resize_tile; xc += 128) {
+        const int c0 = xt[L.xtab_off + xc].sx0 & ~15;
+        const int ws_last = xt[L.xtab_off + std::min(xc + 124, (L.w - 1) & ~3)].sx0 & ~3;
+        const int n = ((ws_last + 11 - c0) >> 4) + 1;
+        if (n > 12 || c0 + 16 * n > g.lv[l - 1].pitch) L.resize_tile = 0;
+      }
+      for (int yc = 0; yc < L.h && L.resize_tile; yc += 32)
+        if (yt[L.ytab_off + std::min(yc + 32, L.h) - 1].sy1 - yt[L.ytab_off + yc].sy0 + 1 > 44) L.resize_tile = 0;
     }
   }
   g.total_cells = cells;

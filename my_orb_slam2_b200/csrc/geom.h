@@ -30,6 +30,7 @@ struct LevelGeom {
   int kept_off, kept_cap;   // slice of the per-image kept-keypoint array
   int xtab_off, ytab_off;   // resize coefficient tables (level >= 1)
   int resize_fast;          // the 4 pixels of an aligned group take their taps within 9 bytes of an aligned address
+  int resize_tile;          // ... and the source window of a 128x32 destination tile fits k_pyramid.cu's shared-memory stage
   float scale;              // mvScaleFactor[level]
   float inv_scale;          // mvInvScaleFactor[level]
   float kp_size;            // (float)(int)(PATCH_SIZE*scale) (:857)

@@ -55,41 +55,80 @@ __global__ void __launch_bounds__(256) pyramid_level_generic_kernel(const __grid
 
 constexpr int PY_WARPS = 4;  // warps per CTA, stacked vertically: a CTA covers 128 x (4 * PY_ROWS) destination pixels
 // PY_ROWS = destination rows per thread: 8 in throughput mode (source rows are reused by the rows that share them), 2
-// when the launch would not fill the GPU (single frames: shorter dependent chains per thread, 4x more CTAs)
+// when the launch would not fill the GPU (single frames: shorter dependent chains per thread, 4x more CTAs).
+// TILE: the CTA first requests every source byte it needs with asynchronous 16-byte copies into shared memory, so
+// a thread waits for HBM once instead of once per source row (the row-by-row variant keeps one 154-byte row per
+// warp in flight: 0.9 TB/s); needs the source window of the CTA to fit (LevelGeom::resize_tile, checked on the host).
+constexpr int PT_CHUNKS = 12;             // 16-byte chunks per staged source row
+constexpr int PT_STRIDE = PT_CHUNKS * 16;
+constexpr int PT_ROWS = 44;               // staged source rows (32 destination rows)
 
-template <int PY_ROWS>
+template <int PY_ROWS, bool TILE>
 __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __grid_constant__ PyrGeom g,
                                                                       uint8_t* __restrict__ pyr,
                                                                       const XTab* __restrict__ xtab,
                                                                       const YTab* __restrict__ ytab, int lvl) {
+  static_assert(!TILE || PY_ROWS * PY_WARPS == 32, "PT_ROWS is sized for 32 destination rows");
+  __shared__ __align__(16) uint8_t s_src[TILE ? PT_ROWS * PT_STRIDE : 16];
   const LevelGeom& D = g.lv[lvl];
   const LevelGeom& S = g.lv[lvl - 1];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int x4 = (blockIdx.x * 32 + lane) * 4;
   const int y0 = (blockIdx.y * PY_WARPS + wid) * PY_ROWS;
   const int b = blockIdx.z;
-  if (x4 >= D.w || y0 >= D.h) return;
+  const XTab* xt = xtab + D.xtab_off;
+  const unsigned spitch = (unsigned)S.pitch, dpitch = (unsigned)D.pitch;
+  const uint8_t* src = pyr + S.lvl_base + (size_t)b * S.lvl_bytes;
+  int c0 = 0, s_first = 0;
+  if (TILE) {
+    const int xc = blockIdx.x * 128, yc = blockIdx.y * (PY_WARPS * PY_ROWS);
+    c0 = __ldg(&xt[xc].sx0) & ~15;
+    const int ws_last = __ldg(&xt[min(xc + 124, (D.w - 1) & ~3)].sx0) & ~3;
+    const int nchunks = ((ws_last + 11 - c0) >> 4) + 1;  // <= PT_CHUNKS
+    const YTab* ytc = ytab + D.ytab_off;
+    s_first = __ldg(&ytc[yc].sy0);
+    const int nrows = __ldg(&ytc[min(yc + PY_WARPS * PY_ROWS, D.h) - 1].sy1) - s_first + 1;  // <= PT_ROWS
+    const int c = threadIdx.x & 15;
+    if (c < nchunks) {
+      const uint8_t* gp = src + (size_t)s_first * spitch + c0 + c * 16;
+      const unsigned sp = (unsigned)__cvta_generic_to_shared(s_src) + c * 16;
+      for (int r = threadIdx.x >> 4; r < nrows; r += PY_WARPS * 2)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sp + r * PT_STRIDE), "l"(gp + (size_t)r * spitch)
+                     : "memory");
+    }
+  }
+  const bool active = x4 < D.w && y0 < D.h;
   // per-pixel taps: bytes o, o+1 of the 12-byte window at ws (o <= 7, checked on the host: LevelGeom::resize_fast).
   // Two byte permutes bring them into the low half-word: PRMT(w0, w1, selA) takes byte o and (o < 7) byte o+1 of the
   // first two words, PRMT(t, w2, selB) replaces byte 1 by the first byte of the third word when o == 7.
-  const XTab* xt = xtab + D.xtab_off;
-  const int ws = __ldg(&xt[x4].sx0) & ~3;
+  const int x4c = min(x4, (D.w - 1) & ~3);
+  const int ws = __ldg(&xt[x4c].sx0) & ~3;
   unsigned a01[4], selA[4], selB[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const int xi = min(x4 + k, D.w - 1);  // pixels past the row end are computed and dropped
+    const int xi = min(x4c + k, D.w - 1);  // pixels past the row end are computed and dropped
     const int o = __ldg(&xt[xi].sx0) - ws;
     a01[k] = __ldg(reinterpret_cast<const unsigned*>(&xt[xi].a0));  // a0 | a1 << 16
     selA[k] = (unsigned)o | ((unsigned)min(o + 1, 7) << 4);
     selB[k] = o == 7 ? 0x40u : 0x10u;
   }
-  const unsigned spitch = (unsigned)S.pitch, dpitch = (unsigned)D.pitch;
-  const uint8_t* sbase = pyr + S.lvl_base + (size_t)b * S.lvl_bytes + ws;
+  if (TILE) {
+    asm volatile("cp.async.wait_all;\n" ::: "memory");
+    __syncthreads();
+  }
+  if (!active) return;
+  const uint8_t* sbase = TILE ? s_src + (ws - c0) : src + ws;
   uint8_t* dp = pyr + D.lvl_base + (size_t)b * D.lvl_bytes + (size_t)y0 * dpitch + x4;
-  asm volatile("" : "+l"(sbase));  // keep the row base in a register pair: rebuilt per source row otherwise
+  if (!TILE) asm volatile("" : "+l"(sbase));  // keep the row base in a register pair: rebuilt per source row otherwise
   auto hrow = [&](int sy, unsigned (&h)[4]) {
-    const unsigned* p = reinterpret_cast<const unsigned*>(sbase + (size_t)((unsigned)sy * spitch));
-    const unsigned w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+    unsigned w0, w1, w2;
+    if (TILE) {
+      const unsigned* p = reinterpret_cast<const unsigned*>(sbase + (sy - s_first) * PT_STRIDE);
+      w0 = p[0]; w1 = p[1]; w2 = p[2];
+    } else {
+      const unsigned* p = reinterpret_cast<const unsigned*>(sbase + (size_t)((unsigned)sy * spitch));
+      w0 = __ldg(p); w1 = __ldg(p + 1); w2 = __ldg(p + 2);
+    }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const unsigned taps = __byte_perm(__byte_perm(w0, w1, selA[k]), w2, selB[k]);  // bytes: S[sx0], S[sx0+1]
@@ -142,10 +181,11 @@ void launch_pyramid_level(const PyrGeom& g, const ExtractorArena& a, int lvl, in
     const int cols = (D.w + 127) / 128;
     if ((long long)cols * ((D.h + 31) / 32) * batch >= 2 * 148 * 4) {
       dim3 grid(cols, (D.h + 8 * PY_WARPS - 1) / (8 * PY_WARPS), batch);
-      pyramid_level_kernel<8><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+      if (D.resize_tile) pyramid_level_kernel<8, true><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+      else pyramid_level_kernel<8, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
     } else {
       dim3 grid(cols, (D.h + 2 * PY_WARPS - 1) / (2 * PY_WARPS), batch);
-      pyramid_level_kernel<2><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+      pyramid_level_kernel<2, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
     }
     return;
   }

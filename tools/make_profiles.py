@@ -53,7 +53,8 @@ for rep in sorted(glob.glob(os.path.join(G, "prof_*_%sf.ncu-rep" % tag))):
         return v * scale
     v = {k: val(k) for k in want}
     traffic[name] = {"dram_bytes_per_launch": v["dram__bytes_read.sum"] + v["dram__bytes_write.sum"], "images": 64,
-                     "time_us": v["gpu__time_duration.sum"]}
+                     "time_us": v["gpu__time_duration.sum"], "warp_inst_per_launch": v["smsp__inst_executed.sum"],
+                     "issue_slots_busy_pct": v["smsp__issue_active.avg.pct_of_peak_sustained_active"]}
     lines.append("| %s | %.1f | %.1f | %.1f | %.1f | %.1f / %.1f / %.1f / %.1f | %.1f / %.1f / %.1f | %.1f + %.1f | %d x %d | %d |" % (
         name, v[want[0]], v[want[1]], v[want[2]], v[want[3]] / 1e6, v[want[4]], v[want[5]], v[want[6]], v[want[7]], v[want[8]],
         v[want[9]], v[want[10]], v[want[11]] / 1e6, v[want[12]] / 1e6, v[want[13]], v[want[14]], v[want[15]]))
