@@ -28,10 +28,13 @@
 //      score; a neighbour in another cell's detection window counts as 0.  The set
 //      of strict local maxima does not depend on the threshold (a neighbour below
 //      the threshold is below the centre anyway), so FAST(t) = {maxima with score
-//      >= t}: every maximum with score >= min(iniTh, minTh) is appended to the
-//      level's list and a per-cell flag records "has a maximum >= iniTh"; the
-//      consumer keeps the iniTh set of flagged cells and the minTh set of the
-//      others (:830-837).
+//      >= t}.
+//  The kernel runs twice: at iniTh over every strip (each maximum is appended to the level's list and flags its
+//  cell), then at minTh, where a strip returns at once unless one of the cells under its owned pixels has no flag,
+//  and appends maxima of unflagged cells only.  On textured images the second launch does nothing, and the first
+//  one computes exact corner strengths for the iniTh survivors only (a third of the minTh survivors); on smooth
+//  regions the minTh pass has few survivors anyway.  The consumer keeps score >= iniTh in flagged cells and
+//  score >= minTh in the others (:830-837).
 // Candidates are x | y<<12 | score<<24 with x,y relative to minBorder, as the
 // reference stores them (:841-846).  List order is not the reference's; the
 // consumer (k_quadtree.cu) breaks ties by the reference's order key computed
@@ -147,8 +150,8 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
                                                            const uint8_t* __restrict__ pyr,
                                                            uint32_t* __restrict__ cand,
                                                            int32_t* __restrict__ cand_count,
-                                                           uint8_t* __restrict__ cell_hi,
-                                                           int32_t* __restrict__ flags) {
+                                                           uint8_t* cell_hi, int32_t* __restrict__ flags,
+                                                           int t_run, int second_pass) {
   extern __shared__ __align__(16) unsigned char fd_smem_raw[];
   FdSmem* s_all = reinterpret_cast<FdSmem*>(fd_smem_raw);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -171,8 +174,41 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
   const int x4 = xw * 4;
   const int xwc = min(xw, pw - 1), xwm = min(xw - 1, pw - 1), xwp = min(xw + 1, pw - 1);  // clamped words are masked
   const uint8_t* img = pyr + L.lvl_base + (size_t)b * L.lvl_bytes;
-  const int t_lo = min(g.ini_th, g.min_th);
+  const int t_lo = t_run;
   const unsigned K = (unsigned)(127 - min(t_lo, 127)) * 0x01010101u;  // a weaker threshold only passes a superset
+  const unsigned inv_w = 0xFFFFFFFFu / (unsigned)L.w_cell + 1u;  // n / d == umulhi(n, inv) for n < 2^32 / d
+  const unsigned inv_h = 0xFFFFFFFFu / (unsigned)L.h_cell + 1u;
+  uint8_t* hi = cell_hi + (size_t)b * g.total_cells + L.cell_base;
+  unsigned open0 = 0xFFFFFFFFu, open1 = 0xFFFFFFFFu;  // pixels (bit 7 of each byte) still looked at: rows < / >= y_split
+  int y_split = 0;
+  if (second_pass) {
+    // the minTh pass only matters for cells without an iniTh corner (:830-837): a strip whose owned pixels all lie
+    // in flagged cells has nothing to add
+    const int ox0 = max(cx0 + 4, kEdge), ox1 = min(cx0 + 4 + kFastOwnCols, x_end) - 1;
+    const int oy0 = max(cy0 + 1, kEdge), oy1 = min(cy0 + 1 + kFastOwnRows, y_end) - 1;
+    if (ox1 < ox0 || oy1 < oy0) return;
+    const int cj0 = (int)__umulhi((unsigned)(ox0 - kEdge), inv_w), cj1 = (int)__umulhi((unsigned)(ox1 - kEdge), inv_w);
+    const int ci0 = (int)__umulhi((unsigned)(oy0 - kEdge), inv_h), ci1 = (int)__umulhi((unsigned)(oy1 - kEdge), inv_h);
+    const int ncj = cj1 - cj0 + 1, ncells = ncj * (ci1 - ci0 + 1);
+    bool open = false;
+    for (int q = lane; q < ncells; q += 32) {
+      const int qi = q / ncj, qj = q - qi * ncj;
+      open |= hi[(ci0 + qi) * L.n_cols + cj0 + qj] == 0;
+    }
+    if (!__any_sync(0xffffffffu, open)) return;  // uniform
+    // ... and inside an open strip only the pixels of unflagged cells are looked at (the owned rows span at most two
+    // cell rows when cells are at least as tall as a strip; otherwise every pixel stays)
+    if (ci1 - ci0 <= 1) {
+      open0 = open1 = 0u;
+      y_split = kEdge + ci1 * L.h_cell;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int cj = min((int)__umulhi((unsigned)max(x4 + k - kEdge, 0), inv_w), L.n_cols - 1);
+        if (hi[ci0 * L.n_cols + cj] == 0) open0 |= 0x80u << (8 * k);
+        if (hi[ci1 * L.n_cols + cj] == 0) open1 |= 0x80u << (8 * k);
+      }
+    }
+  }
   unsigned colmask = 0;
 #pragma unroll
   for (int k = 0; k < 4; ++k)
@@ -214,7 +250,7 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
     if (j >= 6) {
       const int r = j - 6, y = cy0 + r;
       score_w[r * 32 + lane] = 0u;
-      const unsigned rm = (y >= kEdge && y < y_end) ? colmask : 0u;
+      const unsigned rm = (y >= kEdge && y < y_end) ? (colmask & (y < y_split ? open0 : open1)) : 0u;
       const unsigned cc = c[(j - 3) % 7];
       const unsigned vf = swar_gt2(__vabsdiffu4(cc, c[(j - 6) % 7]), __vabsdiffu4(cc, c[j % 7]), K);
       put_nibble(acc, r, gather_bit7(vf & hf[(j - 3) % 4] & rm));
@@ -225,11 +261,8 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
   if (total == 0) return;  // uniform
   __syncwarp();
 
-  const unsigned inv_w = 0xFFFFFFFFu / (unsigned)L.w_cell + 1u;  // n / d == umulhi(n, inv) for n < 2^32 / d
-  const unsigned inv_h = 0xFFFFFFFFu / (unsigned)L.h_cell + 1u;
   uint32_t* out = cand + (size_t)b * g.cand_total + L.cand_off;
   int32_t* out_n = cand_count + b * kMaxLevels + lvl;
-  uint8_t* hi = cell_hi + (size_t)b * g.total_cells + L.cell_base;
   const unsigned lt = (1u << lane) - 1u;
 
   // 3. cell-local 3x3 suppression of list[0..n) (owned pixels that have a score); the maxima compact in place, then
@@ -257,6 +290,7 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
         const int un = max(u1, max(xl ? u0 : 0, xr ? u2 : 0)), dn = max(d1, max(xl ? d0 : 0, xr ? d2 : 0));
         nb = max(nb, max(yu ? un : 0, yd ? dn : 0));
         keep = sc > nb;
+        if (second_pass && keep) keep = hi[ci * L.n_cols + cj] == 0;  // flagged cells keep their iniTh set (first pass)
       }
       const unsigned mk = __ballot_sync(0xffffffffu, keep);
       __syncwarp();  // this chunk has been read by every lane before slots <= base+31 are overwritten
@@ -275,7 +309,7 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
       const int sc = sm.score[r * 128 + cx];
       if (ob + i < L.cand_cap) out[ob + i] = pack_cand(x - kMinBorder, y - kMinBorder, sc);
       else atomicOr(&flags[b], FLAG_CAND_OVERFLOW);
-      if (sc >= g.ini_th) {
+      if (!second_pass && sc >= g.ini_th) {
         const int cj = (int)__umulhi((unsigned)(x - kEdge), inv_w), ci = (int)__umulhi((unsigned)(y - kEdge), inv_h);
         hi[ci * L.n_cols + cj] = 1;
       }
@@ -350,7 +384,13 @@ void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cud
   if (g.fast_strips <= 0) return;
   cudaMemsetAsync(a.cell_hi, 0, (size_t)batch * g.total_cells, s);
   dim3 grid((g.fast_strips + FD_WARPS - 1) / FD_WARPS, batch);
-  fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi, a.flags);
+  // cv::FAST(iniTh) everywhere, then cv::FAST(minTh) where a cell came back empty (:830-837): the second launch
+  // leaves every strip whose cells all have an iniTh corner at once
+  fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi, a.flags,
+                                                                    g.ini_th, 0);
+  if (g.min_th < g.ini_th)
+    fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi,
+                                                                      a.flags, g.min_th, 1);
 }
 
 }  // namespace orbfe
