@@ -305,6 +305,80 @@ def matcher_extras(torch, dist, orbfe, rank, world, local, kp_frame, desc_frame,
     return out
 
 
+def shape_extras(torch, dist, orbfe, rank, world, local, steps, warmup):
+    """configs[0] (TUM1 640x480 mono, 1000 features: extraction only) and configs[2] (EuRoC 752x480 stereo, 1200
+    features, a batch of 256 pairs sharded by frame over the ranks: extraction L+R + ComputeStereoMatches) on the
+    same device-resident footing as `value` (CUDA events on the handle's stream, max over ranks)."""
+    lib = orbfe.lib()
+    dev = torch.device("cuda", local)
+    out = {}
+
+    def timed(step_fn, stream):
+        for _ in range(warmup):
+            step_fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            step_fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # configs[2]: 256 EuRoC pairs per step in total, rank r owns pairs r, r+world, ...
+    s, (w, h) = synth.SETTINGS["euroc"], synth.SHAPES["euroc"]
+    prm = (s["nfeatures"], s["scale_factor"], s["nlevels"], s["ini_th"], s["min_th"])
+    total = 256
+    mine = len(range(rank, total, world))
+    pairs = [synth.synth_pair(w, h, 1000 + rank + world * i) for i in range(4)]
+    dl = torch.from_numpy(np.stack([pairs[i % 4][0] for i in range(mine)])).to(dev)
+    dr = torch.from_numpy(np.stack([pairs[i % 4][1] for i in range(mine)])).to(dev)
+    L = orbfe.Extractor(*prm, w, h, max_batch=mine, device=local)
+    R = orbfe.Extractor(*prm, w, h, max_batch=mine, device=local)
+    mbf, mb = np.float32(s["bf"]), np.float32(s["bf"]) / np.float32(s["fx"])
+
+    def euroc_step():
+        L.upload(dl.data_ptr(), mine, on_device=True)
+        R.upload(dr.data_ptr(), mine, on_device=True)
+        L.run(mine)
+        R.run(mine)
+        orbfe.check(lib.orbfe_stereo_match_run(L._h, R._h, mine, mbf, mb))
+
+    ms = timed(euroc_step, torch.cuda.ExternalStream(L.stream, device=dev))
+    out["euroc_stereo_256"] = {
+        "workload": "configs[2]: 256 EuRoC-shaped 752x480 stereo pairs per step, 1200 features, extract L+R + "
+                    "ComputeStereoMatches, sharded by frame over %d GPU(s) (%d pairs on rank 0)" % (world, mine),
+        "frames_per_s": total * steps / (ms * 1e-3), "ms_per_step": ms / steps, "scaling": "strong"}
+    R.close()
+    L.close()
+    del dl, dr
+
+    # configs[0]: TUM1 mono, 64 frames per step per GPU
+    s, (w, h) = synth.SETTINGS["tum"], synth.SHAPES["tum"]
+    prm = (s["nfeatures"], s["scale_factor"], s["nlevels"], s["ini_th"], s["min_th"])
+    nb = 64
+    imgs = [synth.synth_image(w, h, 2000 + rank * 8 + i) for i in range(8)]
+    di = torch.from_numpy(np.stack([imgs[i % 8] for i in range(nb)])).to(dev)
+    E = orbfe.Extractor(*prm, w, h, max_batch=nb, device=local)
+
+    def tum_step():
+        E.upload(di.data_ptr(), nb, on_device=True)
+        E.run(nb)
+
+    ms = timed(tum_step, torch.cuda.ExternalStream(E.stream, device=dev))
+    out["tum_mono_64"] = {
+        "workload": "configs[0] shape: TUM1 640x480 mono, 1000 features, ORB extraction only, 64 frames per step "
+                    "per GPU on one handle (one stream)",
+        "frames_per_s": nb * world * steps / (ms * 1e-3), "ms_per_step": ms / steps, "scaling": "weak"}
+    E.close()
+    return out
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -493,6 +567,9 @@ def run_gpu(args):
         extras = matcher_extras(torch, dist, orbfe, rank, world, local, kp0, ds0, args.quick_matchers)
     for g in rigs:
         g.close()
+    del d_left, d_right
+    shapes = None if args.no_shapes else shape_extras(torch, dist, orbfe, rank, world, local, args.steps,
+                                                      max(args.warmup, 3))
     if world > 1:
         dist.barrier()
     if rank != 0:
@@ -587,6 +664,7 @@ def run_gpu(args):
         "stages_ms_per_launch": per_launch,
         "cpu_baseline": cpu,
         "matchers": extras,
+        "shapes": shapes,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -604,6 +682,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-matchers", action="store_true", help="skip the configs 3/4 matcher figures")
+    ap.add_argument("--no-shapes", action="store_true", help="skip the TUM / EuRoC shape figures")
     ap.add_argument("--quick-matchers", action="store_true", help="128 k map descriptors instead of 1 M")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

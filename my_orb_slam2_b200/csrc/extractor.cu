@@ -316,7 +316,21 @@ int orbfe_extractor_create(const orbfe_extractor_params* params, int width, int 
   if (rc == ORBFE_OK && cudaEventCreateWithFlags(&e->done, cudaEventDisableTiming) != cudaSuccess) rc = ORBFE_ERR_CUDA;
   if (rc == ORBFE_OK) rc = configure_kernels(e->geom);
   { const char* ng = getenv("ORBFE_NO_GRAPHS"); e->use_graph = !(ng && ng[0] == '1'); }
-  if (rc != ORBFE_OK) { free_arenas(e); if (e->stream) cudaStreamDestroy(e->stream); delete e; return rc; }
+  { const char* nf = getenv("ORBFE_NO_FORK"); e->fork_graph = !(nf && nf[0] == '1'); }
+  if (rc == ORBFE_OK && e->fork_graph &&
+      (cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking) != cudaSuccess ||
+       cudaEventCreateWithFlags(&e->fork_ev, cudaEventDisableTiming) != cudaSuccess ||
+       cudaEventCreateWithFlags(&e->join_ev, cudaEventDisableTiming) != cudaSuccess))
+    rc = ORBFE_ERR_CUDA;
+  if (rc != ORBFE_OK) {
+    free_arenas(e);
+    if (e->fork_ev) cudaEventDestroy(e->fork_ev);
+    if (e->join_ev) cudaEventDestroy(e->join_ev);
+    if (e->side) cudaStreamDestroy(e->side);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+    return rc;
+  }
   *out = reinterpret_cast<orbfe_extractor*>(e);
   return ORBFE_OK;
 }
@@ -334,6 +348,9 @@ void orbfe_extractor_destroy(orbfe_extractor* h) {
   if (e->run_graph) cudaGraphExecDestroy(e->run_graph);
   if (e->stereo_graph) cudaGraphExecDestroy(e->stereo_graph);
   if (e->done) cudaEventDestroy(e->done);
+  if (e->fork_ev) cudaEventDestroy(e->fork_ev);
+  if (e->join_ev) cudaEventDestroy(e->join_ev);
+  if (e->side) cudaStreamDestroy(e->side);
   if (e->owns_stream) cudaStreamDestroy(e->stream);
   delete e;
 }
@@ -491,6 +508,25 @@ static void issue_extract(Extractor* e, int batch, cudaEvent_t* ev) {
   if (ev) cudaEventRecord(ev[5], e->stream);
 }
 
+// the same schedule as a graph with two branches after the pyramid: GaussianBlur needs only the pyramid, so it runs
+// beside FAST + quadtree (the latency-bound quadtree leaves issue slots the blur can use) and joins before describe.
+// Only used under stream capture (e->side joins the capture through the fork event).
+static void issue_extract_forked(Extractor* e, int batch) {
+  const PyrGeom& g = e->geom;
+  const ExtractorArena& a = e->arena;
+  cudaMemsetAsync(a.cand_count, 0, (size_t)batch * kMaxLevels * sizeof(int32_t), e->stream);
+  cudaMemsetAsync(a.flags, 0, (size_t)batch * sizeof(int32_t), e->stream);
+  for (int l = 1; l < g.nlevels; ++l) launch_pyramid_level(g, a, l, batch, e->stream);
+  cudaEventRecord(e->fork_ev, e->stream);
+  cudaStreamWaitEvent(e->side, e->fork_ev, 0);
+  launch_fast_cells(g, a, batch, e->stream);
+  launch_blur_levels(g, a, batch, e->side);
+  cudaEventRecord(e->join_ev, e->side);
+  launch_quadtree(g, a, batch, e->stream);
+  cudaStreamWaitEvent(e->stream, e->join_ev, 0);
+  launch_describe(g, a, batch, e->stream);
+}
+
 int orbfe_extract_run(orbfe_extractor* h, int batch) {
   ORBFE_ARG(h);
   Extractor* e = reinterpret_cast<Extractor*>(h);
@@ -508,7 +544,7 @@ int orbfe_extract_run(orbfe_extractor* h, int batch) {
       if (e->run_graph) { cudaGraphExecDestroy(e->run_graph); e->run_graph = nullptr; }
       cudaGraph_t graph = nullptr;
       ORBFE_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
-      issue_extract(e, batch, nullptr);
+      if (e->fork_graph) issue_extract_forked(e, batch); else issue_extract(e, batch, nullptr);
       ORBFE_CUDA(cudaStreamEndCapture(e->stream, &graph));
       ORBFE_CUDA(cudaGraphInstantiate(&e->run_graph, graph, 0));
       cudaGraphDestroy(graph);

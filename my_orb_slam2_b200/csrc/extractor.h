@@ -27,6 +27,10 @@ struct Extractor {
   bool use_graph = true;
   cudaGraphExec_t run_graph = nullptr;
   int run_graph_batch = 0;
+  // the captured schedule forks after the pyramid (blur beside FAST + quadtree); ORBFE_NO_FORK=1 keeps it linear
+  bool fork_graph = true;
+  cudaStream_t side = nullptr;
+  cudaEvent_t fork_ev = nullptr, join_ev = nullptr;
   cudaGraphExec_t stereo_graph = nullptr;  // orbfe_stereo_match_run with this handle as `left`
   int stereo_graph_batch = 0;
   const void* stereo_graph_right = nullptr;

@@ -7,7 +7,7 @@ set -u
 TAG=${1:-r1}
 OUT=gpurun_out
 mkdir -p $OUT
-CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-matchers --latency-frames 2"
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-matchers --no-shapes --latency-frames 2"
 $CMD > $OUT/plain_$TAG.log 2>&1 || { echo "bench failed without ncu"; tail -5 $OUT/plain_$TAG.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_bench_launches.csv $CMD > $OUT/ncu_bench.log 2>&1
 python tools/one_step.py 64 1 > $OUT/plain_step_$TAG.log 2>&1 || { echo "one_step failed without ncu"; exit 1; }
