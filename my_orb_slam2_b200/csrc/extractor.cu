@@ -10,6 +10,8 @@
 #include <new>
 #include <vector>
 
+#include <cuda.h>
+
 #include "common.cuh"
 #include "extractor.h"
 #include "kernels.h"
@@ -251,6 +253,43 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
   ORBFE_CUDA(cudaMemset(a.kept_count, 0, B * kMaxLevels * sizeof(int32_t)));
   ORBFE_CUDA(cudaMemset(a.flags, 0, B * sizeof(int32_t)));
   ORBFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&e->h_flags), B * sizeof(int32_t), cudaHostAllocDefault));
+  return build_fast_tensor_maps(g, a, e->max_batch);
+}
+
+// CUtensorMap of every level that has FAST strips: a (pitch, h, max_batch) byte tensor over the pyramid arena with a
+// kFastTileW x kFastTileH x 1 box (k_fast.cu).  cuTensorMapEncodeTiled is a driver entry point; it is fetched through
+// the runtime so that liborbfe.so does not link libcuda.
+int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
+  typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn ||
+      q != cudaDriverEntryPointSuccess) {
+    set_error("cuTensorMapEncodeTiled is not available from this driver");
+    return ORBFE_ERR_CUDA;
+  }
+  alignas(64) CUtensorMap maps[kMaxLevels];
+  memset(maps, 0, sizeof(maps));
+  for (int l = 0; l < g.nlevels; ++l) {
+    const LevelGeom& L = g.lv[l];
+    if (L.fast_strips_x <= 0) continue;
+    const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.h, (cuuint64_t)max_batch};
+    const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.lvl_bytes};
+    const cuuint32_t box[3] = {(cuuint32_t)kFastTileW, (cuuint32_t)kFastTileH, 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    const CUresult r = reinterpret_cast<EncodeTiled>(fn)(
+        &maps[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, a.pyr + L.lvl_base, dims, strides, box, estr,
+        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+      set_error("cuTensorMapEncodeTiled failed for level %d (%dx%d, pitch %d): CUresult %d", l, L.w, L.h, L.pitch, (int)r);
+      return ORBFE_ERR_CUDA;
+    }
+  }
+  ORBFE_CUDA(cudaMalloc(&a.fast_maps, sizeof(maps)));
+  ORBFE_CUDA(cudaMemcpy(a.fast_maps, maps, sizeof(maps), cudaMemcpyHostToDevice));
   return ORBFE_OK;
 }
 
@@ -260,6 +299,7 @@ static void free_arenas(Extractor* e) {
   cudaFree(a.cand_count); cudaFree(a.cell_hi); cudaFree(a.kept); cudaFree(a.kept_count); cudaFree(a.out_kp); cudaFree(a.out_desc);
   cudaFree(a.out_count); cudaFree(a.flags); cudaFree(a.st_uright); cudaFree(a.st_depth); cudaFree(a.st_sad);
   cudaFree(a.st_count); cudaFree(a.st_band); cudaFree(a.st_bucket_start); cudaFree(a.st_bucket_items);
+  cudaFree(a.fast_maps);
   if (e->h_flags) cudaFreeHost(e->h_flags);
   if (e->prof_ev) {
     for (int i = 0; i < Extractor::kProfRuns * 9; ++i) cudaEventDestroy(e->prof_ev[i]);

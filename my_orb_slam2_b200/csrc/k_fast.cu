@@ -39,6 +39,8 @@
 // reference stores them (:841-846).  List order is not the reference's; the
 // consumer (k_quadtree.cu) breaks ties by the reference's order key computed
 // from (x,y).
+#include <cuda.h>
+
 #include <cstdio>
 
 #include "kernels.h"
@@ -51,22 +53,44 @@ constexpr int FD_ROWS = kFastOwnRows + 2;  // computed rows per strip (multiple 
 constexpr int FD_ACC = FD_ROWS / 8;     // 32-bit survivor masks per lane (8 rows x 4 pixels each)
 static_assert(FD_ROWS % 8 == 0 && FD_ROWS <= 32, "strip rows");
 constexpr int FD_TROWS = FD_ROWS + 6;   // image tile rows (FAST ring: +-3)
-constexpr int FD_TS = 136;              // image tile stride in bytes: columns -4 .. 131 of the strip
+constexpr int FD_TS = kFastTileW;       // image tile stride in bytes (the TMA box: 136 bytes used, from column -4 of the strip)
 constexpr int FD_TW = FD_TS / 4;
+static_assert(FD_TROWS == kFastTileH, "TMA box rows");
 constexpr int FD_CAP = FD_ROWS * 64;            // list entries per pass (a strip with more survivors takes several passes)
 
-struct FdSmem {
-  uint8_t img[FD_TROWS * FD_TS];
+struct __align__(128) FdSmem {
+  uint8_t img[FD_TROWS * FD_TS];   // TMA destination (128-byte aligned)
   uint8_t score[FD_ROWS * 128];
   uint16_t list[FD_CAP];
+  unsigned long long bar;          // mbarrier the tile's TMA load completes on
 };
 
-__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)),
-               "l"(gmem_src)
-               : "memory");
+// ---- TMA: one elected lane loads the strip's whole image tile (kFastTileW x kFastTileH bytes of image b of a level;
+// rows / columns past the tensor are zero-filled and only feed masked pixels) and the warp waits on the mbarrier ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void tma_load_tile(void* dst, const void* tmap, int x, int y, int z, unsigned long long* bar) {
+  const unsigned b = smem_u32(bar);
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(b) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(b), "r"(FD_TROWS * FD_TS) : "memory");
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n" ::
+          "r"(smem_u32(dst)), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(b)
+      : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+__device__ __forceinline__ void mbar_wait_phase0(unsigned long long* bar) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "FD_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n"
+      "@p bra FD_DONE;\n"
+      "bra FD_WAIT;\n"
+      "FD_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar))
+      : "memory");
+}
 
 // exact corner strength of the pixel at p in the image tile: max over the 16 circular 9-arcs of the
 // minimum of (ring - v) resp. (v - ring) over the arc, 0 if negative.  Unsigned 16x2 min/max only (no negations:
@@ -151,8 +175,9 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
                                                            uint32_t* __restrict__ cand,
                                                            int32_t* __restrict__ cand_count,
                                                            uint8_t* cell_hi, int32_t* __restrict__ flags,
-                                                           int t_run, int second_pass) {
-  extern __shared__ __align__(16) unsigned char fd_smem_raw[];
+                                                           int t_run, int second_pass,
+                                                           const CUtensorMap* __restrict__ maps) {
+  extern __shared__ __align__(128) unsigned char fd_smem_raw[];
   FdSmem* s_all = reinterpret_cast<FdSmem*>(fd_smem_raw);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   int item = blockIdx.x * FD_WARPS + wid;
@@ -164,16 +189,12 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
   const LevelGeom& L = g.lv[lvl];
   item -= L.fast_strip_base;
   const int sy = item / L.fast_strips_x, sx = item - sy * L.fast_strips_x;
-  const int w = L.w, h = L.h, pitch = L.pitch;
+  const int w = L.w, h = L.h;
   constexpr int kEdge = kMinBorder + 3;             // detection domain: kEdge <= x < w-kEdge, kEdge <= y < h-kEdge
   const int cx0 = kMinBorder - 4 + kFastOwnCols * sx;  // first computed column (word aligned); owned = +4 .. +123
   const int cy0 = kEdge - 1 + kFastOwnRows * sy;       // first computed row; owned = +1 .. +30
   const int x_end = w - kEdge, y_end = h - kEdge;
-  const int pw = pitch >> 2;
-  const int xw = (cx0 >> 2) + lane;  // >= 3
-  const int x4 = xw * 4;
-  const int xwc = min(xw, pw - 1), xwm = min(xw - 1, pw - 1), xwp = min(xw + 1, pw - 1);  // clamped words are masked
-  const uint8_t* img = pyr + L.lvl_base + (size_t)b * L.lvl_bytes;
+  const int x4 = cx0 + lane * 4;  // first of the lane's four columns
   const int t_lo = t_run;
   const unsigned K = (unsigned)(127 - min(t_lo, 127)) * 0x01010101u;  // a weaker threshold only passes a superset
   const unsigned inv_w = 0xFFFFFFFFu / (unsigned)L.w_cell + 1u;  // n / d == umulhi(n, inv) for n < 2^32 / d
@@ -213,23 +234,17 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
 #pragma unroll
   for (int k = 0; k < 4; ++k)
     if (x4 + k >= kEdge && x4 + k < x_end) colmask |= 0x80u << (8 * k);
-  unsigned* tile_w = reinterpret_cast<unsigned*>(sm.img);
+  // TMA wants a 16-byte aligned start column: the box starts at the aligned column below cx0-4 (0 or 8 bytes earlier;
+  // the 144-byte box still covers the 136 bytes the strip reads) and the tile is addressed from `timg`
+  const int tma_x = (cx0 - 4) & ~15;
+  const uint8_t* timg = sm.img + (cx0 - 4 - tma_x);
+  const unsigned* tile_w = reinterpret_cast<const unsigned*>(timg);
   unsigned* score_w = reinterpret_cast<unsigned*>(sm.score);
 
-  // ---- 0. stage rows cy0-3 .. cy0+34, columns cx0-4 .. cx0+131 in shared memory (asynchronous copies: all 38 rows
-  // of a lane are in flight together; rows past the image are clamped and only feed masked pixels) ----
-  {
-    const bool edge = lane == 0 || lane == 31;
-    const int xe = lane == 0 ? xwm : xwp, te = lane == 0 ? 0 : FD_TW - 1;
-#pragma unroll
-    for (int j = 0; j < FD_TROWS; ++j) {
-      const unsigned* row = reinterpret_cast<const unsigned*>(img + (size_t)min(cy0 - 3 + j, h - 1) * pitch);
-      cp_async4(tile_w + j * FD_TW + lane + 1, row + xwc);
-      if (edge) cp_async4(tile_w + j * FD_TW + te, row + xe);
-    }
-    cp_async_wait_all();
-    __syncwarp();
-  }
+  // ---- 0. stage rows cy0-3 .. cy0+18, columns tma_x .. tma_x+143 in shared memory: one TMA tile load per strip ----
+  if (lane == 0) tma_load_tile(sm.img, maps + lvl, tma_x, cy0 - 3, b, &sm.bar);
+  __syncwarp();
+  mbar_wait_phase0(&sm.bar);
 
   // ---- 1. dense quick reject (branch-free) ----
   unsigned c[7];   // centre words of the last 7 rows
@@ -329,7 +344,7 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
       if (i < total) {
         e = sm.list[i];
         const int r = e >> 7, cx = e & 127;
-        const int m = corner_strength(sm.img + (r + 3) * FD_TS + cx + 4);
+        const int m = corner_strength(timg + (r + 3) * FD_TS + cx + 4);
         if (m > t_lo) {
           sm.score[r * 128 + cx] = (uint8_t)(m - 1);
           corner = m > 1 && r >= 1 && r <= kFastOwnRows && cx >= 4 && cx < 4 + kFastOwnCols;  // score 0 never wins
@@ -353,7 +368,7 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
     for (int i = lane; i < nwin; i += 32) {
       const int e = sm.list[i];
       const int r = e >> 7, cx = e & 127;
-      const int m = corner_strength(sm.img + (r + 3) * FD_TS + cx + 4);
+      const int m = corner_strength(timg + (r + 3) * FD_TS + cx + 4);
       if (m > t_lo) sm.score[r * 128 + cx] = (uint8_t)(m - 1);
     }
     __syncwarp();
@@ -388,10 +403,11 @@ void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cud
   // cv::FAST(iniTh) everywhere, then cv::FAST(minTh) where a cell came back empty (:830-837): the second launch
   // leaves every strip whose cells all have an iniTh corner at once
   fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi, a.flags,
-                                                                    g.ini_th, 0);
+                                                                    g.ini_th, 0, static_cast<const CUtensorMap*>(a.fast_maps));
   if (g.min_th < g.ini_th)
     fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi,
-                                                                      a.flags, g.min_th, 1);
+                                                                      a.flags, g.min_th, 1,
+                                                                      static_cast<const CUtensorMap*>(a.fast_maps));
 }
 
 }  // namespace orbfe

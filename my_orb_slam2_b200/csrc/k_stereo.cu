@@ -200,15 +200,18 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 8) stereo_match_kernel(
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) sad[s] += __shfl_xor_sync(0xffffffffu, sad[s], o);
       }
-      int bestSad = INT_MAX, bestInc = 0;
+      // strict '<': first minimum (:624); its two neighbours ride along (no dynamically indexed local array)
+      int bestSad = sad[0], bestInc = -Lh, sPrev = 0, sNext = 0;
 #pragma unroll
-      for (int s = 0; s < 11; ++s)
-        if (sad[s] < bestSad) { bestSad = sad[s]; bestInc = s - Lh; }  // strict '<': first minimum (:624)
+      for (int s = 1; s < 11; ++s) {
+        const bool lt = sad[s] < bestSad;
+        bestSad = lt ? sad[s] : bestSad;
+        bestInc = lt ? s - Lh : bestInc;
+        sPrev = lt ? sad[s - 1] : sPrev;
+        sNext = lt ? (s < 10 ? sad[s + 1] : 0) : sNext;
+      }
       if (!(bestInc == -Lh || bestInc == Lh)) {  // :633
-        float d1f = 0.f, d2f = 0.f, d3f = 0.f;
-#pragma unroll
-        for (int s = 1; s < 10; ++s)
-          if (s == bestInc + Lh) { d1f = (float)sad[s - 1]; d2f = (float)sad[s]; d3f = (float)sad[s + 1]; }
+        const float d1f = (float)sPrev, d2f = (float)bestSad, d3f = (float)sNext;
         // deltaR = (d1-d3)/(2*(d1+d3-2*d2))  (:644), every step rounded to fp32
         const float den = __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1f, d3f), __fmul_rn(2.0f, d2f)));
         const float deltaR = __fdiv_rn(__fsub_rn(d1f, d3f), den);

@@ -33,7 +33,15 @@ struct ExtractorArena {
   int32_t* st_bucket_start = nullptr;  // [batch][rows/8 + 2]
   int4* st_bucket_items = nullptr;     // [batch][out_cap * st_items_per_kp] band + right keypoint index per bucket entry
   int st_items_per_kp = 0;
+  // TMA descriptors (CUtensorMap, 128 B each) of the pyramid levels as (x, y, image) byte tensors with a
+  // kFastTileW x kFastTileH box: the FAST kernel stages a strip's image tile with ONE cp.async.bulk.tensor
+  void* fast_maps = nullptr;  // [kMaxLevels]
 };
+
+constexpr int kFastTileW = 144;                    // bytes per tile row (multiple of 16): 136 used + 8 of start alignment
+constexpr int kFastTileH = kFastOwnRows + 2 + 6;   // computed rows + the FAST ring (+-3)
+// one-time host setup of ExtractorArena::fast_maps (extractor.cu; needs the driver's cuTensorMapEncodeTiled)
+int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch);
 
 enum : int { FLAG_CAND_OVERFLOW = 1, FLAG_NODE_OVERFLOW = 2, FLAG_OUT_OVERFLOW = 4 };
 

@@ -5,7 +5,7 @@ for spec in "$@"; do
   name=${spec%%:*}; envs=""
   [ "$spec" != "$name" ] && envs=${spec#*:}
   cp tools/scratch/var/$name.so my_orb_slam2_b200/liborbfe.so
-  for rep in 1 2; do
+  for rep in 1; do
     env $envs python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-matchers --no-shapes --latency-frames 100 2>gpurun_out/ab_$name.err | python -c "
 import json,sys
 d=json.loads(sys.stdin.read().strip().splitlines()[-1])

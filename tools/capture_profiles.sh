@@ -16,4 +16,8 @@ for K in pyramid_level fast_detect quadtree blur_levels describe stereo_match; d
       python tools/one_step.py 64 1 > $OUT/ncu_${K}.log 2>&1
   echo "$K rc=$?"
 done
+python tools/one_hamming.py > $OUT/plain_hamming_$TAG.log 2>&1 || { echo "one_hamming failed without ncu"; exit 1; }
+ncu --set full --clock-control none --import-source on -k regex:hamming_bruteforce -c 1 -f -o $OUT/prof_hamming_bruteforce_${TAG}f \
+    python tools/one_hamming.py > $OUT/ncu_hamming.log 2>&1
+echo "hamming rc=$?"
 ls -la $OUT/*_${TAG}f.ncu-rep

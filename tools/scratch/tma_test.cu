@@ -1,0 +1,77 @@
+// standalone probe: TMA 3-D tile load of a u8 tensor, descriptor in global memory vs __grid_constant__
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <cstdint>
+constexpr int TW = 144, TH = 22;
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ void load_tile(void* dst, const void* tmap, int x, int y, int z, unsigned long long* bar) {
+  const unsigned b = smem_u32(bar);
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(b) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(b), "r"(TW * TH) : "memory");
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n" ::
+      "r"(smem_u32(dst)), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(b) : "memory");
+}
+__device__ void wait0(unsigned long long* bar) {
+  asm volatile("{\n.reg .pred p;\nW:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n@p bra D;\nbra W;\nD:\n}\n" ::"r"(smem_u32(bar)) : "memory");
+}
+struct __align__(128) Sm { uint8_t img[TW * TH]; unsigned long long bar; };
+__global__ void k_global(const CUtensorMap* maps, int x, int y, int z, uint8_t* out) {
+  extern __shared__ __align__(128) unsigned char raw[];
+  Sm* s = reinterpret_cast<Sm*>(raw) + (threadIdx.x >> 5);
+  if ((threadIdx.x & 31) == 0) load_tile(s->img, maps, x, y, z, &s->bar);
+  __syncwarp();
+  wait0(&s->bar);
+  for (int i = threadIdx.x & 31; i < TW * TH; i += 32) out[(threadIdx.x >> 5) * TW * TH + i] = s->img[i];
+}
+__global__ void k_param(const __grid_constant__ CUtensorMap map, int x, int y, int z, uint8_t* out) {
+  extern __shared__ __align__(128) unsigned char raw[];
+  Sm* s = reinterpret_cast<Sm*>(raw) + (threadIdx.x >> 5);
+  if ((threadIdx.x & 31) == 0) load_tile(s->img, &map, x, y, z, &s->bar);
+  __syncwarp();
+  wait0(&s->bar);
+  for (int i = threadIdx.x & 31; i < TW * TH; i += 32) out[(threadIdx.x >> 5) * TW * TH + i] = s->img[i];
+}
+int main(int argc, char** argv) {
+  const int only_variant = argc > 1 ? atoi(argv[1]) : 0, x0 = argc > 2 ? atoi(argv[2]) : 8;
+  const int pitch = 1280, h = 376, nb = 3;
+  std::vector<uint8_t> img((size_t)pitch * h * nb);
+  for (size_t i = 0; i < img.size(); ++i) img[i] = (uint8_t)((i * 2654435761u) >> 13);
+  uint8_t *d, *o; cudaMalloc(&d, img.size()); cudaMalloc(&o, 2 * TW * TH);
+  cudaMemcpy(d, img.data(), img.size(), cudaMemcpyHostToDevice);
+  typedef CUresult (*Enc)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  void* fn = nullptr; cudaDriverEntryPointQueryResult q;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+  printf("entry point: %d %d %p\n", (int)e, (int)q, fn);
+  alignas(64) CUtensorMap m; memset(&m, 0, sizeof(m));
+  cuuint64_t dims[3] = {(cuuint64_t)pitch, (cuuint64_t)h, (cuuint64_t)nb}, strides[2] = {(cuuint64_t)pitch, (cuuint64_t)pitch * h};
+  cuuint32_t box[3] = {TW, TH, 1}, es[3] = {1, 1, 1};
+  CUresult r = ((Enc)fn)(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, d, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  printf("encode: %d\n", (int)r);
+  CUtensorMap* dm; cudaMalloc(&dm, sizeof(m)); cudaMemcpy(dm, &m, sizeof(m), cudaMemcpyHostToDevice);
+  std::vector<uint8_t> got(2 * TW * TH);
+  for (int variant = only_variant; variant <= only_variant; ++variant) {
+    for (int t = 0; t < 3; ++t) {
+      const int x = t == 0 ? x0 : (t == 1 ? 128 : 1240), y = t == 0 ? 15 : (t == 1 ? 29 : 360), z = t;
+      cudaMemset(o, 0xEE, 2 * TW * TH);
+      if (variant == 0) k_global<<<1, 64, 2 * sizeof(Sm)>>>(dm, x, y, z, o); else k_param<<<1, 64, 2 * sizeof(Sm)>>>(m, x, y, z, o);
+      e = cudaDeviceSynchronize();
+      printf("variant %d case %d: %s\n", variant, t, cudaGetErrorString(e));
+      if (e != cudaSuccess) return 1;
+      cudaMemcpy(got.data(), o, got.size(), cudaMemcpyDeviceToHost);
+      int bad = 0;
+      for (int w = 0; w < 2; ++w) for (int j = 0; j < TH; ++j) for (int i = 0; i < TW; ++i) {
+        const int xx = x + i, yy = y + j;
+        const uint8_t want = (xx < pitch && yy < h) ? img[((size_t)z * h + yy) * pitch + xx] : 0;
+        bad += got[w * TW * TH + j * TW + i] != want;
+      }
+      printf("  mismatches %d\n", bad);
+    }
+  }
+  return 0;
+}
