@@ -32,26 +32,47 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
   int tile = blockIdx.x;
   int lvl = 0;
   constexpr bool kTall = BL_ROWS == 32;
-  while (lvl + 1 < g.nlevels && tile >= (kTall ? g.lv[lvl + 1].blur_tile_base : g.lv[lvl + 1].blur_tile_base_small)) ++lvl;
-  const LevelGeom& L = g.lv[lvl];
-  tile -= kTall ? L.blur_tile_base : L.blur_tile_base_small;
-  const int tiles_x = (L.w + 127) / 128;
-  const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
+  const int n_tiles = kTall ? g.blur_tiles : g.blur_tiles_small;
   const int b = blockIdx.y;
-  const int x4 = (tx * BL_TX + threadIdx.x) * 4;
-  const int y0 = (ty * BL_TY + threadIdx.y) * BL_ROWS;
-  if (x4 >= L.w || y0 >= L.h) return;
+  // The last one or two words of a row (x4 + 7 >= w) need column reflection: byte-wise loads, a rolled loop, ~5x the
+  // instructions of the word path.  Left inside the 128-column tiles they would keep a whole warp busy for one or
+  // two lanes; instead the CTAs past n_tiles take them with every lane on its own (row strip, word) job.
+  const bool edge_cta = tile >= n_tiles;
+  int x4, y0;
+  if (!edge_cta) {
+    while (lvl + 1 < g.nlevels && tile >= (kTall ? g.lv[lvl + 1].blur_tile_base : g.lv[lvl + 1].blur_tile_base_small)) ++lvl;
+    const LevelGeom& L0 = g.lv[lvl];
+    tile -= kTall ? L0.blur_tile_base : L0.blur_tile_base_small;
+    const int tiles_x = (L0.w + 127) / 128;
+    const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
+    x4 = (tx * BL_TX + threadIdx.x) * 4;
+    y0 = (ty * BL_TY + threadIdx.y) * BL_ROWS;
+    if (x4 >= L0.w || y0 >= L0.h || x4 + 7 >= L0.w) return;
+  } else {
+    int job = (tile - n_tiles) * (BL_TX * BL_TY) + threadIdx.y * BL_TX + threadIdx.x;
+    for (; lvl < g.nlevels; ++lvl) {
+      const int nj = ((g.lv[lvl].h + BL_ROWS - 1) / BL_ROWS) * 2;
+      if (job < nj) break;
+      job -= nj;
+    }
+    if (lvl >= g.nlevels) return;
+    x4 = ((max(g.lv[lvl].w - 7, 0) + 3) >> 2) * 4 + 4 * (job & 1);  // the first word with x4 + 7 >= w, or the next one
+    y0 = (job >> 1) * BL_ROWS;
+    if (x4 >= g.lv[lvl].w) return;
+  }
+  const LevelGeom& L = g.lv[lvl];
   const uint8_t* src = pyr + L.lvl_base + (size_t)b * L.lvl_bytes;
   uint8_t* dst = blur + L.lvl_base + (size_t)b * L.lvl_bytes;
   const int w = L.w, h = L.h, pitch = L.pitch;
-  const bool slow = (x4 + 7 >= w);  // the words of this strip reach past the last column
+  const bool slow = edge_cta;
   const bool left = (x4 == 0);
   const unsigned K_LO = 0x38302212u;  // 18,34,48,56 (byte 0 first)
   const unsigned K_HI = 0x00122230u;  // 48,34,18,0
 
   const int rows = min(BL_ROWS, h - y0);  // warp-uniform
   if (slow) {
-    // right edge of the level (the last one or two words of a row): byte-wise loads with column reflection, rolled loop
+    // right edge of the level (the last one or two words of a row): byte-wise loads with column reflection, rolled
+    // loop; block-uniform branch (edge CTAs only)
     unsigned win[7][4];
 #pragma unroll
     for (int i = 0; i < 7; ++i)
@@ -188,12 +209,19 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
   }
 }
 
+// CTAs that take the right-edge (row strip, word) jobs of one image: 2 jobs per strip row of every level
+static int blur_edge_ctas(const PyrGeom& g, int rows) {
+  int jobs = 0;
+  for (int l = 0; l < g.nlevels; ++l) jobs += ((g.lv[l].h + rows - 1) / rows) * 2;
+  return (jobs + BL_TX * BL_TY - 1) / (BL_TX * BL_TY);
+}
+
 void launch_blur_levels(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
   dim3 block(BL_TX, BL_TY);
   if ((long long)g.blur_tiles * batch >= 2 * 148 * 4) {
-    blur_levels_kernel<32><<<dim3(g.blur_tiles, batch), block, 0, s>>>(g, a.pyr, a.blur);
+    blur_levels_kernel<32><<<dim3(g.blur_tiles + blur_edge_ctas(g, 32), batch), block, 0, s>>>(g, a.pyr, a.blur);
   } else {  // few images: 128 x 32 tiles (4x more CTAs, 8-row strips per thread)
-    blur_levels_kernel<8><<<dim3(g.blur_tiles_small, batch), block, 0, s>>>(g, a.pyr, a.blur);
+    blur_levels_kernel<8><<<dim3(g.blur_tiles_small + blur_edge_ctas(g, 8), batch), block, 0, s>>>(g, a.pyr, a.blur);
   }
 }
 
