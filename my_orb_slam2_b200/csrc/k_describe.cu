@@ -39,10 +39,53 @@ __device__ PatternT d_pattern_t;
 // end of each row of the radius-15 disc (umax, :454-469); the disc is symmetric: |u| <= umax[|v|] <=> |v| <= umax[|u|]
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
+// IC_Angle as byte dot products: the disc rows are read as aligned words, so a word's four weights depend on the
+// keypoint's alignment a = (kx - 15) & 3, the word j of the row and the row |v|: byte t of word j is column
+// u = 4j + t - 15 - a, inside the disc iff |u| <= umax[|v|].  x = the four u (s8, 0 outside), y = the four 0/1 flags.
+constexpr int IC_PW = 9;  // words per staged disc row: 31 bytes at any alignment fit 36; odd => conflict-free columns
+struct IcTab { uint2 w[4][IC_PW][16]; };
+__device__ IcTab d_ic_tab;
+static IcTab make_ic_tab() {
+  static const int umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+  IcTab t;
+  for (int a = 0; a < 4; ++a)
+    for (int j = 0; j < IC_PW; ++j)
+      for (int av = 0; av < 16; ++av) {
+        unsigned wu = 0, w1 = 0;
+        for (int k = 0; k < 4; ++k) {
+          const int u = 4 * j + k - 15 - a;
+          if (u >= -umax[av] && u <= umax[av]) {
+            wu |= (unsigned)(u & 0xFF) << (8 * k);
+            w1 |= 1u << (8 * k);
+          }
+        }
+        t.w[a][j][av] = make_uint2(wu, w1);
+      }
+  return t;
+}
+
 int upload_pattern() {
   const PatternT t = make_pattern();
-  return cudaMemcpyToSymbol(d_pattern_t, &t, sizeof(t)) == cudaSuccess ? 0 : -1;
+  const IcTab ic = make_ic_tab();
+  return (cudaMemcpyToSymbol(d_pattern_t, &t, sizeof(t)) == cudaSuccess &&
+          cudaMemcpyToSymbol(d_ic_tab, &ic, sizeof(ic)) == cudaSuccess) ? 0 : -1;
 }
+
+// sum over the 4 bytes of a (unsigned) * b (signed) + c
+__device__ __forceinline__ int dp4a_us(unsigned a, unsigned b, int c) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)),
+               "l"(gmem_src)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
 struct KpSlot {
   int kx, ky, lvl, score;  // level coordinates (minBorder added, :865-866); lvl < 0: no keypoint in this slot
@@ -95,41 +138,93 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
   __syncthreads();
   if (slot[0].lvl < 0) return;  // output rows are dense: an empty first slot means an empty CTA
 
-  // ---- 1. IC_Angle moments (:77-104), one warp per keypoint: lane = column u of the radius-15 disc ----
-  {
-    const int u = lane - 15;
-    const int au = u < 0 ? -u : u;
-    const int vlim = lane < 31 ? c_umax[au] : -1;  // rows |v| <= vlim belong to column u
-#pragma unroll 1
-    for (int i = warp; i < DESC_KP; i += DESC_WARPS) {
-      const KpSlot k = slot[i];
-      if (k.lvl < 0) break;
+  // ---- 1. IC_Angle moments (:77-104), one warp per keypoint.  The 31 disc rows are staged in shared memory with
+  // coalesced word loads (3 rows per warp instruction), then lane = ROW v of the disc: 9 words x two DP4A against the
+  // weight table give sum(u * I) and sum(I) over the row's part of the disc; m01 = v * sum(I).  ~120 instructions
+  // per keypoint instead of ~230 for the byte-per-lane column walk. ----
+  constexpr int PW = 10;  // words per descriptor patch row (step 3): 37 bytes at any alignment fit 40
+  constexpr int PBUF = 37 * PW;
+  // two patch buffers per warp: the next keypoint's rows arrive by cp.async while this one is being worked on
+  __shared__ unsigned patch_all[DESC_WARPS][2][PBUF];
+  __shared__ uint2 ic_tab[4 * IC_PW * 16];
+  for (int i = tid; i < 4 * IC_PW * 16; i += DESC_WARPS * 32) ic_tab[i] = (&d_ic_tab.w[0][0][0])[i];
+  // rows ky-15 .. ky+15 of the un-blurred level from the aligned address at or below kx-15, 3 rows per instruction
+  auto stage_disc = [&](int i, unsigned* dst) {
+    const KpSlot k = slot[i];
+    const int prow = lane / IC_PW, pcol = lane - prow * IC_PW;  // lanes 0..26: (row within a group of 3, word)
+    if (k.lvl >= 0 && prow < 3) {
       const LevelGeom& L = g.lv[k.lvl];
       const int pitch = L.pitch;
-      // row pointer, bumped by the pitch (opaque to the compiler: otherwise it rebuilds pyr + offset for every row)
-      const uint8_t* p = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)((k.ky - 15) * pitch + k.kx + u);
-      asm volatile("" : "+l"(p));
-      const size_t pitch64 = (size_t)pitch;
-      int sum = 0, m01 = 0;
+      const uint8_t* base = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)(k.ky - 15 + prow) * pitch +
+                            ((k.kx - 15) & ~3) + 4 * pcol;
+      unsigned* d = dst + prow * IC_PW + pcol;
 #pragma unroll
-      for (int v = -15; v <= 15; ++v) {
-        const int av = v < 0 ? -v : v;
-        if (av <= vlim) {
-          const int val = __ldg(p);
-          sum += val;
-          m01 += v * val;
-        }
-        p += pitch64;
-        asm volatile("" : "+l"(p));  // keep the bump a 64-bit add (not p0 + v * pitch recomputed per row)
+      for (int r0 = 0; r0 < 33; r0 += 3) {
+        if (r0 + prow < 31) cp_async4(d, base);
+        base += 3 * pitch;
+        d += 3 * IC_PW;
       }
-      int m10 = u * sum;
+    }
+    cp_async_commit();
+  };
+  // rows ky-18 .. ky+18 of the blurred level from the aligned address at or below kx-18
+  auto stage_patch = [&](int i, unsigned* dst) {
+    const KpSlot k = slot[i];
+    const int prow = lane / PW, pcol = lane - prow * PW;  // lanes 0..29; lanes 30, 31 idle
+    if (k.lvl >= 0 && prow < 3) {
+      const LevelGeom& L = g.lv[k.lvl];
+      const int pitch = L.pitch;
+      const uint8_t* base = blur + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)(k.ky - 18 + prow) * pitch +
+                            ((k.kx - 18) & ~3) + 4 * pcol;
+      unsigned* d = dst + prow * PW + pcol;
+#pragma unroll
+      for (int r0 = 0; r0 < 39; r0 += 3) {
+        if (r0 + prow < 37) cp_async4(d, base);
+        base += 3 * pitch;
+        d += 3 * PW;
+      }
+    }
+    cp_async_commit();
+  };
+  stage_disc(warp, patch_all[warp][0]);
+  __syncthreads();  // ic_tab
+  {
+    const int v = lane - 15;
+    const int av = lane < 31 ? (v < 0 ? -v : v) : 15;
+    int buf = 0;
+#pragma unroll 1
+    for (int i = warp; i < DESC_KP; i += DESC_WARPS, buf ^= 1) {
+      const KpSlot k = slot[i];
+      if (k.lvl < 0) break;
+      if (i + DESC_WARPS < DESC_KP) stage_disc(i + DESC_WARPS, patch_all[warp][buf ^ 1]); else cp_async_commit();
+      cp_async_wait<1>();
+      __syncwarp();
+      const unsigned* disc = patch_all[warp][buf];
+      const int al = (k.kx - 15) & 3;
+      int m10 = 0, s1 = 0;
+      if (lane < 31) {
+        const uint2* wt = ic_tab + al * (IC_PW * 16) + av;
+#pragma unroll
+        for (int j = 0; j < IC_PW; ++j) {
+          const unsigned px = disc[lane * IC_PW + j];
+          const uint2 wgt = wt[j * 16];
+          m10 = dp4a_us(px, wgt.x, m10);
+          s1 = (int)__dp4a(px, wgt.y, (unsigned)s1);
+        }
+      }
+      int m01 = v * s1;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         m10 += __shfl_xor_sync(0xffffffffu, m10, o);
         m01 += __shfl_xor_sync(0xffffffffu, m01, o);
       }
       if (lane == 0) { slot[i].m01 = m01; slot[i].m10 = m10; }
+      __syncwarp();  // every lane has read this buffer before the keypoint after next lands in it
     }
+    cp_async_wait<0>();
+    __syncwarp();
+    // the first descriptor patch of this warp travels while the angles are computed (step 2)
+    stage_patch(warp, patch_all[warp][0]);
   }
   __syncthreads();
 
@@ -157,41 +252,26 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
   __syncthreads();
 
   // ---- 3. computeOrbDescriptor (:108-147) on the blurred level: lane -> descriptor byte (8 tests = 16 gathers).
-  // The 37 x 37 patch the rotated pattern can reach is first copied into shared memory with coalesced word loads
-  // (3 rows per warp instruction): a gather of 32 scattered bytes then costs ~3 bank-conflict wavefronts instead of
-  // ~20 L1 sectors — the gathers, not the arithmetic, bound this kernel.  The lane's 32 pattern values stay in
-  // registers for the warp's 4 keypoints. ----
-  constexpr int PW = 10;  // words per patch row: 37 bytes at any alignment fit 40 (3 rows = 30 lanes per load)
-  __shared__ unsigned patch_all[DESC_WARPS][37 * PW];
-  unsigned* patch = patch_all[warp];
-  const uint8_t* patch_b = reinterpret_cast<const uint8_t*>(patch);
+  // The 37 x 37 patch the rotated pattern can reach is first copied into shared memory with coalesced word copies
+  // (3 rows per warp instruction, cp.async, the next keypoint's patch in flight): a gather of 32 scattered bytes then
+  // costs ~3 bank-conflict wavefronts instead of ~20 L1 sectors.  The lane's 32 pattern values stay in registers for
+  // the warp's 4 keypoints. ----
   float pat[32];
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
     const float4 t = d_pattern_t.v[q][lane];
     pat[4 * q] = t.x; pat[4 * q + 1] = t.y; pat[4 * q + 2] = t.z; pat[4 * q + 3] = t.w;
   }
-  const int prow = lane / PW, pcol = lane - prow * PW;  // lanes 0..29: (row within a group of 3, word); lanes 30, 31 idle
+  int buf = 0;
 #pragma unroll 1
-  for (int i = warp; i < DESC_KP; i += DESC_WARPS) {
+  for (int i = warp; i < DESC_KP; i += DESC_WARPS, buf ^= 1) {
     const KpSlot k = slot[i];
     if (k.lvl < 0) break;
-    const LevelGeom& L = g.lv[k.lvl];
-    const int step = L.pitch;
-    // rows ky-18 .. ky+18, bytes from the aligned address at or below kx-18 (the keypoint is >= 19 px inside the level)
-    const int x_al = (k.kx - 18) & ~3;
-    const uint8_t* base = blur + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)(k.ky - 18) * step + x_al;
-    asm volatile("" : "+l"(base));
-    __syncwarp();  // the previous keypoint's gathers are done
-    if (prow < 3) {
-#pragma unroll
-      for (int r0 = 0; r0 < 39; r0 += 3) {
-        const int r = r0 + prow;
-        if (r < 37) patch[r * PW + pcol] = __ldg(reinterpret_cast<const unsigned*>(base + (size_t)r * step) + pcol);
-      }
-    }
+    if (i + DESC_WARPS < DESC_KP) stage_patch(i + DESC_WARPS, patch_all[warp][buf ^ 1]); else cp_async_commit();
+    cp_async_wait<1>();
     __syncwarp();
-    const int ctr = 18 * (PW * 4) + (k.kx - x_al);  // byte offset of the keypoint in the patch
+    const uint8_t* patch_b = reinterpret_cast<const uint8_t*>(patch_all[warp][buf]);
+    const int ctr = 18 * (PW * 4) + 18 + ((k.kx - 18) & 3);  // byte offset of the keypoint in the patch
     const float ca = k.ca, sb = k.sb;
     int val = 0;
 #pragma unroll
@@ -206,7 +286,9 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
       val |= (t0 < t1) << j;
     }
     out_desc[((size_t)b * g.out_cap + oi0 + i) * 32 + lane] = (uint8_t)val;
+    __syncwarp();  // every lane has read this buffer before the keypoint after next lands in it
   }
+  cp_async_wait<0>();
 }
 
 void launch_describe(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
