@@ -256,10 +256,10 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
   return build_fast_tensor_maps(g, a, e->max_batch);
 }
 
-// CUtensorMap of every level that has FAST strips: a (pitch, h, max_batch) byte tensor over the pyramid arena with a
-// kFastTileW x kFastTileH x 1 box (k_fast.cu).  cuTensorMapEncodeTiled is a driver entry point; it is fetched through
-// the runtime so that liborbfe.so does not link libcuda.
-int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
+// CUtensorMap of every level that has FAST strips (only those levels have keypoints): a (pitch, h, max_batch) byte
+// tensor over one of the level-major arenas with a box_w x box_h x 1 box.  cuTensorMapEncodeTiled is a driver entry
+// point; it is fetched through the runtime so that liborbfe.so does not link libcuda.
+static int build_level_maps(const PyrGeom& g, uint8_t* arena, int max_batch, int box_w, int box_h, void** out) {
   typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -277,10 +277,10 @@ int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
     if (L.fast_strips_x <= 0) continue;
     const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.h, (cuuint64_t)max_batch};
     const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.lvl_bytes};
-    const cuuint32_t box[3] = {(cuuint32_t)kFastTileW, (cuuint32_t)kFastTileH, 1u};
+    const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
     const cuuint32_t estr[3] = {1u, 1u, 1u};
     const CUresult r = reinterpret_cast<EncodeTiled>(fn)(
-        &maps[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, a.pyr + L.lvl_base, dims, strides, box, estr,
+        &maps[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, arena + L.lvl_base, dims, strides, box, estr,
         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -288,9 +288,15 @@ int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
       return ORBFE_ERR_CUDA;
     }
   }
-  ORBFE_CUDA(cudaMalloc(&a.fast_maps, sizeof(maps)));
-  ORBFE_CUDA(cudaMemcpy(a.fast_maps, maps, sizeof(maps), cudaMemcpyHostToDevice));
+  ORBFE_CUDA(cudaMalloc(out, sizeof(maps)));
+  ORBFE_CUDA(cudaMemcpy(*out, maps, sizeof(maps), cudaMemcpyHostToDevice));
   return ORBFE_OK;
+}
+
+int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
+  int rc = build_level_maps(g, a.pyr, max_batch, kFastTileW, kFastTileH, &a.fast_maps);       // k_fast.cu
+  if (rc == ORBFE_OK) rc = build_level_maps(g, a.blur, max_batch, kDescBoxW, kDescBoxH, &a.desc_maps);  // k_describe.cu
+  return rc;
 }
 
 static void free_arenas(Extractor* e) {
@@ -299,7 +305,7 @@ static void free_arenas(Extractor* e) {
   cudaFree(a.cand_count); cudaFree(a.cell_hi); cudaFree(a.kept); cudaFree(a.kept_count); cudaFree(a.out_kp); cudaFree(a.out_desc);
   cudaFree(a.out_count); cudaFree(a.flags); cudaFree(a.st_uright); cudaFree(a.st_depth); cudaFree(a.st_sad);
   cudaFree(a.st_count); cudaFree(a.st_band); cudaFree(a.st_bucket_start); cudaFree(a.st_bucket_items);
-  cudaFree(a.fast_maps);
+  cudaFree(a.fast_maps); cudaFree(a.desc_maps);
   if (e->h_flags) cudaFreeHost(e->h_flags);
   if (e->prof_ev) {
     for (int i = 0; i < Extractor::kProfRuns * 9; ++i) cudaEventDestroy(e->prof_ev[i]);

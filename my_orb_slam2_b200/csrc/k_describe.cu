@@ -11,6 +11,8 @@
 // rotated pattern reaches <= 18 px, so no access leaves the level image.
 // Float steps that decide bits (angle, sin/cos, the rotated sample coordinates) use the explicitly rounded
 // operations of include/orb_math_shared.h so that no FMA is formed.
+#include <cuda.h>
+
 #include "../../include/orb_math_shared.h"
 #include "kernels.h"
 
@@ -87,6 +89,36 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
+// ---- TMA: the blurred 37-row patch of a keypoint arrives as ONE cp.async.bulk.tensor box (kDescBoxW x kDescBoxH
+// bytes from the 16-byte aligned column at or below kx-18), completing on an mbarrier; it does not pass through the
+// LSU / L1, which bound this kernel when the patch came in as 13 four-byte cp.async per lane ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_load_box(void* dst, const void* tmap, int x, int y, int z, unsigned long long* bar,
+                                             int bytes) {
+  const unsigned b = smem_u32(bar);
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(b), "r"(bytes) : "memory");
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n" ::
+          "r"(smem_u32(dst)), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(b)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "DS_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DS_DONE;\n"
+      "bra DS_WAIT;\n"
+      "DS_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+
 struct KpSlot {
   int kx, ky, lvl, score;  // level coordinates (minBorder added, :865-866); lvl < 0: no keypoint in this slot
   int m01, m10;
@@ -101,7 +133,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
                                                                    orbfe_keypoint* __restrict__ out_kp,
                                                                    uint8_t* __restrict__ out_desc,
                                                                    int32_t* __restrict__ out_count,
-                                                                   int32_t* __restrict__ flags) {
+                                                                   int32_t* __restrict__ flags,
+                                                                   const CUtensorMap* __restrict__ blur_maps) {
   __shared__ KpSlot slot[DESC_KP];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
@@ -142,10 +175,19 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
   // coalesced word loads (3 rows per warp instruction), then lane = ROW v of the disc: 9 words x two DP4A against the
   // weight table give sum(u * I) and sum(I) over the row's part of the disc; m01 = v * sum(I).  ~120 instructions
   // per keypoint instead of ~230 for the byte-per-lane column walk. ----
-  constexpr int PW = 10;  // words per descriptor patch row (step 3): 37 bytes at any alignment fit 40
-  constexpr int PBUF = 37 * PW;
-  // two patch buffers per warp: the next keypoint's rows arrive by cp.async while this one is being worked on
-  __shared__ unsigned patch_all[DESC_WARPS][2][PBUF];
+  constexpr int PS = kDescBoxW;                                // bytes per descriptor patch row (step 3)
+  constexpr int PBUF = (kDescBoxW * kDescBoxH + 127) / 128 * 32;  // words per buffer, a multiple of 128 bytes
+  static_assert(PBUF >= 31 * IC_PW, "the disc rows of step 1 use the same buffers");
+  // two patch buffers per warp: the next keypoint's rows arrive (cp.async in step 1, TMA in step 3) while this one
+  // is being worked on
+  __shared__ __align__(128) unsigned patch_all[DESC_WARPS][2][PBUF];
+  __shared__ unsigned long long patch_bar[DESC_WARPS][2];
+  if (lane == 0) {
+    mbar_init(&patch_bar[warp][0]);
+    mbar_init(&patch_bar[warp][1]);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+  }
   __shared__ uint2 ic_tab[4 * IC_PW * 16];
   for (int i = tid; i < 4 * IC_PW * 16; i += DESC_WARPS * 32) ic_tab[i] = (&d_ic_tab.w[0][0][0])[i];
   // rows ky-15 .. ky+15 of the un-blurred level from the aligned address at or below kx-15, 3 rows per instruction
@@ -167,24 +209,12 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
     }
     cp_async_commit();
   };
-  // rows ky-18 .. ky+18 of the blurred level from the aligned address at or below kx-18
-  auto stage_patch = [&](int i, unsigned* dst) {
+  // rows ky-18 .. ky+18 of the blurred level from the 16-byte aligned column at or below kx-18: one TMA box
+  auto stage_patch = [&](int i, int buf) {
     const KpSlot k = slot[i];
-    const int prow = lane / PW, pcol = lane - prow * PW;  // lanes 0..29; lanes 30, 31 idle
-    if (k.lvl >= 0 && prow < 3) {
-      const LevelGeom& L = g.lv[k.lvl];
-      const int pitch = L.pitch;
-      const uint8_t* base = blur + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)(k.ky - 18 + prow) * pitch +
-                            ((k.kx - 18) & ~3) + 4 * pcol;
-      unsigned* d = dst + prow * PW + pcol;
-#pragma unroll
-      for (int r0 = 0; r0 < 39; r0 += 3) {
-        if (r0 + prow < 37) cp_async4(d, base);
-        base += 3 * pitch;
-        d += 3 * PW;
-      }
-    }
-    cp_async_commit();
+    if (lane == 0 && k.lvl >= 0)
+      tma_load_box(patch_all[warp][buf], blur_maps + k.lvl, (k.kx - 18) & ~15, k.ky - 18, b, &patch_bar[warp][buf],
+                   kDescBoxW * kDescBoxH);
   };
   stage_disc(warp, patch_all[warp][0]);
   __syncthreads();  // ic_tab
@@ -223,8 +253,10 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
     }
     cp_async_wait<0>();
     __syncwarp();
-    // the first descriptor patch of this warp travels while the angles are computed (step 2)
-    stage_patch(warp, patch_all[warp][0]);
+    // the first descriptor patch of this warp travels while the angles are computed (step 2); the buffer was last
+    // written through the generic proxy (cp.async), the TMA writes through the async proxy
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    stage_patch(warp, 0);
   }
   __syncthreads();
 
@@ -262,16 +294,15 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
     const float4 t = d_pattern_t.v[q][lane];
     pat[4 * q] = t.x; pat[4 * q + 1] = t.y; pat[4 * q + 2] = t.z; pat[4 * q + 3] = t.w;
   }
-  int buf = 0;
+  int buf = 0, n = 0;
 #pragma unroll 1
-  for (int i = warp; i < DESC_KP; i += DESC_WARPS, buf ^= 1) {
+  for (int i = warp; i < DESC_KP; i += DESC_WARPS, buf ^= 1, ++n) {
     const KpSlot k = slot[i];
     if (k.lvl < 0) break;
-    if (i + DESC_WARPS < DESC_KP) stage_patch(i + DESC_WARPS, patch_all[warp][buf ^ 1]); else cp_async_commit();
-    cp_async_wait<1>();
-    __syncwarp();
+    if (i + DESC_WARPS < DESC_KP) stage_patch(i + DESC_WARPS, buf ^ 1);
+    mbar_wait(&patch_bar[warp][buf], (unsigned)(n >> 1) & 1u);  // this buffer's (n / 2)-th load
     const uint8_t* patch_b = reinterpret_cast<const uint8_t*>(patch_all[warp][buf]);
-    const int ctr = 18 * (PW * 4) + 18 + ((k.kx - 18) & 3);  // byte offset of the keypoint in the patch
+    const int ctr = 18 * PS + 18 + ((k.kx - 18) & 15);  // byte offset of the keypoint in the patch
     const float ca = k.ca, sb = k.sb;
     int val = 0;
 #pragma unroll
@@ -281,20 +312,19 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
       const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
       const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
       const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-      const int t0 = patch_b[r0 * (PW * 4) + (c0 + ctr)];
-      const int t1 = patch_b[r1 * (PW * 4) + (c1 + ctr)];
+      const int t0 = patch_b[r0 * PS + (c0 + ctr)];
+      const int t1 = patch_b[r1 * PS + (c1 + ctr)];
       val |= (t0 < t1) << j;
     }
     out_desc[((size_t)b * g.out_cap + oi0 + i) * 32 + lane] = (uint8_t)val;
     __syncwarp();  // every lane has read this buffer before the keypoint after next lands in it
   }
-  cp_async_wait<0>();
 }
 
 void launch_describe(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
   dim3 grid((g.out_cap + DESC_KP - 1) / DESC_KP, batch);
   describe_kernel<<<grid, DESC_WARPS * 32, 0, s>>>(g, a.pyr, a.blur, a.kept, a.kept_count, a.out_kp, a.out_desc,
-                                                   a.out_count, a.flags);
+                                                   a.out_count, a.flags, static_cast<const CUtensorMap*>(a.desc_maps));
 }
 
 }  // namespace orbfe

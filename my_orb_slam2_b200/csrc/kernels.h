@@ -36,11 +36,14 @@ struct ExtractorArena {
   // TMA descriptors (CUtensorMap, 128 B each) of the pyramid levels as (x, y, image) byte tensors with a
   // kFastTileW x kFastTileH box: the FAST kernel stages a strip's image tile with ONE cp.async.bulk.tensor
   void* fast_maps = nullptr;  // [kMaxLevels]
+  void* desc_maps = nullptr;  // [kMaxLevels] the BLURRED levels with a kDescBoxW x kDescBoxH box (k_describe.cu)
 };
 
 constexpr int kFastTileW = 144;                    // bytes per tile row (multiple of 16): 136 used + 8 of start alignment
 constexpr int kFastTileH = kFastOwnRows + 2 + 6;   // computed rows + the FAST ring (+-3)
-// one-time host setup of ExtractorArena::fast_maps (extractor.cu; needs the driver's cuTensorMapEncodeTiled)
+constexpr int kDescBoxW = 64;   // bytes: the 37 columns a rotated pattern reaches, from the 16-byte aligned column below
+constexpr int kDescBoxH = 37;   // rows ky-18 .. ky+18
+// one-time host setup of ExtractorArena::fast_maps / desc_maps (extractor.cu; needs the driver's cuTensorMapEncodeTiled)
 int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch);
 
 enum : int { FLAG_CAND_OVERFLOW = 1, FLAG_NODE_OVERFLOW = 2, FLAG_OUT_OVERFLOW = 4 };
