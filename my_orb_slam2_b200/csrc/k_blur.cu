@@ -25,6 +25,17 @@ __device__ __forceinline__ int reflect101i(int p, int len) {
   return p;
 }
 
+// vertical pass of one pixel: sum k*h + 32768 (the rounding term rides in the multiply-add chain).  The ALU pipe
+// (adds, shifts, permutes) is the busier one in this kernel, so only the pair sums are adds; everything else is IMAD.
+__device__ __forceinline__ unsigned vsum(unsigned a0, unsigned a1, unsigned a2, unsigned a3, unsigned a4, unsigned a5,
+                                         unsigned a6) {
+  return 18u * (a0 + a6) + (34u * (a1 + a5) + (48u * (a2 + a4) + (56u * a3 + 32768u)));
+}
+// dst = v >> 16 for four pixels: v < 2^24, so the result is byte 2 of v; three byte permutes pack the four
+__device__ __forceinline__ unsigned pack_round(const unsigned (&v)[4]) {
+  return __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+}
+
 template <int BL_ROWS>
 __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid_constant__ PyrGeom g,
                                                                     const uint8_t* __restrict__ pyr,
@@ -101,13 +112,11 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
 #pragma unroll
       for (int j = 0; j < 4; ++j) win[6][j] = hs[j];
       if (r >= 6) {
-        unsigned out = 0;
+        unsigned v[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const unsigned v = 18u * (win[0][j] + win[6][j]) + 34u * (win[1][j] + win[5][j]) +
-                             48u * (win[2][j] + win[4][j]) + 56u * win[3][j];
-          out |= ((v + 32768u) >> 16) << (8 * j);
-        }
+        for (int j = 0; j < 4; ++j)
+          v[j] = vsum(win[0][j], win[1][j], win[2][j], win[3][j], win[4][j], win[5][j], win[6][j]);
+        const unsigned out = pack_round(v);
         *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * pitch + x4) = out;
       }
     }
@@ -148,13 +157,12 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
       hs[2] = __dp4a(__funnelshift_r(w0, w1, 24), K_LO, __dp4a(__funnelshift_r(w1, w2, 24), K_HI, 0u));
       hs[3] = __dp4a(w1, K_LO, __dp4a(w2, K_HI, 0u));
       if (r >= 6) {
-        unsigned out = 0;
+        unsigned v[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const unsigned v = 18u * (win[(r + 1) % 7][j] + win[r % 7][j]) + 34u * (win[(r + 2) % 7][j] + win[(r + 6) % 7][j]) +
-                             48u * (win[(r + 3) % 7][j] + win[(r + 5) % 7][j]) + 56u * win[(r + 4) % 7][j];
-          out |= ((v + 32768u) >> 16) << (8 * j);
-        }
+        for (int j = 0; j < 4; ++j)
+          v[j] = vsum(win[(r + 1) % 7][j], win[(r + 2) % 7][j], win[(r + 3) % 7][j], win[(r + 4) % 7][j],
+                      win[(r + 5) % 7][j], win[(r + 6) % 7][j], win[r % 7][j]);
+        const unsigned out = pack_round(v);
         *reinterpret_cast<unsigned*>(wp) = out;
         wp += pitch;
       }
@@ -195,13 +203,11 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
 #pragma unroll
       for (int j = 0; j < 4; ++j) win[6][j] = hs[j];
       if (r >= 6) {
-        unsigned out = 0;
+        unsigned v[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const unsigned v = 18u * (win[0][j] + win[6][j]) + 34u * (win[1][j] + win[5][j]) +
-                             48u * (win[2][j] + win[4][j]) + 56u * win[3][j];
-          out |= ((v + 32768u) >> 16) << (8 * j);
-        }
+        for (int j = 0; j < 4; ++j)
+          v[j] = vsum(win[0][j], win[1][j], win[2][j], win[3][j], win[4][j], win[5][j], win[6][j]);
+        const unsigned out = pack_round(v);
         *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * pitch + x4) = out;
       }
       q[0] = nq[0]; q[1] = nq[1]; q[2] = nq[2];
