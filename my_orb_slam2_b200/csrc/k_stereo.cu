@@ -90,6 +90,7 @@ __global__ void __launch_bounds__(512) stereo_bucket_kernel(const __grid_constan
   }
 }
 
+// 8 CTAs (32 warps) per SM: measured best (10 / 12 / 16 spill the SAD accumulators, 5 / 6 lose latency hiding)
 __global__ void __launch_bounds__(ST_WARPS * 32, 8) stereo_match_kernel(
     const __grid_constant__ PyrGeom g, const uint8_t* __restrict__ pyrL, const uint8_t* __restrict__ pyrR,
     const orbfe_keypoint* __restrict__ kpL, const uint8_t* __restrict__ descL, const int32_t* __restrict__ cntL,
@@ -181,10 +182,19 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 8) stereo_match_kernel(
     if (ok) {
       const uint8_t* imL = pyrL + LV.lvl_base + (size_t)b * LV.lvl_bytes;
       const uint8_t* imR = pyrR + LV.lvl_base + (size_t)b * LV.lvl_bytes;
+      // the 11 left and 11 right window rows are 22 different cache lines, mostly L2 / DRAM misses: request them all
+      // at once (the loop below walks them three rows per iteration and would otherwise take the misses in turn)
+      if (lane < 22) {
+        const uint8_t* row = lane < 11 ? imL + (size_t)(cvL - w + lane) * LV.pitch + cuL - w
+                                       : imR + (size_t)(cvL - w + lane - 11) * LV.pitch + cuR - w - Lh;
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(row));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 20));
+      }
       const int centerL = __ldg(imL + (size_t)cvL * LV.pitch + cuL);
       int sad[11];
 #pragma unroll
       for (int s = 0; s < 11; ++s) sad[s] = 0;
+#pragma unroll  // 4 rounds: all their loads are issued before the first round's arithmetic
       for (int p = lane; p < 121; p += 32) {
         const int dy = p / 11 - w, dx = p - (p / 11) * 11 - w;
         const int lv = (int)__ldg(imL + (size_t)(cvL + dy) * LV.pitch + cuL + dx) - centerL;
