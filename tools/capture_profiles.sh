@@ -12,7 +12,8 @@ $CMD > $OUT/plain_$TAG.log 2>&1 || { echo "bench failed without ncu"; tail -5 $O
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_bench_launches.csv $CMD > $OUT/ncu_bench.log 2>&1
 python tools/one_step.py 64 1 > $OUT/plain_step_$TAG.log 2>&1 || { echo "one_step failed without ncu"; exit 1; }
 for K in pyramid_level fast_detect quadtree blur_levels describe stereo_match; do
-  ncu --set full --clock-control none --import-source on -k regex:${K} -c 1 -f -o $OUT/prof_${K}_${TAG}f \
+  C=1; [ $K = fast_detect ] && C=2   # FAST is two launches per extraction (iniTh, then minTh where a cell stayed empty)
+  ncu --set full --clock-control none --import-source on -k regex:${K} -c $C -f -o $OUT/prof_${K}_${TAG}f \
       python tools/one_step.py 64 1 > $OUT/ncu_${K}.log 2>&1
   echo "$K rc=$?"
 done

@@ -44,25 +44,36 @@ lines = []
 for rep in sorted(glob.glob(os.path.join(G, "prof_*_%sf.ncu-rep" % tag))):
     out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
-    hdr, units, r = rows[0], rows[1], rows[2]
-    name = r[hdr.index("Kernel Name")].split("(")[0]
-    def val(k):
-        if k not in hdr: return float("nan")
-        v = float(r[hdr.index(k)].replace(",", "")); u = units[hdr.index(k)]
-        scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0, "ns": 1e-3, "us": 1.0, "ms": 1e3}.get(u, 1.0)
-        return v * scale
-    v = {k: val(k) for k in want}
-    traffic[name] = {"dram_bytes_per_launch": v["dram__bytes_read.sum"] + v["dram__bytes_write.sum"], "images": 64,
-                     "time_us": v["gpu__time_duration.sum"], "warp_inst_per_launch": v["smsp__inst_executed.sum"],
-                     "issue_slots_busy_pct": v["smsp__issue_active.avg.pct_of_peak_sustained_active"]}
-    lines.append("| %s | %.1f | %.1f | %.1f | %.1f | %.1f / %.1f / %.1f / %.1f | %.1f / %.1f / %.1f | %.1f + %.1f | %d x %d | %d |" % (
-        name, v[want[0]], v[want[1]], v[want[2]], v[want[3]] / 1e6, v[want[4]], v[want[5]], v[want[6]], v[want[7]], v[want[8]],
-        v[want[9]], v[want[10]], v[want[11]] / 1e6, v[want[12]] / 1e6, v[want[13]], v[want[14]], v[want[15]]))
+    hdr, units = rows[0], rows[1]
+    krows = [r for r in rows[2:] if len(r) == len(hdr)]  # one row per captured launch (FAST: its two launches)
+    first = True
+    tot = {"dram": 0.0, "time": 0.0, "winst": 0.0}
+    for r in krows:
+        name = r[hdr.index("Kernel Name")].split("(")[0]
+        def val(k):
+            if k not in hdr: return float("nan")
+            v = float(r[hdr.index(k)].replace(",", "")); u = units[hdr.index(k)]
+            scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0, "ns": 1e-3, "us": 1.0, "ms": 1e3}.get(u, 1.0)
+            return v * scale
+        v = {k: val(k) for k in want}
+        tot["dram"] += v["dram__bytes_read.sum"] + v["dram__bytes_write.sum"]
+        tot["time"] += v["gpu__time_duration.sum"]
+        tot["winst"] += v["smsp__inst_executed.sum"]
+        if first:
+            busy = v["smsp__issue_active.avg.pct_of_peak_sustained_active"]
+            first = False
+        label = name if len(krows) == 1 else "%s (launch %d of %d)" % (name, krows.index(r) + 1, len(krows))
+        lines.append("| %s | %.1f | %.1f | %.1f | %.1f | %.1f / %.1f / %.1f / %.1f | %.1f / %.1f / %.1f | %.1f + %.1f | %d x %d | %d |" % (
+            label, v[want[0]], v[want[1]], v[want[2]], v[want[3]] / 1e6, v[want[4]], v[want[5]], v[want[6]], v[want[7]], v[want[8]],
+            v[want[9]], v[want[10]], v[want[11]] / 1e6, v[want[12]] / 1e6, v[want[13]], v[want[14]], v[want[15]]))
+    # per STAGE: the sum over the stage's captured launches (bench.py divides by the stage's live time)
+    traffic[name] = {"dram_bytes_per_launch": tot["dram"], "images": 64, "time_us": tot["time"],
+                     "warp_inst_per_launch": tot["winst"], "issue_slots_busy_pct": busy, "launches_captured": len(krows)}
 if lines:
     with open(os.path.join(P, "%s_kernels_full.md" % tag), "w") as f:
         f.write("# %s — `ncu --set full --clock-control none --import-source on` of each kernel, one launch over 64 KITTI images\n\n" % tag)
         f.write("Command per kernel: `ncu --set full ... -k regex:<kernel> -c 1 python tools/one_step.py 64 1` (the first launch of the "
-                "kernel in one device-resident bench step; the .ncu-rep files stay in gpurun_out/, scratch).\n\n")
+                "kernel in one device-resident bench step, both launches for FAST; the .ncu-rep files stay in gpurun_out/, scratch).\n\n")
         f.write("| kernel | time us | issue slots busy % | warps active % | warp-inst M | pipe ALU / FMA / LSU / XU % | L1 / L2 / DRAM % of peak | DRAM read + write MB | grid x block | regs |\n")
         f.write("|---|---|---|---|---|---|---|---|---|---|\n")
         f.write("\n".join(lines) + "\n")
