@@ -570,14 +570,12 @@ def run_gpu(args):
         for i in range(args.latency_frames + 10):
             j = i % B
             t1 = time.perf_counter()
-            L1.upload(h_left[j].data_ptr(), 1)
-            R1.upload(h_right[j].data_ptr(), 1)
-            L1.run(1)
-            R1.run(1)
-            orbfe.check(lib.orbfe_stereo_match_run(L1._h, R1._h, 1, MBF, MB))
-            orbfe.check(lib.orbfe_extract_download(R1._h, 1, kpR.data_ptr(), dsR.data_ptr(), cap, cntR.data_ptr()))
-            orbfe.check(lib.orbfe_extract_download(L1._h, 1, kpL.data_ptr(), dsL.data_ptr(), cap, cntL.data_ptr()))
-            orbfe.check(lib.orbfe_stereo_match_download(L1._h, 1, ur.data_ptr(), dp.data_ptr(), cap, nm.data_ptr()))
+            # the stereo Frame constructor as one C-ABI call: uploads, both extractions (two streams), the stereo
+            # matcher, the three result downloads queued behind them, one wait per stream
+            orbfe.check(lib.orbfe_stereo_frame(L1._h, R1._h, h_left[j].data_ptr(), h_right[j].data_ptr(), W * H, W, 1,
+                                               MBF, MB, kpL.data_ptr(), dsL.data_ptr(), cntL.data_ptr(),
+                                               kpR.data_ptr(), dsR.data_ptr(), cntR.data_ptr(), ur.data_ptr(),
+                                               dp.data_ptr(), nm.data_ptr(), cap))
             if i >= 10:
                 lat.append(1e3 * (time.perf_counter() - t1))
         L1.close()

@@ -157,6 +157,17 @@ int orbfe_stereo_match_download(orbfe_extractor* left, int batch, float* u_right
 /* ... without waiting (complete after orbfe_extractor_sync / orbfe_extract_finish on `left`). */
 int orbfe_stereo_match_download_async(orbfe_extractor* left, int batch, float* u_right, float* depth, int capacity,
                                       int32_t* n_matched);
+/* The stereo Frame constructor in one call (src/Frame.cc:61-116: the two ORBextractor threads :89-92, the join,
+ * ComputeStereoMatches :108): host images in, keypoints / descriptors of both images and mvuRight / mvDepth out.
+ * The two extractions run on the handles' own streams, the matcher after both, and the three result downloads are
+ * queued behind them without intermediate host synchronisation; returns when everything is on the host.
+ * Arrays hold `capacity` entries per image (>= orbfe_extractor_info::capacity); `batch` pairs, images
+ * `image_stride` bytes apart (0 = densely packed), rows `row_stride` bytes apart. */
+int orbfe_stereo_frame(orbfe_extractor* left, orbfe_extractor* right, const uint8_t* left_images,
+                       const uint8_t* right_images, size_t image_stride, int row_stride, int batch, float mbf, float mb,
+                       orbfe_keypoint* kp_left, uint8_t* desc_left, int32_t* n_left, orbfe_keypoint* kp_right,
+                       uint8_t* desc_right, int32_t* n_right, float* u_right, float* depth, int32_t* n_matched,
+                       int capacity);
 
 /* ------------------------------------------------------------------ */
 /* ORBmatcher  (include/ORBmatcher.h:45-114, src/ORBmatcher.cc)        */

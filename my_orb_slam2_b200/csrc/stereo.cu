@@ -84,6 +84,26 @@ int orbfe_stereo_match_download(orbfe_extractor* hl, int batch, float* u_right, 
   return ORBFE_OK;
 }
 
+int orbfe_stereo_frame(orbfe_extractor* hl, orbfe_extractor* hr, const uint8_t* left_images,
+                       const uint8_t* right_images, size_t image_stride, int row_stride, int batch, float mbf, float mb,
+                       orbfe_keypoint* kp_left, uint8_t* desc_left, int32_t* n_left, orbfe_keypoint* kp_right,
+                       uint8_t* desc_right, int32_t* n_right, float* u_right, float* depth, int32_t* n_matched,
+                       int capacity) {
+  ORBFE_ARG(hl && hr && hl != hr && left_images && right_images && n_left && n_right);
+  int rc = orbfe_extract_upload(hl, left_images, image_stride, row_stride, batch, 0);
+  if (rc == ORBFE_OK) rc = orbfe_extract_upload(hr, right_images, image_stride, row_stride, batch, 0);
+  if (rc == ORBFE_OK) rc = orbfe_extract_run(hl, batch);
+  if (rc == ORBFE_OK) rc = orbfe_extract_run(hr, batch);
+  if (rc == ORBFE_OK) rc = orbfe_stereo_match_run(hl, hr, batch, mbf, mb);
+  // right results leave while the matcher runs on left's stream; left results and the matches follow it
+  if (rc == ORBFE_OK) rc = orbfe_extract_download_async(hr, batch, kp_right, desc_right, capacity, n_right);
+  if (rc == ORBFE_OK) rc = orbfe_extract_download_async(hl, batch, kp_left, desc_left, capacity, n_left);
+  if (rc == ORBFE_OK) rc = orbfe_stereo_match_download_async(hl, batch, u_right, depth, capacity, n_matched);
+  const int rr = orbfe_extract_finish(hr), rl = orbfe_extract_finish(hl);  // always drain both streams
+  if (rc != ORBFE_OK) return rc;
+  return rr != ORBFE_OK ? rr : rl;
+}
+
 int orbfe_stereo_match(orbfe_extractor* hl, orbfe_extractor* hr, int batch, float mbf, float mb, float* u_right,
                        float* depth, int capacity, int32_t* n_matched) {
   int rc = orbfe_stereo_match_run(hl, hr, batch, mbf, mb);

@@ -118,6 +118,7 @@ SYMBOLS = {
     "orbfe_extractor_debug_candidates": (_I, [_P, _I, _I, _I, _P, _P, _P, _P]),
     "orbfe_extractor_debug_level_keypoints": (_I, [_P, _I, _I, _I, _P, _P, _P, _P]),
     "orbfe_stereo_match": (_I, [_P, _P, _I, _F, _F, _P, _P, _I, _P]),
+    "orbfe_stereo_frame": (_I, [_P, _P, _P, _P, C.c_size_t, _I, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I]),
     "orbfe_stereo_match_run": (_I, [_P, _P, _I, _F, _F]),
     "orbfe_stereo_match_download": (_I, [_P, _I, _P, _P, _I, _P]),
     "orbfe_matcher_create": (_I, [_I, C.POINTER(_P)]),
@@ -327,6 +328,27 @@ def stereo_match(left, right, batch, mbf, mb):
     n = np.zeros(batch, np.int32)
     check(lib().orbfe_stereo_match(left._h, right._h, batch, mbf, mb, _p(ur), _p(dp), left.capacity, _p(n)))
     return ur, dp, n
+
+
+def stereo_frame(left, right, left_images, right_images, mbf, mb):
+    """The stereo Frame constructor in one C-ABI call (orbfe_stereo_frame): (B, H, W) u8 host images of both cameras
+    -> (kpL, descL, nL, kpR, descR, nR, uRight, depth, n_matched), arrays with `capacity` rows per image."""
+    li = np.ascontiguousarray(left_images, np.uint8)
+    ri = np.ascontiguousarray(right_images, np.uint8)
+    if li.ndim == 2:
+        li, ri = li[None], ri[None]
+    b, h, w = li.shape
+    cap = left.capacity
+    kl = np.zeros((b, cap), KEYPOINT_DTYPE)
+    kr = np.zeros((b, cap), KEYPOINT_DTYPE)
+    dl = np.zeros((b, cap, 32), np.uint8)
+    dr = np.zeros((b, cap, 32), np.uint8)
+    nl, nr, nm = np.zeros(b, np.int32), np.zeros(b, np.int32), np.zeros(b, np.int32)
+    ur = np.empty((b, cap), np.float32)
+    dp = np.empty((b, cap), np.float32)
+    check(lib().orbfe_stereo_frame(left._h, right._h, _p(li), _p(ri), h * w, w, b, mbf, mb, _p(kl), _p(dl), _p(nl),
+                                   _p(kr), _p(dr), _p(nr), _p(ur), _p(dp), _p(nm), cap))
+    return kl, dl, nl, kr, dr, nr, ur, dp, nm
 
 
 class Matcher:

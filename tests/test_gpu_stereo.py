@@ -51,3 +51,29 @@ def test_stereo_batch_and_no_match_cases(oracle):
         assert np.array_equal(ur[b][:nl[b]], our), "image %d" % b
         assert np.array_equal(dp[b][:nl[b]], odp), "image %d" % b
         assert nm[b] == on
+
+
+def test_stereo_frame_one_call(oracle):
+    """orbfe_stereo_frame (the stereo Frame constructor, src/Frame.cc:61-116, in one C-ABI call) against the oracle,
+    batch of 2, called twice on the same handles (the second call reuses the captured graphs)."""
+    from my_orb_slam2_b200 import orbfe
+    w, h = synth.SHAPES["kitti"]
+    s = synth.SETTINGS["kitti"]
+    params = (s["nfeatures"], s["scale_factor"], s["nlevels"], s["ini_th"], s["min_th"])
+    pairs = [synth.synth_pair(w, h, 70 + i) for i in range(2)]
+    lefts, rights = np.stack([p[0] for p in pairs]), np.stack([p[1] for p in pairs])
+    L = orbfe.Extractor(*params, w, h, max_batch=2)
+    R = orbfe.Extractor(*params, w, h, max_batch=2)
+    mbf, mb = np.float32(s["bf"]), np.float32(s["bf"]) / np.float32(s["fx"])
+    oL, oR = oracle.Extractor(*params), oracle.Extractor(*params)
+    for _ in range(2):
+        kl, dl, nl, kr, dr, nr, ur, dp, nm = orbfe.stereo_frame(L, R, lefts, rights, mbf, mb)
+        for b in range(2):
+            okl, odl = oL.extract(lefts[b])
+            okr, odr = oR.extract(rights[b])
+            our, odp, on = oracle.stereo_matches(oL, oR, okl, odl, okr, odr, mbf, mb)
+            assert nl[b] == len(okl) and nr[b] == len(okr)
+            assert np.array_equal(kl[b][:nl[b]], okl) and np.array_equal(dl[b][:nl[b]], odl)
+            assert np.array_equal(kr[b][:nr[b]], okr) and np.array_equal(dr[b][:nr[b]], odr)
+            assert np.array_equal(ur[b][:nl[b]], our) and np.array_equal(dp[b][:nl[b]], odp)
+            assert nm[b] == on and on > 50
