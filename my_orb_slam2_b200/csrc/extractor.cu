@@ -233,14 +233,30 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
   ORBFE_CUDA(dalloc(&a.cell_hi, B * (size_t)std::max(g.total_cells, 1)));
   ORBFE_CUDA(dalloc(&a.kept, B * g.kept_total));
   ORBFE_CUDA(dalloc(&a.kept_count, B * kMaxLevels));
-  ORBFE_CUDA(dalloc(&a.out_kp, B * g.out_cap));
-  ORBFE_CUDA(dalloc(&a.out_desc, B * g.out_cap * 32));
-  ORBFE_CUDA(dalloc(&a.out_count, B));
-  ORBFE_CUDA(dalloc(&a.flags, B));
-  ORBFE_CUDA(dalloc(&a.st_uright, B * g.out_cap));
-  ORBFE_CUDA(dalloc(&a.st_depth, B * g.out_cap));
+  {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off = align_up(off + bytes, 256); return o; };
+    take(B * g.out_cap * sizeof(orbfe_keypoint));
+    e->off_desc = take(B * g.out_cap * 32);
+    e->off_count = take(B * sizeof(int32_t));
+    e->off_flags = take(B * sizeof(int32_t));
+    e->result_bytes_extract = off;
+    e->off_uright = take(B * g.out_cap * sizeof(float));
+    e->off_depth = take(B * g.out_cap * sizeof(float));
+    e->off_stcount = take(B * sizeof(int32_t));
+    e->result_bytes = off;
+    ORBFE_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->result_block), e->result_bytes));
+    a.out_kp = reinterpret_cast<orbfe_keypoint*>(e->result_block);
+    a.out_desc = e->result_block + e->off_desc;
+    a.out_count = reinterpret_cast<int32_t*>(e->result_block + e->off_count);
+    a.flags = reinterpret_cast<int32_t*>(e->result_block + e->off_flags);
+    a.st_uright = reinterpret_cast<float*>(e->result_block + e->off_uright);
+    a.st_depth = reinterpret_cast<float*>(e->result_block + e->off_depth);
+    a.st_count = reinterpret_cast<int32_t*>(e->result_block + e->off_stcount);
+    if (e->result_bytes <= (1u << 20))  // small batches (single frames): one D2H copy + a host-side scatter
+      ORBFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&e->h_result), e->result_bytes, cudaHostAllocDefault));
+  }
   ORBFE_CUDA(dalloc(&a.st_sad, B * g.out_cap));
-  ORBFE_CUDA(dalloc(&a.st_count, B));
   a.st_items_per_kp = stereo_items_per_kp(g);
   ORBFE_CUDA(dalloc(&a.st_band, B * g.out_cap));
   ORBFE_CUDA(dalloc(&a.st_bucket_start, B * ((size_t)(g.lv[0].h + 7) / 8 + 2)));
@@ -302,9 +318,9 @@ int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
 static void free_arenas(Extractor* e) {
   ExtractorArena& a = e->arena;
   cudaFree(a.pyr); cudaFree(a.blur); cudaFree(a.stage); cudaFree(a.xtab); cudaFree(a.ytab); cudaFree(a.cand); cudaFree(a.node_of);
-  cudaFree(a.cand_count); cudaFree(a.cell_hi); cudaFree(a.kept); cudaFree(a.kept_count); cudaFree(a.out_kp); cudaFree(a.out_desc);
-  cudaFree(a.out_count); cudaFree(a.flags); cudaFree(a.st_uright); cudaFree(a.st_depth); cudaFree(a.st_sad);
-  cudaFree(a.st_count); cudaFree(a.st_band); cudaFree(a.st_bucket_start); cudaFree(a.st_bucket_items);
+  cudaFree(a.cand_count); cudaFree(a.cell_hi); cudaFree(a.kept); cudaFree(a.kept_count); cudaFree(e->result_block);
+  if (e->h_result) cudaFreeHost(e->h_result);
+  cudaFree(a.st_sad); cudaFree(a.st_band); cudaFree(a.st_bucket_start); cudaFree(a.st_bucket_items);
   cudaFree(a.fast_maps); cudaFree(a.desc_maps);
   if (e->h_flags) cudaFreeHost(e->h_flags);
   if (e->prof_ev) {

@@ -38,6 +38,13 @@ struct Extractor {
   // host side of an orbfe_extract_download_async not yet finished (counts are checked by orbfe_extract_finish)
   const int32_t* pending_counts = nullptr;
   int pending_batch = 0, pending_capacity = 0;
+  // the results of a handle live in ONE device block [keypoints | descriptors | counts | flags | uRight | depth |
+  // stereo count] (the arena pointers point into it), so that a small batch can leave with a single D2H copy into
+  // h_result (pinned; only allocated when the block is small) and be scattered to the caller's arrays on the host
+  uint8_t* result_block = nullptr;
+  uint8_t* h_result = nullptr;
+  size_t off_desc = 0, off_count = 0, off_flags = 0, off_uright = 0, off_depth = 0, off_stcount = 0;
+  size_t result_bytes = 0, result_bytes_extract = 0;  // whole block / the prefix without the stereo arrays
   // input side (k_input.cu): raw-frame staging and the rectification maps of orbfe_extractor_set_rectify_maps
   uint8_t* d_raw = nullptr;
   size_t raw_cap = 0;

@@ -1,6 +1,8 @@
 // stereo.cu — host side of orbfe_stereo_match*: Frame::ComputeStereoMatches
 // (reference: src/Frame.cc:496-686) on the device-resident results of two extractor
 // handles.  The kernels are in k_stereo.cu.
+#include <cstring>
+
 #include "common.cuh"
 #include "extractor.h"
 #include "kernels.h"
@@ -95,6 +97,41 @@ int orbfe_stereo_frame(orbfe_extractor* hl, orbfe_extractor* hr, const uint8_t* 
   if (rc == ORBFE_OK) rc = orbfe_extract_run(hl, batch);
   if (rc == ORBFE_OK) rc = orbfe_extract_run(hr, batch);
   if (rc == ORBFE_OK) rc = orbfe_stereo_match_run(hl, hr, batch, mbf, mb);
+  Extractor* l = reinterpret_cast<Extractor*>(hl);
+  Extractor* r = reinterpret_cast<Extractor*>(hr);
+  if (rc == ORBFE_OK && batch == l->max_batch && batch == r->max_batch && l->h_result && r->h_result) {
+    // single frames / small batches: each handle's results are one device block (extractor.h), so they leave with
+    // ONE copy per handle (11 separate copies otherwise, ~4 us of latency each) and are scattered on the host
+    DeviceGuard guard(l->device);
+    ORBFE_CUDA(cudaMemcpyAsync(r->h_result, r->result_block, r->result_bytes_extract, cudaMemcpyDeviceToHost, r->stream));
+    ORBFE_CUDA(cudaMemcpyAsync(l->h_result, l->result_block, l->result_bytes, cudaMemcpyDeviceToHost, l->stream));
+    ORBFE_CUDA(cudaStreamSynchronize(r->stream));
+    ORBFE_CUDA(cudaStreamSynchronize(l->stream));
+    const int cap = l->geom.out_cap;
+    auto scatter = [&](const Extractor* e, orbfe_keypoint* kp, uint8_t* desc, int32_t* n_out) -> int {
+      const int32_t* cnt = reinterpret_cast<const int32_t*>(e->h_result + e->off_count);
+      const int32_t* flg = reinterpret_cast<const int32_t*>(e->h_result + e->off_flags);
+      for (int b = 0; b < batch; ++b) {
+        if (flg[b]) { set_error("image %d: internal slab overflow (flags=%d)", b, flg[b]); return ORBFE_ERR_CAPACITY; }
+        if (cnt[b] > capacity) { set_error("image %d: %d keypoints > capacity %d", b, cnt[b], capacity); return ORBFE_ERR_CAPACITY; }
+        n_out[b] = cnt[b];
+        if (kp) memcpy(kp + (size_t)b * capacity, e->h_result + (size_t)b * cap * sizeof(orbfe_keypoint),
+                       (size_t)cnt[b] * sizeof(orbfe_keypoint));
+        if (desc) memcpy(desc + (size_t)b * capacity * 32, e->h_result + e->off_desc + (size_t)b * cap * 32, (size_t)cnt[b] * 32);
+      }
+      return ORBFE_OK;
+    };
+    rc = scatter(r, kp_right, desc_right, n_right);
+    if (rc == ORBFE_OK) rc = scatter(l, kp_left, desc_left, n_left);
+    if (rc != ORBFE_OK) return rc;
+    for (int b = 0; b < batch; ++b) {
+      const size_t n = (size_t)n_left[b];
+      if (u_right) memcpy(u_right + (size_t)b * capacity, l->h_result + l->off_uright + (size_t)b * cap * 4, n * 4);
+      if (depth) memcpy(depth + (size_t)b * capacity, l->h_result + l->off_depth + (size_t)b * cap * 4, n * 4);
+      if (n_matched) n_matched[b] = reinterpret_cast<const int32_t*>(l->h_result + l->off_stcount)[b];
+    }
+    return ORBFE_OK;
+  }
   // right results leave while the matcher runs on left's stream; left results and the matches follow it
   if (rc == ORBFE_OK) rc = orbfe_extract_download_async(hr, batch, kp_right, desc_right, capacity, n_right);
   if (rc == ORBFE_OK) rc = orbfe_extract_download_async(hl, batch, kp_left, desc_left, capacity, n_left);
