@@ -135,3 +135,21 @@ def test_angle_tolerance_report(fe, oracle):
     n_angle = int((kp["angle"] != okp["angle"]).sum())
     print("angle differences: %d, descriptor bit flips: %d" % (n_angle, flips))
     assert n_angle == 0 and flips == 0
+
+
+@pytest.mark.parametrize("w,h,params", [
+    (256, 128, (300, 1.2, 6, 20, 7)),     # width a multiple of 128: pitch == width, TMA boxes / edge words reach the pitch
+    (384, 256, (600, 1.2, 8, 20, 7)),     # ... on every second level too
+    (131, 97, (200, 1.2, 4, 20, 7)),      # tiny, odd sizes: one or two FAST strips, levels without cells
+    (1000, 333, (1500, 1.2, 8, 25, 5)),   # width % 4 == 0 but not % 16: strips start 8 bytes off a TMA-aligned column
+    (1283, 721, (2500, 1.2, 8, 20, 7)),   # wider than any config, width % 4 == 3 (two partial right-edge words in the blur)
+    (641, 479, (1000, 1.2, 8, 40, 40)),   # iniTh == minTh: no second FAST launch
+])
+def test_odd_shapes(fe, oracle, w, h, params):
+    """Shapes chosen against the staging paths of the kernels (TMA start alignment and out-of-range fill, the blur's
+    right-edge CTAs, strips at level borders), on a textured image and on noise."""
+    for img in (synth.synth_image(w, h, 77), synth.noise_image(w, h, 78)):
+        okp, odesc = oracle.Extractor(*params).extract(img)
+        kp, desc = fe.ORBextractor(*params)(img)
+        assert len(okp) > 0
+        _assert_same(kp, desc, okp, odesc)
