@@ -259,7 +259,7 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
   ORBFE_CUDA(dalloc(&a.st_sad, B * g.out_cap));
   a.st_items_per_kp = stereo_items_per_kp(g);
   ORBFE_CUDA(dalloc(&a.st_band, B * g.out_cap));
-  ORBFE_CUDA(dalloc(&a.st_bucket_start, B * ((size_t)(g.lv[0].h + 7) / 8 + 2)));
+  ORBFE_CUDA(dalloc(&a.st_bucket_start, B * (((size_t)(g.lv[0].h + 7) / 8) * g.nlevels + 2)));
   ORBFE_CUDA(dalloc(&a.st_bucket_items, B * g.out_cap * a.st_items_per_kp));
   if (!xt.empty()) ORBFE_CUDA(cudaMemcpy(a.xtab, xt.data(), xt.size() * sizeof(XTab), cudaMemcpyHostToDevice));
   if (!yt.empty()) ORBFE_CUDA(cudaMemcpy(a.ytab, yt.data(), yt.size() * sizeof(YTab), cudaMemcpyHostToDevice));

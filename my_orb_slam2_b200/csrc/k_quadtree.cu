@@ -339,6 +339,7 @@ int configure_kernels(const PyrGeom& g) {
   if (need > 48 * 1024)
     ORBFE_CUDA(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
   if (upload_pattern() != 0) { set_error("rBRIEF pattern upload failed"); return ORBFE_ERR_CUDA; }
+  if (configure_stereo_kernels(g) != 0) { set_error("cudaFuncSetAttribute(stereo_bucket_kernel) failed"); return ORBFE_ERR_CUDA; }
   if (configure_fast_kernel() != 0) { set_error("cudaFuncSetAttribute(fast_detect_kernel) failed"); return ORBFE_ERR_CUDA; }
   return ORBFE_OK;
 }

@@ -38,17 +38,19 @@ __global__ void __launch_bounds__(512) stereo_bucket_kernel(const __grid_constan
                                                             const int32_t* __restrict__ cntR, int4* __restrict__ band,
                                                             int32_t* __restrict__ bucket_start,
                                                             int4* __restrict__ bucket_items, int items_per_kp) {
-  __shared__ int s_cnt[ST_MAXB + 1];
-  __shared__ int s_wtmp[32];
+  // counting sort by (bucket, octave): a left keypoint of level L only scans the items of octaves L-1 .. L+1 of its
+  // bucket (:565-566), a contiguous slice of the item array
+  extern __shared__ int s_cnt[];  // nb * nlevels + 1
   const int b = blockIdx.x, tid = threadIdx.x;
   const int nR = cntR[b];
   const int n_rows = g.lv[0].h;
   const int nb = (n_rows + ST_BROWS - 1) / ST_BROWS;
+  const int nl = g.nlevels, nk = nb * nl;
   const orbfe_keypoint* kr = kpR + (size_t)b * g.out_cap;
   int4* bands = band + (size_t)b * g.out_cap;
-  int32_t* bstart = bucket_start + (size_t)b * (nb + 1);
+  int32_t* bstart = bucket_start + (size_t)b * (nk + 1);
   int4* bitems = bucket_items + (size_t)b * g.out_cap * items_per_kp;
-  for (int i = tid; i <= nb; i += 512) s_cnt[i] = 0;
+  for (int i = tid; i <= nk; i += 512) s_cnt[i] = 0;
   __syncthreads();
   for (int i = tid; i < nR; i += 512) {
     const orbfe_keypoint k = kr[i];
@@ -56,13 +58,13 @@ __global__ void __launch_bounds__(512) stereo_bucket_kernel(const __grid_constan
     const int maxr = (int)ceilf(__fadd_rn(k.y, r)), minr = (int)floorf(__fsub_rn(k.y, r));
     bands[i] = make_int4(minr, maxr, __float_as_int(k.x), k.octave);
     const int lo = max(minr, 0) / ST_BROWS, hi = min(maxr, n_rows - 1) / ST_BROWS;
-    for (int q = lo; q <= hi; ++q) atomicAdd(&s_cnt[q], 1);
+    for (int q = lo; q <= hi; ++q) atomicAdd(&s_cnt[q * nl + k.octave], 1);
   }
   __syncthreads();
-  // exclusive scan of s_cnt[0..nb) by warp 0 (nb <= 1024)
+  // exclusive scan of s_cnt[0..nk) by warp 0
   if (tid < 32) {
-    const int per = (nb + 31) / 32;
-    const int beg = min(tid * per, nb), end = min(beg + per, nb);
+    const int per = (nk + 31) / 32;
+    const int beg = min(tid * per, nk), end = min(beg + per, nk);
     int s = 0;
     for (int i = beg; i < end; ++i) s += s_cnt[i];
     int v = s;
@@ -73,18 +75,17 @@ __global__ void __launch_bounds__(512) stereo_bucket_kernel(const __grid_constan
     }
     int run = v - s;
     for (int i = beg; i < end; ++i) { const int t = s_cnt[i]; s_cnt[i] = run; run += t; }
-    if (tid == 31) s_cnt[nb] = v;
+    if (tid == 31) s_cnt[nk] = v;
   }
-  (void)s_wtmp;
   __syncthreads();
-  for (int i = tid; i <= nb; i += 512) bstart[i] = s_cnt[i];
+  for (int i = tid; i <= nk; i += 512) bstart[i] = s_cnt[i];
   __syncthreads();
   const int cap_items = g.out_cap * items_per_kp;
   for (int i = tid; i < nR; i += 512) {
     const int4 bd = bands[i];
     const int lo = max(bd.x, 0) / ST_BROWS, hi = min(bd.y, n_rows - 1) / ST_BROWS;
     for (int q = lo; q <= hi; ++q) {
-      const int slot = atomicAdd(&s_cnt[q], 1);
+      const int slot = atomicAdd(&s_cnt[q * nl + bd.w], 1);
       if (slot < cap_items) bitems[slot] = make_int4(bd.x, bd.y, bd.z, bd.w | (i << 8));  // band inline: no second lookup
     }
   }
@@ -116,11 +117,12 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 8) stereo_match_kernel(
   const bool searchable = rowi >= 0 && rowi < n_rows && !(maxU < 0.f);
   unsigned best = ((unsigned)TH_HIGH << 16);  // bestDist = TH_HIGH, strict '<' below (:560,:581)
   if (searchable) {
-    const int nb = (n_rows + ST_BROWS - 1) / ST_BROWS;
-    const int32_t* bstart = bucket_start + (size_t)b * (nb + 1);
+    const int nb = (n_rows + ST_BROWS - 1) / ST_BROWS, nl = g.nlevels;
+    const int32_t* bstart = bucket_start + (size_t)b * (nb * nl + 1);
     const int4* bitems = bucket_items + (size_t)b * g.out_cap * items_per_kp;
-    const int bk = rowi / ST_BROWS;
-    const int beg = bstart[bk], end = bstart[bk + 1];
+    // the bucket's items are sorted by octave: only octaves levelL-1 .. levelL+1 are candidates (:565-566)
+    const int k0 = (rowi / ST_BROWS) * nl;
+    const int beg = bstart[k0 + max(levelL - 1, 0)], end = bstart[k0 + min(levelL + 1, nl - 1) + 1];
     const uint8_t* dR = descR + (size_t)b * g.out_cap * 32;
     // 4 items per lane in flight: the item loads of a 128-item chunk are issued together, then the descriptor loads
     for (int base = beg; base < end; base += 128) {
@@ -134,8 +136,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 8) stereo_match_kernel(
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const float uR = __int_as_float(bd[u].z);
-        const int oct = bd[u].w & 0xFF;
-        cand[u] = rowi >= bd[u].x && rowi <= bd[u].y && oct >= levelL - 1 && oct <= levelL + 1 && uR >= minU && uR <= maxU;
+        cand[u] = rowi >= bd[u].x && rowi <= bd[u].y && uR >= minU && uR <= maxU;
       }
 #pragma unroll
       for (int h = 0; h < 4; h += 2) {  // descriptor loads two at a time (register budget)
@@ -291,7 +292,8 @@ __global__ void __launch_bounds__(1024) stereo_median_kernel(const __grid_consta
 void launch_stereo(const PyrGeom& g, const ExtractorArena& l, const ExtractorArena& r, int batch, float mbf, float mb,
                    cudaStream_t s, cudaEvent_t* ev) {
   if (ev) cudaEventRecord(ev[0], s);
-  stereo_bucket_kernel<<<batch, 512, 0, s>>>(g, r.out_kp, r.out_count, l.st_band, l.st_bucket_start, l.st_bucket_items,
+  const size_t bucket_smem = ((size_t)((g.lv[0].h + ST_BROWS - 1) / ST_BROWS) * g.nlevels + 1) * sizeof(int);
+  stereo_bucket_kernel<<<batch, 512, bucket_smem, s>>>(g, r.out_kp, r.out_count, l.st_band, l.st_bucket_start, l.st_bucket_items,
                                             l.st_items_per_kp);
   dim3 grid((g.out_cap + ST_WARPS - 1) / ST_WARPS, batch);
   stereo_match_kernel<<<grid, ST_WARPS * 32, 0, s>>>(g, l.pyr, r.pyr, l.out_kp, l.out_desc, l.out_count, r.out_kp,
@@ -301,6 +303,13 @@ void launch_stereo(const PyrGeom& g, const ExtractorArena& l, const ExtractorAre
   stereo_median_kernel<<<batch, 1024, (size_t)g.out_cap * sizeof(int), s>>>(g, l.out_count, l.st_uright, l.st_depth,
                                                                             l.st_sad, l.st_count);
   if (ev) cudaEventRecord(ev[2], s);
+}
+
+// the bucket kernel's counters (buckets x levels) can exceed the 48 KB default for very tall images
+int configure_stereo_kernels(const PyrGeom& g) {
+  const size_t need = ((size_t)((g.lv[0].h + ST_BROWS - 1) / ST_BROWS) * g.nlevels + 1) * sizeof(int);
+  if (need <= 48 * 1024) return 0;
+  return cudaFuncSetAttribute(stereo_bucket_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need) == cudaSuccess ? 0 : -1;
 }
 
 int stereo_items_per_kp(const PyrGeom& g) {

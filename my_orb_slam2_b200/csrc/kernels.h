@@ -30,7 +30,7 @@ struct ExtractorArena {
   int32_t* st_sad = nullptr;    // [batch][out_cap]
   int32_t* st_count = nullptr;  // [batch]
   int4* st_band = nullptr;             // [batch][out_cap] right keypoint: minr, maxr, x bits, octave
-  int32_t* st_bucket_start = nullptr;  // [batch][rows/8 + 2]
+  int32_t* st_bucket_start = nullptr;  // [batch][(rows/8) * nlevels + 1] items sorted by (8-row bucket, octave)
   int4* st_bucket_items = nullptr;     // [batch][out_cap * st_items_per_kp] band + right keypoint index per bucket entry
   int st_items_per_kp = 0;
   // TMA descriptors (CUtensorMap, 128 B each) of the pyramid levels as (x, y, image) byte tensors with a
@@ -57,6 +57,7 @@ void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cud
 void launch_quadtree(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
 size_t quadtree_smem_bytes(int node_cap);
 int upload_pattern();          // k_describe.cu: rBRIEF pattern -> device (once per device); 0 on success
+int configure_stereo_kernels(const PyrGeom& g);
 int configure_fast_kernel();  // opt in to > 48 KB dynamic shared memory; 0 on success
 // GaussianBlur(7x7, sigma 2) of every level (:1107-1108), one launch
 void launch_blur_levels(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s);
