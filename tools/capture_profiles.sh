@@ -11,6 +11,9 @@ CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-matchers --no-s
 $CMD > $OUT/plain_$TAG.log 2>&1 || { echo "bench failed without ncu"; tail -5 $OUT/plain_$TAG.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_bench_launches.csv $CMD > $OUT/ncu_bench.log 2>&1
 python tools/one_step.py 64 1 > $OUT/plain_step_$TAG.log 2>&1 || { echo "one_step failed without ncu"; exit 1; }
+# per-launch metrics of one whole step (every kernel of L, R and stereo once)
+M=gpu__time_duration.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__warps_active.avg.pct_of_peak_sustained_active,smsp__inst_executed.sum,l1tex__throughput.avg.pct_of_peak_sustained_elapsed,lts__throughput.avg.pct_of_peak_sustained_elapsed,dram__bytes_read.sum,dram__bytes_write.sum,launch__grid_size,launch__registers_per_thread
+ncu --metrics $M --clock-control none -c 60 --csv --log-file $OUT/${TAG}_step_metrics_ncu.csv python tools/one_step.py 64 1 > $OUT/ncu_step.log 2>&1
 for K in pyramid_level fast_detect quadtree blur_levels describe stereo_match; do
   C=1; [ $K = fast_detect ] && C=2   # FAST is two launches per extraction (iniTh, then minTh where a cell stayed empty)
   ncu --set full --clock-control none --import-source on -k regex:${K} -c $C -f -o $OUT/prof_${K}_${TAG}f \

@@ -32,6 +32,18 @@ if os.path.exists(src):
         for k in sorted(tot, key=lambda k: -tot[k]):
             f.write("| %s | %d | %.1f | %.1f %% | %.1f |\n" % (k, cnt[k], tot[k], 100 * tot[k] / s, tot[k] / cnt[k]))
 
+src = os.path.join(G, "%s_step_metrics_ncu.csv" % tag)
+if os.path.exists(src):
+    with open(os.path.join(P, "%s_step_metrics_ncu.csv" % tag), "w") as f:
+        f.write(open(src).read())
+    tab = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_metrics_table.py"), src], capture_output=True, text=True).stdout
+    with open(os.path.join(P, "%s_step_launches.md" % tag), "w") as f:
+        f.write("# %s — per-launch ncu metrics of one device-resident bench step\n\n" % tag)
+        f.write("Command: `ncu --metrics gpu__time_duration.sum,... --clock-control none -c 60 --csv python tools/one_step.py 64 1` "
+                "(64 KITTI stereo pairs: left handle, right handle, stereo).  Times are serialised, cold-cache ncu replays: compare "
+                "SHARES with `bench.py` `stages_ms_per_launch`, not absolutes.\n\n")
+        f.write(tab)
+
 want = ["gpu__time_duration.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
         "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
