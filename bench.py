@@ -557,6 +557,16 @@ def run_gpu(args):
         g.finish()
     torch.cuda.synchronize()
     t_e2e = max_over_ranks(time.perf_counter() - t0)
+    # what the host link can do: one pinned 30 MB image batch to the device, best of 5 (the e2e leg moves
+    # 2 * B * W * H bytes in and the results out every step)
+    h2d_gbs = 0.0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(5):
+        ev0.record()
+        d_left.copy_(h_left, non_blocking=True)
+        ev1.record()
+        torch.cuda.synchronize()
+        h2d_gbs = max(h2d_gbs, h_left.numel() / (ev0.elapsed_time(ev1) * 1e-3) / 1e9)
     n_left = int(rigs[0].cntL.numpy().sum())
     n_match = int(rigs[0].nm.numpy().sum())
     kpL, kpR, dsL, dsR, cntL, cntR = rigs[0].kpL, rigs[0].kpR, rigs[0].dsL, rigs[0].dsR, rigs[0].cntL, rigs[0].cntR
@@ -677,7 +687,12 @@ def run_gpu(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "host": {"cpus_near_gpu": numa, "note": "each rank is pinned to the CPUs NVML reports next to its GPU before "
-                                                "its pinned buffers are allocated"},
+                                                "its pinned buffers are allocated",
+                 "h2d_gbs_measured": h2d_gbs,
+                 "e2e_h2d_gbs": 2 * B * W * H * args.steps / t_e2e / 1e9,
+                 "e2e_bound": "host-to-device link: the e2e leg's input traffic alone runs at e2e_h2d_gbs of the "
+                              "h2d_gbs_measured one pinned copy reaches on rank 0 (all ranks share the host's PCIe / "
+                              "memory path when N > 1)"},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                      "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src,
                      "timed": "per-stage CUDA events on the handle's stream, %d steps run right after the timed region with "
