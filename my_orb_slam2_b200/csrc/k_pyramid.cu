@@ -179,7 +179,9 @@ void launch_pyramid_level(const PyrGeom& g, const ExtractorArena& a, int lvl, in
   const LevelGeom& D = g.lv[lvl];
   if (D.resize_fast) {
     const int cols = (D.w + 127) / 128;
-    if ((long long)cols * ((D.h + 31) / 32) * batch >= 2 * 148 * 4) {
+    // 8 rows per thread + staged tiles as soon as the launch has two CTAs per SM (the 2-row variant is for single
+    // frames: at 64 images it ran levels 6 and 7 in 12.4 / 10.1 us where level 5 took 11.8 us with the 8-row kernel)
+    if ((long long)cols * ((D.h + 31) / 32) * batch >= 2 * 148) {
       dim3 grid(cols, (D.h + 8 * PY_WARPS - 1) / (8 * PY_WARPS), batch);
       if (D.resize_tile) pyramid_level_kernel<8, true><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
       else pyramid_level_kernel<8, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
