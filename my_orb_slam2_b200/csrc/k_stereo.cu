@@ -24,7 +24,6 @@ namespace orbfe {
 
 constexpr int ST_WARPS = 4;
 constexpr int ST_BROWS = 8;       // image rows per bucket of the row table
-constexpr int ST_MAXB = 1024;     // buckets per image (rows <= 8192)
 constexpr int TH_HIGH = ORBFE_TH_HIGH, TH_LOW = ORBFE_TH_LOW;
 
 __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
