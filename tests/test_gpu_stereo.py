@@ -62,16 +62,22 @@ def test_stereo_frame_one_call(oracle):
     params = (s["nfeatures"], s["scale_factor"], s["nlevels"], s["ini_th"], s["min_th"])
     pairs = [synth.synth_pair(w, h, 70 + i) for i in range(2)]
     lefts, rights = np.stack([p[0] for p in pairs]), np.stack([p[1] for p in pairs])
-    L = orbfe.Extractor(*params, w, h, max_batch=2)
-    R = orbfe.Extractor(*params, w, h, max_batch=2)
     mbf, mb = np.float32(s["bf"]), np.float32(s["bf"]) / np.float32(s["fx"])
     oL, oR = oracle.Extractor(*params), oracle.Extractor(*params)
-    for _ in range(2):
+    want = []
+    for b in range(2):
+        okl, odl = oL.extract(lefts[b])
+        okr, odr = oR.extract(rights[b])
+        want.append((okl, odl, okr, odr) + tuple(oracle.stereo_matches(oL, oR, okl, odl, okr, odr, mbf, mb)))
+    # max_batch == batch: results leave as one block per handle and are scattered on the host; max_batch > batch: the
+    # general path (separate copies straight into the caller's arrays)
+    for max_batch in (2, 2, 3):
+        if max_batch == 3 or "L" not in locals():
+            L = orbfe.Extractor(*params, w, h, max_batch=max_batch)
+            R = orbfe.Extractor(*params, w, h, max_batch=max_batch)
         kl, dl, nl, kr, dr, nr, ur, dp, nm = orbfe.stereo_frame(L, R, lefts, rights, mbf, mb)
         for b in range(2):
-            okl, odl = oL.extract(lefts[b])
-            okr, odr = oR.extract(rights[b])
-            our, odp, on = oracle.stereo_matches(oL, oR, okl, odl, okr, odr, mbf, mb)
+            okl, odl, okr, odr, our, odp, on = want[b]
             assert nl[b] == len(okl) and nr[b] == len(okr)
             assert np.array_equal(kl[b][:nl[b]], okl) and np.array_equal(dl[b][:nl[b]], odl)
             assert np.array_equal(kr[b][:nr[b]], okr) and np.array_equal(dr[b][:nr[b]], odr)
