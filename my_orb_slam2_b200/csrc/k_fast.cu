@@ -124,8 +124,9 @@ __device__ __forceinline__ int corner_strength(const uint8_t* p) {
 }
 
 // bit 7 of a byte is set iff that byte of x or of y is > t (K = (127 - t) * 0x01010101, t <= 127); other bits: garbage
-__device__ __forceinline__ unsigned swar_gt2(unsigned x, unsigned y, unsigned K) {
-  return ((x & 0x7F7F7F7Fu) + K) | x | ((y & 0x7F7F7F7Fu) + K) | y;
+__device__ __forceinline__ unsigned add_fma(unsigned a, unsigned b, unsigned one);
+__device__ __forceinline__ unsigned swar_gt2(unsigned x, unsigned y, unsigned K, unsigned one) {
+  return add_fma(x & 0x7F7F7F7Fu, K, one) | x | add_fma(y & 0x7F7F7F7Fu, K, one) | y;
 }
 // bits 7,15,23,31 of m -> bits 28..31 (distinct partial products, no carries)
 __device__ __forceinline__ unsigned gather_bit7(unsigned m) { return (m & 0x80808080u) * 0x00204081u; }
@@ -149,6 +150,39 @@ __device__ __forceinline__ int mask_scan(const unsigned (&acc)[FD_ACC], int lane
   }
   *excl = incl - cnt;
   return __shfl_sync(0xffffffffu, incl, 31);
+}
+
+// a + C as IMAD (a * one + C, `one` = 1 from a kernel parameter so that ptxas keeps the multiply): the kernel is bound by
+// the ALU pipe (stall_math / not_selected everywhere in the ncu source view) while the FMA pipe that runs IMAD idles
+template <unsigned C>
+__device__ __forceinline__ unsigned add_imm_fma(unsigned a, unsigned one) {
+  unsigned d;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "n"(C));
+  return d;
+}
+__device__ __forceinline__ unsigned add_fma(unsigned a, unsigned b, unsigned one) {
+  unsigned d;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
+  return d;
+}
+
+// the whole-list flatten (no window): a running shared-memory byte address instead of an index, and both per-entry
+// additions (entry value, address bump) on the FMA pipe: STS + 2 IMAD per slot.  Slot S = row S/4, column bit S%4.
+template <int S>
+__device__ __forceinline__ void flatten_slot(const unsigned (&acc)[FD_ACC], unsigned col, unsigned& p, unsigned one) {
+  if constexpr (S < FD_ROWS * 4) {
+    constexpr int r = S >> 2, k = S & 3;
+    if (acc[r >> 3] & (1u << (4 * (r & 7) + k))) {
+      const unsigned v = add_imm_fma<(unsigned)((r << 7) + k)>(col, one);
+      asm volatile("st.shared.u16 [%0], %1;" ::"r"(p), "h"((unsigned short)v) : "memory");
+      p = add_imm_fma<2u>(p, one);
+    }
+    flatten_slot<S + 1>(acc, col, p, one);
+  }
+}
+__device__ __forceinline__ void flatten_all(const unsigned (&acc)[FD_ACC], int lane, int excl, uint16_t* list, unsigned one) {
+  unsigned p = (unsigned)__cvta_generic_to_shared(list) + 2u * (unsigned)excl;
+  flatten_slot<0>(acc, (unsigned)lane * 4u, p, one);
 }
 
 // write the entries (row<<7 | column) whose flat index lies in [lo, lo+FD_CAP) into list[index - lo]; WINDOWED=false
@@ -176,7 +210,7 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
                                                            int32_t* __restrict__ cand_count,
                                                            uint8_t* cell_hi, int32_t* __restrict__ flags,
                                                            int t_run, int second_pass,
-                                                           const CUtensorMap* __restrict__ maps) {
+                                                           const CUtensorMap* __restrict__ maps, unsigned one) {
   extern __shared__ __align__(128) unsigned char fd_smem_raw[];
   FdSmem* s_all = reinterpret_cast<FdSmem*>(fd_smem_raw);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -260,14 +294,14 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
       const unsigned w0 = tile_w[j * FD_TW + lane], w2 = tile_w[j * FD_TW + lane + 2];
       const unsigned pl = __funnelshift_r(w0, w1, 8);   // pixels x-3
       const unsigned pr = __funnelshift_r(w1, w2, 24);  // pixels x+3
-      hf[j % 4] = swar_gt2(__vabsdiffu4(w1, pl), __vabsdiffu4(w1, pr), K);
+      hf[j % 4] = swar_gt2(__vabsdiffu4(w1, pl), __vabsdiffu4(w1, pr), K, one);
     }
     if (j >= 6) {
       const int r = j - 6, y = cy0 + r;
       score_w[r * 32 + lane] = 0u;
       const unsigned rm = (y >= kEdge && y < y_end) ? (colmask & (y < y_split ? open0 : open1)) : 0u;
       const unsigned cc = c[(j - 3) % 7];
-      const unsigned vf = swar_gt2(__vabsdiffu4(cc, c[(j - 6) % 7]), __vabsdiffu4(cc, c[j % 7]), K);
+      const unsigned vf = swar_gt2(__vabsdiffu4(cc, c[(j - 6) % 7]), __vabsdiffu4(cc, c[j % 7]), K, one);
       put_nibble(acc, r, gather_bit7(vf & hf[(j - 3) % 4] & rm));
     }
   }
@@ -335,7 +369,7 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
     // ---- 2. exact corner strength of the survivors -> score tile; owned corners compact in place ----
     // (a data-dependent walk over the set bits only, ffs + clear-lowest, measured slower in either launch:
     // 0.203 vs 0.195 ms in the iniTh launch, 0.177 vs 0.172 ms when used in the minTh launch only)
-    flatten_window<false>(acc, lane, excl, 0, sm.list);
+    flatten_all(acc, lane, excl, sm.list, one);
     __syncwarp();
     int nc = 0;
     for (int base = 0; base < total; base += 32) {
@@ -404,11 +438,11 @@ void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cud
   // cv::FAST(iniTh) everywhere, then cv::FAST(minTh) where a cell came back empty (:830-837): the second launch
   // leaves every strip whose cells all have an iniTh corner at once
   fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi, a.flags,
-                                                                    g.ini_th, 0, static_cast<const CUtensorMap*>(a.fast_maps));
+                                                                    g.ini_th, 0, static_cast<const CUtensorMap*>(a.fast_maps), 1u);
   if (g.min_th < g.ini_th)
     fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi,
                                                                       a.flags, g.min_th, 1,
-                                                                      static_cast<const CUtensorMap*>(a.fast_maps));
+                                                                      static_cast<const CUtensorMap*>(a.fast_maps), 1u);
 }
 
 }  // namespace orbfe
