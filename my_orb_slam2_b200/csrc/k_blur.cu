@@ -38,7 +38,7 @@ __device__ __forceinline__ unsigned vsum(unsigned a0, unsigned a1, unsigned a2, 
 #define BL_PAIRS 2
 #endif
   // BL_PAIRS of the three symmetric pairs are summed first (adds, ALU pipe); the others are two multiply-adds each
-  // (FMA pipe).  Measured: 3 pairs 0.1088 ms, 2 pairs 0.1055 ms
+  // (FMA pipe).  Measured: 3 pairs 0.1088 ms, 2 pairs 0.1055 ms, 0 pairs 0.1079 ms
   unsigned t = mad_u32(a3, 56u, 32768u);
   if (BL_PAIRS >= 1) t = mad_u32(a2 + a4, 48u, t); else { t = mad_u32(a2, 48u, t); t = mad_u32(a4, 48u, t); }
   if (BL_PAIRS >= 2) t = mad_u32(a1 + a5, 34u, t); else { t = mad_u32(a1, 34u, t); t = mad_u32(a5, 34u, t); }
