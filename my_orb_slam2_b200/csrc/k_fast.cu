@@ -204,13 +204,15 @@ __device__ __forceinline__ void flatten_window(const unsigned (&acc)[FD_ACC], in
   }
 }
 
+template <bool SECOND>  // compile-time: the iniTh launch carries none of the open-cell bookkeeping of the minTh launch
 __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_constant__ PyrGeom g,
                                                            const uint8_t* __restrict__ pyr,
                                                            uint32_t* __restrict__ cand,
                                                            int32_t* __restrict__ cand_count,
                                                            uint8_t* cell_hi, int32_t* __restrict__ flags,
-                                                           int t_run, int second_pass,
+                                                           int t_run,
                                                            const CUtensorMap* __restrict__ maps, unsigned one) {
+  constexpr bool second_pass = SECOND;
   extern __shared__ __align__(128) unsigned char fd_smem_raw[];
   FdSmem* s_all = reinterpret_cast<FdSmem*>(fd_smem_raw);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -427,22 +429,24 @@ __global__ void __launch_bounds__(FD_T, 14) fast_detect_kernel(const __grid_cons
 }
 
 int configure_fast_kernel() {
-  return cudaFuncSetAttribute(fast_detect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)(FD_WARPS * sizeof(FdSmem))) == cudaSuccess ? 0 : -1;
+  const int bytes = (int)(FD_WARPS * sizeof(FdSmem));
+  return (cudaFuncSetAttribute(fast_detect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess &&
+          cudaFuncSetAttribute(fast_detect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess)
+             ? 0 : -1;
 }
 
 void launch_fast_cells(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
   if (g.fast_strips <= 0) return;
   cudaMemsetAsync(a.cell_hi, 0, (size_t)batch * g.total_cells, s);
   dim3 grid((g.fast_strips + FD_WARPS - 1) / FD_WARPS, batch);
+  const CUtensorMap* maps = static_cast<const CUtensorMap*>(a.fast_maps);
   // cv::FAST(iniTh) everywhere, then cv::FAST(minTh) where a cell came back empty (:830-837): the second launch
   // leaves every strip whose cells all have an iniTh corner at once
-  fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi, a.flags,
-                                                                    g.ini_th, 0, static_cast<const CUtensorMap*>(a.fast_maps), 1u);
+  fast_detect_kernel<false><<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi,
+                                                                          a.flags, g.ini_th, maps, 1u);
   if (g.min_th < g.ini_th)
-    fast_detect_kernel<<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi,
-                                                                      a.flags, g.min_th, 1,
-                                                                      static_cast<const CUtensorMap*>(a.fast_maps), 1u);
+    fast_detect_kernel<true><<<grid, FD_T, FD_WARPS * sizeof(FdSmem), s>>>(g, a.pyr, a.cand, a.cand_count, a.cell_hi,
+                                                                           a.flags, g.min_th, maps, 1u);
 }
 
 }  // namespace orbfe

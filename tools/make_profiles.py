@@ -79,6 +79,8 @@ for rep in sorted(glob.glob(os.path.join(G, "prof_*_%sf.ncu-rep" % tag))):
             label, v[want[0]], v[want[1]], v[want[2]], v[want[3]] / 1e6, v[want[4]], v[want[5]], v[want[6]], v[want[7]], v[want[8]],
             v[want[9]], v[want[10]], v[want[11]] / 1e6, v[want[12]] / 1e6, v[want[13]], v[want[14]], v[want[15]]))
     # per STAGE: the sum over the stage's captured launches (bench.py divides by the stage's live time)
+    if len(krows) > 1:  # the launches of one stage are instantiations of one template: key without "void " / "<...>"
+        name = name.replace("void ", "").split("<")[0]
     traffic[name] = {"dram_bytes_per_launch": tot["dram"], "images": 64, "time_us": tot["time"],
                      "warp_inst_per_launch": tot["winst"], "issue_slots_busy_pct": busy, "launches_captured": len(krows)}
 if lines:
