@@ -85,7 +85,12 @@ __device__ __forceinline__ int quadrant(const int4 bx, int x, int y) {
   return (x < mx ? 0 : 1) + (y < my ? 0 : 2);      // n1,n2,n3,n4 (:513-525)
 }
 
-__global__ void __launch_bounds__(QT_T) quadtree_kernel(const __grid_constant__ PyrGeom g,
+// MINB = 1: as many registers as the kernel wants (55: two CTAs per SM), the fastest single CTA — single frames, where
+// level 0's CTA is the critical path.  MINB = 3: 40 registers, three CTAs per SM — batches with more CTAs than two
+// per SM, where the kernel is latency-bound and a third resident CTA pays (0.0583 -> 0.0556 ms per 64 images,
+// +1.1 % frames/s; it costs a single pair 6 us).
+template <int MINB>
+__global__ void __launch_bounds__(QT_T, MINB) quadtree_kernel(const __grid_constant__ PyrGeom g,
                                                         uint32_t* cand, const uint8_t* __restrict__ cell_hi,
                                                         uint16_t* __restrict__ node_of, int32_t* cand_count,
                                                         uint32_t* __restrict__ kept, int32_t* __restrict__ kept_count,
@@ -336,8 +341,10 @@ int configure_kernels(const PyrGeom& g) {
     set_error("nfeatures too large: quadtree needs %zu bytes of shared memory", need);
     return ORBFE_ERR_ARG;
   }
-  if (need > 48 * 1024)
-    ORBFE_CUDA(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+  if (need > 48 * 1024) {
+    ORBFE_CUDA(cudaFuncSetAttribute(quadtree_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+    ORBFE_CUDA(cudaFuncSetAttribute(quadtree_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+  }
   if (upload_pattern() != 0) { set_error("rBRIEF pattern upload failed"); return ORBFE_ERR_CUDA; }
   if (configure_stereo_kernels(g) != 0) { set_error("cudaFuncSetAttribute(stereo_bucket_kernel) failed"); return ORBFE_ERR_CUDA; }
   if (configure_fast_kernel() != 0) { set_error("cudaFuncSetAttribute(fast_detect_kernel) failed"); return ORBFE_ERR_CUDA; }
@@ -346,8 +353,11 @@ int configure_kernels(const PyrGeom& g) {
 
 void launch_quadtree(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
   dim3 grid(batch, g.nlevels);
-  quadtree_kernel<<<grid, QT_T, quadtree_smem_bytes(g.max_node_cap), s>>>(g, a.cand, a.cell_hi, a.node_of, a.cand_count, a.kept,
-                                                                          a.kept_count, a.flags);
+  const size_t smem = quadtree_smem_bytes(g.max_node_cap);
+  if ((long long)batch * g.nlevels > 2 * 148)
+    quadtree_kernel<3><<<grid, QT_T, smem, s>>>(g, a.cand, a.cell_hi, a.node_of, a.cand_count, a.kept, a.kept_count, a.flags);
+  else
+    quadtree_kernel<1><<<grid, QT_T, smem, s>>>(g, a.cand, a.cell_hi, a.node_of, a.cand_count, a.kept, a.kept_count, a.flags);
 }
 
 }  // namespace orbfe
