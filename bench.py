@@ -663,7 +663,7 @@ def run_gpu(args):
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
         kname = {"fast": "fast_detect_kernel", "blur": "void blur_levels_kernel<32>", "describe": "describe_kernel",
-                 "pyramid": "void pyramid_level_kernel<8, 1>", "quadtree": "quadtree_kernel"}[dom]
+                 "pyramid": "void pyramid_level_kernel<8, 1>", "quadtree": "void quadtree_kernel<3>"}[dom]
         traffic = tj[kname]["dram_bytes_per_launch"] * B / tj[kname]["images"]
         # the bound that applies (north_star: "fraction of the HBM or integer-pipe roofline"): warp instructions of
         # the kernel (deterministic for these inputs; counted by ncu, committed in profiles/) / LIVE launch time,
