@@ -22,7 +22,7 @@
 
 namespace orbfe {
 
-constexpr int ST_WARPS = 4;
+constexpr int ST_WARPS = 1;  // one warp per CTA: a slot frees as soon as its keypoint is done (4 warps 0.116 ms, 2 warps 0.112, 1 warp 0.109)
 constexpr int ST_BROWS = 8;       // image rows per bucket of the row table
 constexpr int TH_HIGH = ORBFE_TH_HIGH, TH_LOW = ORBFE_TH_LOW;
 
@@ -90,8 +90,8 @@ __global__ void __launch_bounds__(512) stereo_bucket_kernel(const __grid_constan
   }
 }
 
-// 8 CTAs (32 warps) per SM: measured best (10 / 12 / 16 spill the SAD accumulators, 5 / 6 lose latency hiding)
-__global__ void __launch_bounds__(ST_WARPS * 32, 8) stereo_match_kernel(
+// 32 warps per SM (64 registers): measured best (40 / 48 / 51 registers spill the SAD accumulators, 80 lose latency hiding)
+__global__ void __launch_bounds__(ST_WARPS * 32, 32) stereo_match_kernel(
     const __grid_constant__ PyrGeom g, const uint8_t* __restrict__ pyrL, const uint8_t* __restrict__ pyrR,
     const orbfe_keypoint* __restrict__ kpL, const uint8_t* __restrict__ descL, const int32_t* __restrict__ cntL,
     const orbfe_keypoint* __restrict__ kpR, const uint8_t* __restrict__ descR, const int4* __restrict__ band,
