@@ -16,7 +16,8 @@
 
 namespace orbfe {
 
-constexpr int BL_TX = 32, BL_TY = 4;  // CTA covers 128 x (4 * BL_ROWS) pixels; BL_ROWS = 32 (throughput) or 8 (few images)
+constexpr int BL_TX = 32;  // a CTA is BL_TY warps stacked vertically and covers 128 x (BL_TY * BL_ROWS) pixels: 128 x 32 either as
+                           // one warp of 32-row strips (throughput) or as four warps of 8-row strips (few images)
 constexpr int BL_PF = 3;                            // rows of loads in flight per thread
 
 __device__ __forceinline__ int reflect101i(int p, int len) {
@@ -50,13 +51,13 @@ __device__ __forceinline__ unsigned pack_round(const unsigned (&v)[4]) {
   return __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
 }
 
-template <int BL_ROWS>
+template <int BL_ROWS, int BL_TY>
 __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid_constant__ PyrGeom g,
                                                                     const uint8_t* __restrict__ pyr,
                                                                     uint8_t* __restrict__ blur) {
   int tile = blockIdx.x;
   int lvl = 0;
-  constexpr bool kTall = BL_ROWS == 32;
+  constexpr bool kTall = BL_ROWS * BL_TY == 128;  // 128 x 128 tiles (geometry: blur_tile_base), else 128 x 32 (_small)
   const int n_tiles = kTall ? g.blur_tiles : g.blur_tiles_small;
   const int b = blockIdx.y;
   // The last one or two words of a row (x4 + 7 >= w) need column reflection: byte-wise loads, a rolled loop, ~5x the
@@ -230,18 +231,20 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
 }
 
 // CTAs that take the right-edge (row strip, word) jobs of one image: 2 jobs per strip row of every level
-static int blur_edge_ctas(const PyrGeom& g, int rows) {
+static int blur_edge_ctas(const PyrGeom& g, int rows, int threads) {
   int jobs = 0;
   for (int l = 0; l < g.nlevels; ++l) jobs += ((g.lv[l].h + rows - 1) / rows) * 2;
-  return (jobs + BL_TX * BL_TY - 1) / (BL_TX * BL_TY);
+  return (jobs + threads - 1) / threads;
 }
 
 void launch_blur_levels(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
-  dim3 block(BL_TX, BL_TY);
   if ((long long)g.blur_tiles * batch >= 2 * 148 * 4) {
-    blur_levels_kernel<32><<<dim3(g.blur_tiles + blur_edge_ctas(g, 32), batch), block, 0, s>>>(g, a.pyr, a.blur);
-  } else {  // few images: 128 x 32 tiles (4x more CTAs, 8-row strips per thread)
-    blur_levels_kernel<8><<<dim3(g.blur_tiles_small + blur_edge_ctas(g, 8), batch), block, 0, s>>>(g, a.pyr, a.blur);
+    // throughput: one-warp CTAs of 32-row strips (a slot frees as soon as its warp is done)
+    blur_levels_kernel<32, 1><<<dim3(g.blur_tiles_small + blur_edge_ctas(g, 32, 32), batch), dim3(BL_TX, 1), 0, s>>>(
+        g, a.pyr, a.blur);
+  } else {  // few images: 8-row strips per thread, four warps per 128 x 32 tile
+    blur_levels_kernel<8, 4><<<dim3(g.blur_tiles_small + blur_edge_ctas(g, 8, 128), batch), dim3(BL_TX, 4), 0, s>>>(
+        g, a.pyr, a.blur);
   }
 }
 
