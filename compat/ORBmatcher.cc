@@ -189,12 +189,22 @@ void fill_projection(orbfe_projection& pr, const cv::Mat& T34, bool is_sim3, con
 
 ORBmatcher::ORBmatcher(float nnratio, bool checkOri) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
 
+// src/ORBmatcher.cc:1715-1731.  The static single-pair helper is a SCALAR function (one 32-byte pair): callers such as
+// the unchanged MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:291) call it ~N^2/2 times per map point, so a
+// device round trip per pair (tens of microseconds) would stall LocalMapping.  It is therefore eight popcounts inline,
+// exactly the integer the device kernels compute; every data-parallel use (the matchers, the brute force, the
+// batched orbfe_descriptor_distance / orbfe_compute_distinctive_descriptors) runs on the GPU.
 int ORBmatcher::DescriptorDistance(const cv::Mat& a, const cv::Mat& b) {
-  orbfe_matcher* m = t_matcher.get(sDevice);
-  int32_t d = 256;
-  if (!m || orbfe_descriptor_distance(m, a.ptr(0), b.ptr(0), 1, &d) != ORBFE_OK)
-    std::fprintf(stderr, "ORBmatcher::DescriptorDistance: %s\n", orbfe_last_error());
-  return d;
+  const unsigned char* pa = a.ptr(0);
+  const unsigned char* pb = b.ptr(0);
+  int dist = 0;
+  for (int i = 0; i < 4; ++i) {
+    uint64_t x, y;
+    std::memcpy(&x, pa + 8 * i, 8);
+    std::memcpy(&y, pb + 8 * i, 8);
+    dist += __builtin_popcountll(x ^ y);
+  }
+  return dist;
 }
 
 int ORBmatcher::SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th) {

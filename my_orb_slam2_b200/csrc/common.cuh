@@ -46,4 +46,25 @@ struct DeviceGuard {
   }
 };
 
+// Capture `issue()` (kernel launches on `stream`) into an executable graph.  Whatever fails between BeginCapture and
+// Instantiate, the capture is always ended and the intermediate graph destroyed, so the stream never stays in capture
+// mode; on failure *exec stays null and the caller runs the plain launches instead (and stops trying graphs).
+template <class Issue>
+static inline bool capture_graph(cudaStream_t stream, cudaGraphExec_t* exec, Issue&& issue) {
+  *exec = nullptr;
+  if (cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  issue();
+  const cudaError_t launch_err = cudaGetLastError();
+  cudaGraph_t graph = nullptr;
+  const cudaError_t end_err = cudaStreamEndCapture(stream, &graph);  // also ends an invalidated capture
+  bool ok = launch_err == cudaSuccess && end_err == cudaSuccess && graph != nullptr;
+  if (ok && cudaGraphInstantiate(exec, graph, 0) != cudaSuccess) { *exec = nullptr; ok = false; }
+  if (graph) cudaGraphDestroy(graph);
+  if (!ok) cudaGetLastError();
+  return ok;
+}
+
 }  // namespace orbfe

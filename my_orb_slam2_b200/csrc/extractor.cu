@@ -376,6 +376,7 @@ int orbfe_extractor_create(const orbfe_extractor_params* params, int width, int 
     rc = ORBFE_ERR_CUDA;
   }
   if (rc == ORBFE_OK && cudaEventCreateWithFlags(&e->done, cudaEventDisableTiming) != cudaSuccess) rc = ORBFE_ERR_CUDA;
+  if (rc == ORBFE_OK && cudaEventCreateWithFlags(&e->stereo_done, cudaEventDisableTiming) != cudaSuccess) rc = ORBFE_ERR_CUDA;
   if (rc == ORBFE_OK) rc = configure_kernels(e->geom);
   { const char* ng = getenv("ORBFE_NO_GRAPHS"); e->use_graph = !(ng && ng[0] == '1'); }
   { const char* nf = getenv("ORBFE_NO_FORK"); e->fork_graph = !(nf && nf[0] == '1'); }
@@ -386,6 +387,8 @@ int orbfe_extractor_create(const orbfe_extractor_params* params, int width, int 
     rc = ORBFE_ERR_CUDA;
   if (rc != ORBFE_OK) {
     free_arenas(e);
+    if (e->done) cudaEventDestroy(e->done);
+    if (e->stereo_done) cudaEventDestroy(e->stereo_done);
     if (e->fork_ev) cudaEventDestroy(e->fork_ev);
     if (e->join_ev) cudaEventDestroy(e->join_ev);
     if (e->side) cudaStreamDestroy(e->side);
@@ -410,6 +413,7 @@ void orbfe_extractor_destroy(orbfe_extractor* h) {
   if (e->run_graph) cudaGraphExecDestroy(e->run_graph);
   if (e->stereo_graph) cudaGraphExecDestroy(e->stereo_graph);
   if (e->done) cudaEventDestroy(e->done);
+  if (e->stereo_done) cudaEventDestroy(e->stereo_done);
   if (e->fork_ev) cudaEventDestroy(e->fork_ev);
   if (e->join_ev) cudaEventDestroy(e->join_ev);
   if (e->side) cudaStreamDestroy(e->side);
@@ -596,22 +600,19 @@ int orbfe_extract_run(orbfe_extractor* h, int batch) {
   DeviceGuard guard(e->device);
   const PyrGeom& g = e->geom;
   cudaEvent_t* ev = (e->profiling && e->prof_runs < Extractor::kProfRuns) ? e->prof_ev + 6 * e->prof_runs : nullptr;
+  if (!ev && e->use_graph && (!e->run_graph || e->run_graph_batch != batch)) {
+    // one cudaGraphLaunch instead of 3 memsets + 11 kernel launches: what matters for single-frame latency, where
+    // the kernels are a few microseconds each.  Captured once per batch size, on the calling thread only.
+    if (e->run_graph) { cudaGraphExecDestroy(e->run_graph); e->run_graph = nullptr; }
+    const bool ok = capture_graph(e->stream, &e->run_graph, [&] {
+      if (e->fork_graph) issue_extract_forked(e, batch); else issue_extract(e, batch, nullptr);
+    });
+    if (ok) e->run_graph_batch = batch; else e->use_graph = false;  // plain launches from now on
+  }
   if (ev || !e->use_graph) {
     issue_extract(e, batch, ev);
     if (ev) ++e->prof_runs;
   } else {
-    // one cudaGraphLaunch instead of 3 memsets + 11 kernel launches: what matters for single-frame latency, where
-    // the kernels are a few microseconds each.  Captured once per batch size, on the calling thread only.
-    if (!e->run_graph || e->run_graph_batch != batch) {
-      if (e->run_graph) { cudaGraphExecDestroy(e->run_graph); e->run_graph = nullptr; }
-      cudaGraph_t graph = nullptr;
-      ORBFE_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
-      if (e->fork_graph) issue_extract_forked(e, batch); else issue_extract(e, batch, nullptr);
-      ORBFE_CUDA(cudaStreamEndCapture(e->stream, &graph));
-      ORBFE_CUDA(cudaGraphInstantiate(&e->run_graph, graph, 0));
-      cudaGraphDestroy(graph);
-      e->run_graph_batch = batch;
-    }
     ORBFE_CUDA(cudaGraphLaunch(e->run_graph, e->stream));
   }
   e->launches += (g.nlevels - 1) + (g.fast_strips > 0 ? 1 : 0) + 3;

@@ -20,6 +20,9 @@ struct Extractor {
   cudaStream_t stream = nullptr;
   bool owns_stream = true;
   cudaEvent_t done = nullptr;   // recorded after the last queued work (cross-handle ordering for stereo)
+  // recorded on THIS (left) handle's stream after the stereo kernels; the right handle's stream waits on it, so that
+  // the right handle's next upload / run cannot overwrite the pyramid, keypoints and descriptors the matcher reads
+  cudaEvent_t stereo_done = nullptr;
   int32_t* h_flags = nullptr;   // pinned
   int64_t launches = 0;
   int last_batch = 0;

@@ -256,6 +256,9 @@ __global__ void __launch_bounds__(1024) stereo_median_kernel(const __grid_consta
   const int nL = cntL[b];
   const size_t off = (size_t)b * g.out_cap;
   if (tid == 0) { s_n = 0; s_median = 0; s_removed = 0; }
+  // the reference initialises mvuRight / mvDepth to -1 for all N (:498-499): entries past this image's keypoint
+  // count are defined too, so a caller that downloads `capacity` entries never sees stale values
+  for (int i = nL + tid; i < g.out_cap; i += blockDim.x) { u_right[off + i] = -1.f; depth[off + i] = -1.f; }
   __syncthreads();
   for (int i = tid; i < nL; i += blockDim.x) {
     const int v = sad[off + i];

@@ -32,25 +32,33 @@ int orbfe_stereo_match_run(orbfe_extractor* hl, orbfe_extractor* hr, int batch, 
   cudaEvent_t* ev = nullptr;
   if (l->profiling && l->prof_ev && l->prof_stereo_runs < Extractor::kProfRuns)
     ev = l->prof_ev + 6 * Extractor::kProfRuns + 3 * l->prof_stereo_runs++;
-  if (ev || !l->use_graph) {
-    launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream, ev);
-  } else {
-    // the three stereo kernels as one graph launch (keyed by everything baked into the kernel parameters)
-    if (!l->stereo_graph || l->stereo_graph_batch != batch || l->stereo_graph_right != r || l->stereo_graph_mbf != mbf ||
-        l->stereo_graph_mb != mb) {
-      if (l->stereo_graph) { cudaGraphExecDestroy(l->stereo_graph); l->stereo_graph = nullptr; }
-      cudaGraph_t graph = nullptr;
-      ORBFE_CUDA(cudaStreamBeginCapture(l->stream, cudaStreamCaptureModeThreadLocal));
+  // the three stereo kernels as one graph launch (keyed by everything baked into the kernel parameters)
+  if (!ev && l->use_graph &&
+      (!l->stereo_graph || l->stereo_graph_batch != batch || l->stereo_graph_right != r || l->stereo_graph_mbf != mbf ||
+       l->stereo_graph_mb != mb)) {
+    if (l->stereo_graph) { cudaGraphExecDestroy(l->stereo_graph); l->stereo_graph = nullptr; }
+    const bool ok = capture_graph(l->stream, &l->stereo_graph, [&] {
       launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream, nullptr);
-      ORBFE_CUDA(cudaStreamEndCapture(l->stream, &graph));
-      ORBFE_CUDA(cudaGraphInstantiate(&l->stereo_graph, graph, 0));
-      cudaGraphDestroy(graph);
+    });
+    if (ok) {
       l->stereo_graph_batch = batch;
       l->stereo_graph_right = r;
       l->stereo_graph_mbf = mbf;
       l->stereo_graph_mb = mb;
+    } else {
+      l->use_graph = false;  // plain launches from now on
     }
+  }
+  if (ev || !l->use_graph) {
+    launch_stereo(l->geom, l->arena, r->arena, batch, mbf, mb, l->stream, ev);
+  } else {
     ORBFE_CUDA(cudaGraphLaunch(l->stereo_graph, l->stream));
+  }
+  if (l != r && l->stream != r->stream) {
+    // write-after-read: the matcher reads the right handle's pyramid, keypoints and descriptors on left's stream;
+    // the right handle's NEXT upload / run (on its own stream) must not start before these reads are done
+    ORBFE_CUDA(cudaEventRecord(l->stereo_done, l->stream));
+    ORBFE_CUDA(cudaStreamWaitEvent(r->stream, l->stereo_done, 0));
   }
   l->launches += kLaunchesPerStereo;
   ORBFE_CUDA(cudaGetLastError());

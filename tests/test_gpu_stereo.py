@@ -83,3 +83,57 @@ def test_stereo_frame_one_call(oracle):
             assert np.array_equal(kr[b][:nr[b]], okr) and np.array_equal(dr[b][:nr[b]], odr)
             assert np.array_equal(ur[b][:nl[b]], our) and np.array_equal(dp[b][:nl[b]], odp)
             assert nm[b] == on and on > 50
+
+
+def test_stereo_pipelined_pairs_without_host_sync():
+    """Two DIFFERENT batches of pairs queued back to back on the two handles' streams with no host synchronisation in
+    between (the bench's device-resident loop): the matcher of step k reads the right handle's pyramid / keypoints /
+    descriptors on the LEFT stream, so the right handle's upload + run of step k+1 must wait for it
+    (orbfe_stereo_match_run orders the right stream after the stereo kernels).  Results must equal the synchronous path."""
+    import torch
+    from my_orb_slam2_b200 import orbfe
+    w, h = synth.SHAPES["kitti"]
+    s = synth.SETTINGS["kitti"]
+    params = (s["nfeatures"], s["scale_factor"], s["nlevels"], s["ini_th"], s["min_th"])
+    mbf, mb = np.float32(s["bf"]), np.float32(s["bf"]) / np.float32(s["fx"])
+    B, steps = 8, 4
+    dev = torch.device("cuda", 0)
+    sets = []
+    for k in range(steps):
+        pairs = [synth.synth_pair(w, h, 300 + 10 * k + i) for i in range(2)]
+        idx = np.arange(B) % 2
+        sets.append((torch.from_numpy(np.stack([p[0] for p in pairs])[idx]).to(dev),
+                     torch.from_numpy(np.stack([p[1] for p in pairs])[idx]).to(dev)))
+    L = orbfe.Extractor(*params, w, h, max_batch=B)
+    R = orbfe.Extractor(*params, w, h, max_batch=B)
+    cap = L.capacity
+    lib = orbfe.lib()
+
+    def run(sync_every_step):
+        outs = []
+        for dl, dr in sets:
+            ur = torch.empty((B, cap), dtype=torch.float32).pin_memory()
+            dp = torch.empty((B, cap), dtype=torch.float32).pin_memory()
+            nm = torch.zeros(B, dtype=torch.int32).pin_memory()
+            L.upload(dl.data_ptr(), B, on_device=True)
+            R.upload(dr.data_ptr(), B, on_device=True)
+            L.run(B)
+            R.run(B)
+            orbfe.check(lib.orbfe_stereo_match_run(L._h, R._h, B, mbf, mb))
+            orbfe.check(lib.orbfe_stereo_match_download_async(L._h, B, ur.data_ptr(), dp.data_ptr(), cap, nm.data_ptr()))
+            if sync_every_step:
+                L.sync()
+                R.sync()
+            outs.append((ur, dp, nm))
+        L.sync()
+        R.sync()
+        return [(a.numpy().copy(), b.numpy().copy(), c.numpy().copy()) for a, b, c in outs]
+
+    want = run(True)
+    for _ in range(3):
+        got = run(False)
+        for k in range(steps):
+            assert np.array_equal(got[k][2], want[k][2]), "step %d match counts" % k
+            # entries past an image's keypoint count are -1 (the reference initialises all N to -1)
+            assert np.array_equal(got[k][0], want[k][0]) and np.array_equal(got[k][1], want[k][1]), "step %d" % k
+    assert want[0][2].min() > 50 and not np.array_equal(want[0][0], want[1][0])
