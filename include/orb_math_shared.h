@@ -74,9 +74,13 @@ ORB_HD float orb_fast_atan2_deg(float y, float x) {
  * The cos/sin themselves are evaluated in double (Cody-Waite reduction by
  * pi/2 + degree-13/14 polynomials; |error| < 1e-15, i.e. the float result is
  * the correctly rounded one except with probability ~1e-8). */
+ORB_HD void orb_sincos_rad(float ang, float* cos_out, float* sin_out);
 ORB_HD void orb_sincos_deg(float angle_deg, float* cos_out, float* sin_out) {
   const float factorPI = (float)(3.14159265358979323846 / 180.0);
-  const float ang = ORB_FMUL(angle_deg, factorPI);
+  orb_sincos_rad(ORB_FMUL(angle_deg, factorPI), cos_out, sin_out);
+}
+/* cos / sin of a float angle in RADIANS, rounded to float (the body orb_sincos_deg evaluates). */
+ORB_HD void orb_sincos_rad(float ang, float* cos_out, float* sin_out) {
   double x = (double)ang;
   double ax = x < 0.0 ? -x : x;
   /* quadrant: k = round-to-nearest(ax * 2/pi) via truncation of +0.5 */
