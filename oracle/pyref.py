@@ -56,6 +56,19 @@ def lib():
         L.ref_extractor_level.restype = P
         L.ref_extractor_level.argtypes = [P, C.c_int, P, P, P]
         L.ref_extractor_tables.argtypes = [P, P, P, P, P]
+        L.ref_descriptor_distance.restype = C.c_int
+        L.ref_descriptor_distance.argtypes = [P, P]
+        L.ref_stereo_matches.restype = C.c_int
+        L.ref_stereo_matches.argtypes = [P, P, C.c_float, C.c_float, P, P]
+        L.ref_extract_pair_threads.argtypes = [P, P, P, P, C.c_int, C.c_int, C.c_int]
+        L.ref_extractor_results.restype = C.c_int
+        L.ref_extractor_results.argtypes = [P, P, P, C.c_int]
+        L.ref_search_by_projection_map.restype = C.c_int
+        L.ref_search_by_projection_map.argtypes = [P, P, C.c_float, C.c_float, P]
+        L.ref_search_by_projection_last.restype = C.c_int
+        L.ref_search_by_projection_last.argtypes = [P, P, P, C.c_float, C.c_int, C.c_int, P]
+        L.ref_search_for_triangulation.restype = C.c_int
+        L.ref_search_for_triangulation.argtypes = [P, P, P, C.c_float, C.c_float, C.c_int, C.c_int, P, C.c_int]
         _lib = L
     return _lib
 
@@ -104,3 +117,64 @@ class Extractor:
         out = [np.zeros(self.nlevels, np.float32) for _ in range(4)]
         lib().ref_extractor_tables(self._h, *[_p(a) for a in out])
         return out
+
+    def results(self):
+        """Keypoints / descriptors the handle holds (after extract() or extract_pair_threads())."""
+        cap = self.nfeatures + 4 * self.nlevels + 64
+        while True:
+            kps = np.zeros(cap, KEYPOINT_DTYPE)
+            desc = np.zeros((cap, 32), np.uint8)
+            n = lib().ref_extractor_results(self._h, _p(kps), _p(desc), cap)
+            if n <= cap:
+                return kps[:n].copy(), desc[:n].copy()
+            cap = n
+
+
+def descriptor_distance(a, b):
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    return lib().ref_descriptor_distance(_p(a), _p(b))
+
+
+def extract_pair_threads(left_ex, right_ex, left, right):
+    """The extraction step of the stereo Frame constructor: two std::threads (src/Frame.cc:89-92)."""
+    left = np.ascontiguousarray(left, np.uint8)
+    right = np.ascontiguousarray(right, np.uint8)
+    lib().ref_extract_pair_threads(left_ex._h, right_ex._h, _p(left), _p(right), left.shape[1], left.shape[0],
+                                   left.shape[1])
+    return left_ex.results(), right_ex.results()
+
+
+def stereo_matches(left_ex, right_ex, mbf, mb):
+    """Frame::ComputeStereoMatches on what the two handles hold from their last extraction -> (uRight, depth, n)."""
+    n_left = len(left_ex.results()[0])
+    ur = np.full(max(n_left, 1), -1, np.float32)
+    dp = np.full(max(n_left, 1), -1, np.float32)
+    n = lib().ref_stereo_matches(left_ex._h, right_ex._h, np.float32(mbf), np.float32(mb), _p(ur), _p(dp))
+    return ur[:n_left], dp[:n_left], n
+
+
+# The matcher entry points take the SAME view structs as oracle.pyoracle (make_frame_view, ...): pass those objects.
+def _ref(v):
+    return C.byref(v.struct) if hasattr(v, "struct") else C.byref(v)
+
+
+def search_by_projection_map(frame, mps, th, nnratio):
+    out = np.full(frame.struct.n if hasattr(frame, "struct") else frame.n, -1, np.int32)
+    n = lib().ref_search_by_projection_map(_ref(frame), _ref(mps), th, nnratio, _p(out))
+    return out, n
+
+
+def search_by_projection_last(cur, cam, last, th, mono, check_ori):
+    out = np.full(cur.struct.n if hasattr(cur, "struct") else cur.n, -1, np.int32)
+    n = lib().ref_search_by_projection_last(_ref(cur), _ref(cam), _ref(last), th, int(mono), int(check_ori), _p(out))
+    return out, n
+
+
+def search_for_triangulation(kf1, kf2, F12, ex, ey, only_stereo, check_ori):
+    n1 = kf1.struct.n if hasattr(kf1, "struct") else kf1.n
+    pairs = np.zeros((max(n1, 1), 2), np.int32)
+    F12 = np.ascontiguousarray(F12, np.float32)
+    n = lib().ref_search_for_triangulation(_ref(kf1), _ref(kf2), _p(F12), ex, ey, int(only_stereo), int(check_ori),
+                                           _p(pairs), n1)
+    return pairs[:n].copy()

@@ -16,6 +16,7 @@
 // The library must be linked with -Wl,-Bsymbolic so that the reference's calls bind to the definitions below.
 #include <dlfcn.h>
 
+#include <atomic>
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
@@ -28,6 +29,7 @@
 #include "../include/orb_math_shared.h"
 #include "../include/orbfe_types.h"
 #include "ORBextractor.h"
+#include "ref_driver.h"
 
 #define REF_MODE_LIBM 1
 #define REF_MODE_HEAP_TIES 2
@@ -38,41 +40,33 @@ static int g_mode = 0;
 namespace {
 constexpr size_t kNodeSize = sizeof(std::_List_node<ORB_SLAM2::ExtractorNode>);
 constexpr size_t kArenaBytes = (size_t)256 << 20;
-thread_local unsigned char* t_arena = nullptr;
-thread_local size_t t_arena_used = 0;
-thread_local long t_arena_live = 0;
-thread_local bool t_arena_on = false;
+// ONE arena for the process (objects of the node size may be allocated by one thread and freed by another, e.g. a
+// std::thread state): a bump pointer advanced atomically, so that within each thread later allocations get higher
+// addresses.  Rewound at the start of a reference call when nothing from the arena is alive.
+unsigned char* g_arena = nullptr;
+std::atomic<size_t> g_arena_used{0};
+std::atomic<long> g_arena_live{0};
+std::atomic<int> g_arena_on{0};  // set for the duration of a reference call
 
 inline bool in_arena(void* p) {
-  return t_arena && (unsigned char*)p >= t_arena && (unsigned char*)p < t_arena + kArenaBytes;
+  return g_arena && (unsigned char*)p >= g_arena && (unsigned char*)p < g_arena + kArenaBytes;
 }
-struct ArenaScope {  // one reference call
-  ArenaScope() {
-    if (g_mode & REF_MODE_HEAP_TIES) return;
-    if (!t_arena) t_arena = (unsigned char*)std::malloc(kArenaBytes);
-    if (t_arena_live != 0) { std::fprintf(stderr, "ref_driver: %ld list nodes outlived a call\n", t_arena_live); std::abort(); }
-    t_arena_used = 0;
-    t_arena_on = true;
-  }
-  ~ArenaScope() { t_arena_on = false; }
-};
 }  // namespace
 
 void* operator new(size_t n) {
-  if (t_arena_on && n == kNodeSize) {
+  if (n == kNodeSize && g_arena_on.load(std::memory_order_relaxed)) {
     const size_t sz = (n + 15) & ~(size_t)15;
-    if (t_arena_used + sz > kArenaBytes) { std::fprintf(stderr, "ref_driver: node arena exhausted\n"); std::abort(); }
-    void* p = t_arena + t_arena_used;
-    t_arena_used += sz;
-    ++t_arena_live;
-    return p;
+    const size_t off = g_arena_used.fetch_add(sz);
+    if (off + sz > kArenaBytes) { std::fprintf(stderr, "ref_driver: node arena exhausted\n"); std::abort(); }
+    g_arena_live.fetch_add(1);
+    return g_arena + off;
   }
   void* p = std::malloc(n ? n : 1);
   if (!p) throw std::bad_alloc();
   return p;
 }
 void operator delete(void* p) noexcept {
-  if (in_arena(p)) { --t_arena_live; return; }
+  if (in_arena(p)) { g_arena_live.fetch_sub(1); return; }
   std::free(p);
 }
 void operator delete(void* p, size_t) noexcept { operator delete(p); }
@@ -111,21 +105,23 @@ size_t ref_list_node_size(void) { return kNodeSize; }
 }  // extern "C"
 
 // silence the reference's per-level std::cout line (src/ORBextractor.cc:854) for the duration of a call
-namespace {
-struct CoutMute {
-  std::ios_base::iostate old;
-  CoutMute() : old(std::cout.rdstate()) { std::cout.setstate(std::ios_base::failbit); }
-  ~CoutMute() { std::cout.clear(old); }
-};
-}  // namespace
+RefCallScope::RefCallScope() {
+  mute_ = new std::ios_base::iostate(std::cout.rdstate());
+  std::cout.setstate(std::ios_base::failbit);
+  if (!(g_mode & REF_MODE_HEAP_TIES)) {
+    if (!g_arena) g_arena = (unsigned char*)std::malloc(kArenaBytes);  // virtual until touched
+    if (g_arena_live.load() == 0) g_arena_used.store(0);
+    g_arena_on.store(1);
+  }
+}
+RefCallScope::~RefCallScope() {
+  g_arena_on.store(0);
+  std::ios_base::iostate* st = static_cast<std::ios_base::iostate*>(mute_);
+  std::cout.clear(*st);
+  delete st;
+}
 
 // ---------------------------------------------------------------- ORBextractor
-struct ref_extractor {
-  ORB_SLAM2::ORBextractor* ex;
-  std::vector<cv::KeyPoint> kps;
-  cv::Mat desc;
-};
-
 extern "C" {
 
 ref_extractor* ref_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th) {
@@ -143,8 +139,7 @@ void ref_extractor_destroy(ref_extractor* r) {
 // at most `capacity` are copied out)
 int ref_extract(ref_extractor* r, const uint8_t* image, int width, int height, int stride, orbfe_keypoint* kps,
                 uint8_t* desc, int capacity) {
-  CoutMute mute;
-  ArenaScope arena;
+  RefCallScope scope;
   cv::Mat img(height, width, CV_8UC1, const_cast<uint8_t*>(image), (size_t)stride);
   r->kps.clear();
   r->desc = cv::Mat();

@@ -15,6 +15,7 @@
 
 #include <algorithm>
 #include <cassert>
+#include <climits>
 #include <cmath>
 #include <cstddef>
 #include <cstdint>
@@ -22,7 +23,14 @@
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <fstream>
+#include <limits>
+#include <list>
+#include <map>
 #include <memory>
+#include <numeric>
+#include <set>
+#include <sstream>
 #include <string>
 #include <vector>
 
@@ -389,6 +397,8 @@ class _OutputArray : public _InputArray {
  public:
   _OutputArray() : w_(nullptr) {}
   _OutputArray(Mat& m) : _InputArray(m), w_(&m) {}  // NOLINT
+  // a temporary header (e.g. `R.copyTo(T.rowRange(0,3).colRange(0,3))`): fixed size, written in place
+  _OutputArray(const Mat& m) { own_.reset(new Mat(m)); m_ = own_.get(); w_ = own_.get(); }  // NOLINT
   void create(int r, int c, int type) const { if (w_) w_->create(r, c, type); }
   void create(Size sz, int type) const { if (w_) w_->create(sz, type); }
   void release() const { if (w_) w_->release(); }

@@ -103,3 +103,88 @@ def test_ctor_tables_equal_reference_source(oracle):
         assert np.array_equal(inv, np.array(o.info.inv_scale_factors[:n], np.float32))
         assert np.array_equal(s2, np.array(o.info.level_sigma2[:n], np.float32))
         assert np.array_equal(inv2, np.array(o.info.inv_level_sigma2[:n], np.float32))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Frame::ComputeStereoMatches (src/Frame.cc:496-686) and the hot ORBmatcher members, compiled from the unmodified
+# src/Frame.cc / src/ORBmatcher.cc / src/MapPoint.cc / src/KeyFrame.cc / src/Map.cc (+ the vendored DBoW2 sources).
+# ---------------------------------------------------------------------------------------------------------------
+from cases import views  # noqa: E402
+
+
+@pytest.mark.parametrize("shape,seeds", [("kitti", (0, 1, 2, 3)), ("euroc", (0, 1, 2, 3)), ("tum", (5,))])
+def test_stereo_matches_equal_reference_source(oracle, shape, seeds):
+    s = synth.SETTINGS[shape]
+    w, h = synth.SHAPES[shape]
+    bf, fx = s["bf"] or 40.0, s["fx"]
+    mbf, mb = np.float32(bf), np.float32(bf) / np.float32(fx)
+    pyref.set_mode(pyref.MODE_DETERMINISTIC)
+    for seed in seeds:
+        left, right = synth.synth_pair(w, h, seed)
+        oL, oR = oracle.Extractor(*_params(shape)), oracle.Extractor(*_params(shape))
+        kl, dl = oL.extract(left)
+        kr, dr = oR.extract(right)
+        our, odp, on = oracle.stereo_matches(oL, oR, kl, dl, kr, dr, mbf, mb)
+        rL, rR = pyref.Extractor(*_params(shape)), pyref.Extractor(*_params(shape))
+        # the extraction as the stereo Frame constructor runs it: two threads (src/Frame.cc:89-92)
+        (rkl, rdl), (rkr, rdr) = pyref.extract_pair_threads(rL, rR, left, right)
+        assert np.array_equal(rkl, kl) and np.array_equal(rdl, dl) and np.array_equal(rkr, kr) and np.array_equal(rdr, dr)
+        rur, rdp, rn = pyref.stereo_matches(rL, rR, mbf, mb)
+        assert rn == on and on > 50, "%s seed %d: %d vs %d matches" % (shape, seed, rn, on)
+        assert np.array_equal(rur, our), "%s seed %d: mvuRight" % (shape, seed)
+        assert np.array_equal(rdp, odp), "%s seed %d: mvDepth" % (shape, seed)
+
+
+def test_descriptor_distance_equals_reference_source(oracle):
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 256, (256, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (256, 32), dtype=np.uint8)
+    b[:32] = a[:32]
+    b[32:64] = ~a[32:64]
+    for i in range(256):
+        assert pyref.descriptor_distance(a[i], b[i]) == oracle.descriptor_distance(a[i], b[i])
+    assert pyref.descriptor_distance(a[0], b[0]) == 0 and pyref.descriptor_distance(a[40], b[40]) == 256
+
+
+def _norm(a):
+    return np.where(a == -2, -1, a)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_search_by_projection_equals_reference_source(oracle, seed):
+    ex = oracle.Extractor(*_params("kitti"))
+    kp, desc = ex.extract(synth.synth_image(1241, 376, seed))
+    frame = synth.frame_arrays(kp, desc, (0.0, 0.0, 1241.0, 376.0), seed=seed)
+    # a11: (Frame, local map points), config 4 size, th 1 / 3 / 5
+    mps = synth.map_points_case(frame, 20000, 1500, seed=seed)
+    fv, mv = views(oracle, frame=frame, mps=mps)
+    for th, ratio in ((1.0, 0.8), (3.0, 0.8), (5.0, 0.9)):
+        oa, on = oracle.search_by_projection_map(fv, mv, th, ratio)
+        ra, rn = pyref.search_by_projection_map(fv, mv, th, ratio)
+        assert rn == on and on > 300, "th %g: %d vs %d" % (th, rn, on)
+        assert np.array_equal(ra, oa), "th %g" % th
+    # a12: (CurrentFrame, LastFrame) with and without the rotation histogram, stereo and mono, forward / backward
+    for tz in (0.0, 1.5, -1.5):
+        last, cam = synth.last_frame_case(frame, seed=seed, tz=tz)
+        fv, lv, cv = views(oracle, frame=frame, last=last, cam=cam)
+        for th, mono, ori in ((7.0, False, True), (7.0, False, False), (15.0, True, True), (14.0, False, True)):
+            oa, on = oracle.search_by_projection_last(fv, cv, lv, th, mono, ori)
+            ra, rn = pyref.search_by_projection_last(fv, cv, lv, th, mono, ori)
+            assert rn == on, "tz %g th %g mono %d ori %d: %d vs %d" % (tz, th, mono, ori, rn, on)
+            assert np.array_equal(_norm(ra), _norm(oa)), "tz %g th %g mono %d ori %d" % (tz, th, mono, ori)
+        assert on > 100
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_search_for_triangulation_equals_reference_source(oracle, seed):
+    ex = oracle.Extractor(*_params("kitti"))
+    kp, desc = ex.extract(synth.synth_image(1241, 376, seed))
+    k1, k2, F12, ep = synth.keyframe_pair_case(kp, desc, seed=seed)
+    v1 = views(oracle, kf=k1)
+    v2 = views(oracle, kf=k2)
+    for only_stereo in (False, True):
+        for ori in (False, True):
+            op = oracle.search_for_triangulation(v1, v2, F12, float(ep[0]), float(ep[1]), only_stereo, ori)
+            rp = pyref.search_for_triangulation(v1, v2, F12, float(ep[0]), float(ep[1]), only_stereo, ori)
+            assert np.array_equal(rp, op), "only_stereo %d ori %d: %d vs %d pairs" % (only_stereo, ori, len(rp), len(op))
+    assert len(op) > 50
