@@ -289,6 +289,17 @@ int orbfe_hamming_bruteforce_device(orbfe_matcher* m, const uint8_t* d_query, in
  * [shard][nq]) into the global top-2 (device arrays [nq]). */
 int orbfe_hamming_merge_device(orbfe_matcher* m, const uint64_t* d_best_all, const uint64_t* d_second_all,
                                int shards, int nq, uint64_t* d_best, uint64_t* d_second);
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as
+ * orbfe_hamming_bruteforce_device (device pointers in and out, asynchronous on `stream`, a cudaStream_t; NULL = the
+ * legacy default stream) on the CURRENT device, but no matcher handle and NO allocation: the per-slice partial results
+ * live in a 4 MiB file-scope static __device__ array (my_orb_slam2_b200/csrc/noalloc.cu) that every GPU loading the
+ * library holds until exit.  Limit: nq <= 32768 queries (any map size with index_base + nm <= 2^32); larger calls
+ * return ORBFE_ERR_CAPACITY with a message.  All calls on a device share that array: calls that overlap on the GPU
+ * (different streams / threads) race, so serialise them.  The first call on each device resolves the array's device
+ * address with cudaGetSymbolAddress; make that first call outside graph capture. */
+int orbfe_hamming_bruteforce_device_noalloc(void* stream, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm,
+                                            int64_t index_base, uint64_t* d_best, uint64_t* d_second);
 int orbfe_matcher_sync(orbfe_matcher* m);
 /* Measured 32-bit POPC results per second of the matcher's device (register-only probe kernel): the roofline
  * denominator of the Hamming kernels ("measure it"). */

@@ -152,6 +152,7 @@ SYMBOLS = {
     "orbfe_hamming_bruteforce": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_bruteforce_device": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_merge_device": (_I, [_P, _P, _P, _I, _I, _P, _P]),
+    "orbfe_hamming_bruteforce_device_noalloc": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_matcher_sync": (_I, [_P]),
     "orbfe_measure_popc_peak": (_I, [_P, C.POINTER(C.c_double)]),
 }
