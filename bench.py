@@ -4,15 +4,19 @@
     frames/sec of ORB extract + match on KITTI-shaped 1241x376 stereo pairs, 2000 features per image
     (configs[1]: ORB extraction of both images + Frame::ComputeStereoMatches), plus p50 frame latency.
 
-A "step" is one pass of the hot path over one batch of `--batch` synthetic stereo pairs per GPU.
+A "step" is `--batches` (100) passes of the hot path, each over one batch of `--batch` (64) synthetic stereo pairs per
+GPU, so that `--steps 20` times >= 2 s of GPU work; every rank owns 64 DISTINCT pairs and each batch starts at another
+offset into them (a handle slot sees a different image every batch).
   value : whole-job stereo frames/s with the inputs already resident in HBM (device images -> pyramid level 0 ->
           all kernels -> results left on the device), timed with CUDA events on the handles' streams.
   e2e   : the same through the C ABI with HOST buffers: pinned host images -> H2D -> kernels -> keypoints,
           descriptors, uRight, depth back in host memory, every step, inside the timed region.
   roofline / stages : per-stage CUDA-event times recorded inside the timed region by the library itself.
-  cpu_baseline      : the CPU oracle (a port of the reference's code path; the reference itself cannot be built here)
-                      timed single-threaded on a bounded sample of the same workload.
-`--impl reference` times that CPU path on all host cores instead of the GPU path.
+  cpu_baseline      : the UNMODIFIED reference sources compiled here (oracle/_ref/libref_orbslam2.so: src/ORBextractor.cc,
+                      Frame.cc, ... against an OpenCV stand-in whose pixel primitives are scalar restatements), timed
+                      single-threaded as ORB-SLAM2 runs it, with its real two L/R threads, p50/p95, the port beside it and
+                      the measured SIMD factor of real cv2 primitives over the stand-ins.
+`--impl reference` times that CPU path on all host cores (one instance per core) instead of the GPU path.
 Multi-GPU (`torchrun ... bench.py --gpus N`): frames are sharded by rank, no data-path collective ("weak").
 """
 import argparse
@@ -35,7 +39,9 @@ S = synth.SETTINGS[SHAPE]
 PARAMS = (S["nfeatures"], S["scale_factor"], S["nlevels"], S["ini_th"], S["min_th"])
 MBF = np.float32(S["bf"])
 MB = np.float32(S["bf"]) / np.float32(S["fx"])
-N_UNIQUE = 8  # distinct synthetic pairs; the batch cycles through them (each copy has its own buffers)
+N_UNIQUE = 64  # distinct synthetic pairs per rank (one batch); every batch of a step starts at another offset
+WORKLOAD = "configs[1]: KITTI00-shaped stereo pair 1241x376, 2000 features, extract + ComputeStereoMatches"
+METRIC = "stereo frames/sec, ORB extract (L+R) + ComputeStereoMatches, KITTI 1241x376 2k feat"
 
 
 def make_pairs(n_unique, seed0):
@@ -83,22 +89,146 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(k)
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.004)
 
     def result(self):
         self.stop_flag = True
         return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons)}
+                "reasons": sorted(self.reasons), "samples": len(self.samples), "period_ms": 4}
 
 
-def cpu_pair_seconds(pyoracle, left, right):
-    """One stereo frame through the CPU oracle (extract L, extract R, ComputeStereoMatches); returns seconds."""
+def ref_pair(pyref, rL, rR, left, right, threads):
+    """One stereo frame through the compiled reference: ORBextractor::operator() for L and R (sequentially, or on the
+    reference's two std::threads, src/Frame.cc:89-92), then Frame::ComputeStereoMatches.  Returns seconds."""
     t0 = time.perf_counter()
-    oL, oR = pyoracle.Extractor(*PARAMS), pyoracle.Extractor(*PARAMS)
+    if threads:
+        pyref.extract_pair_threads(rL, rR, left, right)
+    else:
+        rL.extract(left)
+        rR.extract(right)
+    pyref.stereo_matches(rL, rR, MBF, MB)
+    return time.perf_counter() - t0
+
+
+def port_pair(pyoracle, oL, oR, left, right):
+    t0 = time.perf_counter()
     kl, dl = oL.extract(left)
     kr, dr = oR.extract(right)
     pyoracle.stereo_matches(oL, oR, kl, dl, kr, dr, MBF, MB)
     return time.perf_counter() - t0
+
+
+def simd_factor(pyoracle, img):
+    """How much faster real (SIMD) OpenCV runs the pixel primitives than the scalar stand-ins the compiled reference
+    and the port use: pyramid (7 x resize) + whole-level FAST at 20 + 8 x GaussianBlur on one frame.  None without cv2."""
+    try:
+        import cv2
+    except Exception:
+        return None
+    sizes, sf = [], np.float32(1.0)
+    for lv in range(S["nlevels"]):
+        inv = np.float32(1.0) / sf
+        sizes.append((int(np.rint(np.float32(W) * inv)), int(np.rint(np.float32(H) * inv))))
+        sf = np.float32(float(sf) * float(np.float32(S["scale_factor"])))
+    cv2.setNumThreads(1)
+    fast = cv2.FastFeatureDetector_create(S["ini_th"], True)
+
+    def chain_cv2():
+        lv = img
+        for i, (w, h) in enumerate(sizes):
+            if i:
+                lv = cv2.resize(lv, (w, h), interpolation=cv2.INTER_LINEAR)
+            fast.detect(lv)
+            cv2.GaussianBlur(lv, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
+
+    def chain_port():
+        lv = img
+        for i, (w, h) in enumerate(sizes):
+            if i:
+                lv = pyoracle.resize_linear(lv, w, h)
+            pyoracle.fast9_16(lv, S["ini_th"], True)
+            pyoracle.gaussian_blur7(lv)
+
+    out = []
+    for fn in (chain_cv2, chain_port):
+        fn()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            fn()
+        out.append((time.perf_counter() - t0) / 3)
+    return {"cv2_ms": 1e3 * out[0], "scalar_ms": 1e3 * out[1], "factor": out[1] / out[0], "cv2_version": cv2.__version__,
+            "what": "7 x resize + 8 x FAST(20, nms) on whole levels + 8 x GaussianBlur 7x7 on one KITTI frame, 1 thread"}
+
+
+def cpu_baseline(lefts, rights, seconds):
+    """The CPU baseline block (rank 0, N = 1): bounded samples of the same workload on the host cores."""
+    from oracle import pyoracle, pyref
+    pyoracle.build()
+    pyref.set_mode(pyref.MODE_AS_IS)  # libm cos/sin + plain malloc: the reference exactly as it runs
+    rL, rR = pyref.Extractor(*PARAMS), pyref.Extractor(*PARAMS)
+    n = len(lefts)
+    ref_pair(pyref, rL, rR, lefts[0], rights[0], False)
+    ts, k = [], 0
+    while sum(ts) < seconds:
+        ts.append(ref_pair(pyref, rL, rR, lefts[k % n], rights[k % n], False))
+        k += 1
+    t2, k2 = [], 0
+    while sum(t2) < seconds / 2:
+        t2.append(ref_pair(pyref, rL, rR, lefts[k2 % n], rights[k2 % n], True))
+        k2 += 1
+    oL, oR = pyoracle.Extractor(*PARAMS), pyoracle.Extractor(*PARAMS)
+    tp, k3 = [], 0
+    while sum(tp) < seconds / 4:
+        tp.append(port_pair(pyoracle, oL, oR, lefts[k3 % n], rights[k3 % n]))
+        k3 += 1
+    pyref.set_mode(pyref.MODE_DETERMINISTIC)
+    return {"value": len(ts) / sum(ts), "unit": "frames/s", "cores": 1, "kind": "reference",
+            "sample": "%d stereo frames (ORBextractor L then R + ComputeStereoMatches), single thread, unmodified "
+                      "src/ORBextractor.cc + src/Frame.cc compiled -O3 against scalar stand-ins of the OpenCV "
+                      "primitives (see simd)" % len(ts),
+            "ms_p50": 1e3 * float(np.percentile(ts, 50)), "ms_p95": 1e3 * float(np.percentile(ts, 95)),
+            "two_threads": {"value": len(t2) / sum(t2), "cores": 2, "ms_p50": 1e3 * float(np.percentile(t2, 50)),
+                            "ms_p95": 1e3 * float(np.percentile(t2, 95)),
+                            "sample": "%d frames, L and R on two std::threads as src/Frame.cc:89-92" % len(t2)},
+            "port": {"value": len(tp) / sum(tp), "cores": 1, "kind": "port",
+                     "sample": "%d frames through the oracle restatement (oracle/*.cc)" % len(tp)},
+            "simd": simd_factor(pyoracle, lefts[0])}
+
+
+def parity_block(orbfe, lefts, rights, local):
+    """GPU results against the compiled reference on a few pairs of the bench's own inputs, plus the reference's as-is
+    divergence (heap-address quadtree ties, src/ORBextractor.cc:686; libm cos/sin, :112-113) per image."""
+    from oracle import pyref
+    n = min(4, len(lefts))
+    L = orbfe.Extractor(*PARAMS, W, H, max_batch=n, device=local)
+    R = orbfe.Extractor(*PARAMS, W, H, max_batch=n, device=local)
+    kl, dl, nl, kr, dr, nr, ur, dp, nm = orbfe.stereo_frame(L, R, lefts[:n], rights[:n], MBF, MB)
+    R.close()
+    L.close()
+    rL, rR = pyref.Extractor(*PARAMS), pyref.Extractor(*PARAMS)
+    equal, asis = True, []
+    for b in range(n):
+        pyref.set_mode(pyref.MODE_DETERMINISTIC)
+        (rkl, rdl), (rkr, rdr) = pyref.extract_pair_threads(rL, rR, lefts[b], rights[b])
+        rur, rdp, rn = pyref.stereo_matches(rL, rR, MBF, MB)
+        ok = (nl[b] == len(rkl) and nr[b] == len(rkr) and np.array_equal(kl[b][:nl[b]], rkl)
+              and np.array_equal(dl[b][:nl[b]], rdl) and np.array_equal(kr[b][:nr[b]], rkr)
+              and np.array_equal(dr[b][:nr[b]], rdr) and np.array_equal(ur[b][:nl[b]], rur)
+              and np.array_equal(dp[b][:nl[b]], rdp) and int(nm[b]) == rn)
+        equal = equal and bool(ok)
+        pyref.set_mode(pyref.MODE_LIBM)
+        _, ldl = rL.extract(lefts[b])
+        pyref.set_mode(pyref.MODE_HEAP_TIES)
+        hk, _ = rL.extract(lefts[b])
+        a = set(zip(rkl["x"].tolist(), rkl["y"].tolist(), rkl["octave"].tolist()))
+        h = set(zip(hk["x"].tolist(), hk["y"].tolist(), hk["octave"].tolist()))
+        asis.append({"keypoints": int(len(rkl)), "descriptor_bits_changed_by_libm_cos_sin": int(np.unpackbits(ldl ^ rdl).sum()),
+                     "keypoints_lost_with_heap_address_ties": len(a - h), "keypoints_gained_with_heap_address_ties": len(h - a)})
+    pyref.set_mode(pyref.MODE_DETERMINISTIC)
+    return {"pairs_checked": n, "gpu_equal_to_reference_source": equal,
+            "what": "keypoints, descriptors (L and R), mvuRight, mvDepth bit-equal to the compiled unmodified reference "
+                    "(deterministic mode: creation-order quadtree ties, correctly rounded cos/sin)",
+            "angle_bin_flips": 0 if equal else None, "as_is_divergence_left_images": asis}
 
 
 _CPU_STATE = {}
@@ -106,36 +236,33 @@ _CPU_STATE = {}
 
 def _cpu_init(per_core):
     """Pool initializer: each worker process generates its own frames and extractors once, outside any timing."""
-    from oracle import pyoracle
+    from oracle import pyref
     lefts, rights = make_pairs(per_core, 1000 + (os.getpid() % 9973))
-    _CPU_STATE.update(lefts=lefts, rights=rights, oL=pyoracle.Extractor(*PARAMS), oR=pyoracle.Extractor(*PARAMS),
-                      po=pyoracle)
+    pyref.set_mode(pyref.MODE_AS_IS)
+    _CPU_STATE.update(lefts=lefts, rights=rights, rL=pyref.Extractor(*PARAMS), rR=pyref.Extractor(*PARAMS), pr=pyref)
 
 
 def _cpu_worker(reps):
     st = _CPU_STATE
-    po, oL, oR = st["po"], st["oL"], st["oR"]
     t0 = time.perf_counter()
     for r in range(reps):
         for i in range(len(st["lefts"])):
-            kl, dl = oL.extract(st["lefts"][i])
-            kr, dr = oR.extract(st["rights"][i])
-            po.stereo_matches(oL, oR, kl, dl, kr, dr, MBF, MB)
+            ref_pair(st["pr"], st["rL"], st["rR"], st["lefts"][i], st["rights"][i], False)
     return time.perf_counter() - t0
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port; /root/reference needs OpenCV C++ and cannot be built)
-    on all host cores, one instance per core, each looping over its own frames."""
+    """--impl reference: the reference's own CPU implementation of the path (oracle/_ref/libref_orbslam2.so, the
+    unmodified sources compiled here) on all host cores, one instance per core, each looping over its own frames."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import multiprocessing as mp
-    from oracle import pyoracle
-    pyoracle.build()
+    from oracle import pyref
+    pyref.lib()
     cores = os.cpu_count() or 1
     per_core = 2
-    reps = 4
+    reps = 2
     ctx = mp.get_context("fork")
     with ctx.Pool(cores, initializer=_cpu_init, initargs=(per_core,)) as pool:
         for _ in range(args.warmup):
@@ -149,14 +276,14 @@ def run_reference(args):
     total = sum(times)
     value = frames * args.steps / total
     line = {
-        "impl": "reference", "metric": "stereo frames/sec, ORB extract (L+R) + ComputeStereoMatches, KITTI 1241x376 2k feat",
+        "impl": "reference", "metric": METRIC,
         "value": value, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "configs[1]: KITTI00-shaped stereo pair 1241x376, 2000 features, extract + ComputeStereoMatches",
-                   "frames_per_step": frames},
-        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port",
-                         "sample": "%d stereo frames per step, one oracle instance per core" % frames},
+        "config": {"workload": WORKLOAD, "frames_per_step": frames},
+        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "reference",
+                         "sample": "%d stereo frames per step, one instance of the compiled unmodified reference per "
+                                   "core (scalar stand-ins for the OpenCV primitives)" % frames},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -424,25 +551,31 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = args.batch
+    NB = args.batches
     dev = torch.device("cuda", local)
 
-    # ---- synthetic inputs: frames sharded by rank (rank r owns seeds 100*r ...) ----
-    lefts_u, rights_u = make_pairs(N_UNIQUE, 100 * rank)
-    idx = np.arange(B) % N_UNIQUE
-    h_left = torch.empty((B, H, W), dtype=torch.uint8).pin_memory()
-    h_right = torch.empty((B, H, W), dtype=torch.uint8).pin_memory()
+    # ---- synthetic inputs: frames sharded by rank (rank r owns seeds 1000*r ...), N_UNIQUE distinct pairs; the host
+    # and device buffers hold N_UNIQUE + B images (image i = pair i mod N_UNIQUE) so that a batch of B consecutive
+    # images can start at any offset < N_UNIQUE ----
+    lefts_u, rights_u = make_pairs(N_UNIQUE, 1000 * rank)
+    idx = np.arange(N_UNIQUE + B) % N_UNIQUE
+    h_left = torch.empty((N_UNIQUE + B, H, W), dtype=torch.uint8).pin_memory()
+    h_right = torch.empty((N_UNIQUE + B, H, W), dtype=torch.uint8).pin_memory()
     h_left.numpy()[:] = lefts_u[idx]
     h_right.numpy()[:] = rights_u[idx]
     d_left = h_left.to(dev)
     d_right = h_right.to(dev)
+    offs = [(7 * j) % N_UNIQUE for j in range(max(NB, N_UNIQUE))]  # 7 is coprime to 64: all offsets are visited
+    dptr = [(d_left.data_ptr() + o * W * H, d_right.data_ptr() + o * W * H) for o in offs]
+    hptr = [(h_left.data_ptr() + o * W * H, h_right.data_ptr() + o * W * H) for o in offs]
 
     lib = orbfe.lib()
 
     class Rig:
         """A stereo rig: left + right extractor handles, each on its own stream as the reference drives them from
-        two threads (src/Frame.cc:89-92; the stereo matcher joins them), plus pinned host result buffers.  The
-        kernels of the two handles overlap on the GPU (tails and the latency-bound quadtree of one are filled by
-        the other).  Several rigs let the e2e leg overlap one step's copies with another step's kernels and a third one's result drain."""
+        two threads (src/Frame.cc:89-92; the stereo matcher joins them, and the right stream is ordered after the
+        matcher's reads), plus pinned host result buffers.  Several rigs let the e2e leg overlap one batch's copies
+        with another batch's kernels and a third one's result drain."""
 
         def __init__(self):
             self.L = orbfe.Extractor(*PARAMS, W, H, max_batch=B, device=local)
@@ -485,19 +618,24 @@ def run_gpu(args):
     cap = L.capacity
     sL = torch.cuda.ExternalStream(L.stream, device=dev)
 
-    def step_device():
-        L.upload(d_left.data_ptr(), B, on_device=True)
-        R.upload(d_right.data_ptr(), B, on_device=True)
+    def batch_device(j, ptrs=None):
+        pl, pr = dptr[j % len(dptr)] if ptrs is None else ptrs
+        L.upload(pl, B, on_device=True)
+        R.upload(pr, B, on_device=True)
         rigs[0].kernels()
 
-    def step_e2e(k):
+    def step_device():
+        for j in range(NB):
+            batch_device(j)
+
+    def batch_e2e(k):
         """pinned host images -> H2D -> kernels -> keypoints, descriptors, uRight, depth in pinned host memory.
-        Software-pipelined over the rigs: step k's copies overlap step k-1's kernels (different streams); measured
-        50.3k / 51.3k / 51.7k frames/s with 2 / 3 / 4 rigs (the input traffic sits at 47-48 of the link's 55 GB/s)."""
+        Software-pipelined over the rigs: batch k's copies overlap batch k-1's kernels (different streams)."""
         g = rigs[k % len(rigs)]
-        g.finish()  # step k-2's results are complete and checked before its buffers are reused
-        g.L.upload(h_left.data_ptr(), B)
-        g.R.upload(h_right.data_ptr(), B)
+        g.finish()  # the results of the batch that used this rig last are complete and checked before reuse
+        pl, pr = hptr[k % len(hptr)]
+        g.L.upload(pl, B)
+        g.R.upload(pr, B)
         g.kernels()
         g.download_async()
 
@@ -514,11 +652,18 @@ def run_gpu(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
     # ---- device-resident leg (value) ----
-    # every step ends on L's stream (the stereo matcher waits for R's stream), so events on L's stream bracket it
-    # (alternating the steps between the two rigs, four streams, was measured: no gain, 54.9k vs 54.8k frames/s)
+    # every batch ends on L's stream (the stereo matcher waits for R's stream), so events on L's stream bracket it
     for _ in range(args.warmup):
-        step_device()
+        for j in range(min(NB, 8)):
+            batch_device(j)
     barrier()
     launches0 = L.launch_count + R.launch_count
     sampler = ClockSampler(local)
@@ -532,17 +677,40 @@ def run_gpu(args):
     ms_dev = max_over_ranks(e0.elapsed_time(e1))
     clocks = sampler.result()
     launches = L.launch_count + R.launch_count - launches0
-    # a few copies per step (cudaMemcpy2DAsync D2D of level 0) are not kernels of ours and are not counted
+    # a few copies per batch (cudaMemcpy2DAsync D2D of level 0) are not kernels of ours and are not counted
+
+    # ---- the same leg on DENSE images (uniform noise: every pixel a candidate region, ~4x the FAST / quadtree work;
+    # right = left shifted by 8 px so the stereo matcher has true matches) ----
+    n_noise = [synth.noise_image(W, H, 5000 + 100 * rank + i) for i in range(B)]
+    d_nl = torch.from_numpy(np.stack(n_noise)).to(dev)
+    d_nr = torch.from_numpy(np.stack([np.roll(im, -8, axis=1) for im in n_noise])).to(dev)
+    nb_noise = max(4, NB // 5)
+    for j in range(3):
+        batch_device(j, (d_nl.data_ptr(), d_nr.data_ptr()))
+    barrier()
+    n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0.record(sL)
+    for j in range(nb_noise):
+        batch_device(j, (d_nl.data_ptr(), d_nr.data_ptr()))
+    n1.record(sL)
+    barrier()
+    ms_noise = max_over_ranks(n0.elapsed_time(n1))
+    noise = {"value": B * nb_noise * world / (ms_noise * 1e-3), "unit": "frames/s", "ms_per_batch": ms_noise / nb_noise,
+             "batches": nb_noise, "unique_pairs": B,
+             "workload": "same path on uniform-noise images (dense corners), right = left shifted 8 px"}
+    del d_nl, d_nr
 
     # ---- per-stage pass: the same step, K more times, with the library's per-stage CUDA events on each handle's
     # stream and the two handles serialised (host sync in between) so that a stage's time is that kernel alone ----
     L.set_profiling(True)
     R.set_profiling(True)
-    for _ in range(args.steps):
-        L.upload(d_left.data_ptr(), B, on_device=True)
+    n_stage = min(100, max(10, NB))
+    for j in range(n_stage):
+        pl, pr = dptr[j % len(dptr)]
+        L.upload(pl, B, on_device=True)
         L.run(B)
         L.sync()
-        R.upload(d_right.data_ptr(), B, on_device=True)
+        R.upload(pr, B, on_device=True)
         R.run(B)
         R.sync()
         orbfe.check(lib.orbfe_stereo_match_run(L._h, R._h, B, MBF, MB))
@@ -553,28 +721,50 @@ def run_gpu(args):
     R.set_profiling(False)
 
     # ---- end-to-end leg (host buffers through the C ABI) ----
-    for k in range(len(rigs) * max(1, args.warmup // 2)):
-        step_e2e(k)
+    for k in range(len(rigs) * max(2, args.warmup)):
+        batch_e2e(k)
     for g in rigs:
         g.finish()
     barrier()
+    sampler2 = ClockSampler(local)
+    sampler2.start()
     t0 = time.perf_counter()
-    for k in range(args.steps):
-        step_e2e(k)
+    for k in range(args.steps * NB):
+        batch_e2e(k)
     for g in rigs:
         g.finish()
     torch.cuda.synchronize()
     t_e2e = max_over_ranks(time.perf_counter() - t0)
-    # what the host link can do: one pinned 30 MB image batch to the device, best of 5 (the e2e leg moves
-    # 2 * B * W * H bytes in and the results out every step)
-    h2d_gbs = 0.0
+    clocks_e2e = sampler2.result()
+    # what the host link can do with ALL ranks copying at once (no kernels): every rank moves its pinned image buffer
+    # to the device / a result-sized buffer back, 5 times back to back, after a barrier; the sum over the ranks is
+    # the concurrent ceiling the e2e leg's traffic is compared with
+    nbytes = h_left.numel()
+    barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
     for _ in range(5):
-        ev0.record()
         d_left.copy_(h_left, non_blocking=True)
-        ev1.record()
-        torch.cuda.synchronize()
-        h2d_gbs = max(h2d_gbs, h_left.numel() / (ev0.elapsed_time(ev1) * 1e-3) / 1e9)
+    ev1.record()
+    torch.cuda.synchronize()
+    h2d_rank = 5 * nbytes / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+    barrier()
+    ev0.record()
+    for _ in range(5):
+        h_right.copy_(d_right, non_blocking=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    d2h_rank = 5 * nbytes / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+    barrier()
+    ev0.record()
+    for _ in range(5):
+        d_left.copy_(h_left, non_blocking=True)
+        h_right.copy_(d_right, non_blocking=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    bidir_rank = 5 * 2 * nbytes / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+    h2d_all, d2h_all, bidir_all = sum_over_ranks(h2d_rank), sum_over_ranks(d2h_rank), sum_over_ranks(bidir_rank)
+    h_right.numpy()[:] = rights_u[idx]
     n_left = int(rigs[0].cntL.numpy().sum())
     n_match = int(rigs[0].nm.numpy().sum())
     kpL, kpR, dsL, dsR, cntL, cntR = rigs[0].kpL, rigs[0].kpR, rigs[0].dsL, rigs[0].dsR, rigs[0].cntL, rigs[0].cntR
@@ -618,18 +808,33 @@ def run_gpu(args):
             dist.destroy_process_group()
         return
 
-    # ---- CPU baseline on a bounded sample (rank 0, N=1 only) ----
-    cpu = None
+    # ---- the drop-in call sequence Tracking would execute (src/Frame.cc:89-102), timed in C++: compat::ORBextractor
+    # operator() for L and R from two threads on pageable cv::Mat buffers, join, ComputeStereoMatches ----
+    dropin = None
+    exe = os.path.join(ROOT, "compat", "_build", "bench_dropin")
+    if os.path.exists(exe) and not args.no_dropin:
+        import subprocess
+        import tempfile
+        with tempfile.NamedTemporaryFile(suffix=".raw") as tf:
+            for i in range(8):
+                tf.write(lefts_u[i].tobytes())
+                tf.write(rights_u[i].tobytes())
+            tf.flush()
+            env = dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "")) \
+                if "CUDA_VISIBLE_DEVICES" in os.environ else dict(os.environ)
+            try:
+                r = subprocess.run([exe, tf.name, "8", str(W), str(H), str(S["nfeatures"]), repr(float(S["bf"])),
+                                    repr(float(S["fx"])), str(args.latency_frames), "20"], capture_output=True, text=True,
+                                   timeout=120, env=env)
+                dropin = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else {"error": r.stderr[-300:]}
+            except Exception as ex:  # the figure is an extra: never fail the bench line for it
+                dropin = {"error": repr(ex)[:300]}
+
+    # ---- CPU baseline + parity block on bounded samples (rank 0, N=1 only) ----
+    cpu, parity = None, None
     if world == 1 and not args.no_cpu_baseline:
-        from oracle import pyoracle
-        pyoracle.build()
-        t_cpu, n_cpu = 0.0, 0
-        while t_cpu < args.cpu_seconds:
-            t_cpu += cpu_pair_seconds(pyoracle, lefts_u[n_cpu % N_UNIQUE], rights_u[n_cpu % N_UNIQUE])
-            n_cpu += 1
-        cpu = {"value": n_cpu / t_cpu, "unit": "frames/s", "cores": 1, "kind": "port",
-               "sample": "%d stereo frames (extract L+R sequentially + ComputeStereoMatches), single thread; "
-                         "the reference uses 2 threads for L/R (src/Frame.cc:89-92)" % n_cpu}
+        cpu = cpu_baseline(lefts_u, rights_u, args.cpu_seconds)
+        parity = parity_block(orbfe, lefts_u, rights_u, local)
 
     # ---- roofline of the dominant kernel ----
     peaks = {}
@@ -677,40 +882,69 @@ def run_gpu(args):
                      "warp_inst_per_launch": winst * B / tj[kname]["images"]}
     except Exception:
         pass
-    frames = B * args.steps * world
+    frames = B * NB * args.steps * world
     value = frames / (ms_dev * 1e-3)
+    e2e_value = frames / t_e2e
+    h2d_step = 2 * B * NB * W * H
+    d2h_step = int(NB * (2 * B * cap * 60 + 2 * B * cap * 4 + 3 * B * 4))
+    e2e_h2d_gbs = h2d_step * args.steps * world / t_e2e / 1e9
+    e2e_d2h_gbs = d2h_step * args.steps * world / t_e2e / 1e9
+    topo = None
+    try:
+        import subprocess
+        topo = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout[:4000]
+    except Exception:
+        pass
     line = {
-        "metric": "stereo frames/sec, ORB extract (L+R) + ComputeStereoMatches, KITTI 1241x376 2k feat",
+        "metric": METRIC,
         "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "configs[1]: KITTI00-shaped stereo pair 1241x376, 2000 features, extract + ComputeStereoMatches",
-                   "pairs_per_step_per_gpu": B, "unique_pairs": N_UNIQUE,
-                   "l2": "inputs + pyramids of one step = %.0f MB > 126 MB L2" % (2 * B * (W * H + lp * 1.03) / 1e6),
+        "config": {"workload": WORKLOAD,
+                   "pairs_per_batch_per_gpu": B, "batches_per_step": NB, "pairs_per_step_per_gpu": B * NB,
+                   "unique_pairs": N_UNIQUE, "timed_region_s": ms_dev * 1e-3,
+                   "l2": "inputs + pyramids of one batch = %.0f MB > 126 MB L2; every batch reads other images" %
+                         (2 * B * (W * H + lp * 1.03) / 1e6),
                    "keypoints_per_image": kp_per_img, "stereo_matches_per_frame": n_match / max(B, 1)},
-        "e2e": {"value": B * args.steps * world / t_e2e, "unit": "frames/s", "h2d_bytes_per_step": 2 * B * W * H,
-                "d2h_bytes_per_step": int(2 * B * cap * 60 + 2 * B * cap * 4 + 3 * B * 4)},
+        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step,
+                "timed_region_s": t_e2e,
+                "latency_ms_p50": float(np.percentile(lat, 50)) if lat else None,
+                "latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
+                "latency_what": "one stereo pair in flight through orbfe_stereo_frame: pinned host images in, keypoints / "
+                                "descriptors / uRight / depth on the host out",
+                "dropin_latency": dropin,
+                "dropin_what": "compat::ORBextractor::operator() for L and R on two threads (pageable buffers) + "
+                               "ComputeStereoMatches, the sequence of src/Frame.cc:89-102, timed in C++ "
+                               "(compat/bench_dropin.cc)",
+                "clocks": clocks_e2e},
         "latency_ms_p50": float(np.percentile(lat, 50)) if lat else None,
         "latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
         "gpu_launches": int(launches),
         "clocks": clocks,
+        "noise": noise,
         "host": {"cpus_near_gpu": numa, "note": "each rank is pinned to the CPUs NVML reports next to its GPU before "
                                                 "its pinned buffers are allocated",
-                 "h2d_gbs_measured": h2d_gbs,
-                 "e2e_h2d_gbs": 2 * B * W * H * args.steps / t_e2e / 1e9,
-                 "e2e_bound": "host-to-device link: the e2e leg's input traffic alone runs at e2e_h2d_gbs of the "
-                              "h2d_gbs_measured one pinned copy reaches on rank 0 (all ranks share the host's PCIe / "
-                              "memory path when N > 1)"},
+                 "h2d_gbs_concurrent": h2d_all, "d2h_gbs_concurrent": d2h_all, "bidir_gbs_concurrent": bidir_all,
+                 "probe": "all %d rank(s) copy their pinned %.0f MB image buffer at the same time, no kernels; sums over "
+                          "ranks (bidir = H2D and D2H queued together)" % (world, nbytes / 1e6),
+                 "h2d_gbs_rank0": h2d_rank, "d2h_gbs_rank0": d2h_rank,
+                 "e2e_h2d_gbs": e2e_h2d_gbs, "e2e_d2h_gbs": e2e_d2h_gbs,
+                 "e2e_frac_of_link": e2e_h2d_gbs / h2d_all if h2d_all > 0 else None,
+                 "e2e_bound": "host-to-device link: the e2e leg must move 2 x W x H input bytes per pair; "
+                              "e2e_frac_of_link = its input traffic / the measured concurrent H2D ceiling of the same "
+                              "ranks",
+                 "topology": topo},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                      "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src,
-                     "timed": "per-stage CUDA events on the handle's stream, %d steps run right after the timed region with "
-                              "the two handles serialised (the timed region overlaps their streams)" % args.steps,
+                     "timed": "per-stage CUDA events on the handle's stream, %d batches run right after the timed region "
+                              "with the two handles serialised (the timed region overlaps their streams)" % n_stage,
                      "bound_note": "every extraction kernel is bound by integer instruction issue (ALU pipe), not HBM: "
-                                   "see profiles/r1_kernels_full.md (issue slots busy, pipe utilisation)",
+                                   "see profiles/ (issue slots busy, pipe utilisation)",
                      "algorithmic_bytes_per_launch": alg[dom] * B, "issue": issue,
-                     "extract_frac": (b_extract * 2 * B * args.steps / (ms_dev * 1e-3) / 1e9) / peak_gbs},
+                     "extract_frac": (b_extract * 2 * frames / world / (ms_dev * 1e-3) / 1e9) / peak_gbs},
         "stages_ms_per_launch": per_launch,
         "cpu_baseline": cpu,
+        "parity": parity,
         "matchers": extras,
         "shapes": shapes,
     }
@@ -725,7 +959,9 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=64, help="stereo pairs per step per GPU")
+    ap.add_argument("--batch", type=int, default=64, help="stereo pairs per batch per GPU")
+    ap.add_argument("--batches", type=int, default=100, help="batches per step (a step = batches x batch pairs)")
+    ap.add_argument("--no-dropin", action="store_true", help="skip the C++ drop-in latency figure")
     ap.add_argument("--rigs", type=int, default=3, help="stereo rigs the e2e leg pipelines over (copies of step k+1, "
                     "kernels of step k, result drain of step k-1)")
     ap.add_argument("--latency-frames", type=int, default=200)

@@ -14,11 +14,12 @@ int ORBextractor::sDevice = 0;
 static_assert(sizeof(cv::KeyPoint) == sizeof(orbfe_keypoint), "cv::KeyPoint must be 28 bytes (x,y,size,angle,response,octave,class_id)");
 
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST)
-    : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST) {
+    : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST),
+      mDevice(sDevice) {
   // the getter tables do not depend on the image size: take them from a probe handle (src/ORBextractor.cc:415-446)
   orbfe_extractor_params p = {nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST};
   orbfe_extractor* probe = nullptr;
-  if (orbfe_extractor_create(&p, 256, 256, 1, sDevice, &probe) != ORBFE_OK) {
+  if (orbfe_extractor_create(&p, 256, 256, 1, mDevice, &probe) != ORBFE_OK) {
     std::fprintf(stderr, "ORBextractor: %s\n", orbfe_last_error());
     return;
   }
@@ -36,12 +37,20 @@ ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int
 
 ORBextractor::~ORBextractor() { orbfe_extractor_destroy(mHandle); }
 
+void ORBextractor::setDevice(int device) {
+  if (device == mDevice) return;
+  orbfe_extractor_destroy(mHandle);  // the arenas live on the old device; the next operator() re-creates them
+  mHandle = nullptr;
+  mWidth = mHeight = 0;
+  mDevice = device;
+}
+
 void ORBextractor::ensureHandle(int width, int height) {
   if (mHandle && width == mWidth && height == mHeight) return;
   orbfe_extractor_destroy(mHandle);
   mHandle = nullptr;
   orbfe_extractor_params p = {nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST};
-  if (orbfe_extractor_create(&p, width, height, 1, sDevice, &mHandle) != ORBFE_OK) {
+  if (orbfe_extractor_create(&p, width, height, 1, mDevice, &mHandle) != ORBFE_OK) {
     std::fprintf(stderr, "ORBextractor: %s\n", orbfe_last_error());
     mHandle = nullptr;
     return;
@@ -49,6 +58,7 @@ void ORBextractor::ensureHandle(int width, int height) {
   orbfe_extractor_info info;
   orbfe_extractor_get_info(mHandle, &info);
   mCapacity = info.capacity;
+  mDescScratch.resize((size_t)mCapacity * 32);
   mWidth = width;
   mHeight = height;
 }
@@ -63,17 +73,19 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
   if (image.empty()) return;  // src/ORBextractor.cc:1068
   ensureHandle(image.cols, image.rows);
   _keypoints.clear();
+  mOk = mHandle != nullptr;
   if (!mHandle) {  // the reference has no error channel: empty outputs + a log line
     _descriptors.release();
     return;
   }
   _keypoints.resize(mCapacity);
-  cv::Mat desc(mCapacity, 32, CV_8U);
+  unsigned char* desc = mDescScratch.data();
   int32_t n = 0;
   const int rc = orbfe_extract(mHandle, image.ptr(0), (int)image.step, reinterpret_cast<orbfe_keypoint*>(_keypoints.data()),
-                               desc.ptr(0), mCapacity, &n);
+                               desc, mCapacity, &n);
   if (rc != ORBFE_OK) {
     std::fprintf(stderr, "ORBextractor: %s\n", orbfe_last_error());
+    mOk = false;
     n = 0;
   }
   _keypoints.resize(n);
@@ -86,7 +98,7 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
 #else
     cv::Mat& out = _descriptors;
 #endif
-    std::memcpy(out.ptr(0), desc.ptr(0), (size_t)n * 32);
+    std::memcpy(out.ptr(0), desc, (size_t)n * 32);
   }
   if (keepHostPyramid) {
     for (int lv = 0; lv < nlevels; ++lv) {

@@ -42,7 +42,14 @@ class ORBextractor {
 
   // the device handle (for compat/FrameStereo.h)
   orbfe_extractor* handle() const { return mHandle; }
+  // The GPU the NEXT constructed extractor lives on (process-wide default), and the device of THIS object: the two
+  // extractors of a rig, or the rigs of several cameras, can sit on different GPUs.
   static void SetDevice(int device) { sDevice = device; }
+  void setDevice(int device);
+  int device() const { return mDevice; }
+  // false when the last operator() failed on the device side (lost device, CUDA error): the reference has no error
+  // channel, so the outputs are empty like a featureless frame; this tells the two apart.
+  bool ok() const { return mOk; }
 
  protected:
   int nfeatures;
@@ -61,6 +68,9 @@ class ORBextractor {
   void ensureHandle(int width, int height);
   orbfe_extractor* mHandle = nullptr;
   int mWidth = 0, mHeight = 0, mCapacity = 0;
+  int mDevice = 0;
+  bool mOk = true;
+  std::vector<unsigned char> mDescScratch;  // capacity x 32, kept across calls (no per-frame allocation)
   static int sDevice;
 };
 
