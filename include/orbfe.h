@@ -301,6 +301,39 @@ int orbfe_hamming_merge_device(orbfe_matcher* m, const uint64_t* d_best_all, con
 int orbfe_hamming_bruteforce_device_noalloc(void* stream, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm,
                                             int64_t index_base, uint64_t* d_best, uint64_t* d_second);
 int orbfe_matcher_sync(orbfe_matcher* m);
+
+/* ---- multi-GPU exchange of the brute-force top-2 (BASELINE.json config 5; SURVEY.md 8(b)
+ * `orbfe_hamming_bruteforce(..., comm?, ...)` and 8(e) "map descriptors sharded, NCCL-over-NVLink min-pair reduce") ----
+ * One process (or thread) per GPU.  Rank 0 makes an id (orbfe_comm_unique_id = ncclGetUniqueId; libnccl.so.2 is
+ * dlopen'ed, path override: ORBFE_NCCL_LIB), hands its 128 bytes to the other ranks by any means (MPI, a file,
+ * torch.distributed ...), and every rank calls orbfe_comm_create (collective: ncclCommInitRank, then the ranks map each
+ * other's exchange buffers through CUDA IPC when they share a node and peer access exists; ORBFE_COMM_NO_P2P=1
+ * keeps the NCCL path).  max_queries bounds nq of later calls (the exchange buffer holds 2 x nranks x 2 x max_queries
+ * u64 on every rank). */
+typedef struct orbfe_comm orbfe_comm;
+#define ORBFE_COMM_ID_BYTES 128
+enum { ORBFE_EXCHANGE_AUTO = 0, ORBFE_EXCHANGE_NCCL = 1, ORBFE_EXCHANGE_PEER = 2 };
+int orbfe_comm_unique_id(uint8_t* id_out /* ORBFE_COMM_ID_BYTES */);
+int orbfe_comm_create(const uint8_t* id, int nranks, int rank, int device, int max_queries, orbfe_comm** out);
+void orbfe_comm_destroy(orbfe_comm* c);
+/* peer_memory = 1 when the ranks exchange through mapped peer memory (NVLink stores), 0 = NCCL all-gather */
+int orbfe_comm_info(orbfe_comm* c, int* nranks, int* rank, int* peer_memory, int* nccl_version);
+/* ORBFE_ERR_CUDA (with a message) if a consuming kernel gave up waiting for a peer (a rank did not make the matching
+ * call within ORBFE_COMM_TIMEOUT_S seconds, default 30); call after orbfe_matcher_sync. */
+int orbfe_comm_status(orbfe_comm* c);
+/* The sharded brute force: every rank passes the SAME queries and ITS shard of the map (global row numbers
+ * index_base .. index_base + nm_local); on return (asynchronous on the matcher's stream) d_best / d_second hold
+ * the GLOBAL top-2 keys (dist << 32 | global index, ties -> lowest index) on EVERY rank.  Collective: all ranks call it
+ * in the same order with the same nq and `exchange`.  exchange = ORBFE_EXCHANGE_AUTO picks peer memory when available:
+ * the kernel that merges the rank's slices stores its keys into every rank's buffer over NVLink and publishes a flag,
+ * and the consuming kernel waits for all flags and takes the top-2 (no collective call); ORBFE_EXCHANGE_NCCL = one
+ * in-place ncclAllGather between the two kernels. */
+int orbfe_hamming_bruteforce_sharded(orbfe_matcher* m, orbfe_comm* c, const uint8_t* d_query, int nq,
+                                     const uint8_t* d_map_shard, int nm_local, int64_t index_base, uint64_t* d_best,
+                                     uint64_t* d_second, int exchange);
+/* optional per-call device timing (CUDA events on the matcher's stream): brute-force kernel | exchange + merge */
+int orbfe_comm_set_timing(orbfe_comm* c, int enable);
+int orbfe_comm_last_times(orbfe_comm* c, float* kernel_ms, float* exchange_merge_ms);
 /* Measured 32-bit POPC results per second of the matcher's device (register-only probe kernel): the roofline
  * denominator of the Hamming kernels ("measure it"). */
 int orbfe_measure_popc_peak(orbfe_matcher* m, double* popc32_per_second);

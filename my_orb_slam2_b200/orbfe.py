@@ -154,6 +154,14 @@ SYMBOLS = {
     "orbfe_hamming_merge_device": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "orbfe_hamming_bruteforce_device_noalloc": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_matcher_sync": (_I, [_P]),
+    "orbfe_comm_unique_id": (_I, [_P]),
+    "orbfe_comm_create": (_I, [_P, _I, _I, _I, _I, C.POINTER(_P)]),
+    "orbfe_comm_destroy": (None, [_P]),
+    "orbfe_comm_info": (_I, [_P, C.POINTER(_I), C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)]),
+    "orbfe_comm_status": (_I, [_P]),
+    "orbfe_hamming_bruteforce_sharded": (_I, [_P, _P, _P, _I, _P, _I, C.c_int64, _P, _P, _I]),
+    "orbfe_comm_set_timing": (_I, [_P, _I]),
+    "orbfe_comm_last_times": (_I, [_P, C.POINTER(_F), C.POINTER(_F)]),
     "orbfe_measure_popc_peak": (_I, [_P, C.POINTER(C.c_double)]),
 }
 
@@ -501,6 +509,61 @@ class Matcher:
 
     def hamming_merge_device(self, d_best_all, d_second_all, shards, nq, d_best, d_second):
         check(lib().orbfe_hamming_merge_device(self._h, d_best_all, d_second_all, shards, nq, d_best, d_second))
+
+
+COMM_ID_BYTES = 128
+EXCHANGE_AUTO, EXCHANGE_NCCL, EXCHANGE_PEER = 0, 1, 2
+
+
+def comm_unique_id():
+    """Rank 0's half of the bootstrap (ncclGetUniqueId through the library): 128 bytes to hand to every rank."""
+    buf = np.zeros(COMM_ID_BYTES, np.uint8)
+    check(lib().orbfe_comm_unique_id(_p(buf)))
+    return buf
+
+
+class Comm:
+    """orbfe_comm: the library's own communicator for the sharded brute force (NCCL bootstrap + mapped peer buffers)."""
+
+    def __init__(self, unique_id, nranks, rank, device, max_queries):
+        uid = np.ascontiguousarray(unique_id, np.uint8)
+        assert uid.size == COMM_ID_BYTES
+        h = C.c_void_p()
+        check(lib().orbfe_comm_create(_p(uid), nranks, rank, device, max_queries, C.byref(h)))
+        self._h, self.nranks, self.rank, self.device = h, nranks, rank, device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbfe_comm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self):
+        n, r, p, v = _I(), _I(), _I(), _I()
+        check(lib().orbfe_comm_info(self._h, C.byref(n), C.byref(r), C.byref(p), C.byref(v)))
+        return {"nranks": n.value, "rank": r.value, "peer_memory": bool(p.value), "nccl_version": v.value}
+
+    def status(self):
+        check(lib().orbfe_comm_status(self._h))
+
+    def set_timing(self, enable=True):
+        check(lib().orbfe_comm_set_timing(self._h, int(enable)))
+
+    def last_times(self):
+        a, b = _F(), _F()
+        check(lib().orbfe_comm_last_times(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def hamming_bruteforce_sharded(self, matcher, d_query, nq, d_map_shard, nm_local, index_base, d_best, d_second,
+                                   exchange=EXCHANGE_AUTO):
+        """Device pointers (ints); asynchronous on the matcher's stream; collective over the ranks."""
+        check(lib().orbfe_hamming_bruteforce_sharded(matcher._h, self._h, d_query, nq, d_map_shard, nm_local,
+                                                     index_base, d_best, d_second, exchange))
 
 
 class Vocabulary:

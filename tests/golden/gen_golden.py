@@ -248,6 +248,30 @@ def main():
         np.savez_compressed(path, image=img, params=np.array(params, np.float64), keypoints=kp, descriptors=desc,
                             level_last=levels[-1], **stage)
         print(name, "keypoints", len(kp), "->", os.path.relpath(path, ROOT))
+    # full-size fixtures on BASELINE.json's three shapes (the image is regenerated from its seed by the tests, so only
+    # its sha256 is stored): keypoints, descriptors, candidate counts and a sha256 per pyramid level + per level's
+    # GaussianBlur (= a cv2 known answer for each of the 7 resize transitions and 8 blurs of the shape)
+    import hashlib
+    for shape in ("tum", "kitti", "euroc"):
+        w, h = synth.SHAPES[shape]
+        st = synth.SETTINGS[shape]
+        params = (st["nfeatures"], st["scale_factor"], st["nlevels"], st["ini_th"], st["min_th"])
+        img = synth.synth_image(w, h, seed=0)
+        ex = PyExtractor(*params)
+        kp, desc, stage, levels = ex.extract(img)
+        sha = lambda a: np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), np.uint8)
+        path = os.path.join(HERE, "extract_full_%s.npz" % shape)
+        np.savez_compressed(
+            path, image_sha256=sha(img), shape=np.array([w, h], np.int32), seed=np.int32(0),
+            params=np.array(params, np.float64), keypoints=kp, descriptors=desc, level_last=levels[-1],
+            level_sha256=np.stack([sha(l) for l in levels]),
+            blur_sha256=np.stack([sha(cv2.GaussianBlur(l, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)) for l in levels]),
+            level_dims=np.array([[l.shape[1], l.shape[0]] for l in levels], np.int32),
+            cand_counts=np.array([len(stage["cand_%d" % lv]) for lv in range(len(levels))], np.int32),
+            cand_sha256=np.stack([sha(stage["cand_%d" % lv].astype(np.int32)) for lv in range(len(levels))]),
+            kept_counts=np.array([len(stage["kept_%d" % lv]) for lv in range(len(levels))], np.int32),
+            cv2_version=np.array(cv2.__version__))
+        print("full", shape, "keypoints", len(kp), "->", os.path.relpath(path, ROOT))
     # primitive known-answer vectors
     rng = np.random.default_rng(7)
     src = rng.integers(0, 256, (97, 131), dtype=np.uint8)

@@ -44,6 +44,30 @@ def test_golden_fixtures(fe, golden_dir, name):
     assert np.array_equal(ex.mvImagePyramid[int(p[2]) - 1], g["level_last"])
 
 
+@pytest.mark.parametrize("shape", ["tum", "kitti", "euroc"])
+def test_full_size_golden_fixtures(fe, golden_dir, shape):
+    """CUDA path against the committed cv2-4.13 chain at full size (tests/golden/gen_golden.py): keypoints, descriptors,
+    every pyramid level by sha256."""
+    import hashlib
+    from my_orb_slam2_b200 import synth
+    g = np.load(os.path.join(golden_dir, "extract_full_%s.npz" % shape))
+    w, h = (int(v) for v in g["shape"])
+    img = synth.synth_image(w, h, seed=int(g["seed"]))
+    p = g["params"]
+    ex = fe.ORBextractor(int(p[0]), float(p[1]), int(p[2]), int(p[3]), int(p[4]))
+    kp, desc = ex(img)
+    gk = g["keypoints"]
+    assert len(kp) == len(gk)
+    for i, f in enumerate(["x", "y", "size", "angle", "response"]):
+        assert np.array_equal(kp[f], gk[:, i]), f
+    assert np.array_equal(kp["octave"], gk[:, 5].astype(np.int32))
+    assert np.array_equal(desc, g["descriptors"])
+    pyr = ex.mvImagePyramid
+    for lv in range(int(p[2])):
+        d = np.frombuffer(hashlib.sha256(np.ascontiguousarray(pyr[lv]).tobytes()).digest(), np.uint8)
+        assert np.array_equal(d, g["level_sha256"][lv]), "pyramid level %d" % lv
+
+
 @pytest.mark.parametrize("shape,seed", [("tum", 0), ("kitti", 0), ("euroc", 0), ("kitti", 3)])
 def test_full_size_vs_oracle_with_stage_dumps(fe, oracle, shape, seed):
     s = synth.SETTINGS[shape]

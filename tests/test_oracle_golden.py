@@ -45,6 +45,41 @@ def test_extract_matches_cv2_fixture(oracle, golden_dir, name):
         assert np.array_equal(np.stack([xs, ys, sc], 1).reshape(-1, 3), g["cand_%d" % lv].reshape(-1, 3))
 
 
+def _sha(a):
+    import hashlib
+    return np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), np.uint8)
+
+
+@pytest.mark.parametrize("shape", ["tum", "kitti", "euroc"])
+def test_full_size_matches_cv2_fixture(oracle, golden_dir, shape):
+    """BASELINE.json's three shapes at full size and full feature count against the cv2 4.13 chain: every pyramid level
+    (the 7 resize transitions), every level's GaussianBlur, every level's candidate list, keypoints and descriptors."""
+    from my_orb_slam2_b200 import synth
+    g = np.load(os.path.join(golden_dir, "extract_full_%s.npz" % shape))
+    w, h = (int(v) for v in g["shape"])
+    img = synth.synth_image(w, h, seed=int(g["seed"]))
+    assert np.array_equal(_sha(img), g["image_sha256"]), "the synthetic generator changed: regenerate tests/golden"
+    ex = _extractor(oracle, g["params"])
+    kp, desc = ex.extract(img)
+    gk = g["keypoints"]
+    assert len(kp) == len(gk)
+    for i, f in enumerate(["x", "y", "size", "angle", "response"]):
+        assert np.array_equal(kp[f], gk[:, i]), f
+    assert np.array_equal(kp["octave"], gk[:, 5].astype(np.int32))
+    assert np.array_equal(desc, g["descriptors"])
+    nl = int(g["params"][2])
+    assert np.array_equal(ex.level(nl - 1), g["level_last"])
+    for lv in range(nl):
+        lvl = ex.level(lv)
+        assert [lvl.shape[1], lvl.shape[0]] == list(g["level_dims"][lv])
+        assert np.array_equal(_sha(lvl), g["level_sha256"][lv]), "pyramid level %d" % lv
+        assert np.array_equal(_sha(oracle.gaussian_blur7(lvl)), g["blur_sha256"][lv]), "blur of level %d" % lv
+        xs, ys, sc = ex.candidates(lv)
+        c = np.stack([xs, ys, sc], 1).reshape(-1, 3).astype(np.int32)
+        assert len(c) == int(g["cand_counts"][lv])
+        assert np.array_equal(_sha(c), g["cand_sha256"][lv]), "candidates of level %d" % lv
+
+
 def test_quotas_and_umax(oracle):
     # SURVEY.md 8(a) a1: quotas and umax of the constructor (src/ORBextractor.cc:435-469)
     want = {1000: [217, 181, 151, 126, 105, 87, 73, 60], 2000: [434, 362, 302, 251, 209, 175, 145, 122],
