@@ -303,26 +303,30 @@ def matcher_extras(torch, dist, orbfe, rank, world, local, kp_frame, desc_frame,
     start, cnt = sharding.map_shard(nm, rank, world)
     d_q = torch.from_numpy(q).to(dev)
     d_m = torch.from_numpy(mp[start:start + cnt].copy()).to(dev)
-    sb = sharding.ShardedBruteForce(m, dev)
-    for _ in range(3):
-        sb.run(d_q, d_m, start)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    reps = 5
-    e0.record()
-    for _ in range(reps):
-        best, second = sb.run(d_q, d_m, start)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / reps
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    sb = sharding.ShardedBruteForce(m, dev, max_queries=nq)
+
+    def time_mode(mode, reps=5):
+        for _ in range(3):
+            sb.run(d_q, d_m, start, exchange=mode)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            b, s2 = sb.run(d_q, d_m, start, exchange=mode)
+        e1.record()
+        torch.cuda.synchronize()
+        t = e0.elapsed_time(e1) / reps
+        if world > 1:
+            tt = torch.tensor([t], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t = float(tt.item())
+        return t, b, s2
+
+    ms, best, second = time_mode(0)   # the library's default exchange (peer memory over NVLink when the ranks can map it)
     pairs = float(nq) * nm
-    out["bruteforce_hamming"] = {
+    bf = {
         "workload": "configs[4]: %d queries x %d map descriptors, map sharded over %d GPU(s)" % (nq, nm, world),
         "ms": ms, "pairs_per_s": pairs / (ms * 1e-3), "algorithmic_popc32_per_s": 8.0 * pairs / (ms * 1e-3),
         "popc_peak_per_gpu_measured": popc_peak, "frac_of_popc_peak": 8.0 * pairs / (ms * 1e-3) / (popc_peak * world),
@@ -330,6 +334,49 @@ def matcher_extras(torch, dist, orbfe, rank, world, local, kp_frame, desc_frame,
                 "rate (8 popc32 per pair) may exceed the POPC pipe's own peak",
         "first_best_key": int(best[0].item()) & 0xFFFFFFFFFFFFFFFF,
     }
+    if world > 1:
+        # the exchange, broken down (device times of the LAST call, max over ranks): brute-force kernel | exchange + merge
+        info = sb.comm.info()
+        sb.comm.set_timing(True)
+        brk = {}
+        modes = [("nccl_in_library", orbfe.EXCHANGE_NCCL), ("torch_all_gather", "torch")]
+        if info["peer_memory"]:
+            modes.insert(0, ("peer_memory_nvlink", orbfe.EXCHANGE_PEER))
+        equal = True
+        ref_b, ref_s = best.clone(), second.clone()
+        for name, mode in modes:
+            t_all, b, s2 = time_mode(mode)
+            equal = equal and bool(torch.equal(b, ref_b)) and bool(torch.equal(s2, ref_s))
+            entry = {"ms": t_all}
+            if mode != "torch":
+                k_ms, x_ms = sb.comm.last_times()
+                tt = torch.tensor([k_ms, x_ms], dtype=torch.float64, device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                entry["kernel_ms"], entry["exchange_merge_ms"] = float(tt[0].item()), float(tt[1].item())
+            brk[name] = entry
+        sb.comm.set_timing(False)
+        sb.comm.status()
+        # parity with N > 1 ranks on hardware: EVERY rank's global top-2 (all 8192 queries) must equal the single-GPU
+        # result over the whole map, computed on rank 0 and broadcast
+        if rank == 0:
+            d_full = torch.from_numpy(mp).to(dev)
+            sb1, ss1 = torch.empty_like(best), torch.empty_like(second)
+            m.hamming_bruteforce_device(d_q.data_ptr(), nq, d_full.data_ptr(), nm, 0, sb1.data_ptr(), ss1.data_ptr())
+            m.sync()
+            del d_full
+        else:
+            sb1, ss1 = torch.empty_like(best), torch.empty_like(second)
+        dist.broadcast(sb1, src=0)
+        dist.broadcast(ss1, src=0)
+        ok = torch.tensor([int(equal and bool(torch.equal(best, sb1)) and bool(torch.equal(second, ss1)))], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        bf["exchange"] = {"default": "peer_memory_nvlink" if info["peer_memory"] else "nccl_in_library",
+                          "nccl_version": info["nccl_version"], "paths": brk,
+                          "what": "per path: whole call (max over ranks) and, from CUDA events inside the library, the "
+                                  "brute-force kernel vs the exchange + global merge (peer path: merge+push kernel and "
+                                  "wait+merge kernel; NCCL path: merge kernel, ncclAllGather, merge kernel)"}
+        bf["sharded_equal_to_single"] = bool(ok.item())
+    out["bruteforce_hamming"] = bf
     if rank == 0:
         # config 4: SearchByProjection (map overload, then last-frame overload) through the C ABI, host views
         bounds = (0.0, 0.0, float(W), float(H))
@@ -477,10 +524,47 @@ def shape_extras(torch, dist, orbfe, rank, world, local, steps, warmup):
         orbfe.check(lib.orbfe_stereo_match_run(L._h, R._h, mine, mbf, mb))
 
     ms = timed(euroc_step, torch.cuda.ExternalStream(L.stream, device=dev))
+    sharded_equal = None
+    if world > 1:
+        # parity with N > 1 ranks on hardware: the results of the timed, sharded configuration (this rank's first 4 slots
+        # = its 4 distinct pairs) are gathered on rank 0, which extracts the same 4 x world pairs alone in ONE batch
+        import hashlib
+        cap = L.capacity
+        kl, kr = np.zeros((mine, cap), orbfe.KEYPOINT_DTYPE), np.zeros((mine, cap), orbfe.KEYPOINT_DTYPE)
+        dsl, dsr = np.zeros((mine, cap, 32), np.uint8), np.zeros((mine, cap, 32), np.uint8)
+        nl, nr = np.zeros(mine, np.int32), np.zeros(mine, np.int32)
+        L.download(mine, kl, dsl, nl)
+        R.download(mine, kr, dsr, nr)
+        ur, dp, nm = orbfe.stereo_match(L, R, mine, mbf, mb)
+
+        def digest(i, kl, dsl, nl, kr, dsr, nr, ur, dp):
+            hsh = hashlib.sha256()
+            for a in (kl[i][:nl[i]], dsl[i][:nl[i]], kr[i][:nr[i]], dsr[i][:nr[i]], ur[i][:nl[i]], dp[i][:nl[i]]):
+                hsh.update(np.ascontiguousarray(a).tobytes())
+            return hsh.hexdigest()
+
+        own = [digest(i, kl, dsl, nl, kr, dsr, nr, ur, dp) for i in range(min(4, mine))]
+        gathered = [None] * world if rank == 0 else None
+        dist.gather_object(own, gathered, dst=0)
+        flag = [None]
+        if rank == 0:
+            allp = [synth.synth_pair(w, h, 1000 + r + world * i) for r in range(world) for i in range(4)]
+            n1 = len(allp)
+            L1 = orbfe.Extractor(*prm, w, h, max_batch=n1, device=local)
+            R1 = orbfe.Extractor(*prm, w, h, max_batch=n1, device=local)
+            o = orbfe.stereo_frame(L1, R1, np.stack([p[0] for p in allp]), np.stack([p[1] for p in allp]), mbf, mb)
+            single = [digest(i, o[0], o[1], o[2], o[3], o[4], o[5], o[6], o[7]) for i in range(n1)]
+            flag[0] = all(gathered[r][i] == single[4 * r + i] for r in range(world) for i in range(len(gathered[r])))
+            R1.close()
+            L1.close()
+        dist.broadcast_object_list(flag, src=0)
+        sharded_equal = bool(flag[0])
     out["euroc_stereo_256"] = {
         "workload": "configs[2]: 256 EuRoC-shaped 752x480 stereo pairs per step, 1200 features, extract L+R + "
                     "ComputeStereoMatches, sharded by frame over %d GPU(s) (%d pairs on rank 0)" % (world, mine),
         "frames_per_s": total * steps / (ms * 1e-3), "ms_per_step": ms / steps, "scaling": "strong"}
+    if sharded_equal is not None:
+        out["euroc_stereo_256"]["sharded_equal_to_single"] = sharded_equal
     R.close()
     L.close()
     del dl, dr

@@ -275,7 +275,8 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
 // CUtensorMap of every level that has FAST strips (only those levels have keypoints): a (pitch, h, max_batch) byte
 // tensor over one of the level-major arenas with a box_w x box_h x 1 box.  cuTensorMapEncodeTiled is a driver entry
 // point; it is fetched through the runtime so that liborbfe.so does not link libcuda.
-static int build_level_maps(const PyrGeom& g, uint8_t* arena, int max_batch, int box_w, int box_h, void** out) {
+static int build_level_maps(const PyrGeom& g, uint8_t* arena, int max_batch, int box_w, int box_h,
+                            CUtensorMapSwizzle swizzle, void** out) {
   typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -297,7 +298,7 @@ static int build_level_maps(const PyrGeom& g, uint8_t* arena, int max_batch, int
     const cuuint32_t estr[3] = {1u, 1u, 1u};
     const CUresult r = reinterpret_cast<EncodeTiled>(fn)(
         &maps[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, arena + L.lvl_base, dims, strides, box, estr,
-        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+        CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
       set_error("cuTensorMapEncodeTiled failed for level %d (%dx%d, pitch %d): CUresult %d", l, L.w, L.h, L.pitch, (int)r);
@@ -310,8 +311,11 @@ static int build_level_maps(const PyrGeom& g, uint8_t* arena, int max_batch, int
 }
 
 int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
-  int rc = build_level_maps(g, a.pyr, max_batch, kFastTileW, kFastTileH, &a.fast_maps);       // k_fast.cu
-  if (rc == ORBFE_OK) rc = build_level_maps(g, a.blur, max_batch, kDescBoxW, kDescBoxH, &a.desc_maps);  // k_describe.cu
+  int rc = build_level_maps(g, a.pyr, max_batch, kFastTileW, kFastTileH, CU_TENSOR_MAP_SWIZZLE_NONE, &a.fast_maps);  // k_fast.cu
+  // k_describe.cu: 64-byte rows written with the 64-byte swizzle (bank spread of the rBRIEF gathers)
+  static_assert(kDescBoxW == 64, "CU_TENSOR_MAP_SWIZZLE_64B: the box's inner extent is the swizzle span");
+  if (rc == ORBFE_OK)
+    rc = build_level_maps(g, a.blur, max_batch, kDescBoxW, kDescBoxH, CU_TENSOR_MAP_SWIZZLE_64B, &a.desc_maps);
   return rc;
 }
 

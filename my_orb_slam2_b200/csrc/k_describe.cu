@@ -1,9 +1,10 @@
-// k_describe.cu — everything after DistributeOctTree for the kept keypoints.  A CTA takes 32 output rows; the
-// per-pixel parts run one warp per keypoint, the scalar parts (level lookup, atan2, sin/cos, keypoint record) one
-// THREAD per keypoint so that their instruction stream is paid once per 32 keypoints, not once per keypoint:
+// k_describe.cu — everything after DistributeOctTree for the kept keypoints.  A CTA takes 32 output rows; after the
+// row -> (level, kept record) lookup (one thread per keypoint, one CTA barrier) every warp owns 4 keypoints through all
+// steps, with its global loads issued early (moments: the disc rows of all 4 keypoints in flight at once; descriptor
+// patches: two TMA boxes in flight per warp), because the kernel is bound by memory latency, not by issue slots:
 //   * the fix-up of src/ORBextractor.cc:859-870 (pt += minBorder, octave, size);
 //   * computeOrientation -> IC_Angle (:472-479, :77-104): m10/m01 over the radius-15 disc of the UN-blurred level
-//     (lane u = column of the disc, loop over its 31 rows), warp-shuffle reduction, cv::fastAtan2 polynomial;
+//     (lane = row of the disc, DP4A against a weight table), warp-shuffle reduction, cv::fastAtan2 polynomial;
 //   * computeOrbDescriptor (:108-147) on the blurred level (k_blur.cu): lane i builds descriptor byte i
 //     (8 tests = 16 gathers) from its 32 fp32 pattern values (loaded once per warp, coalesced float4);
 //   * the rescale by mvScaleFactor[level] and the level-order concatenation of operator() (:1117-1125).
@@ -136,12 +137,14 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
                                                                    int32_t* __restrict__ flags,
                                                                    const CUtensorMap* __restrict__ blur_maps) {
   __shared__ KpSlot slot[DESC_KP];
+  __shared__ uint2 ic_tab[4 * IC_PW * 16];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
   const int oi0 = blockIdx.x * DESC_KP;  // first output row of this CTA
 
   // ---- 0. one thread per keypoint: which level does output row oi belong to (levels are concatenated in order
   // 0..L-1, :1096-1126), and its kept record ----
+  for (int i = tid; i < 4 * IC_PW * 16; i += DESC_WARPS * 32) ic_tab[i] = (&d_ic_tab.w[0][0][0])[i];
   if (tid < DESC_KP) {
     const int oi = oi0 + tid;
     const int32_t* kc = kept_count + b * kMaxLevels;
@@ -171,44 +174,21 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
   __syncthreads();
   if (slot[0].lvl < 0) return;  // output rows are dense: an empty first slot means an empty CTA
 
-  // ---- 1. IC_Angle moments (:77-104), one warp per keypoint.  The 31 disc rows are staged in shared memory with
-  // coalesced word loads (3 rows per warp instruction), then lane = ROW v of the disc: 9 words x two DP4A against the
-  // weight table give sum(u * I) and sum(I) over the row's part of the disc; m01 = v * sum(I).  ~120 instructions
-  // per keypoint instead of ~230 for the byte-per-lane column walk. ----
-  constexpr int PS = kDescBoxW;                                // bytes per descriptor patch row (step 3)
-  constexpr int PBUF = (kDescBoxW * kDescBoxH + 127) / 128 * 32;  // words per buffer, a multiple of 128 bytes
-  static_assert(PBUF >= 31 * IC_PW, "the disc rows of step 1 use the same buffers");
-  // two patch buffers per warp: the next keypoint's rows arrive (cp.async in step 1, TMA in step 3) while this one
-  // is being worked on
-  __shared__ __align__(128) unsigned patch_all[DESC_WARPS][2][PBUF];
+  // ---- 1. IC_Angle moments (:77-104).  A warp owns keypoints warp, warp+8, warp+16, warp+24 of the CTA through all
+  // remaining steps (no CTA barrier after this point).  The 31 disc rows of ALL FOUR keypoints are requested at once
+  // with coalesced cp.async word copies (3 rows per warp instruction; one commit group per keypoint), so the warp
+  // waits for HBM / L2 once instead of once per keypoint (the kernel is bound by memory latency: ncu showed 65 % of
+  // the samples on the waits of this step with one keypoint in flight).  Then lane = ROW v of the disc: 9 words x two
+  // DP4A against the weight table give sum(u * I) and sum(I) over the row's part of the disc; m01 = v * sum(I).
+  // (Reading the rows straight from global memory, one row per lane, was measured 2x slower: 31 sectors per load.) ----
+  constexpr int PBUF = (kDescBoxW * kDescBoxH + 511) / 512 * 128;  // words per patch buffer, a multiple of 512 bytes
+  constexpr int KPW = DESC_KP / DESC_WARPS;                        // keypoints per warp
+  // two patch buffers per warp, 512-byte aligned: the TMA writes the box with the 64-byte swizzle (16-byte chunk
+  // index ^= bits 7-8 of the shared address = (row >> 1) & 3), so that the 512 scattered byte gathers of a keypoint
+  // spread over all 32 banks: with plain 64-byte rows a warp's 32 gathers cost 4.8 shared-memory wavefronts on
+  // average, swizzled 3.1 (simulated over the pattern, all alignments and angles; 3.0 is what 32 random words do)
+  __shared__ __align__(512) unsigned patch_all[DESC_WARPS][2][PBUF];
   __shared__ unsigned long long patch_bar[DESC_WARPS][2];
-  if (lane == 0) {
-    mbar_init(&patch_bar[warp][0]);
-    mbar_init(&patch_bar[warp][1]);
-    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
-  }
-  __shared__ uint2 ic_tab[4 * IC_PW * 16];
-  for (int i = tid; i < 4 * IC_PW * 16; i += DESC_WARPS * 32) ic_tab[i] = (&d_ic_tab.w[0][0][0])[i];
-  // rows ky-15 .. ky+15 of the un-blurred level from the aligned address at or below kx-15, 3 rows per instruction
-  auto stage_disc = [&](int i, unsigned* dst) {
-    const KpSlot k = slot[i];
-    const int prow = lane / IC_PW, pcol = lane - prow * IC_PW;  // lanes 0..26: (row within a group of 3, word)
-    if (k.lvl >= 0 && prow < 3) {
-      const LevelGeom& L = g.lv[k.lvl];
-      const int pitch = L.pitch;
-      const uint8_t* base = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)(k.ky - 15 + prow) * pitch +
-                            ((k.kx - 15) & ~3) + 4 * pcol;
-      unsigned* d = dst + prow * IC_PW + pcol;
-#pragma unroll
-      for (int r0 = 0; r0 < 33; r0 += 3) {
-        if (r0 + prow < 31) cp_async4(d, base);
-        base += 3 * pitch;
-        d += 3 * IC_PW;
-      }
-    }
-    cp_async_commit();
-  };
   // rows ky-18 .. ky+18 of the blurred level from the 16-byte aligned column at or below kx-18: one TMA box
   auto stage_patch = [&](int i, int buf) {
     const KpSlot k = slot[i];
@@ -216,72 +196,108 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
       tma_load_box(patch_all[warp][buf], blur_maps + k.lvl, (k.kx - 18) & ~15, k.ky - 18, b, &patch_bar[warp][buf],
                    kDescBoxW * kDescBoxH);
   };
-  stage_disc(warp, patch_all[warp][0]);
-  __syncthreads();  // ic_tab
+  if (lane == 0) {
+    mbar_init(&patch_bar[warp][0]);
+    mbar_init(&patch_bar[warp][1]);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  // rows ky-15 .. ky+15 of the un-blurred level from the aligned address at or below kx-15, 3 rows (3 x 36 contiguous
+  // bytes) per warp instruction; the warp's 4 discs (4 x 1116 bytes) share the two patch buffers (5120 bytes), which
+  // the descriptor patches only need afterwards
+  static_assert(KPW * 31 * IC_PW <= 2 * PBUF, "the discs of a warp's keypoints are staged in its two patch buffers");
+  unsigned* disc_all = patch_all[warp][0];
+  {
+    const int prow = lane / IC_PW, pcol = lane - prow * IC_PW;  // lanes 0..26: (row within a group of 3, word)
+#pragma unroll
+    for (int q = 0; q < KPW; ++q) {
+      const KpSlot k = slot[warp + q * DESC_WARPS];
+      if (k.lvl >= 0 && prow < 3) {
+        const LevelGeom& L = g.lv[k.lvl];
+        const int pitch = L.pitch;
+        const uint8_t* base = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)(k.ky - 15 + prow) * pitch +
+                              ((k.kx - 15) & ~3) + 4 * pcol;
+        unsigned* d = disc_all + q * (31 * IC_PW) + prow * IC_PW + pcol;
+#pragma unroll
+        for (int r0 = 0; r0 < 33; r0 += 3) {
+          if (r0 + prow < 31) cp_async4(d, base);
+          base += 3 * pitch;
+          d += 3 * IC_PW;
+        }
+      }
+      cp_async_commit();
+    }
+  }
   {
     const int v = lane - 15;
     const int av = lane < 31 ? (v < 0 ? -v : v) : 15;
-    int buf = 0;
-#pragma unroll 1
-    for (int i = warp; i < DESC_KP; i += DESC_WARPS, buf ^= 1) {
-      const KpSlot k = slot[i];
-      if (k.lvl < 0) break;
-      if (i + DESC_WARPS < DESC_KP) stage_disc(i + DESC_WARPS, patch_all[warp][buf ^ 1]); else cp_async_commit();
-      cp_async_wait<1>();
+    int m10[KPW], m01[KPW];
+#pragma unroll
+    for (int q = 0; q < KPW; ++q) {
+      if (q == 0) cp_async_wait<KPW - 1>();
+      if (q == 1) cp_async_wait<(KPW > 2 ? KPW - 2 : 0)>();
+      if (q == 2) cp_async_wait<(KPW > 3 ? KPW - 3 : 0)>();
+      if (q >= 3) cp_async_wait<0>();
       __syncwarp();
-      const unsigned* disc = patch_all[warp][buf];
-      const int al = (k.kx - 15) & 3;
-      int m10 = 0, s1 = 0;
+      const unsigned* disc = disc_all + q * (31 * IC_PW);
+      const int al = (slot[warp + q * DESC_WARPS].kx - 15) & 3;
+      const uint2* wt = ic_tab + al * (IC_PW * 16) + av;
+      int a = 0, s1 = 0;
       if (lane < 31) {
-        const uint2* wt = ic_tab + al * (IC_PW * 16) + av;
 #pragma unroll
         for (int j = 0; j < IC_PW; ++j) {
           const unsigned px = disc[lane * IC_PW + j];
           const uint2 wgt = wt[j * 16];
-          m10 = dp4a_us(px, wgt.x, m10);
+          a = dp4a_us(px, wgt.x, a);
           s1 = (int)__dp4a(px, wgt.y, (unsigned)s1);
         }
       }
-      int m01 = v * s1;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-      }
-      if (lane == 0) { slot[i].m01 = m01; slot[i].m10 = m10; }
-      __syncwarp();  // every lane has read this buffer before the keypoint after next lands in it
+      m10[q] = a;
+      m01[q] = v * s1;
     }
-    cp_async_wait<0>();
-    __syncwarp();
-    // the first descriptor patch of this warp travels while the angles are computed (step 2); the buffer was last
-    // written through the generic proxy (cp.async), the TMA writes through the async proxy
-    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int q = 0; q < KPW; ++q) {
+        m10[q] += __shfl_xor_sync(0xffffffffu, m10[q], o);
+        m01[q] += __shfl_xor_sync(0xffffffffu, m01[q], o);
+      }
+    }
+    __syncwarp();  // every lane has read the discs
+    // the first two descriptor patches travel while the angles are computed; the buffers were last written through
+    // the generic proxy (cp.async), the TMA writes through the async proxy
+    if (lane == 0) asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
     stage_patch(warp, 0);
+    stage_patch(warp + DESC_WARPS, 1);
+    // ---- 2. lane q of the warp finishes keypoint q: angle (cv::fastAtan2, :103), its cos / sin (:112-113, documented
+    // deviation 3), and the keypoint record with the rescale of operator() (:1117-1125) ----
+    int my10 = 0, my01 = 0;
+#pragma unroll
+    for (int q = 0; q < KPW; ++q)
+      if (lane == q) { my10 = m10[q]; my01 = m01[q]; }
+    if (lane < KPW) {
+      const int i = warp + lane * DESC_WARPS;
+      const KpSlot k = slot[i];
+      if (k.lvl >= 0) {
+        const LevelGeom& L = g.lv[k.lvl];
+        const float angle = orb_fast_atan2_deg((float)my01, (float)my10);
+        float ca, sb;
+        orb_sincos_deg(angle, &ca, &sb);
+        slot[i].ca = ca;
+        slot[i].sb = sb;
+        orbfe_keypoint o;
+        o.x = (float)k.kx;
+        o.y = (float)k.ky;
+        if (k.lvl != 0) { o.x = __fmul_rn(o.x, L.scale); o.y = __fmul_rn(o.y, L.scale); }
+        o.size = L.kp_size;
+        o.angle = angle;
+        o.response = (float)k.score;
+        o.octave = k.lvl;
+        o.class_id = -1;
+        out_kp[(size_t)b * g.out_cap + oi0 + i] = o;
+      }
+    }
+    __syncwarp();  // slot[].ca / sb of the warp's keypoints are visible to all its lanes
   }
-  __syncthreads();
-
-  // ---- 2. one thread per keypoint: angle (cv::fastAtan2, :103), its cos / sin (:112-113, documented deviation 3),
-  // and the keypoint record with the rescale of operator() (:1117-1125) ----
-  if (tid < DESC_KP && slot[tid].lvl >= 0) {
-    const KpSlot k = slot[tid];
-    const LevelGeom& L = g.lv[k.lvl];
-    const float angle = orb_fast_atan2_deg((float)k.m01, (float)k.m10);
-    float ca, sb;
-    orb_sincos_deg(angle, &ca, &sb);
-    slot[tid].ca = ca;
-    slot[tid].sb = sb;
-    orbfe_keypoint o;
-    o.x = (float)k.kx;
-    o.y = (float)k.ky;
-    if (k.lvl != 0) { o.x = __fmul_rn(o.x, L.scale); o.y = __fmul_rn(o.y, L.scale); }
-    o.size = L.kp_size;
-    o.angle = angle;
-    o.response = (float)k.score;
-    o.octave = k.lvl;
-    o.class_id = -1;
-    out_kp[(size_t)b * g.out_cap + oi0 + tid] = o;
-  }
-  __syncthreads();
 
   // ---- 3. computeOrbDescriptor (:108-147) on the blurred level: lane -> descriptor byte (8 tests = 16 gathers).
   // The 37 x 37 patch the rotated pattern can reach is first copied into shared memory with coalesced word copies
@@ -299,25 +315,38 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
   for (int i = warp; i < DESC_KP; i += DESC_WARPS, buf ^= 1, ++n) {
     const KpSlot k = slot[i];
     if (k.lvl < 0) break;
-    if (i + DESC_WARPS < DESC_KP) stage_patch(i + DESC_WARPS, buf ^ 1);
     mbar_wait(&patch_bar[warp][buf], (unsigned)(n >> 1) & 1u);  // this buffer's (n / 2)-th load
-    const uint8_t* patch_b = reinterpret_cast<const uint8_t*>(patch_all[warp][buf]);
-    const int ctr = 18 * PS + 18 + ((k.kx - 18) & 15);  // byte offset of the keypoint in the patch
+    // Rounding on the FMA pipe instead of 1024 F2I per keypoint on the XU pipe: for |v| < 2^22, v + M (M = 1.5 * 2^23 +
+    // 18, an EVEN integer, so ties still go to the even neighbour of v) is exactly M + rint(v), and its float bits are
+    // 0x4B400012 + rint(v): the low bits of the sum ARE the patch row / column (18 + r in 0..36).  Byte address of
+    // sample (r, c) in the swizzled patch: row * 64 + (col ^ ((row & 6) << 3)), col = 18 + c + (kx - 18) % 16 < 64.
+    // Everything constant is folded into `kc` (multiples of 64 except the column shift, so the XOR of bits 4-5 is not
+    // disturbed): 32-bit shared-window address arithmetic, wrapping mod 2^32.
+    constexpr float kMagic = 12582912.f + 18.f;
+    constexpr unsigned kBits = 0x4B400000u;
+    const unsigned kc = smem_u32(patch_all[warp][buf]) - kBits * 64u - kBits + (unsigned)((k.kx - 18) & 15);
     const float ca = k.ca, sb = k.sb;
     int val = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float x0 = pat[4 * j], y0 = pat[4 * j + 1], x1 = pat[4 * j + 2], y1 = pat[4 * j + 3];
-      const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));
-      const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
-      const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
-      const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-      const int t0 = patch_b[r0 * PS + (c0 + ctr)];
-      const int t1 = patch_b[r1 * PS + (c1 + ctr)];
+      const unsigned r0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)), kMagic));
+      const unsigned c0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)), kMagic));
+      const unsigned r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)), kMagic));
+      const unsigned c1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)), kMagic));
+      const unsigned a0 = r0 * 64u + ((c0 + kc) ^ ((r0 << 3) & 0x30u));
+      const unsigned a1 = r1 * 64u + ((c1 + kc) ^ ((r1 << 3) & 0x30u));
+      unsigned t0, t1;
+      asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t0) : "r"(a0));
+      asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t1) : "r"(a1));
       val |= (t0 < t1) << j;
     }
     out_desc[((size_t)b * g.out_cap + oi0 + i) * 32 + lane] = (uint8_t)val;
-    __syncwarp();  // every lane has read this buffer before the keypoint after next lands in it
+    __syncwarp();  // every lane has read this buffer: the keypoint after next may land in it
+    if (i + 2 * DESC_WARPS < DESC_KP) {
+      if (lane == 0) asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // generic reads before async writes
+      stage_patch(i + 2 * DESC_WARPS, buf);
+    }
   }
 }
 
