@@ -330,8 +330,8 @@ def matcher_extras(torch, dist, orbfe, rank, world, local, kp_frame, desc_frame,
         "workload": "configs[4]: %d queries x %d map descriptors, map sharded over %d GPU(s)" % (nq, nm, world),
         "ms": ms, "pairs_per_s": pairs / (ms * 1e-3), "algorithmic_popc32_per_s": 8.0 * pairs / (ms * 1e-3),
         "popc_peak_per_gpu_measured": popc_peak, "frac_of_popc_peak": 8.0 * pairs / (ms * 1e-3) / (popc_peak * world),
-        "note": "the kernel spends 5 POPC per pair (carry-save compression of the 8 XOR words), so the algorithmic "
-                "rate (8 popc32 per pair) may exceed the POPC pipe's own peak",
+        "note": "the kernel spends 4 POPC per pair (four carry-save adders compress the 8 XOR words into words of "
+                "weight 1, 1, 2, 4), so the algorithmic rate (8 popc32 per pair) may exceed the POPC pipe's own peak",
         "first_best_key": int(best[0].item()) & 0xFFFFFFFFFFFFFFFF,
     }
     if world > 1:

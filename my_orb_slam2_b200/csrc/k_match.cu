@@ -12,12 +12,19 @@
 //   * per (query, map slice) partial top-2 go to a small workspace and a second kernel
 //     merges slices (and, multi-GPU, shards) as 64-bit keys dist<<32 | global index.
 #include <climits>
+#include <cstdlib>
 
 #include "match_kernels.h"
 
 namespace orbfe {
 
-constexpr int BF_T = 128;        // threads per CTA
+#ifndef ORBFE_BF_T
+#define ORBFE_BF_T 128
+#endif
+#ifndef ORBFE_BF_GROUP
+#define ORBFE_BF_GROUP 4
+#endif
+constexpr int BF_T = ORBFE_BF_T;  // threads per CTA
 constexpr int BF_QPT = 4;        // queries per thread
 constexpr int BF_TILE = 256;     // map descriptors per shared-memory tile (8 KB)
 
@@ -146,6 +153,175 @@ __global__ void __launch_bounds__(BF_T) hamming_bruteforce_kernel(const uint4* _
   }
 }
 
+// ---- v2 of the brute-force kernel (round 2): fewer ALU operations per pair, map tiles by bulk TMA ----
+// The round-1 kernel above spends 27 LOP3 per pair (8 XOR + carry-save tree) and is bound by the ALU pipe (85 % busy),
+// not by POPC.  Here the XOR is split off the LINEAR parts of the adder tree: with x_i = q_i ^ m_i,
+//   l1 = x0^x1^x2 = (q0^q1^q2) ^ (m0^m1^m2),  l2 likewise for 3..5,  l3 = l1^l2^x6 = Q3 ^ M3,
+// where the q-terms are per-query constants and the m-terms are computed once per map row and shared by the thread's
+// BF_QPT queries; only the three majorities need the x_i themselves.  A fourth carry-save adder folds the three
+// weight-2 words into one weight-2 and one weight-4 word: 16 LOP3 + 4 POPC per pair (was 27 + 5), and
+//   d = popc(l3) + popc(x7) + 2 popc(hs) + 4 popc(hc).
+// The running top-2 is only touched when a distance beats the query's current second best (one compare per pair and
+// ONE rarely-taken branch per map row for the thread's queries) instead of 3 min/max + a key per pair: rows are scanned
+// in increasing index, so a later row with an equal distance never wins and ties still go to the lowest index.
+// Map tiles arrive by cp.async.bulk (one 8 KB bulk copy per tile, issued by one thread, completing on an mbarrier),
+// double-buffered: the LSU only serves the broadcast reads of the tile.
+// LOP3 through inline asm: opaque to the compiler's algebra, which otherwise re-associates the XORs into the majorities
+// (5 LOP3 per majority instead of 3 + 1) and re-derives the shared map-row terms once per query
+__device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ uint32_t xor2(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("xor.b32 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ unsigned bf_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bf_bulk_load(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  const unsigned b = bf_smem_u32(bar);
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(b), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::
+                   "r"(bf_smem_u32(dst)), "l"(src), "r"(bytes), "r"(b)
+               : "memory");
+}
+__device__ __forceinline__ void bf_mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "BF_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra BF_DONE;\n"
+      "bra BF_WAIT;\n"
+      "BF_DONE:\n"
+      "}\n" ::"r"(bf_smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+
+constexpr int BF_GROUP = ORBFE_BF_GROUP;
+__device__ __forceinline__ uint32_t bf_dist(const uint32_t (&q)[8], uint32_t qa, uint32_t qb, uint32_t qc,
+                                            const uint4& lo, const uint4& hi, uint32_t ma, uint32_t mb, uint32_t mc) {
+  const uint32_t h1 = maj3(xor2(q[0], lo.x), xor2(q[1], lo.y), xor2(q[2], lo.z));
+  const uint32_t h2 = maj3(xor2(q[3], lo.w), xor2(q[4], hi.x), xor2(q[5], hi.y));
+  const uint32_t h3 = maj3(xor2(qa, ma), xor2(qb, mb), xor2(q[6], hi.z));
+  const uint32_t hs = xor3(h1, h2, h3), hc = maj3(h1, h2, h3);
+  return __popc(xor2(qc, mc)) + __popc(xor2(q[7], hi.w)) + 2u * __popc(hs) + 4u * __popc(hc);
+}
+
+template <int QPT>
+__global__ void __launch_bounds__(BF_T) hamming_bruteforce2_kernel(const uint4* __restrict__ query, int nq,
+                                                                   const uint4* __restrict__ map, int nm, int slice_len,
+                                                                   long long index_base,
+                                                                   unsigned long long* __restrict__ part_best,
+                                                                   unsigned long long* __restrict__ part_second) {
+  __shared__ __align__(128) uint4 tile[2][BF_TILE * 2];
+  __shared__ unsigned long long bar[2];
+  const int tid = threadIdx.x;
+  const int q0 = (blockIdx.x * BF_T + tid) * QPT;
+  const int m_begin = blockIdx.y * slice_len;
+  const int m_end = min(nm, m_begin + slice_len);
+  const int ntiles = (m_end - m_begin + BF_TILE - 1) / BF_TILE;
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(bf_smem_u32(&bar[0])) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(bf_smem_u32(&bar[1])) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    for (int t = 0; t < 2 && t < ntiles; ++t) {
+      const int t0 = m_begin + t * BF_TILE;
+      bf_bulk_load(tile[t], map + 2 * (size_t)t0, (unsigned)min(BF_TILE, m_end - t0) * 32u, &bar[t]);
+    }
+  }
+  uint32_t q[QPT][8], qa[QPT], qb[QPT], qc[QPT];
+#pragma unroll
+  for (int k = 0; k < QPT; ++k) {
+    const int qi = min(q0 + k, nq - 1);
+    const uint4 lo = __ldg(query + 2 * qi), hi = __ldg(query + 2 * qi + 1);
+    q[k][0] = lo.x; q[k][1] = lo.y; q[k][2] = lo.z; q[k][3] = lo.w;
+    q[k][4] = hi.x; q[k][5] = hi.y; q[k][6] = hi.z; q[k][7] = hi.w;
+    qa[k] = lo.x ^ lo.y ^ lo.z;
+    qb[k] = lo.w ^ hi.x ^ hi.y;
+    qc[k] = qa[k] ^ qb[k] ^ hi.z;
+  }
+  uint32_t b1[QPT], b2[QPT], thr[QPT];  // keys dist << 20 | row within the slice; thr = distance of the second best
+#pragma unroll
+  for (int k = 0; k < QPT; ++k) { b1[k] = 0xFFFFFFFFu; b2[k] = 0xFFFFFFFFu; thr[k] = 0xFFFu; }
+  __syncthreads();  // the barriers are initialised before anyone waits on them
+
+  for (int t = 0; t < ntiles; ++t) {
+    const int buf = t & 1;
+    const int t0 = m_begin + t * BF_TILE;
+    const int tn = min(BF_TILE, m_end - t0);
+    bf_mbar_wait(&bar[buf], (unsigned)(t >> 1) & 1u);
+    const uint4* tl = tile[buf];
+    const uint32_t jbase = (uint32_t)(t0 - m_begin);
+    // BF_GROUP rows at a time: the distances of a group feed a running minimum per query (no branch between rows, so
+    // the rows' instruction streams overlap) and stay in registers; only when one of them beats a second best as it
+    // stood BEFORE the group (a superset of the rows that update anything) are the group's distances walked again, in
+    // row order, for the exact update.  A warp takes that path for ~10 % of the rows of a slice (128 queries x 2 / row).
+    for (int j0 = 0; j0 < tn; j0 += BF_GROUP) {
+      uint32_t md[QPT], d[BF_GROUP][QPT];
+#pragma unroll
+      for (int k = 0; k < QPT; ++k) md[k] = 0xFFFu;
+#pragma unroll
+      for (int g = 0; g < BF_GROUP; ++g) {
+        const int j = min(j0 + g, tn - 1);  // a short last group repeats its last row (skipped in the update below)
+        const uint4 lo = tl[2 * j], hi = tl[2 * j + 1];
+        const uint32_t ma = xor3(lo.x, lo.y, lo.z), mb = xor3(lo.w, hi.x, hi.y), mc = xor3(ma, mb, hi.z);
+#pragma unroll
+        for (int k = 0; k < QPT; ++k) {
+          d[g][k] = bf_dist(q[k], qa[k], qb[k], qc[k], lo, hi, ma, mb, mc);
+          md[k] = min(md[k], d[g][k]);
+        }
+      }
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < QPT; ++k) any |= md[k] < thr[k];
+      if (any) {
+#pragma unroll
+        for (int g = 0; g < BF_GROUP; ++g) {
+          if (j0 + g < tn) {
+            const uint32_t jj = jbase + (uint32_t)(j0 + g);
+#pragma unroll
+            for (int k = 0; k < QPT; ++k) {
+              if (d[g][k] < thr[k]) {
+                const uint32_t key = (d[g][k] << 20) + jj;
+                b2[k] = min(b2[k], max(b1[k], key));
+                b1[k] = min(b1[k], key);
+                thr[k] = b2[k] >> 20;
+              }
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();  // every thread has read this buffer
+    if (tid == 0 && t + 2 < ntiles) {
+      const int n0 = m_begin + (t + 2) * BF_TILE;
+      asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+      bf_bulk_load(tile[buf], map + 2 * (size_t)n0, (unsigned)min(BF_TILE, m_end - n0) * 32u, &bar[buf]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < QPT; ++k) {
+    const int qi = q0 + k;
+    if (qi < nq) {
+      const size_t o = (size_t)blockIdx.y * nq + qi;
+      const unsigned long long base = (unsigned long long)(index_base + m_begin);
+      part_best[o] = b1[k] == 0xFFFFFFFFu ? ~0ull
+                                          : ((unsigned long long)(b1[k] >> 20) << 32) | (base + (b1[k] & 0xFFFFFu));
+      part_second[o] = b2[k] == 0xFFFFFFFFu ? ~0ull
+                                            : ((unsigned long long)(b2[k] >> 20) << 32) | (base + (b2[k] & 0xFFFFFu));
+    }
+  }
+}
+
 // top-2 of the union of `parts` (best, second) pairs per query; arrays laid out [part][nq]
 __global__ void hamming_merge_kernel(const unsigned long long* __restrict__ best_all,
                                      const unsigned long long* __restrict__ second_all, int parts, int nq,
@@ -167,10 +343,15 @@ void launch_descriptor_distance(const uint8_t* a, const uint8_t* b, int n, int32
                                                              reinterpret_cast<const uint4*>(b), n, out);
 }
 
-int bruteforce_slices(int nq, int nm, int* slice_len) {
-  // enough CTAs for ~3 waves of 148 SMs, slices a multiple of the tile, at most 2^20 rows per slice
+int bruteforce_slices(int nq, int nm, int* slice_len, int max_slices) {
+  // 12 CTAs of 128 threads per SM's worth of slices (5 are resident at 96 registers; short slices keep the tail
+  // small: 3 / 6 / 12 per SM ran the kernel at 514 / 744 / 772 G pairs/s), slices a multiple of the tile, at most
+  // 2^20 rows per slice;
+  // max_slices > 0 caps the number of slices (callers with a fixed partial-result buffer)
   const int qblocks = (nq + BF_T * BF_QPT - 1) / (BF_T * BF_QPT);
-  int want = (148 * 3 + qblocks - 1) / qblocks;
+  static const int waves = [] { const char* e = getenv("ORBFE_BF_WAVES"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 12; }();
+  int want = (148 * waves + qblocks - 1) / qblocks;
+  if (max_slices > 0 && want > max_slices) want = max_slices;
   int len = (nm + want - 1) / want;
   len = (len + BF_TILE - 1) / BF_TILE * BF_TILE;
   if (len < BF_TILE) len = BF_TILE;
@@ -183,9 +364,15 @@ void launch_hamming_bruteforce(const uint8_t* query, int nq, const uint8_t* map,
                                long long index_base, unsigned long long* part_best, unsigned long long* part_second,
                                cudaStream_t s) {
   dim3 grid((nq + BF_T * BF_QPT - 1) / (BF_T * BF_QPT), slices);
-  hamming_bruteforce_kernel<<<grid, BF_T, 0, s>>>(reinterpret_cast<const uint4*>(query), nq,
-                                                  reinterpret_cast<const uint4*>(map), nm, slice_len, index_base,
-                                                  part_best, part_second);
+  static const int version = [] { const char* e = getenv("ORBFE_BF_KERNEL"); return e && e[0] == '1' ? 1 : 2; }();
+  if (version == 1)
+    hamming_bruteforce_kernel<<<grid, BF_T, 0, s>>>(reinterpret_cast<const uint4*>(query), nq,
+                                                    reinterpret_cast<const uint4*>(map), nm, slice_len, index_base,
+                                                    part_best, part_second);
+  else
+    hamming_bruteforce2_kernel<BF_QPT><<<grid, BF_T, 0, s>>>(reinterpret_cast<const uint4*>(query), nq,
+                                                             reinterpret_cast<const uint4*>(map), nm, slice_len,
+                                                             index_base, part_best, part_second);
 }
 
 void launch_hamming_merge(const unsigned long long* best_all, const unsigned long long* second_all, int parts, int nq,

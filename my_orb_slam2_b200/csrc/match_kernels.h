@@ -10,7 +10,7 @@ namespace orbfe {
 
 // ---- k_match.cu ----
 void launch_descriptor_distance(const uint8_t* a, const uint8_t* b, int n, int32_t* out, cudaStream_t s);
-int bruteforce_slices(int nq, int nm, int* slice_len);
+int bruteforce_slices(int nq, int nm, int* slice_len, int max_slices = 0);
 double measure_popc_peak(cudaStream_t s);  // 32-bit POPC results per second of the current device (register-only probe)
 void launch_hamming_bruteforce(const uint8_t* query, int nq, const uint8_t* map, int nm, int slice_len, int slices,
                                long long index_base, unsigned long long* part_best, unsigned long long* part_second,

@@ -75,7 +75,8 @@ int orbfe_hamming_bruteforce_device_noalloc(void* stream, const uint8_t* d_query
     return ORBFE_OK;
   }
   int slice_len = 0;
-  const int slices = bruteforce_slices(nq, nm, &slice_len);
+  // the slicing is capped so that the partial results fit the static array (fewer, longer slices for many queries)
+  const int slices = bruteforce_slices(nq, nm, &slice_len, (int)(kScratchEntries / ((size_t)2 * nq)));
   const size_t need = (size_t)slices * nq * 2;
   if (need > kScratchEntries) {
     set_error("orbfe_hamming_bruteforce_device_noalloc: %d slices x %d queries need %zu scratch entries > %zu "
