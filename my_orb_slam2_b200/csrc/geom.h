@@ -5,6 +5,24 @@
 #include <cstddef>
 #include <cstdint>
 
+// Device-side assertions of the checked build (`make EXTRA=-DORBFE_CHECKS`, tools/checked_build.sh): every shared-memory
+// index and global offset the kernels derive from data is tested against the extent of the array it addresses; a
+// failure prints the expression and traps (the CUDA error fails the calling test).  compute-sanitizer is closed on
+// this GPU pool, so this build + guard bands around the device arenas (extractor.cu) is the memcheck of the repo.
+#ifdef ORBFE_CHECKS
+#include <cstdio>
+#define ORBFE_DCHECK(c)                                                                                          \
+  do {                                                                                                           \
+    if (!(c)) {                                                                                                  \
+      printf("ORBFE_DCHECK failed: %s  (%s:%d) block (%d,%d) thread %d\n", #c, __FILE__, __LINE__, (int)blockIdx.x, \
+             (int)blockIdx.y, (int)threadIdx.x);                                                                 \
+      __trap();                                                                                                  \
+    }                                                                                                            \
+  } while (0)
+#else
+#define ORBFE_DCHECK(c) do { } while (0)
+#endif
+
 namespace orbfe {
 
 constexpr int kMinBorder = 16;   // EDGE_THRESHOLD-3 (src/ORBextractor.cc:785)

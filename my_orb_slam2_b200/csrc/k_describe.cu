@@ -240,6 +240,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
       __syncwarp();
       const unsigned* disc = disc_all + q * (31 * IC_PW);
       const int al = (slot[warp + q * DESC_WARPS].kx - 15) & 3;
+      ORBFE_DCHECK(al >= 0 && al < 4 && av >= 0 && av < 16);
       const uint2* wt = ic_tab + al * (IC_PW * 16) + av;
       int a = 0, s1 = 0;
       if (lane < 31) {
@@ -336,6 +337,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
       const unsigned c1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)), kMagic));
       const unsigned a0 = r0 * 64u + ((c0 + kc) ^ ((r0 << 3) & 0x30u));
       const unsigned a1 = r1 * 64u + ((c1 + kc) ^ ((r1 << 3) & 0x30u));
+      ORBFE_DCHECK(a0 - smem_u32(patch_all[warp][buf]) < (unsigned)(kDescBoxW * kDescBoxH) &&
+                   a1 - smem_u32(patch_all[warp][buf]) < (unsigned)(kDescBoxW * kDescBoxH));
       unsigned t0, t1;
       asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t0) : "r"(a0));
       asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t1) : "r"(a1));

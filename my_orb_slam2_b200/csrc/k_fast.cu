@@ -183,6 +183,7 @@ __device__ __forceinline__ void flatten_slot(const unsigned (&acc)[FD_ACC], unsi
 __device__ __forceinline__ void flatten_all(const unsigned (&acc)[FD_ACC], int lane, int excl, uint16_t* list, unsigned one) {
   unsigned p = (unsigned)__cvta_generic_to_shared(list) + 2u * (unsigned)excl;
   flatten_slot<0>(acc, (unsigned)lane * 4u, p, one);
+  ORBFE_DCHECK(p <= (unsigned)__cvta_generic_to_shared(list) + 2u * FD_CAP);
 }
 
 // write the entries (row<<7 | column) whose flat index lies in [lo, lo+FD_CAP) into list[index - lo]; WINDOWED=false
@@ -197,6 +198,7 @@ __device__ __forceinline__ void flatten_window(const unsigned (&acc)[FD_ACC], in
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       if (a & (1u << k)) {
+        ORBFE_DCHECK(WINDOWED || (unsigned)off < (unsigned)FD_CAP);
         if (!WINDOWED || (unsigned)off < (unsigned)FD_CAP) list[off] = (uint16_t)((r << 7) | (col + k));
         ++off;
       }
@@ -325,10 +327,14 @@ __global__ void __launch_bounds__(FD_T, 28) fast_detect_kernel(const __grid_cons
       bool keep = false;
       int e = 0;
       if (i < n) {
+        ORBFE_DCHECK(i < FD_CAP);
         e = sm.list[i];
         const int r = e >> 7, cx = e & 127;
         const int x = cx0 + cx, y = cy0 + r;
+        ORBFE_DCHECK(r >= 1 && r <= FD_ROWS - 2 && cx >= 1 && cx <= 126);  // the 8 neighbours are inside the score tile
+        ORBFE_DCHECK(x >= kEdge && x < x_end && y >= kEdge && y < y_end);
         const int cj = (int)__umulhi((unsigned)(x - kEdge), inv_w), ci = (int)__umulhi((unsigned)(y - kEdge), inv_h);
+        ORBFE_DCHECK(cj >= 0 && cj < L.n_cols && ci >= 0 && ci < L.n_rows);
         // detection window of the pixel's cell (:803-818 minus FAST's 3-px margin)
         const int wx0 = kEdge + cj * L.w_cell, wx1 = min(wx0 + L.w_cell, x_end);
         const int wy0 = kEdge + ci * L.h_cell, wy1 = min(wy0 + L.h_cell, y_end);
@@ -345,6 +351,7 @@ __global__ void __launch_bounds__(FD_T, 28) fast_detect_kernel(const __grid_cons
       }
       const unsigned mk = __ballot_sync(0xffffffffu, keep);
       __syncwarp();  // this chunk has been read by every lane before slots <= base+31 are overwritten
+      ORBFE_DCHECK(!keep || nmax + __popc(mk & lt) <= i);  // in-place compaction never runs ahead of the reads
       if (keep) sm.list[nmax + __popc(mk & lt)] = (uint16_t)e;
       nmax += __popc(mk);
     }
@@ -381,6 +388,8 @@ __global__ void __launch_bounds__(FD_T, 28) fast_detect_kernel(const __grid_cons
       if (i < total) {
         e = sm.list[i];
         const int r = e >> 7, cx = e & 127;
+        ORBFE_DCHECK(i < FD_CAP && r >= 0 && r < FD_ROWS && cx >= 0 && cx < 128);
+        ORBFE_DCHECK(timg + (r + 6) * FD_TS + cx + 7 < sm.img + sizeof(sm.img) && timg + r * FD_TS + cx + 1 >= sm.img);
         const int m = corner_strength(timg + (r + 3) * FD_TS + cx + 4);
         if (m > t_lo) {
           sm.score[r * 128 + cx] = (uint8_t)(m - 1);
@@ -389,6 +398,7 @@ __global__ void __launch_bounds__(FD_T, 28) fast_detect_kernel(const __grid_cons
       }
       const unsigned mk = __ballot_sync(0xffffffffu, corner);
       __syncwarp();  // this chunk has been read by every lane before slots <= base+31 are overwritten
+      ORBFE_DCHECK(!corner || nc + __popc(mk & lt) <= i);
       if (corner) sm.list[nc + __popc(mk & lt)] = (uint16_t)e;
       nc += __popc(mk);
     }

@@ -85,9 +85,11 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
     c0 = __ldg(&xt[xc].sx0) & ~15;
     const int ws_last = __ldg(&xt[min(xc + 124, (D.w - 1) & ~3)].sx0) & ~3;
     const int nchunks = ((ws_last + 11 - c0) >> 4) + 1;  // <= PT_CHUNKS
+    ORBFE_DCHECK(nchunks >= 1 && nchunks <= PT_CHUNKS);
     const YTab* ytc = ytab + D.ytab_off;
     s_first = __ldg(&ytc[yc].sy0);
     const int nrows = __ldg(&ytc[min(yc + PY_WARPS * PY_ROWS, D.h) - 1].sy1) - s_first + 1;  // <= PT_ROWS
+    ORBFE_DCHECK(nrows >= 1 && nrows <= PT_ROWS);
     const int c = threadIdx.x & 15;
     if (c < nchunks) {
       const uint8_t* gp = src + (size_t)s_first * spitch + c0 + c * 16;
@@ -123,6 +125,7 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
   auto hrow = [&](int sy, unsigned (&h)[4]) {
     unsigned w0, w1, w2;
     if (TILE) {
+      ORBFE_DCHECK(sy >= s_first && sy - s_first < PT_ROWS && ws - c0 >= 0 && ws - c0 + 12 <= PT_STRIDE);
       const unsigned* p = reinterpret_cast<const unsigned*>(sbase + (sy - s_first) * PT_STRIDE);
       w0 = p[0]; w1 = p[1]; w2 = p[2];
     } else {

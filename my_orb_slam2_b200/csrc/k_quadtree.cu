@@ -180,6 +180,7 @@ __global__ void __launch_bounds__(QT_T, MINB) quadtree_kernel(const __grid_const
   __syncthreads();
   for (int i = tid; i < n_ini; i += QT_T) sm.surv[i] = sm.cnt[1][i] > 0 ? 1 : 0;
   __syncthreads();
+  ORBFE_DCHECK(n_ini <= C);
   int S = block_excl_scan(sm.surv, n_ini, wtmp);
   for (int i = tid; i < n_ini; i += QT_T)
     if (sm.cnt[1][i] > 0) { sm.box[0][sm.surv[i]] = sm.box[1][i]; sm.cnt[0][sm.surv[i]] = sm.cnt[1][i]; }
@@ -194,6 +195,7 @@ __global__ void __launch_bounds__(QT_T, MINB) quadtree_kernel(const __grid_const
   while (true) {
     int4* box = sm.box[cur];
     int* cnt = sm.cnt[cur];
+    ORBFE_DCHECK(S >= 1 && S <= C);
     // ---- A: speculative child counts ----
     for (int i = tid; i < 4 * S; i += QT_T) sm.cc[i] = 0;
     for (int i = tid; i < S; i += QT_T) { sm.elist[i] = cnt[i] > 1 ? 1 : 0; sm.nrank[i] = -1; }
@@ -201,6 +203,7 @@ __global__ void __launch_bounds__(QT_T, MINB) quadtree_kernel(const __grid_const
     __syncthreads();
     for (int k = tid; k < n; k += QT_T) {
       const int nd = nk[k];
+      ORBFE_DCHECK(nd < S);
       if (cnt[nd] > 1) {
         const uint32_t c = ck[k];
         atomicAdd(&sm.cc[nd * 4 + quadrant(box[nd], cand_x(c), cand_y(c))], 1);
@@ -275,6 +278,7 @@ __global__ void __launch_bounds__(QT_T, MINB) quadtree_kernel(const __grid_const
           if (c > 0) {
             const int pos = TP - 1 - pi;  // push_front: later pushes sit nearer the front (:623-662)
             ++pi;
+            ORBFE_DCHECK(pos >= 0 && pos < S2 && S2 <= C);
             nbox[pos] = make_int4((q & 1) ? mx : bx.x, (q & 1) ? bx.y : mx, (q & 2) ? my : bx.z, (q & 2) ? bx.w : my);
             ncnt[pos] = c;
             sm.cc[i * 4 + q] = pos;
@@ -284,6 +288,7 @@ __global__ void __launch_bounds__(QT_T, MINB) quadtree_kernel(const __grid_const
         if (many) atomicAdd(&s_misc[1], many);
       } else {
         const int pos = TP + sm.surv[i];
+        ORBFE_DCHECK(pos >= 0 && pos < S2 && S2 <= C);
         nbox[pos] = box[i];
         ncnt[pos] = cnt[i];
         sm.surv[i] = pos;
@@ -324,7 +329,10 @@ __global__ void __launch_bounds__(QT_T, MINB) quadtree_kernel(const __grid_const
     const unsigned long long ord = (cy << 32) | (cx << 24) | ((unsigned long long)y << 12) | (unsigned long long)x;
     return ((unsigned long long)cand_score(c) << 40) | (~ord & 0xFFFFFFFFFFull);
   };
-  for (int k = tid; k < n; k += QT_T) atomicMax(&sm.best[nk[k]], order_key(ck[k]));
+  for (int k = tid; k < n; k += QT_T) {
+    ORBFE_DCHECK(nk[k] < S && S <= C);
+    atomicMax(&sm.best[nk[k]], order_key(ck[k]));
+  }
   __syncthreads();
   uint32_t* out = kept + (size_t)b * g.kept_total + L.kept_off;
   for (int k = tid; k < n; k += QT_T) {

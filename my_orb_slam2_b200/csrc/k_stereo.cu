@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 32) stereo_match_kernel(
     // the bucket's items are sorted by octave: only octaves levelL-1 .. levelL+1 are candidates (:565-566)
     const int k0 = (rowi / ST_BROWS) * nl;
     const int beg = bstart[k0 + max(levelL - 1, 0)], end = bstart[k0 + min(levelL + 1, nl - 1) + 1];
+    ORBFE_DCHECK(levelL >= 0 && levelL < nl && beg >= 0 && beg <= end && end <= g.out_cap * items_per_kp);
     const uint8_t* dR = descR + (size_t)b * g.out_cap * 32;
     // 4 items per lane in flight: the item loads of a 128-item chunk are issued together, then the descriptor loads
     for (int base = beg; base < end; base += 128) {
@@ -168,6 +169,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 32) stereo_match_kernel(
   const int bestDist = (int)(best >> 16);
   if (bestDist < (TH_HIGH + TH_LOW) / 2) {  // :591 (bestDist stays TH_HIGH when not searchable)
     const int bestIdxR = (int)(best & 0xFFFFu);
+    ORBFE_DCHECK(bestIdxR < g.out_cap);
     const float uR0 = kr[bestIdxR].x;
     const LevelGeom& LV = g.lv[levelL];
     const float sf = LV.inv_scale;
@@ -190,6 +192,8 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 32) stereo_match_kernel(
         asm volatile("prefetch.global.L1 [%0];" ::"l"(row));
         asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 20));
       }
+      ORBFE_DCHECK(cvL - w >= 0 && cvL + w < LV.h && cuL - w >= 0 && cuL + w < LV.w && cuR - w - Lh >= 0 &&
+                   cuR + w + Lh < LV.pitch);
       const int centerL = __ldg(imL + (size_t)cvL * LV.pitch + cuL);
       int sad[11];
 #pragma unroll
