@@ -8,12 +8,14 @@
  * bench.py's cpu_baseline / --impl reference legs may load it.  The product
  * (my_orb_slam2_b200, liborbfe.so) never links, imports or calls it.
  *
- * PARITY STATUS: "parity unpinned" by the reference itself — the reference has
- * no tests / golden vectors, and cannot be compiled here (OpenCV C++, Eigen and
- * Pangolin are absent).  The pixel arithmetic lives in OpenCV (un-vendored,
- * version not pinned by the reference); the oracle pins OpenCV 4.13.0
- * semantics, and each primitive is checked bit-for-bit against python cv2
- * 4.13.0 (tests/test_oracle_cv2.py + committed fixtures in tests/golden/).
+ * PARITY STATUS: pinned.  (1) tests/test_ref_compiled.py holds this restatement
+ * bit-equal to the UNMODIFIED reference sources compiled in place
+ * (oracle/_ref/libref_orbslam2.so: /root/reference/src/{ORBextractor,Frame,
+ * ORBmatcher,...}.cc against the OpenCV stand-in of oracle/ref_shim/) on the
+ * full-size configs; (2) the pixel arithmetic that lives in OpenCV
+ * (un-vendored, version not pinned by the reference) is pinned to OpenCV 4.13.0:
+ * each primitive and the whole extraction are checked bit-for-bit against
+ * committed python-cv2 4.13.0 fixtures (tests/golden/, tests/test_oracle_golden.py).
  */
 #ifndef ORB_ORACLE_H_
 #define ORB_ORACLE_H_
