@@ -680,9 +680,12 @@ def run_gpu(args):
             self.R.run(B)
             orbfe.check(lib.orbfe_stereo_match_run(self.L._h, self.R._h, B, MBF, MB))
 
-        def download_async(self):
+        def download_async(self, right=True):
             cap = self.L.capacity
-            orbfe.check(lib.orbfe_extract_download_async(self.R._h, B, self.kpR.data_ptr(), self.dsR.data_ptr(), cap,
+            # right=False: the right image's keypoints / descriptors stay on the device (only their counts leave);
+            # Frame reads them nowhere outside ComputeStereoMatches (src/Frame.cc:516-594), which ran on the device
+            orbfe.check(lib.orbfe_extract_download_async(self.R._h, B, self.kpR.data_ptr() if right else None,
+                                                         self.dsR.data_ptr() if right else None, cap,
                                                          self.cntR.data_ptr()))
             orbfe.check(lib.orbfe_extract_download_async(self.L._h, B, self.kpL.data_ptr(), self.dsL.data_ptr(), cap,
                                                          self.cntL.data_ptr()))
@@ -712,7 +715,7 @@ def run_gpu(args):
         for j in range(NB):
             batch_device(j)
 
-    def batch_e2e(k):
+    def batch_e2e(k, right=True):
         """pinned host images -> H2D -> kernels -> keypoints, descriptors, uRight, depth in pinned host memory.
         Software-pipelined over the rigs: batch k's copies overlap batch k-1's kernels (different streams)."""
         g = rigs[k % len(rigs)]
@@ -721,7 +724,7 @@ def run_gpu(args):
         g.L.upload(pl, B)
         g.R.upload(pr, B)
         g.kernels()
-        g.download_async()
+        g.download_async(right)
 
     def barrier():
         torch.cuda.synchronize()
@@ -820,6 +823,26 @@ def run_gpu(args):
     torch.cuda.synchronize()
     t_e2e = max_over_ranks(time.perf_counter() - t0)
     clocks_e2e = sampler2.result()
+    # the same leg with the right image's keypoints / descriptors left on the device (an OPTION of the C ABI: NULL
+    # output pointers; the default above is faithful to what Frame keeps): half the D2H traffic.  Reported beside the
+    # headline because D2H is the expensive direction of this host at N ranks (host.d2h_gbs_concurrent)
+    n_lo = max(args.steps // 2, 1) * NB
+    for k in range(len(rigs)):
+        batch_e2e(k, right=False)
+    for g in rigs:
+        g.finish()
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(n_lo):
+        batch_e2e(k, right=False)
+    for g in rigs:
+        g.finish()
+    torch.cuda.synchronize()
+    t_e2e_lo = max_over_ranks(time.perf_counter() - t0)
+    e2e_left_only = {"value": n_lo * B * world / t_e2e_lo, "unit": "frames/s",
+                     "d2h_bytes_per_step": int(NB * B * (cap * (28 + 32 + 8) + 12)),
+                     "what": "as e2e, but the right image's keypoints and descriptors stay on the device (NULL output "
+                             "pointers): Frame reads them only inside ComputeStereoMatches (src/Frame.cc:516-594)"}
     # what the host link can do with ALL ranks copying at once (no kernels): every rank moves its pinned image buffer
     # to the device / a result-sized buffer back, 5 times back to back, after a barrier; the sum over the ranks is
     # the concurrent ceiling the e2e leg's traffic is compared with
@@ -1006,6 +1029,7 @@ def run_gpu(args):
                 "dropin_what": "compat::ORBextractor::operator() for L and R on two threads (pageable buffers) + "
                                "ComputeStereoMatches, the sequence of src/Frame.cc:89-102, timed in C++ "
                                "(compat/bench_dropin.cc)",
+                "left_only": e2e_left_only,
                 "clocks": clocks_e2e},
         "latency_ms_p50": float(np.percentile(lat, 50)) if lat else None,
         "latency_ms_p95": float(np.percentile(lat, 95)) if lat else None,
