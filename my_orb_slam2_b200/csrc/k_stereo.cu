@@ -115,6 +115,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 32) stereo_match_kernel(
   const float minU = __fsub_rn(uL, maxD), maxU = uL;  // :554-555 (minD = 0)
   const bool searchable = rowi >= 0 && rowi < n_rows && !(maxU < 0.f);
   unsigned best = ((unsigned)TH_HIGH << 16);  // bestDist = TH_HIGH, strict '<' below (:560,:581)
+  int best_x = 0;  // x bits of the lane's best right keypoint (rides along: no dependent kr[bestIdxR] load afterwards)
   if (searchable) {
     const int nb = (n_rows + ST_BROWS - 1) / ST_BROWS, nl = g.nlevels;
     const int32_t* bstart = bucket_start + (size_t)b * (nb * nl + 1);
@@ -153,15 +154,20 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 32) stereo_match_kernel(
         for (int u = 0; u < 2; ++u) {
           if (cand[h + u]) {
             const unsigned dist = (unsigned)hamming256(d0, d1, r0[u], r1[u]);
-            best = min(best, (dist << 16) | (unsigned)(bd[h + u].w >> 8));
+            const unsigned key = (dist << 16) | (unsigned)(bd[h + u].w >> 8);
+            if (key < best) { best = key; best_x = bd[h + u].z; }
           }
         }
       }
     }
   }
   if (!active) return;
+  const unsigned my_best = best;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+  // the winning lane (keys are unique: they carry the right keypoint's index) hands over its keypoint's x
+  const unsigned owners = __ballot_sync(0xffffffffu, my_best == best);
+  best_x = __shfl_sync(0xffffffffu, best_x, __ffs(owners) - 1);
 
   const size_t oidx = (size_t)b * g.out_cap + iL;
   float res_u = -1.f, res_d = -1.f;
@@ -170,7 +176,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32, 32) stereo_match_kernel(
   if (bestDist < (TH_HIGH + TH_LOW) / 2) {  // :591 (bestDist stays TH_HIGH when not searchable)
     const int bestIdxR = (int)(best & 0xFFFFu);
     ORBFE_DCHECK(bestIdxR < g.out_cap);
-    const float uR0 = kr[bestIdxR].x;
+    const float uR0 = __int_as_float(best_x);  // == kr[bestIdxR].x (the bucket item carries the bits)
     const LevelGeom& LV = g.lv[levelL];
     const float sf = LV.inv_scale;
     const float scaleduL = roundf(__fmul_rn(uL, sf));
