@@ -1044,9 +1044,13 @@ def run_gpu(args):
                  "h2d_gbs_rank0": h2d_rank, "d2h_gbs_rank0": d2h_rank,
                  "e2e_h2d_gbs": e2e_h2d_gbs, "e2e_d2h_gbs": e2e_d2h_gbs,
                  "e2e_frac_of_link": e2e_h2d_gbs / h2d_all if h2d_all > 0 else None,
-                 "e2e_bound": "host-to-device link: the e2e leg must move 2 x W x H input bytes per pair; "
-                              "e2e_frac_of_link = its input traffic / the measured concurrent H2D ceiling of the same "
-                              "ranks",
+                 "e2e_frac_of_bidir_link": (e2e_h2d_gbs + e2e_d2h_gbs) / bidir_all if bidir_all > 0 else None,
+                 "e2e_bound": "the host link: the e2e leg must move 2 x W x H input bytes per pair in and ~0.26 MB of "
+                              "results out.  e2e_frac_of_link = its input traffic / the measured concurrent H2D-only "
+                              "ceiling of the same ranks (the bound at 1-2 ranks); e2e_frac_of_bidir_link = its traffic "
+                              "in BOTH directions / the measured ceiling with both directions busy (the bound from 4 "
+                              "ranks on: this host's aggregate stops near 150 GB/s as soon as D2H traffic is mixed in, "
+                              "although H2D alone reaches 236 GB/s at 8 ranks) — see e2e.left_only",
                  "topology": topo},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                      "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src,
