@@ -28,7 +28,10 @@ namespace orbfe {
 constexpr int kMinBorder = 16;   // EDGE_THRESHOLD-3 (src/ORBextractor.cc:785)
 constexpr int kMaxLevels = 16;
 constexpr int kFastOwnCols = 120;  // k_fast.cu: a strip computes 128 x (rows+2) pixels and owns the inner 120 x rows
-constexpr int kFastOwnRows = 14;
+#ifndef ORBFE_FAST_OWN_ROWS
+#define ORBFE_FAST_OWN_ROWS 14
+#endif
+constexpr int kFastOwnRows = ORBFE_FAST_OWN_ROWS;
 
 struct LevelGeom {
   int w, h, pitch;          // level image; pitch multiple of 128

@@ -206,8 +206,12 @@ __device__ __forceinline__ void flatten_window(const unsigned (&acc)[FD_ACC], in
   }
 }
 
-template <bool SECOND>  // compile-time: the iniTh launch carries none of the open-cell bookkeeping of the minTh launch
-__global__ void __launch_bounds__(FD_T, 28) fast_detect_kernel(const __grid_constant__ PyrGeom g,
+// compile-time: the iniTh launch carries none of the open-cell bookkeeping of the minTh launch
+#ifndef ORBFE_FAST_MINB
+#define ORBFE_FAST_MINB 28
+#endif
+template <bool SECOND>
+__global__ void __launch_bounds__(FD_T, ORBFE_FAST_MINB) fast_detect_kernel(const __grid_constant__ PyrGeom g,
                                                            const uint8_t* __restrict__ pyr,
                                                            uint32_t* __restrict__ cand,
                                                            int32_t* __restrict__ cand_count,
