@@ -979,8 +979,10 @@ def run_gpu(args):
     traffic = None
     issue = None
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
-        kname = {"fast": "fast_detect_kernel", "blur": "void blur_levels_kernel<32>", "describe": "describe_kernel",
+        tpath = [p for p in (os.path.join(ROOT, "profiles", t) for t in ("r2_traffic.json", "r1_traffic.json"))
+                 if os.path.exists(p)][0]   # the latest committed capture
+        tj = json.load(open(tpath))
+        kname = {"fast": "fast_detect_kernel", "blur": "void blur_levels_kernel<32, 1>", "describe": "describe_kernel",
                  "pyramid": "void pyramid_level_kernel<8, 1>", "quadtree": "void quadtree_kernel<3>"}[dom]
         traffic = tj[kname]["dram_bytes_per_launch"] * B / tj[kname]["images"]
         # the bound that applies (north_star: "fraction of the HBM or integer-pipe roofline"): warp instructions of
