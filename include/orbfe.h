@@ -289,6 +289,14 @@ int orbfe_hamming_bruteforce_device(orbfe_matcher* m, const uint8_t* d_query, in
  * [shard][nq]) into the global top-2 (device arrays [nq]). */
 int orbfe_hamming_merge_device(orbfe_matcher* m, const uint64_t* d_best_all, const uint64_t* d_second_all,
                                int shards, int nq, uint64_t* d_best, uint64_t* d_second);
+/* The same top-2 keys as orbfe_hamming_bruteforce_device, computed on the tensor cores: 256-bit Hamming distance as a
+ * {0,1} int8 GEMM (d = |q| + |m| - 2 q.m; tcgen05.mma kind::i8, TMEM accumulators, TMA operand tiles;
+ * my_orb_slam2_b200/csrc/k_match_mma.cu).  OPTIONAL second path of BASELINE.json config 5 — north_star's stated choice
+ * (popc) stays the default; bench.py reports both with bit-equal keys.  Asynchronous on the matcher's stream; nm >= 1;
+ * scratch grows to nm x 256 bytes (the map expanded to one byte per bit).  orbfe_matcher_sync returns ORBFE_ERR_CUDA if
+ * the kernel's internal pipeline timed out. */
+int orbfe_hamming_bruteforce_tc_device(orbfe_matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm,
+                                       int64_t index_base, uint64_t* d_best, uint64_t* d_second);
 /* No counterpart in the reference: added for callers that cannot allocate
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as
  * orbfe_hamming_bruteforce_device (device pointers in and out, asynchronous on `stream`, a cudaStream_t; NULL = the

@@ -18,6 +18,13 @@ void launch_hamming_bruteforce(const uint8_t* query, int nq, const uint8_t* map,
 void launch_hamming_merge(const unsigned long long* best_all, const unsigned long long* second_all, int parts, int nq,
                           unsigned long long* best, unsigned long long* second, cudaStream_t s);
 
+// ---- k_match_mma.cu: the same brute force on the tensor cores (tcgen05 kind::i8; optional second path) ----
+int hamming_mma_slices(int nq, int nm, int sms, int* tiles_per_slice);
+size_t hamming_mma_scratch_bytes(int nq, int nm, int slices);
+int launch_hamming_mma(const uint8_t* query, int nq, const uint8_t* map, int nm, long long index_base, uint8_t* scratch,
+                       int slices, int tiles_per_slice, int sms, unsigned long long* best, unsigned long long* second,
+                       unsigned** err_out, cudaStream_t s);
+
 void launch_distinctive(const uint8_t* desc, const int32_t* offsets, int n_points, int32_t* best_idx,
                         uint8_t* best_desc, cudaStream_t s);
 

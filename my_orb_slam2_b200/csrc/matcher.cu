@@ -37,6 +37,8 @@ void orbfe_matcher_destroy(orbfe_matcher* h) {
   if (m->d_buf) cudaFree(m->d_buf);
   if (m->h_buf) cudaFreeHost(m->h_buf);
   if (m->d_cand) cudaFree(m->d_cand);
+  if (m->d_tc) cudaFree(m->d_tc);
+  if (m->h_tc_err) cudaFreeHost(m->h_tc_err);
   if (m->h_small) cudaFreeHost(m->h_small);
   cudaStreamDestroy(m->stream);
   delete m;
@@ -50,6 +52,43 @@ int orbfe_matcher_sync(orbfe_matcher* h) {
   Matcher* m = reinterpret_cast<Matcher*>(h);
   DeviceGuard guard(m->device);
   ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+  if (m->tc_pending) {  // the tensor-core brute force reports a pipeline time-out through a pinned word
+    m->tc_pending = false;
+    if (m->h_tc_err && *reinterpret_cast<volatile unsigned*>(m->h_tc_err) != 0) {
+      set_error("orbfe_hamming_bruteforce_tc_device: the tcgen05 pipeline timed out (internal error); use the POPC path");
+      return ORBFE_ERR_CUDA;
+    }
+  }
+  return ORBFE_OK;
+}
+
+int orbfe_hamming_bruteforce_tc_device(orbfe_matcher* h, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm,
+                                       int64_t index_base, uint64_t* d_best, uint64_t* d_second) {
+  ORBFE_ARG(h && d_query && d_best && d_second && nq >= 1 && nm >= 1 && d_map);
+  ORBFE_ARG(index_base >= 0 && index_base + (int64_t)nm <= ((int64_t)1 << 32));
+  Matcher* m = reinterpret_cast<Matcher*>(h);
+  DeviceGuard guard(m->device);
+  if (m->sms == 0) ORBFE_CUDA(cudaDeviceGetAttribute(&m->sms, cudaDevAttrMultiProcessorCount, m->device));
+  int tps = 0;
+  const int slices = hamming_mma_slices(nq, nm, m->sms, &tps);
+  const size_t need = hamming_mma_scratch_bytes(nq, nm, slices);
+  if (need > m->tc_cap) {
+    if (m->d_tc) { ORBFE_CUDA(cudaStreamSynchronize(m->stream)); cudaFree(m->d_tc); m->d_tc = nullptr; m->tc_cap = 0; }
+    ORBFE_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_tc), need));
+    m->tc_cap = need;
+  }
+  if (!m->h_tc_err) ORBFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&m->h_tc_err), 64, cudaHostAllocDefault));
+  unsigned* d_err = nullptr;
+  const int rc = launch_hamming_mma(d_query, nq, d_map, nm, index_base, m->d_tc, slices, tps, m->sms,
+                                    reinterpret_cast<unsigned long long*>(d_best),
+                                    reinterpret_cast<unsigned long long*>(d_second), &d_err, m->stream);
+  if (rc != 0) {
+    set_error("orbfe_hamming_bruteforce_tc_device: set-up failed (%d): %s", rc, cudaGetErrorString(cudaGetLastError()));
+    return ORBFE_ERR_CUDA;
+  }
+  ORBFE_CUDA(cudaMemcpyAsync(m->h_tc_err, d_err, 4, cudaMemcpyDeviceToHost, m->stream));
+  m->tc_pending = true;
+  m->launches += 5;
   return ORBFE_OK;
 }
 

@@ -21,6 +21,11 @@ struct Matcher {
   size_t cand_cap = 0;
   int32_t* h_small = nullptr; // pinned, 16 ints
   int64_t launches = 0;
+  uint8_t* d_tc = nullptr;     // scratch of the tensor-core brute force (expanded descriptors, partial keys)
+  size_t tc_cap = 0;
+  unsigned* h_tc_err = nullptr;  // pinned: error word of the last tensor-core call
+  bool tc_pending = false;
+  int sms = 0;
 };
 
 inline int arena_reserve(Matcher* m, size_t bytes) {

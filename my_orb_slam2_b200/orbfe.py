@@ -152,6 +152,7 @@ SYMBOLS = {
     "orbfe_hamming_bruteforce": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_bruteforce_device": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_merge_device": (_I, [_P, _P, _P, _I, _I, _P, _P]),
+    "orbfe_hamming_bruteforce_tc_device": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_hamming_bruteforce_device_noalloc": (_I, [_P, _P, _I, _P, _I, C.c_int64, _P, _P]),
     "orbfe_matcher_sync": (_I, [_P]),
     "orbfe_comm_unique_id": (_I, [_P]),
@@ -506,6 +507,10 @@ class Matcher:
     def hamming_bruteforce_device(self, d_query, nq, d_map, nm, index_base, d_best, d_second):
         """Device-pointer variant (ints from torch .data_ptr()); asynchronous on the matcher's stream."""
         check(lib().orbfe_hamming_bruteforce_device(self._h, d_query, nq, d_map, nm, index_base, d_best, d_second))
+
+    def hamming_bruteforce_tc_device(self, d_query, nq, d_map, nm, index_base, d_best, d_second):
+        """The tensor-core variant (tcgen05 kind::i8 GEMM on the expanded bits); same keys, asynchronous."""
+        check(lib().orbfe_hamming_bruteforce_tc_device(self._h, d_query, nq, d_map, nm, index_base, d_best, d_second))
 
     def hamming_merge_device(self, d_best_all, d_second_all, shards, nq, d_best, d_second):
         check(lib().orbfe_hamming_merge_device(self._h, d_best_all, d_second_all, shards, nq, d_best, d_second))

@@ -47,6 +47,33 @@ def test_bruteforce_vs_oracle(oracle, nq, nm, base):
     assert np.array_equal(best, ob) and np.array_equal(second, os_)
 
 
+@pytest.mark.parametrize("nq,nm,base", [(1, 1, 0), (7, 33, 5), (300, 5000, (1 << 32) - 5000), (1000, 100000, 11),
+                                        (8192, 20000, 0)])
+def test_bruteforce_tensor_core_path_vs_oracle(oracle, nq, nm, base):
+    """orbfe_hamming_bruteforce_tc_device (tcgen05 kind::i8 GEMM on the expanded bits, k_match_mma.cu): keys bit-equal
+    to the oracle's double loop over DescriptorDistance, ragged sizes, duplicates (ties to the lowest index), twice in a
+    row on the same matcher (scratch and TMEM reuse)."""
+    import torch
+    from my_orb_slam2_b200 import orbfe
+    q, m = synth.bruteforce_case(nq, nm, min(nq, nm) // 2, seed=nq + 1)
+    if nm > 40:
+        m[17] = m[3]
+        m[nm - 1] = m[3]
+        q[0] = m[3]
+    ob, os_ = oracle.hamming_bruteforce(q, m, base)
+    dev = torch.device("cuda", 0)
+    d_q, d_m = torch.from_numpy(q).to(dev), torch.from_numpy(m).to(dev)
+    mt = orbfe.Matcher()
+    for _ in range(2):
+        best = torch.zeros(nq, dtype=torch.int64, device=dev)
+        second = torch.zeros(nq, dtype=torch.int64, device=dev)
+        torch.cuda.synchronize()
+        mt.hamming_bruteforce_tc_device(d_q.data_ptr(), nq, d_m.data_ptr(), nm, base, best.data_ptr(), second.data_ptr())
+        mt.sync()
+        assert np.array_equal(best.cpu().numpy().view(np.uint64), ob)
+        assert np.array_equal(second.cpu().numpy().view(np.uint64), os_)
+
+
 def test_bruteforce_full_size_properties():
     """Config 5 per-GPU shard (8192 x 131072) and a 1M map: checked through properties the oracle-free way:
     planted duplicates are found, sharded top-2 merged == unsharded top-2, best <= second."""
