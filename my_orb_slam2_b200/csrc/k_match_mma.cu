@@ -104,6 +104,11 @@ __device__ __forceinline__ void mm_tma_load_2d(void* dst, const CUtensorMap* map
           "r"(mm_smem(dst)), "l"(map), "r"(x), "r"(y), "r"(mm_smem(bar))
       : "memory");
 }
+__device__ __forceinline__ void mm_bulk_load(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::
+                   "r"(mm_smem(dst)), "l"(src), "r"(bytes), "r"(mm_smem(bar))
+               : "memory");
+}
 // shared-memory matrix descriptor: K-major, 128-byte swizzle, 8-row groups 1024 bytes apart (sm_100 version field = 1)
 __device__ __forceinline__ unsigned long long mm_desc(unsigned smem_addr) {
   return (unsigned long long)((smem_addr >> 4) & 0x3FFFu) | ((unsigned long long)(1024u >> 4) << 32) | (1ull << 46) |
@@ -126,8 +131,10 @@ __device__ __forceinline__ void mm_commit(unsigned long long* bar) {
 }
 __device__ __forceinline__ void mm_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void mm_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
-// 32 lanes x 32 columns of 32 bits: thread i of the warp gets TMEM lane (lane field + i), columns col .. col+31
-__device__ __forceinline__ void mm_tmem_ld32(unsigned taddr, int (&r)[32]) {
+// 32 lanes x 32 columns of 32 bits: thread i of the warp gets TMEM lane (lane field + i), columns col .. col+31.
+// Issue and wait are separate so that the next chunk travels while this one is processed; the wait takes the
+// registers as in/out operands, which keeps the compiler from reading them before the load has landed.
+__device__ __forceinline__ void mm_tmem_ld32_issue(unsigned taddr, int (&r)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -138,12 +145,24 @@ __device__ __forceinline__ void mm_tmem_ld32(unsigned taddr, int (&r)[32]) {
         "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr)
       : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void mm_tmem_ld_wait(int (&r)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                 "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]),
+                 "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]),
+                 "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+               :
+               : "memory");
 }
 
 struct __align__(1024) MmSmem {
   uint8_t a[2][MM_KB][MM_TILE_BYTES];          // the item's two query tiles (64 KB)
   uint8_t b[MM_STAGES][MM_KB][MM_TILE_BYTES];  // map tile ring (128 KB)
+  // |m_j| of the map tiles, 8 slots by running tile number: slot n is reloaded for tile n+8, whose load can only be
+  // issued after MMA n+4 has finished, which needed the epilogue of tile n+2 (two accumulator buffers) — so the
+  // epilogue of tile n is done with it
+  int32_t pm_s[8][MM_TILE];
   unsigned long long full[MM_STAGES], empty[MM_STAGES], a_full, a_empty, t_full[2], t_empty[2];
   unsigned tmem_base;
 };
@@ -183,7 +202,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) hamming_mma_kernel(
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      unsigned stage = 0, phase = 0, a_phase = 0;
+      unsigned stage = 0, phase = 0, a_phase = 0, seq = 0;
       for (int item = blockIdx.x; item < n_items && ok; item += gridDim.x) {
         const int slice = item / n_pairs, pair = item - slice * n_pairs;
         const int t0 = slice * tiles_per_slice, t1 = min(t0 + tiles_per_slice, n_tiles_total);
@@ -197,8 +216,10 @@ __global__ void __launch_bounds__(MM_THREADS, 1) hamming_mma_kernel(
         for (int t = t0; t < t1; ++t) {
           ok = mm_bar_wait(&sm.empty[stage], phase ^ 1u);
           if (!ok) break;
-          mm_bar_expect_tx(&sm.full[stage], MM_KB * MM_TILE_BYTES);
+          mm_bar_expect_tx(&sm.full[stage], MM_KB * MM_TILE_BYTES + MM_TILE * 4);
           for (int kb = 0; kb < MM_KB; ++kb) mm_tma_load_2d(sm.b[stage][kb], &mmap, kb * 128, t * MM_TILE, &sm.full[stage]);
+          mm_bulk_load(sm.pm_s[seq & 7u], pm + (size_t)t * MM_TILE, MM_TILE * 4, &sm.full[stage]);
+          ++seq;
           if (++stage == MM_STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -246,7 +267,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) hamming_mma_kernel(
     const int a = ew >> 2;              // which A tile (warps 2-5: tile 0, warps 6-9: tile 1)
     const unsigned quarter = warp & 3;  // a warp may only touch TMEM lanes 32 * (warp id % 4) ..
     const int row = (int)quarter * 32 + lane;
-    unsigned acc = 0, acc_phase = 0;
+    unsigned acc = 0, acc_phase = 0, seq = 0;
     for (int item = blockIdx.x; item < n_items && ok; item += gridDim.x) {
       const int slice = item / n_pairs, pair = item - slice * n_pairs;
       const int t0 = slice * tiles_per_slice, t1 = min(t0 + tiles_per_slice, n_tiles_total);
@@ -257,20 +278,22 @@ __global__ void __launch_bounds__(MM_THREADS, 1) hamming_mma_kernel(
       // distance at a lower row index can still be the second best), in s units
       int thr = qvalid ? (int)min(__ldcg(gthr + qi), 0xFFFu) + 1 - my_pq : -0x4000;
       unsigned b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;  // (d << 20) | row within the slice
-      for (int t = t0; t < t1; ++t) {
+      for (int t = t0; t < t1; ++t, ++seq) {
         ok = mm_bar_wait(&sm.t_full[acc], acc_phase);
         if (!ok) break;
         mm_fence_after();
         const int j0 = t * MM_TILE;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          int r[32];
-          mm_tmem_ld32(tmem + ((quarter * 32u) << 16) + acc * 256u + a * 128u + c * 32u, r);
-          const int4* pmv = reinterpret_cast<const int4*>(pm + j0 + c * 32);
+        const unsigned tbase = tmem + ((quarter * 32u) << 16) + acc * 256u + a * 128u;
+        const int32_t* pmt = sm.pm_s[seq & 7u];
+        // the chunk after the one being processed is already on its way out of TMEM
+        int r0[32], r1[32];
+        mm_tmem_ld32_issue(tbase, r0);
+        auto process = [&](int (&r)[32], int c) {
+          const int4* pmv = reinterpret_cast<const int4*>(pmt + c * 32);
           int mn = 0x7FFFFFFF;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const int4 p = __ldg(pmv + i);  // uniform across the warp
+            const int4 p = pmv[i];  // broadcast read
             r[4 * i] = p.x - 2 * r[4 * i];
             r[4 * i + 1] = p.y - 2 * r[4 * i + 1];
             r[4 * i + 2] = p.z - 2 * r[4 * i + 2];
@@ -289,10 +312,22 @@ __global__ void __launch_bounds__(MM_THREADS, 1) hamming_mma_kernel(
               }
             }
           }
-        }
+        };
+        mm_tmem_ld_wait(r0);
+        mm_tmem_ld32_issue(tbase + 32u, r1);
+        process(r0, 0);
+        mm_tmem_ld_wait(r1);
+        mm_tmem_ld32_issue(tbase + 64u, r0);
+        process(r1, 1);
+        mm_tmem_ld_wait(r0);
+        mm_tmem_ld32_issue(tbase + 96u, r1);
+        process(r0, 2);
+        mm_tmem_ld_wait(r1);
+        // the accumulator buffer is free as soon as its last chunk is in registers
         mm_fence_before();
         __syncwarp();
         if (lane == 0) mm_bar_arrive(&sm.t_empty[acc]);
+        process(r1, 3);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
       if (!ok) break;
