@@ -37,7 +37,7 @@ constexpr int MM_K = 256;                    // bytes per expanded descriptor ro
 constexpr int MM_KB = 2;                     // 128-byte swizzle atoms along K
 constexpr int MM_STAGES = 4;                 // B ring
 constexpr int MM_TILE_BYTES = MM_TILE * 128; // one (tile, k-block): 16 KB
-constexpr int MM_EPI_WARPS = 8;
+constexpr int MM_EPI_WARPS = 16;              // 2 column halves x 2 A tiles x 4 TMEM lane quarters
 constexpr int MM_THREADS = 32 * (2 + MM_EPI_WARPS);
 constexpr unsigned MM_PAD_POPC = 0x1000;     // popcount of a padding map row: never a candidate
 
@@ -263,8 +263,9 @@ __global__ void __launch_bounds__(MM_THREADS, 1) hamming_mma_kernel(
     }
   } else {
     // ===================== epilogue: thread = one query =====================
-    const int ew = warp - 2;            // 0..7
-    const int a = ew >> 2;              // which A tile (warps 2-5: tile 0, warps 6-9: tile 1)
+    const int ew = warp - 2;            // 0..15
+    const int a = (ew >> 2) & 1;        // which A tile
+    const int half = ew >> 3;           // which 64 of the tile's 128 columns (its own top-2: one more partial per slice)
     const unsigned quarter = warp & 3;  // a warp may only touch TMEM lanes 32 * (warp id % 4) ..
     const int row = (int)quarter * 32 + lane;
     unsigned acc = 0, acc_phase = 0, seq = 0;
@@ -283,7 +284,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) hamming_mma_kernel(
         if (!ok) break;
         mm_fence_after();
         const int j0 = t * MM_TILE;
-        const unsigned tbase = tmem + ((quarter * 32u) << 16) + acc * 256u + a * 128u;
+        const unsigned tbase = tmem + ((quarter * 32u) << 16) + acc * 256u + a * 128u + half * 64u;
         const int32_t* pmt = sm.pm_s[seq & 7u];
         // the chunk after the one being processed is already on its way out of TMEM
         int r0[32], r1[32];
@@ -315,24 +316,18 @@ __global__ void __launch_bounds__(MM_THREADS, 1) hamming_mma_kernel(
         };
         mm_tmem_ld_wait(r0);
         mm_tmem_ld32_issue(tbase + 32u, r1);
-        process(r0, 0);
-        mm_tmem_ld_wait(r1);
-        mm_tmem_ld32_issue(tbase + 64u, r0);
-        process(r1, 1);
-        mm_tmem_ld_wait(r0);
-        mm_tmem_ld32_issue(tbase + 96u, r1);
-        process(r0, 2);
+        process(r0, 2 * half);
         mm_tmem_ld_wait(r1);
         // the accumulator buffer is free as soon as its last chunk is in registers
         mm_fence_before();
         __syncwarp();
         if (lane == 0) mm_bar_arrive(&sm.t_empty[acc]);
-        process(r1, 3);
+        process(r1, 2 * half + 1);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
       if (!ok) break;
       if (qvalid) {
-        const size_t o = (size_t)slice * nq + qi;
+        const size_t o = (size_t)(slice * 2 + half) * nq + qi;
         const unsigned long long base = (unsigned long long)(index_base + (long long)t0 * MM_TILE);
         part_best[o] = b1 == 0xFFFFFFFFu ? ~0ull : ((unsigned long long)(b1 >> 20) << 32) | (base + (b1 & 0xFFFFFu));
         part_second[o] = b2 == 0xFFFFFFFFu ? ~0ull : ((unsigned long long)(b2 >> 20) << 32) | (base + (b2 & 0xFFFFFu));
@@ -387,7 +382,7 @@ int hamming_mma_slices(int nq, int nm, int sms, int* tiles_per_slice) {
 
 size_t hamming_mma_scratch_bytes(int nq, int nm, int slices) {
   const size_t nm_pad = ((size_t)nm + MM_TILE - 1) / MM_TILE * MM_TILE, nq_pad = ((size_t)nq + 255) / 256 * 256;
-  return (size_t)nq * MM_K + (size_t)nm * MM_K + 4096 + nq_pad * 4 + nm_pad * 4 + nq_pad * 4 + (size_t)2 * slices * nq * 8 +
+  return (size_t)nq * MM_K + (size_t)nm * MM_K + 4096 + nq_pad * 4 + nm_pad * 4 + nq_pad * 4 + (size_t)4 * slices * nq * 8 +
          4096;
 }
 
@@ -403,8 +398,8 @@ int launch_hamming_mma(const uint8_t* query, int nq, const uint8_t* map, int nm,
   int32_t* pq = reinterpret_cast<int32_t*>(p); p += up(nq_pad * 4);
   int32_t* pm = reinterpret_cast<int32_t*>(p); p += up(nm_pad * 4);
   unsigned* gthr = reinterpret_cast<unsigned*>(p); p += up(nq_pad * 4);
-  unsigned long long* pb = reinterpret_cast<unsigned long long*>(p); p += up((size_t)slices * nq * 8);
-  unsigned long long* ps = reinterpret_cast<unsigned long long*>(p); p += up((size_t)slices * nq * 8);
+  unsigned long long* pb = reinterpret_cast<unsigned long long*>(p); p += up((size_t)2 * slices * nq * 8);
+  unsigned long long* ps = reinterpret_cast<unsigned long long*>(p); p += up((size_t)2 * slices * nq * 8);
   unsigned* err = reinterpret_cast<unsigned*>(p);
   *err_out = err;
   CUtensorMap qmap, mmap;
@@ -423,7 +418,7 @@ int launch_hamming_mma(const uint8_t* query, int nq, const uint8_t* map, int nm,
   const int grid = std::min(sms, n_pairs * slices);
   hamming_mma_kernel<<<grid, MM_THREADS, smem, s>>>(qmap, mmap, nq, nm, n_pairs, slices, tiles_per_slice, index_base, pq, pm,
                                                     gthr, pb, ps, err);
-  launch_hamming_merge(pb, ps, slices, nq, best, second, s);
+  launch_hamming_merge(pb, ps, 2 * slices, nq, best, second, s);  // two column halves per slice
   return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 
