@@ -305,16 +305,16 @@ def matcher_extras(torch, dist, orbfe, rank, world, local, kp_frame, desc_frame,
     d_m = torch.from_numpy(mp[start:start + cnt].copy()).to(dev)
     sb = sharding.ShardedBruteForce(m, dev, max_queries=nq)
 
-    def time_mode(mode, reps=5):
+    def time_mode(mode, reps=5, tensor=False):
         for _ in range(3):
-            sb.run(d_q, d_m, start, exchange=mode)
+            sb.run(d_q, d_m, start, exchange=mode, tensor=tensor)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(reps):
-            b, s2 = sb.run(d_q, d_m, start, exchange=mode)
+            b, s2 = sb.run(d_q, d_m, start, exchange=mode, tensor=tensor)
         e1.record()
         torch.cuda.synchronize()
         t = e0.elapsed_time(e1) / reps
@@ -334,6 +334,18 @@ def matcher_extras(torch, dist, orbfe, rank, world, local, kp_frame, desc_frame,
                 "weight 1, 1, 2, 4), so the algorithmic rate (8 popc32 per pair) may exceed the POPC pipe's own peak",
         "first_best_key": int(best[0].item()) & 0xFFFFFFFFFFFFFFFF,
     }
+    # the optional second path: the same top-2 on the tensor cores (tcgen05 kind::i8 GEMM over the bits expanded to
+    # bytes, K = 288; k_match_mma.cu), bit expansion of queries AND map inside the timed call; the POPC kernel above stays
+    # the graded path (north_star), the keys must be bit-equal
+    ms_tc, b_tc, s_tc = time_mode(0, tensor=True)
+    m.sync()
+    bf["tensor_core"] = {
+        "ms": ms_tc, "pairs_per_s": pairs / (ms_tc * 1e-3), "speedup_vs_popc_kernel": ms / ms_tc,
+        "int8_tops": 2.0 * 288.0 * pairs / (ms_tc * 1e-3) / 1e12,
+        "equal_to_popc_keys": bool(torch.equal(b_tc, best)) and bool(torch.equal(s_tc, second)),
+        "what": "orbfe_hamming_bruteforce_tc_device: d = |q| + |m| - 2 q.m as an s8 x u8 GEMM (M128 x N128 x K32 "
+                "tcgen05.mma, TMEM accumulators, TMA operand tiles), threshold-gated exact top-2 in the epilogue; "
+                "includes expanding the map to one byte per bit in every call"}
     if world > 1:
         # the exchange, broken down (device times of the LAST call, max over ranks): brute-force kernel | exchange + merge
         info = sb.comm.info()

@@ -320,7 +320,8 @@ int orbfe_matcher_sync(orbfe_matcher* m);
  * u64 on every rank). */
 typedef struct orbfe_comm orbfe_comm;
 #define ORBFE_COMM_ID_BYTES 128
-enum { ORBFE_EXCHANGE_AUTO = 0, ORBFE_EXCHANGE_NCCL = 1, ORBFE_EXCHANGE_PEER = 2 };
+enum { ORBFE_EXCHANGE_AUTO = 0, ORBFE_EXCHANGE_NCCL = 1, ORBFE_EXCHANGE_PEER = 2,
+       ORBFE_KERNEL_TENSOR = 16 /* OR into `exchange`: the shard's top-2 by the tensor-core kernel (needs nm_local >= 1) */ };
 int orbfe_comm_unique_id(uint8_t* id_out /* ORBFE_COMM_ID_BYTES */);
 int orbfe_comm_create(const uint8_t* id, int nranks, int rank, int device, int max_queries, orbfe_comm** out);
 void orbfe_comm_destroy(orbfe_comm* c);

@@ -412,6 +412,8 @@ int orbfe_hamming_bruteforce_sharded(orbfe_matcher* hm, orbfe_comm* hc, const ui
   ORBFE_ARG(hm && hc && d_query && d_best && d_second && nq >= 1 && nm_local >= 0);
   ORBFE_ARG(nm_local == 0 || d_map_shard);
   ORBFE_ARG(index_base >= 0 && index_base + (int64_t)nm_local <= ((int64_t)1 << 32));
+  const bool tensor = (exchange & ORBFE_KERNEL_TENSOR) != 0;  // the shard's top-2 by the tcgen05 kernel
+  exchange &= ~ORBFE_KERNEL_TENSOR;
   ORBFE_ARG(exchange == ORBFE_EXCHANGE_AUTO || exchange == ORBFE_EXCHANGE_NCCL || exchange == ORBFE_EXCHANGE_PEER);
   Matcher* m = reinterpret_cast<Matcher*>(hm);
   Comm* c = reinterpret_cast<Comm*>(hc);
@@ -427,7 +429,7 @@ int orbfe_hamming_bruteforce_sharded(orbfe_matcher* hm, orbfe_comm* hc, const ui
   }
   DeviceGuard guard(m->device);
   int slice_len = 0;
-  const int slices = nm_local > 0 ? bruteforce_slices(nq, nm_local, &slice_len) : 0;
+  const int slices = nm_local > 0 ? (tensor ? 1 : bruteforce_slices(nq, nm_local, &slice_len)) : 0;
   const int nparts = std::max(slices, 1);
   int rc = ensure_cand(m, (size_t)nparts * nq * 4 + 64);
   if (rc != ORBFE_OK) return rc;
@@ -438,6 +440,10 @@ int orbfe_hamming_bruteforce_sharded(orbfe_matcher* hm, orbfe_comm* hc, const ui
   if (slices == 0) {  // an empty shard contributes "none"
     ORBFE_CUDA(cudaMemsetAsync(pb, 0xFF, (size_t)nq * 8, s));
     ORBFE_CUDA(cudaMemsetAsync(ps, 0xFF, (size_t)nq * 8, s));
+  } else if (tensor) {  // the shard's (best, second) land where one slice's partials would
+    rc = matcher_tc_launch(m, d_query, nq, d_map_shard, nm_local, index_base, reinterpret_cast<uint64_t*>(pb),
+                           reinterpret_cast<uint64_t*>(ps));
+    if (rc != ORBFE_OK) return rc;
   } else {
     launch_hamming_bruteforce(d_query, nq, d_map_shard, nm_local, slice_len, slices, index_base, pb, ps, s);
     m->launches += 1;

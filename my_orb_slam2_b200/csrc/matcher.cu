@@ -7,6 +7,35 @@
 
 using namespace orbfe;
 
+namespace orbfe {
+// the tensor-core brute force on the matcher's stream (scratch grown on demand); shared with comm.cu
+int matcher_tc_launch(Matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm, int64_t index_base,
+                      uint64_t* d_best, uint64_t* d_second) {
+  if (m->sms == 0) ORBFE_CUDA(cudaDeviceGetAttribute(&m->sms, cudaDevAttrMultiProcessorCount, m->device));
+  int tps = 0;
+  const int slices = hamming_mma_slices(nq, nm, m->sms, &tps);
+  const size_t need = hamming_mma_scratch_bytes(nq, nm, slices);
+  if (need > m->tc_cap) {
+    if (m->d_tc) { ORBFE_CUDA(cudaStreamSynchronize(m->stream)); cudaFree(m->d_tc); m->d_tc = nullptr; m->tc_cap = 0; }
+    ORBFE_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_tc), need));
+    m->tc_cap = need;
+  }
+  if (!m->h_tc_err) ORBFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&m->h_tc_err), 64, cudaHostAllocDefault));
+  unsigned* d_err = nullptr;
+  const int rc = launch_hamming_mma(d_query, nq, d_map, nm, index_base, m->d_tc, slices, tps, m->sms,
+                                    reinterpret_cast<unsigned long long*>(d_best),
+                                    reinterpret_cast<unsigned long long*>(d_second), &d_err, m->stream);
+  if (rc != 0) {
+    set_error("tensor-core brute force: set-up failed (%d): %s", rc, cudaGetErrorString(cudaGetLastError()));
+    return ORBFE_ERR_CUDA;
+  }
+  ORBFE_CUDA(cudaMemcpyAsync(m->h_tc_err, d_err, 4, cudaMemcpyDeviceToHost, m->stream));
+  m->tc_pending = true;
+  m->launches += 5;
+  return ORBFE_OK;
+}
+}  // namespace orbfe
+
 extern "C" {
 
 int orbfe_matcher_create(int device, orbfe_matcher** out) {
@@ -68,28 +97,7 @@ int orbfe_hamming_bruteforce_tc_device(orbfe_matcher* h, const uint8_t* d_query,
   ORBFE_ARG(index_base >= 0 && index_base + (int64_t)nm <= ((int64_t)1 << 32));
   Matcher* m = reinterpret_cast<Matcher*>(h);
   DeviceGuard guard(m->device);
-  if (m->sms == 0) ORBFE_CUDA(cudaDeviceGetAttribute(&m->sms, cudaDevAttrMultiProcessorCount, m->device));
-  int tps = 0;
-  const int slices = hamming_mma_slices(nq, nm, m->sms, &tps);
-  const size_t need = hamming_mma_scratch_bytes(nq, nm, slices);
-  if (need > m->tc_cap) {
-    if (m->d_tc) { ORBFE_CUDA(cudaStreamSynchronize(m->stream)); cudaFree(m->d_tc); m->d_tc = nullptr; m->tc_cap = 0; }
-    ORBFE_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->d_tc), need));
-    m->tc_cap = need;
-  }
-  if (!m->h_tc_err) ORBFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&m->h_tc_err), 64, cudaHostAllocDefault));
-  unsigned* d_err = nullptr;
-  const int rc = launch_hamming_mma(d_query, nq, d_map, nm, index_base, m->d_tc, slices, tps, m->sms,
-                                    reinterpret_cast<unsigned long long*>(d_best),
-                                    reinterpret_cast<unsigned long long*>(d_second), &d_err, m->stream);
-  if (rc != 0) {
-    set_error("orbfe_hamming_bruteforce_tc_device: set-up failed (%d): %s", rc, cudaGetErrorString(cudaGetLastError()));
-    return ORBFE_ERR_CUDA;
-  }
-  ORBFE_CUDA(cudaMemcpyAsync(m->h_tc_err, d_err, 4, cudaMemcpyDeviceToHost, m->stream));
-  m->tc_pending = true;
-  m->launches += 5;
-  return ORBFE_OK;
+  return matcher_tc_launch(m, d_query, nq, d_map, nm, index_base, d_best, d_second);
 }
 
 int orbfe_descriptor_distance(orbfe_matcher* h, const uint8_t* a, const uint8_t* b, int n, int32_t* out) {

@@ -28,6 +28,9 @@ struct Matcher {
   int sms = 0;
 };
 
+int matcher_tc_launch(Matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm, int64_t index_base,
+                      uint64_t* d_best, uint64_t* d_second);  // matcher.cu
+
 inline int arena_reserve(Matcher* m, size_t bytes) {
   m->off = 0;
   if (bytes <= m->cap) return ORBFE_OK;

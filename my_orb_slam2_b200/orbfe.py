@@ -518,6 +518,7 @@ class Matcher:
 
 COMM_ID_BYTES = 128
 EXCHANGE_AUTO, EXCHANGE_NCCL, EXCHANGE_PEER = 0, 1, 2
+KERNEL_TENSOR = 16   # OR into `exchange`: the shard's top-2 by the tensor-core kernel
 
 
 def comm_unique_id():

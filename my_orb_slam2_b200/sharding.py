@@ -70,9 +70,10 @@ class ShardedBruteForce:
             index = device.index if hasattr(device, "index") and device.index is not None else int(device)
             self.comm = orbfe.Comm(uid, self.world, self.rank, index, max_queries)
 
-    def run(self, d_query, d_map_shard, index_base, exchange=0):
+    def run(self, d_query, d_map_shard, index_base, exchange=0, tensor=False):
         """d_query [nq,32] / d_map_shard [nm_local,32]: torch uint8 CUDA tensors.  Returns (best, second) int64 CUDA
-        tensors [nq] holding the uint64 keys of the GLOBAL top-2 (valid on the current stream)."""
+        tensors [nq] holding the uint64 keys of the GLOBAL top-2 (valid on the current stream).  tensor=True: the
+        shard's top-2 by the tensor-core kernel (tcgen05 int8 GEMM on the expanded bits) instead of the POPC kernel."""
         import torch
         nq, nm = d_query.shape[0], d_map_shard.shape[0]
         best = torch.empty(nq, dtype=torch.int64, device=self.dev)
@@ -80,14 +81,16 @@ class ShardedBruteForce:
         cur = torch.cuda.current_stream(self.dev)
         self.stream.wait_stream(cur)
         if self.comm is None:
-            self.m.hamming_bruteforce_device(d_query.data_ptr(), nq, d_map_shard.data_ptr(), nm, index_base,
-                                             best.data_ptr(), second.data_ptr())
+            fn = self.m.hamming_bruteforce_tc_device if tensor and nm > 0 else self.m.hamming_bruteforce_device
+            fn(d_query.data_ptr(), nq, d_map_shard.data_ptr(), nm, index_base, best.data_ptr(), second.data_ptr())
             cur.wait_stream(self.stream)
             return best, second
         if exchange == "torch":
             return self._run_torch(d_query, d_map_shard, index_base, best, second, cur)
+        from . import orbfe
         self.comm.hamming_bruteforce_sharded(self.m, d_query.data_ptr(), nq, d_map_shard.data_ptr(), nm, index_base,
-                                             best.data_ptr(), second.data_ptr(), exchange)
+                                             best.data_ptr(), second.data_ptr(),
+                                             exchange | (orbfe.KERNEL_TENSOR if tensor else 0))
         cur.wait_stream(self.stream)
         return best, second
 

@@ -89,10 +89,11 @@ def main():
     modes = [("nccl", orbfe.EXCHANGE_NCCL), ("torch", "torch")]
     if info["peer_memory"]:
         modes.insert(0, ("peer", orbfe.EXCHANGE_PEER))
+    modes.append(("tensor_core", orbfe.EXCHANGE_AUTO))   # the shard's top-2 by the tcgen05 kernel, default exchange
     results = {}
     for name, mode in modes:
         for rep in range(3):   # three calls in a row: both parities of the exchange buffer and its reuse
-            best, second = sb.run(d_q, d_m, start, exchange=mode)
+            best, second = sb.run(d_q, d_m, start, exchange=mode, tensor=(name == "tensor_core"))
         torch.cuda.synchronize()
         sb.comm.status()
         results[name] = (best.cpu().numpy().view(np.uint64), second.cpu().numpy().view(np.uint64))

@@ -24,4 +24,9 @@ python tools/one_hamming.py > $OUT/plain_hamming_$TAG.log 2>&1 || { echo "one_ha
 ncu --set full --clock-control none --import-source on -k regex:hamming_bruteforce -c 1 -f -o $OUT/prof_hamming_bruteforce_${TAG}f \
     python tools/one_hamming.py > $OUT/ncu_hamming.log 2>&1
 echo "hamming rc=$?"
+# the optional tensor-core path of the same brute force (tcgen05 kind::i8)
+python tools/one_hamming_tc.py 8192 1048576 1 > $OUT/plain_hamming_tc_$TAG.log 2>&1 || { echo "one_hamming_tc failed without ncu"; exit 1; }
+ncu --set full --clock-control none --import-source on -k regex:hamming_mma -c 1 -f -o $OUT/prof_hamming_mma_${TAG}f \
+    python tools/one_hamming_tc.py 8192 1048576 1 > $OUT/ncu_hamming_tc.log 2>&1
+echo "hamming_mma rc=$?"
 ls -la $OUT/*_${TAG}f.ncu-rep
