@@ -14,10 +14,12 @@
 //       warp 1      MMA issuer (one elected lane): per B tile 2 x 8 tcgen05.mma.cta_group::1.kind::i8 (M128 x N128 x K32)
 //                   into one of two 256-column TMEM accumulator buffers; tcgen05.commit frees the B stage and hands the
 //                   accumulator to the epilogue;
-//       warps 2..9  epilogue: thread = one query; tcgen05.ld its 128 dot products of the tile (32 columns at a time),
-//                   s = |m_j| - 2 dot as a running minimum, and only when a chunk's minimum beats the query's current
-//                   second best (rare) the chunk's 32 values are walked in row order for the exact top-2 update —
-//                   the same tie rule as the POPC kernel (rows ascend, a later equal distance never wins).
+//       warps 2..17 epilogue: thread = one query x one 64-column half of an accumulator; tcgen05.ld 32 columns at a
+//                   time (the next chunk in flight), a running minimum, and only when a chunk's minimum beats the
+//                   query's current second best (rare) the chunk's 32 values are walked in row order for the exact
+//                   top-2 update — the same tie rule as the POPC kernel (rows ascend, a later equal distance never wins).
+//                   (A weight-stationary tcgen05.mma.ws variant sharing the B slice between the two A tiles was
+//                   measured equal: 1.805 vs 1.783 ms.)
 //     Work item = (pair of A tiles = 256 queries, slice of the map).  Every slice restarts its top-2, so a query's
 //     current GLOBAL second-best distance is shared through `gthr` (atomicMin at the end of an item, read at the start
 //     of the next): a bound >= the true second best never prunes a row of the true top-2, and it keeps the exact-update
@@ -115,11 +117,6 @@ __device__ __forceinline__ void mm_tma_load_2d(void* dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n" ::
           "r"(mm_smem(dst)), "l"(map), "r"(x), "r"(y), "r"(mm_smem(bar))
       : "memory");
-}
-__device__ __forceinline__ void mm_bulk_load(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::
-                   "r"(mm_smem(dst)), "l"(src), "r"(bytes), "r"(mm_smem(bar))
-               : "memory");
 }
 // shared-memory matrix descriptor: K-major, 128-byte swizzle, 8-row groups 1024 bytes apart (sm_100 version field = 1)
 __device__ __forceinline__ unsigned long long mm_desc(unsigned smem_addr) {
