@@ -416,12 +416,9 @@ int launch_hamming_mma(const uint8_t* query, int nq, const uint8_t* map, int nm,
       mm_encode_map(&qxmap, qx, nq, 32, 32, CU_TENSOR_MAP_SWIZZLE_32B) != 0 ||
       mm_encode_map(&mxmap, mx, (int)nm_pad, 32, 32, CU_TENSOR_MAP_SWIZZLE_32B) != 0)
     return -1;
-  static bool configured = false;
   const int smem = (int)sizeof(MmSmem) + 1024;
-  if (!configured) {
-    if (cudaFuncSetAttribute(hamming_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -2;
-    configured = true;
-  }
+  // a per-device attribute (several GPUs may be driven from one process): set on every call, it costs microseconds
+  if (cudaFuncSetAttribute(hamming_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -2;
   cudaMemsetAsync(err, 0, 4, s);
   expand_bits_kernel<true><<<(int)((nq_pad + 7) / 8), 256, 0, s>>>(query, nq, (int)nq_pad, qb, qx, pq);
   expand_bits_kernel<false><<<(int)((nm_pad + 7) / 8), 256, 0, s>>>(map, nm, (int)nm_pad, mb, mx, nullptr);
