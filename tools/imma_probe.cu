@@ -1,4 +1,7 @@
 // Throughput probe: legacy mma.sync.m16n8k32 u8 x u8 -> s32 on sm_100a (register operands only).
+// Measured on B200 (round 2): 138.9 G mma/s = 1.14 Pop/s, one m16n8k32 per 8.4 clk per SM sub-partition — a quarter of the
+// tcgen05 kind::i8 rate, which is why the tensor-core brute force (csrc/k_match_mma.cu) is written with tcgen05 / TMEM.
+// (mma.sync m16n8k256 b1 and.popc still compiles for sm_100a but is emulated: 8 IMMA.16832 + ~140 unpack instructions.)
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o imma_probe imma_probe.cu && ./imma_probe
 #include <cstdio>
 #include <cstdint>
