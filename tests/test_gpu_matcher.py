@@ -74,6 +74,28 @@ def test_bruteforce_tensor_core_path_vs_oracle(oracle, nq, nm, base):
         assert np.array_equal(second.cpu().numpy().view(np.uint64), os_)
 
 
+def test_bruteforce_tensor_core_equals_popc_on_random_shapes():
+    """Seeded random (nq, nm, index_base) incl. sizes around the 128 / 256 tile edges: both device paths, same keys."""
+    import torch
+    from my_orb_slam2_b200 import orbfe
+    rng = np.random.default_rng(123)
+    dev = torch.device("cuda", 0)
+    mt = orbfe.Matcher()
+    shapes = [(127, 127), (128, 128), (129, 129), (255, 4095), (256, 4096), (257, 4097), (513, 16385)]
+    shapes += [(int(rng.integers(1, 700)), int(rng.integers(1, 70000))) for _ in range(8)]
+    for nq, nm in shapes:
+        base = int(rng.integers(0, (1 << 32) - nm))
+        q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+        m = rng.integers(0, 256, (nm, 32), dtype=np.uint8)
+        m[rng.integers(0, nm, max(nm // 50, 1))] = q[rng.integers(0, nq, max(nm // 50, 1))]   # exact hits and ties
+        d_q, d_m = torch.from_numpy(q).to(dev), torch.from_numpy(m).to(dev)
+        out = [torch.zeros(nq, dtype=torch.int64, device=dev) for _ in range(4)]
+        mt.hamming_bruteforce_device(d_q.data_ptr(), nq, d_m.data_ptr(), nm, base, out[0].data_ptr(), out[1].data_ptr())
+        mt.hamming_bruteforce_tc_device(d_q.data_ptr(), nq, d_m.data_ptr(), nm, base, out[2].data_ptr(), out[3].data_ptr())
+        mt.sync()
+        assert torch.equal(out[0], out[2]) and torch.equal(out[1], out[3]), (nq, nm, base)
+
+
 def test_bruteforce_full_size_properties():
     """Config 5 per-GPU shard (8192 x 131072) and a 1M map: checked through properties the oracle-free way:
     planted duplicates are found, sharded top-2 merged == unsharded top-2, best <= second."""
