@@ -31,6 +31,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 
 #include "match_kernels.h"
 
@@ -379,7 +380,8 @@ int hamming_mma_slices(int nq, int nm, int sms, int* tiles_per_slice) {
   const int n_pairs = (nq + 2 * MM_TILE - 1) / (2 * MM_TILE);
   const int n_tiles = (nm + MM_TILE - 1) / MM_TILE;
   // about 8 items per SM (load balance of the persistent CTAs), slices of at least 16 tiles, at most 2^20 rows
-  int slices = (8 * sms + n_pairs - 1) / n_pairs;
+  static const int items = [] { const char* e = getenv("ORBFE_TC_ITEMS"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 8; }();
+  int slices = (items * sms + n_pairs - 1) / n_pairs;
   slices = std::max(1, std::min(slices, (n_tiles + 15) / 16));
   int tps = (n_tiles + slices - 1) / slices;
   tps = std::min(tps, (1 << 20) / MM_TILE);
