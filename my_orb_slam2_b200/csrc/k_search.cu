@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(1024) build_grid_kernel(const DevFrame f) {
 // ---- SearchByProjection(Frame&, const vector<MapPoint*>&, th): candidates (src/ORBmatcher.cc:46-118) ----
 __global__ void sbp_map_candidates_kernel(const DevFrame f, const DevMapPoints mp, float th, SearchScratch sc,
                                           int fill) {
+  if (fill && sc.cand_capacity_needed[0] > sc.cand_cap) return;  // the candidate buffer is too small: the host repeats the pass
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= mp.m) return;
   int count = 0;
@@ -84,6 +85,7 @@ __global__ void sbp_map_candidates_kernel(const DevFrame f, const DevMapPoints m
 // ---- SearchByProjection(Frame& Cur, const Frame& Last, th, bMono): candidates (:1392-1492) ----
 __global__ void sbp_last_candidates_kernel(const DevFrame f, const DevLastFrame lf, const orbfe_camera_pose cam,
                                            const float tlc_z, float th, int mono, SearchScratch sc, int fill) {
+  if (fill && sc.cand_capacity_needed[0] > sc.cand_cap) return;  // the candidate buffer is too small: the host repeats the pass
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= lf.n) return;
   int count = 0;
@@ -162,6 +164,7 @@ __global__ void __launch_bounds__(1024) resolve_kernel(const DevFrame f, int row
   __shared__ int s_changed, s_nmatch, s_ind[3];
   __shared__ int s_hist[HISTO];
   const int tid = threadIdx.x, T = blockDim.x;
+  if (sc.cand_capacity_needed[0] > sc.cand_cap) return;  // nothing was filled: the host grows the buffer and repeats
   int32_t* b_old = sc.block_a;
   int32_t* b_new = sc.block_b;
   for (int i = tid; i < f.n; i += T) b_old[i] = INT_MAX;

@@ -84,6 +84,7 @@ __device__ bool project_point(int mode, const DevFrame& f, const DevPoints& p, c
 // candidates of the two overloads with a claim chain (PM_RELOC, PM_SIM3); CSR as in k_search.cu
 __global__ void proj_candidates_kernel(int mode, const DevFrame f, const DevPoints p, const DevProjection P, float th,
                                        SearchScratch sc, int fill) {
+  if (fill && sc.cand_capacity_needed[0] > sc.cand_cap) return;  // the candidate buffer is too small: the host repeats the pass
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= p.m) return;
   int count = 0;
@@ -248,6 +249,7 @@ __global__ void __launch_bounds__(1024) bow_finish_kernel(const DevKeyFrame k1, 
 __global__ void init_candidates_kernel(const DevFrame f2, const orbfe_keypoint* __restrict__ keys1,
                                        const uint8_t* __restrict__ desc1, int n1, const float* __restrict__ prev,
                                        float window, SearchScratch sc, int fill) {
+  if (fill && sc.cand_capacity_needed[0] > sc.cand_cap) return;  // the candidate buffer is too small: the host repeats the pass
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n1) return;
   int count = 0;

@@ -78,6 +78,8 @@ struct SearchScratch {
   int32_t* cand_count;   // [rows + 1] -> exclusive offsets after the scan
   uint32_t* cand;        // [total] idx | dist<<16 | octave<<25
   int32_t* cand_capacity_needed;  // [1] total candidates (device)
+  int cand_cap;          // entries `cand` can hold: the fill pass and the resolve step leave at once when the total
+                         // exceeds it (the host then grows the buffer and repeats them: no mid-call sync otherwise)
   int32_t* result;       // [rows] chosen feature per row (-1 none)
   int32_t* block_a;      // [n features] first blocking claimer (iteration t)
   int32_t* block_b;      // [n features] (iteration t+1)

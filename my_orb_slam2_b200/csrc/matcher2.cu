@@ -390,6 +390,7 @@ int orbfe_search_for_initialization(orbfe_matcher* h, const orbfe_frame_view* f1
   rc = ensure_cand(m, (size_t)m->h_small[0] + 16);
   if (rc != ORBFE_OK) return rc;
   sc.cand = m->d_cand;
+  sc.cand_cap = (int)std::min<size_t>(m->cand_cap, (size_t)0x7FFFFFFF);
   launch_init_candidates(d2, keys1, desc1, f1->n, prev, (float)window, sc, 1, m->stream);
   if (launch_init_resolve(d2, keys1, f1->n, nnratio, check_ori, sc, m12, m21, prev, dn, m->stream) != 0) {
     set_error("search_for_initialization: cannot reserve %zu bytes of shared memory", n2 * 2);

@@ -116,6 +116,7 @@ inline void alloc_scratch(Matcher* m, int rows, int nfeat, DevFrame* f, SearchSc
   f->cell_start = arena_alloc<int32_t>(m, (size_t)ORBFE_GRID_COLS * ORBFE_GRID_ROWS + 1);
   f->cell_items = arena_alloc<int32_t>(m, nfeat);
   sc->cand = nullptr;
+  sc->cand_cap = 0;
   sc->proj = nullptr;
   sc->hist = nullptr;
 }
@@ -125,19 +126,28 @@ inline int finish_projection(Matcher* m, DevFrame& df, int rows, const int32_t* 
                              int mode, float nnratio, int check_ori, int accept_th, SearchScratch& sc,
                              void (*launch_fill)(void*, int), void* ctx, int32_t* assigned, int32_t* n_matches) {
   launch_scan_counts(sc.cand_count, rows, sc.cand_capacity_needed, m->stream);
-  ORBFE_CUDA(cudaMemcpyAsync(m->h_small, sc.cand_capacity_needed, 4, cudaMemcpyDeviceToHost, m->stream));
-  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
-  const int total = m->h_small[0];
-  int rc = ensure_cand(m, (size_t)total + 16);
+  // no host round trip for the candidate total: the fill pass and the resolve step run against the buffer as it is
+  // (sized by earlier calls, at least 256 K entries) and leave at once if the total does not fit; only then does the
+  // host grow the buffer and repeat the two steps
+  int rc = ensure_cand(m, (size_t)1 << 18);
   if (rc != ORBFE_OK) return rc;
-  sc.cand = m->d_cand;
-  launch_fill(ctx, 1);
-  launch_resolve(df, rows, row_obs, row_angle, mode, nnratio, check_ori, accept_th, sc, m->stream);
-  m->launches += 3;
-  if (df.n > 0) ORBFE_CUDA(cudaMemcpyAsync(assigned, sc.assigned, (size_t)df.n * 4, cudaMemcpyDeviceToHost, m->stream));
-  ORBFE_CUDA(cudaMemcpyAsync(m->h_small, sc.counters, 16, cudaMemcpyDeviceToHost, m->stream));
-  ORBFE_CUDA(cudaStreamSynchronize(m->stream));
-  ORBFE_CUDA(cudaGetLastError());
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    sc.cand = m->d_cand;
+    sc.cand_cap = (int)std::min<size_t>(m->cand_cap, (size_t)0x7FFFFFFF);
+    launch_fill(ctx, 1);
+    launch_resolve(df, rows, row_obs, row_angle, mode, nnratio, check_ori, accept_th, sc, m->stream);
+    m->launches += attempt == 0 ? 3 : 2;
+    if (df.n > 0) ORBFE_CUDA(cudaMemcpyAsync(assigned, sc.assigned, (size_t)df.n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORBFE_CUDA(cudaMemcpyAsync(m->h_small, sc.counters, 16, cudaMemcpyDeviceToHost, m->stream));
+    ORBFE_CUDA(cudaMemcpyAsync(m->h_small + 8, sc.cand_capacity_needed, 4, cudaMemcpyDeviceToHost, m->stream));
+    ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+    ORBFE_CUDA(cudaGetLastError());
+    const int total = m->h_small[8];
+    if (total <= sc.cand_cap) break;
+    if (attempt == 1) { set_error("candidate buffer still too small (%d > %d)", total, sc.cand_cap); return ORBFE_ERR_CAPACITY; }
+    rc = ensure_cand(m, (size_t)total + 16);
+    if (rc != ORBFE_OK) return rc;
+  }
   if (n_matches) *n_matches = m->h_small[0];
   return ORBFE_OK;
 }
