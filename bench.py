@@ -499,7 +499,7 @@ def shape_extras(torch, dist, orbfe, rank, world, local, steps, warmup):
     dev = torch.device("cuda", local)
     out = {}
 
-    def timed(step_fn, stream):
+    def timed(step_fn, stream, finalize=None):
         for _ in range(warmup):
             step_fn()
         torch.cuda.synchronize()
@@ -509,6 +509,8 @@ def shape_extras(torch, dist, orbfe, rank, world, local, steps, warmup):
         e0.record(stream)
         for _ in range(steps):
             step_fn()
+        if finalize is not None:
+            finalize()
         e1.record(stream)
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
@@ -519,23 +521,44 @@ def shape_extras(torch, dist, orbfe, rank, world, local, steps, warmup):
     # configs[2]: 256 EuRoC pairs per step in total, rank r owns pairs r, r+world, ...
     s, (w, h) = synth.SETTINGS["euroc"], synth.SHAPES["euroc"]
     prm = (s["nfeatures"], s["scale_factor"], s["nlevels"], s["ini_th"], s["min_th"])
-    total = 256
+    total = int(os.environ.get("ORBFE_BENCH_EUROC_TOTAL", "256"))
     mine = len(range(rank, total, world))
     pairs = [synth.synth_pair(w, h, 1000 + rank + world * i) for i in range(4)]
     dl = torch.from_numpy(np.stack([pairs[i % 4][0] for i in range(mine)])).to(dev)
     dr = torch.from_numpy(np.stack([pairs[i % 4][1] for i in range(mine)])).to(dev)
-    L = orbfe.Extractor(*prm, w, h, max_batch=mine, device=local)
-    R = orbfe.Extractor(*prm, w, h, max_batch=mine, device=local)
+    # two rigs (an extractor pair each) take the steps in turn: consecutive batches overlap, so the fixed tails of a
+    # batch (one quadtree CTA per level and image, the small pyramid levels, the 64-CTA stereo kernels) are filled by
+    # the next batch's kernels — what a stream of 256-pair batches looks like on every rank
+    n_rigs = max(1, int(os.environ.get("ORBFE_BENCH_EUROC_RIGS", "2")))
+    rigs = [(orbfe.Extractor(*prm, w, h, max_batch=mine, device=local), orbfe.Extractor(*prm, w, h, max_batch=mine, device=local))
+            for _ in range(n_rigs)]
+    L, R = rigs[0]
     mbf, mb = np.float32(s["bf"]), np.float32(s["bf"]) / np.float32(s["fx"])
+    turn = [0]
 
     def euroc_step():
-        L.upload(dl.data_ptr(), mine, on_device=True)
-        R.upload(dr.data_ptr(), mine, on_device=True)
-        L.run(mine)
-        R.run(mine)
-        orbfe.check(lib.orbfe_stereo_match_run(L._h, R._h, mine, mbf, mb))
+        Lk, Rk = rigs[turn[0] % n_rigs]
+        turn[0] += 1
+        Lk.upload(dl.data_ptr(), mine, on_device=True)
+        Rk.upload(dr.data_ptr(), mine, on_device=True)
+        Lk.run(mine)
+        Rk.run(mine)
+        orbfe.check(lib.orbfe_stereo_match_run(Lk._h, Rk._h, mine, mbf, mb))
 
-    ms = timed(euroc_step, torch.cuda.ExternalStream(L.stream, device=dev))
+    st0 = torch.cuda.ExternalStream(L.stream, device=dev)
+    joins = [torch.cuda.Event() for _ in rigs[1:]]
+
+    def euroc_join():  # the timed stream (rig 0, left) ends after every other rig's left stream (which ends its rig)
+        for ev, (Lk, _) in zip(joins, rigs[1:]):
+            ev.record(torch.cuda.ExternalStream(Lk.stream, device=dev))
+            st0.wait_event(ev)
+
+    ms = timed(euroc_step, st0, euroc_join)
+    # the parity check below reads rig 0's results: make its last batch the freshest one
+    torch.cuda.synchronize()
+    turn[0] = 0
+    euroc_step()
+    torch.cuda.synchronize()
     sharded_equal = None
     if world > 1:
         # parity with N > 1 ranks on hardware: the results of the timed, sharded configuration (this rank's first 4 slots
@@ -575,10 +598,12 @@ def shape_extras(torch, dist, orbfe, rank, world, local, steps, warmup):
         "workload": "configs[2]: 256 EuRoC-shaped 752x480 stereo pairs per step, 1200 features, extract L+R + "
                     "ComputeStereoMatches, sharded by frame over %d GPU(s) (%d pairs on rank 0)" % (world, mine),
         "frames_per_s": total * steps / (ms * 1e-3), "ms_per_step": ms / steps, "scaling": "strong"}
+    out["euroc_stereo_256"]["rigs"] = n_rigs
     if sharded_equal is not None:
         out["euroc_stereo_256"]["sharded_equal_to_single"] = sharded_equal
-    R.close()
-    L.close()
+    for Lk, Rk in rigs:
+        Rk.close()
+        Lk.close()
     del dl, dr
 
     # configs[0]: TUM1 mono, 2 x 64 frames per step per GPU on two handles (two streams, like the two extractors of a
