@@ -19,7 +19,8 @@
 //                   query's current second best (rare) the chunk's 32 values are walked in row order for the exact
 //                   top-2 update — the same tie rule as the POPC kernel (rows ascend, a later equal distance never wins).
 //                   (A weight-stationary tcgen05.mma.ws variant sharing the B slice between the two A tiles was
-//                   measured equal: 1.805 vs 1.783 ms.)
+//                   measured equal: 1.805 vs 1.783 ms.  With the epilogue's work removed the call takes 1.54 ms: the
+//                   TMA -> MMA pipeline alone runs the tensor pipe at ~82 %, the epilogue costs the other 0.24 ms.)
 //     Work item = (pair of A tiles = 256 queries, slice of the map).  Every slice restarts its top-2, so a query's
 //     current GLOBAL second-best distance is shared through `gthr` (atomicMin at the end of an item, read at the start
 //     of the next): a bound >= the true second best never prunes a row of the true top-2, and it keeps the exact-update
@@ -89,7 +90,9 @@ __device__ __forceinline__ void mm_bar_expect_tx(unsigned long long* bar, unsign
 __device__ __forceinline__ void mm_bar_arrive(unsigned long long* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(mm_smem(bar)) : "memory");
 }
-// bounded wait: false after 2 s (a wrong descriptor or a missing arrival must not hang the GPU)
+// bounded wait: false after `mm_timeout_ns` (a wrong descriptor or a missing arrival must not hang the GPU); the bound
+// is generous (default 10 s, ORBFE_TC_TIMEOUT_S) because a time-sliced GPU can legitimately stall a CTA for long
+__device__ unsigned long long mm_timeout_ns = 10000000000ull;
 __device__ __forceinline__ bool mm_bar_wait(unsigned long long* bar, unsigned parity) {
   const unsigned b = mm_smem(bar);
   unsigned long long t0 = 0;
@@ -109,7 +112,7 @@ __device__ __forceinline__ bool mm_bar_wait(unsigned long long* bar, unsigned pa
       unsigned long long t;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
       if (t0 == 0) t0 = t;
-      else if (t - t0 > 2000000000ull) return false;
+      else if (t - t0 > mm_timeout_ns) return false;
     }
   }
 }
@@ -421,6 +424,11 @@ int launch_hamming_mma(const uint8_t* query, int nq, const uint8_t* map, int nm,
   const int smem = (int)sizeof(MmSmem) + 1024;
   // a per-device attribute (several GPUs may be driven from one process): set on every call, it costs microseconds
   if (cudaFuncSetAttribute(hamming_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -2;
+  if (const char* e = getenv("ORBFE_TC_TIMEOUT_S")) {
+    const double sec = atof(e);
+    const unsigned long long ns = (unsigned long long)((sec > 0.001 ? sec : 0.001) * 1e9);
+    cudaMemcpyToSymbolAsync(mm_timeout_ns, &ns, sizeof(ns), 0, cudaMemcpyHostToDevice, s);
+  }
   cudaMemsetAsync(err, 0, 4, s);
   expand_bits_kernel<true><<<(int)((nq_pad + 7) / 8), 256, 0, s>>>(query, nq, (int)nq_pad, qb, qx, pq);
   expand_bits_kernel<false><<<(int)((nm_pad + 7) / 8), 256, 0, s>>>(map, nm, (int)nm_pad, mb, mx, nullptr);
