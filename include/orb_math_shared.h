@@ -181,4 +181,46 @@ ORB_HD int orb_predict_scale(float max_distance, float current_dist, float log_s
   return c < 0 ? 0 : c;
 }
 
+
+/* cv::undistortPoints(src, dst, K, D, noArray(), K) for ONE point (OpenCV 4.13 semantics: cvUndistortPointsInternal with
+ * the default TermCriteria(MAX_ITER, 5, 0.01) = five fixed-point iterations, R = I, P = K), as Frame::UndistortKeyPoints
+ * (src/Frame.cc:429-460) and Frame::ComputeImageBounds (:462-494) call it.  All arithmetic in double, in OpenCV's
+ * order, no FMA; checked bit-for-bit against python-cv2 4.13 (tests/golden/undistort.npz).  k = {k1, k2, p1, p2, k3}
+ * (mDistCoef: 4 or 5 coefficients, Tracking.cc:72-90; k3 = 0 when absent). */
+ORB_HD void orb_undistort_point(float u, float v, float ffx, float ffy, float fcx, float fcy, const float* kf,
+                                float* xu, float* yu) {
+  const double fx = (double)ffx, fy = (double)ffy, cx = (double)fcx, cy = (double)fcy;
+  const double k0 = (double)kf[0], k1 = (double)kf[1], k2 = (double)kf[2], k3 = (double)kf[3], k4 = (double)kf[4];
+  const double ifx = ORB_DDIV(1.0, fx), ify = ORB_DDIV(1.0, fy);
+  double x = ORB_DMUL(ORB_DSUB((double)u, cx), ifx), y = ORB_DMUL(ORB_DSUB((double)v, cy), ify);
+  const double x0 = x, y0 = y;
+  for (int j = 0; j < 5; ++j) {
+    const double r2 = ORB_DADD(ORB_DMUL(x, x), ORB_DMUL(y, y));
+    /* icdist = (1 + ((k[7]*r2 + k[6])*r2 + k[5])*r2) / (1 + ((k[4]*r2 + k[1])*r2 + k[0])*r2), k[5..7] = 0 */
+    const double num = ORB_DADD(1.0, ORB_DMUL(ORB_DADD(ORB_DMUL(ORB_DADD(ORB_DMUL(0.0, r2), 0.0), r2), 0.0), r2));
+    const double den = ORB_DADD(1.0, ORB_DMUL(ORB_DADD(ORB_DMUL(ORB_DADD(ORB_DMUL(k4, r2), k1), r2), k0), r2));
+    const double icdist = ORB_DDIV(num, den);
+    if (icdist < 0.0) {  /* "test: undistortPoints.regression_14583" */
+      x = x0;
+      y = y0;
+      break;
+    }
+    /* deltaX = 2*k[2]*x*y + k[3]*(r2 + 2*x*x) + k[8]*r2 + k[9]*r2*r2 (k[8..11] = 0) */
+    const double xy2a = ORB_DMUL(ORB_DMUL(ORB_DMUL(2.0, k2), x), y);
+    const double dx = ORB_DADD(ORB_DADD(ORB_DADD(xy2a, ORB_DMUL(k3, ORB_DADD(r2, ORB_DMUL(ORB_DMUL(2.0, x), x)))),
+                                        ORB_DMUL(0.0, r2)), ORB_DMUL(ORB_DMUL(0.0, r2), r2));
+    const double xy2b = ORB_DMUL(ORB_DMUL(ORB_DMUL(2.0, k3), x), y);
+    const double dy = ORB_DADD(ORB_DADD(ORB_DADD(ORB_DMUL(k2, ORB_DADD(r2, ORB_DMUL(ORB_DMUL(2.0, y), y))), xy2b),
+                                        ORB_DMUL(0.0, r2)), ORB_DMUL(ORB_DMUL(0.0, r2), r2));
+    x = ORB_DMUL(ORB_DSUB(x0, dx), icdist);
+    y = ORB_DMUL(ORB_DSUB(y0, dy), icdist);
+  }
+  /* R = I, P = K: xx = fx*x + 0*y + cx, yy = 0*x + fy*y + cy, ww = 1 / (0*x + 0*y + 1) */
+  const double xx = ORB_DADD(ORB_DADD(ORB_DMUL(fx, x), ORB_DMUL(0.0, y)), cx);
+  const double yy = ORB_DADD(ORB_DADD(ORB_DMUL(0.0, x), ORB_DMUL(fy, y)), cy);
+  const double ww = ORB_DDIV(1.0, ORB_DADD(ORB_DADD(ORB_DMUL(0.0, x), ORB_DMUL(0.0, y)), 1.0));
+  *xu = (float)ORB_DMUL(xx, ww);
+  *yu = (float)ORB_DMUL(yy, ww);
+}
+
 #endif /* ORB_MATH_SHARED_H_ */

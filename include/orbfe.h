@@ -348,6 +348,26 @@ int orbfe_comm_last_times(orbfe_comm* c, float* kernel_ms, float* exchange_merge
 int orbfe_measure_popc_peak(orbfe_matcher* m, double* popc32_per_second);
 
 /* ------------------------------------------------------------------ */
+/* The rest of the mono / RGB-D Frame constructors (src/Frame.cc:118-228), */
+/* on the resident results of orbfe_extract_run                            */
+/* ------------------------------------------------------------------ */
+/* Frame::UndistortKeyPoints (src/Frame.cc:429-460): keys_un[b][i] = keypoint i of image b with pt = cv::undistortPoints(pt,
+ * mK, mDistCoef, noArray(), mK) (OpenCV 4.13: five fixed-point iterations in double, bit-exact); every other field is
+ * copied; when k[0] == 0 the keypoints are copied unchanged (:431-435).  Host output [batch][capacity] (may be NULL: the
+ * undistorted keypoints also stay on the device for orbfe_stereo_from_rgbd).  Synchronous. */
+int orbfe_undistort_keypoints(orbfe_extractor* h, int batch, const orbfe_camera* cam, orbfe_keypoint* keys_un,
+                              int capacity);
+/* Frame::ComputeImageBounds (src/Frame.cc:462-494): bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY} of a width x height
+ * image (the four undistorted corners, or the image rectangle when k[0] == 0).  Host arithmetic (four points). */
+int orbfe_image_bounds(const orbfe_camera* cam, int width, int height, float* bounds);
+/* Frame::ComputeStereoFromRGBD (src/Frame.cc:688-712) after orbfe_undistort_keypoints: depth = CV_32F images on the
+ * host ([batch] images, image_stride / row_stride in floats; Tracking::GrabImageRGBD has already applied
+ * mDepthMapFactor); per keypoint d = depth(int(v), int(u)) at the DISTORTED position, and when d > 0: mvDepth = d,
+ * mvuRight = keys_un.x - mbf / d; else both -1.  Host outputs [batch][capacity].  Synchronous. */
+int orbfe_stereo_from_rgbd(orbfe_extractor* h, int batch, const float* depth, size_t image_stride, int row_stride,
+                           float mbf, float* u_right, float* depth_out, int capacity);
+
+/* ------------------------------------------------------------------ */
 /* DBoW2 vocabulary transform                        */
 /* Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1127-1262, called from */
 /* Frame::ComputeBoW (src/Frame.cc:420-427) and KeyFrame::ComputeBoW   */

@@ -143,6 +143,13 @@ typedef struct orbfe_points3d_view {
   const float* angle;        /* relocalisation overload only: pKF->mvKeysUn[i].angle */
 } orbfe_points3d_view;
 
+/* mK and mDistCoef as Tracking builds them from the settings file (src/Tracking.cc:58-100): pinhole intrinsics and the
+ * OpenCV distortion coefficients k1, k2, p1, p2, k3 (k3 = 0 when the file has four). */
+typedef struct orbfe_camera {
+  float fx, fy, cx, cy;
+  float k[5];
+} orbfe_camera;
+
 /* Pose + calibration of the frame / keyframe the points are projected into. */
 typedef struct orbfe_projection {
   float tcw[12];           /* rows 0..2 of Tcw (3x4 row-major), or of the Sim3 Scw when

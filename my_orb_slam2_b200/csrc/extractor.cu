@@ -373,6 +373,7 @@ static void free_arenas(Extractor* e) {
   if (e->h_result) cudaFreeHost(e->h_result);
   dfree(a.st_sad); dfree(a.st_band); dfree(a.st_bucket_start); dfree(a.st_bucket_items);
   cudaFree(a.fast_maps); cudaFree(a.desc_maps);
+  cudaFree(a.kp_un); cudaFree(a.depth_img);
   if (e->h_flags) cudaFreeHost(e->h_flags);
   if (e->prof_ev) {
     for (int i = 0; i < Extractor::kProfRuns * 9; ++i) cudaEventDestroy(e->prof_ev[i]);
@@ -668,6 +669,7 @@ int orbfe_extract_run(orbfe_extractor* h, int batch) {
   }
   e->launches += (g.nlevels - 1) + (g.fast_strips > 0 ? 1 : 0) + 3;
   e->last_batch = batch;
+  e->arena.kp_un_valid = false;  // mvKeysUn belongs to the previous extraction
   ORBFE_CUDA(cudaGetLastError());
   return ORBFE_OK;
 }

@@ -37,6 +37,10 @@ struct ExtractorArena {
   // kFastTileW x kFastTileH box: the FAST kernel stages a strip's image tile with ONE cp.async.bulk.tensor
   void* fast_maps = nullptr;  // [kMaxLevels]
   void* desc_maps = nullptr;  // [kMaxLevels] the BLURRED levels with a kDescBoxW x kDescBoxH box (k_describe.cu)
+  // the rest of the mono / RGB-D Frame constructors (frame.cu), allocated on first use
+  orbfe_keypoint* kp_un = nullptr;  // [batch][out_cap] undistorted keypoints (Frame::mvKeysUn)
+  float* depth_img = nullptr;       // [batch][h][w] CV_32F depth images (ComputeStereoFromRGBD)
+  bool kp_un_valid = false;
 };
 
 constexpr int kFastTileW = 144;                    // bytes per tile row (multiple of 16): 136 used + 8 of start alignment
@@ -70,6 +74,10 @@ void launch_stereo(const PyrGeom& g, const ExtractorArena& left, const Extractor
 constexpr int kLaunchesPerExtract(int nlevels) { return (nlevels - 1) + 3; }
 constexpr int kLaunchesPerStereo = 3;
 int stereo_items_per_kp(const PyrGeom& g);
+
+// ---- frame.cu: Frame::UndistortKeyPoints / ComputeStereoFromRGBD on the resident keypoints ----
+void launch_undistort(const PyrGeom& g, const ExtractorArena& a, int batch, const orbfe_camera& cam, cudaStream_t s);
+void launch_stereo_from_rgbd(const PyrGeom& g, const ExtractorArena& a, int batch, int w, int h, float mbf, cudaStream_t s);
 
 // ---- k_input.cu: cvtColor *2GRAY and remap INTER_LINEAR straight into level 0 ----
 void launch_gray(const uint8_t* src, size_t image_stride, int row_stride, int channels, int rgb, uint8_t* dst, int pitch,

@@ -267,3 +267,38 @@ class Frame:
         ur, dp, n = orbfe.stereo_match(self.mpORBextractorLeft._h, self.mpORBextractorRight._h, 1, self.mbf, self.mb)
         self.mvuRight, self.mvDepth = ur[0][:self.N].copy(), dp[0][:self.N].copy()
         return int(n[0])
+
+
+class MonoFrame:
+    """Monocular Frame (src/Frame.cc:176-228): ExtractORB, UndistortKeyPoints, ComputeImageBounds.
+    K = (fx, fy, cx, cy), distCoef = (k1, k2, p1, p2[, k3]) as Tracking builds them (src/Tracking.cc:58-100)."""
+
+    def __init__(self, imGray, extractor, K, distCoef):
+        self.mpORBextractorLeft = extractor
+        self.cam = tuple(K) + tuple(distCoef)
+        self.mvKeys, self.mDescriptors = extractor(imGray)                 # ExtractORB(0, imGray)  (:204)
+        self.N = len(self.mvKeys)
+        self.UndistortKeyPoints()                                          # :211
+        self.mvuRight = np.full(self.N, -1, np.float32)                    # :214-215
+        self.mvDepth = np.full(self.N, -1, np.float32)
+        h, w = imGray.shape
+        self.mnMinX, self.mnMaxX, self.mnMinY, self.mnMaxY = orbfe.image_bounds(self.cam, w, h)   # ComputeImageBounds (:222)
+
+    def UndistortKeyPoints(self):
+        """void Frame::UndistortKeyPoints() (src/Frame.cc:429-460) on the device-resident keypoints."""
+        if self.N == 0:
+            self.mvKeysUn = self.mvKeys.copy()
+            return
+        self.mvKeysUn = self.mpORBextractorLeft._h.undistort_keypoints(1, self.cam)[0][:self.N].copy()
+
+
+class RGBDFrame(MonoFrame):
+    """RGB-D Frame (src/Frame.cc:118-173): the mono steps + ComputeStereoFromRGBD(imDepth) (:688-712); imDepth is the
+    CV_32F depth image after Tracking::GrabImageRGBD applied mDepthMapFactor."""
+
+    def __init__(self, imGray, imDepth, extractor, K, distCoef, bf):
+        super().__init__(imGray, extractor, K, distCoef)
+        self.mbf = np.float32(bf)
+        if self.N:
+            ur, dz = self.mpORBextractorLeft._h.stereo_from_rgbd(1, imDepth, self.mbf)
+            self.mvuRight, self.mvDepth = ur[0][:self.N].copy(), dz[0][:self.N].copy()

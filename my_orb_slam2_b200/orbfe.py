@@ -121,6 +121,9 @@ SYMBOLS = {
     "orbfe_stereo_frame": (_I, [_P, _P, _P, _P, C.c_size_t, _I, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I]),
     "orbfe_stereo_match_run": (_I, [_P, _P, _I, _F, _F]),
     "orbfe_stereo_match_download": (_I, [_P, _I, _P, _P, _I, _P]),
+    "orbfe_undistort_keypoints": (_I, [_P, _I, _P, _P, _I]),
+    "orbfe_image_bounds": (_I, [_P, _I, _I, _P]),
+    "orbfe_stereo_from_rgbd": (_I, [_P, _I, _P, C.c_size_t, _I, _F, _P, _P, _I]),
     "orbfe_matcher_create": (_I, [_I, C.POINTER(_P)]),
     "orbfe_matcher_destroy": (None, [_P]),
     "orbfe_matcher_launch_count": (C.c_int64, [_P]),
@@ -282,6 +285,26 @@ class Extractor:
     def sync(self):
         check(lib().orbfe_extractor_sync(self._h))
 
+    # -- the rest of the mono / RGB-D Frame constructors (src/Frame.cc:118-228) -----------------------
+    def undistort_keypoints(self, batch, cam):
+        """Frame::UndistortKeyPoints on the last run's keypoints: cam = (fx, fy, cx, cy, k1, k2, p1, p2[, k3]).
+        Returns mvKeysUn as [batch][capacity] keypoints (rows beyond the image's count are untouched zeros)."""
+        out = np.zeros((batch, self.capacity), KEYPOINT_DTYPE)
+        check(lib().orbfe_undistort_keypoints(self._h, batch, _p(camera(cam)), _p(out), self.capacity))
+        return out
+
+    def stereo_from_rgbd(self, batch, depth, mbf):
+        """Frame::ComputeStereoFromRGBD after undistort_keypoints: depth [batch, H, W] float32 -> (mvuRight, mvDepth)."""
+        depth = np.ascontiguousarray(depth, np.float32)
+        if depth.ndim == 2:
+            depth = depth[None]
+        b, h, w = depth.shape
+        ur = np.empty((batch, self.capacity), np.float32)
+        dz = np.empty((batch, self.capacity), np.float32)
+        check(lib().orbfe_stereo_from_rgbd(self._h, batch, _p(depth), h * w, w, np.float32(mbf), _p(ur), _p(dz),
+                                           self.capacity))
+        return ur, dz
+
     def share_stream(self, other):
         check(lib().orbfe_extractor_share_stream(self._h, other._h))
 
@@ -329,6 +352,20 @@ class Extractor:
 
     def level_keypoints(self, lv, image_index=0):
         return self._debug(lib().orbfe_extractor_debug_level_keypoints, lv, image_index)
+
+
+def camera(cam):
+    """(fx, fy, cx, cy, k1, k2, p1, p2[, k3]) -> the 9 floats of orbfe_camera."""
+    c = np.zeros(9, np.float32)
+    c[:len(cam)] = np.asarray(cam, np.float32)
+    return c
+
+
+def image_bounds(cam, width, height):
+    """Frame::ComputeImageBounds -> (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    b = np.zeros(4, np.float32)
+    check(lib().orbfe_image_bounds(_p(camera(cam)), width, height, _p(b)))
+    return b
 
 
 def stereo_match(left, right, batch, mbf, mb):

@@ -106,6 +106,11 @@ void orc_compute_distinctive_descriptors(const uint8_t* desc, const int32_t* off
                                          uint8_t* best_desc);
 /* shared arithmetic probes (include/orb_math_shared.h) for the known-answer tests */
 float orc_log_f32(float x);
+/* the rest of the mono / RGB-D Frame constructors (src/Frame.cc:429-494, :688-712) */
+void orc_undistort_keypoints(const orbfe_keypoint* keys, int n, const orbfe_camera* cam, orbfe_keypoint* keys_un);
+void orc_image_bounds(const orbfe_camera* cam, int cols, int rows, float* bounds);
+void orc_stereo_from_rgbd(const orbfe_keypoint* keys, const orbfe_keypoint* keys_un, int n, const float* depth, int w,
+                          int h, int stride, float mbf, float* u_right, float* depth_out);
 int orc_predict_scale(float max_distance, float dist, float log_scale_factor, int nlevels);
 
 /* ---- DBoW2 vocabulary transform (orb_bow.cc) ---- */

@@ -106,6 +106,10 @@ def lib():
         L.orc_ic_angle.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
         L.orc_sincos_deg.argtypes = [C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_orb_descriptor.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.orc_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_image_bounds.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.orc_stereo_from_rgbd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float,
+                                           C.c_void_p, C.c_void_p]
         L.orc_extractor_create.restype = C.c_void_p
         L.orc_extractor_create.argtypes = [C.POINTER(ExtractorParams), C.c_int]
         L.orc_extractor_destroy.argtypes = [C.c_void_p]
@@ -312,6 +316,42 @@ def stereo_matches(ext_left, ext_right, kp_l, desc_l, kp_r, desc_r, mbf, mb):
     n = lib().orc_stereo_matches(ext_left._h, ext_right._h, _p(kp_l), _p(desc_l), len(kp_l), _p(kp_r), _p(desc_r),
                                  len(kp_r), mbf, mb, _p(ur), _p(dp))
     return ur, dp, n
+
+
+def _camera(cam):
+    """(fx, fy, cx, cy, k1, k2, p1, p2[, k3]) -> the 9 floats of orbfe_camera."""
+    c = np.zeros(9, np.float32)
+    c[:len(cam)] = np.asarray(cam, np.float32)
+    return c
+
+
+def undistort_keypoints(kp, cam):
+    """Frame::UndistortKeyPoints (src/Frame.cc:429-460)."""
+    kp = np.ascontiguousarray(kp, KEYPOINT_DTYPE)
+    out = np.empty_like(kp)
+    c = _camera(cam)
+    lib().orc_undistort_keypoints(_p(kp), len(kp), _p(c), _p(out))
+    return out
+
+
+def image_bounds(cam, cols, rows):
+    """Frame::ComputeImageBounds (src/Frame.cc:462-494) -> (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    c = _camera(cam)
+    b = np.zeros(4, np.float32)
+    lib().orc_image_bounds(_p(c), cols, rows, _p(b))
+    return b
+
+
+def stereo_from_rgbd(kp, kp_un, depth, mbf):
+    """Frame::ComputeStereoFromRGBD (src/Frame.cc:688-712) -> (mvuRight, mvDepth)."""
+    kp = np.ascontiguousarray(kp, KEYPOINT_DTYPE)
+    kp_un = np.ascontiguousarray(kp_un, KEYPOINT_DTYPE)
+    depth = np.ascontiguousarray(depth, np.float32)
+    ur = np.empty(len(kp), np.float32)
+    dz = np.empty(len(kp), np.float32)
+    lib().orc_stereo_from_rgbd(_p(kp), _p(kp_un), len(kp), _p(depth), depth.shape[1], depth.shape[0], depth.shape[1],
+                               np.float32(mbf), _p(ur), _p(dz))
+    return ur, dz
 
 
 # ---------------------------------------------------------------- matcher views

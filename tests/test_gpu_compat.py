@@ -42,6 +42,42 @@ def test_cpp_dropin_matches_oracle(oracle, tmp_path):
     assert np.array_equal(ur, our) and np.array_equal(dp, odp)
 
 
+def test_cpp_dropin_mono_rgbd_tail_matches_oracle(oracle, tmp_path):
+    """compat/FrameMono.h: the bodies of Frame::UndistortKeyPoints / ComputeImageBounds / ComputeStereoFromRGBD driven as
+    the RGB-D Frame constructor does (src/Frame.cc:118-173), TUM1 camera, against the oracle."""
+    exe = os.path.join(ROOT, "compat", "_build", "test_compat_mono")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "compat")])
+    s = synth.SETTINGS["tum"]
+    w, h = synth.SHAPES["tum"]
+    img = synth.synth_image(w, h, 31)
+    rng = np.random.default_rng(31)
+    depth = rng.uniform(0.4, 9.0, (h, w)).astype(np.float32)
+    depth[rng.random((h, w)) < 0.2] = 0.0
+    img.tofile(tmp_path / "i.raw")
+    depth.tofile(tmp_path / "d.f32")
+    mbf = np.float32(40.0)
+    out = tmp_path / "out.bin"
+    subprocess.check_call([exe, str(tmp_path / "i.raw"), str(tmp_path / "d.f32"), str(w), str(h), str(s["nfeatures"]),
+                           repr(float(mbf)), str(out)])
+    raw = out.read_bytes()
+    n = int(np.frombuffer(raw[:4], np.int32)[0])
+    bounds = np.frombuffer(raw[4:20], np.float32)
+    off = 20
+    kp = np.frombuffer(raw[off:off + n * 28], oracle.KEYPOINT_DTYPE); off += n * 28
+    kpu = np.frombuffer(raw[off:off + n * 28], oracle.KEYPOINT_DTYPE); off += n * 28
+    ur = np.frombuffer(raw[off:off + n * 4], np.float32); off += n * 4
+    dz = np.frombuffer(raw[off:off + n * 4], np.float32)
+    cam = (517.306408, 516.469215, 318.643040, 255.313989, 0.262383, -0.953104, -0.005358, 0.002628, 1.163314)
+    ok, _ = oracle.Extractor(s["nfeatures"], s["scale_factor"], s["nlevels"], s["ini_th"], s["min_th"]).extract(img)
+    assert n == len(ok) and np.array_equal(kp, ok)
+    oku = oracle.undistort_keypoints(ok, cam)
+    assert np.array_equal(kpu, oku)
+    our, odz = oracle.stereo_from_rgbd(ok, oku, depth, mbf)
+    assert np.array_equal(ur, our) and np.array_equal(dz, odz)
+    assert np.array_equal(bounds, oracle.image_bounds(cam, w, h))
+
+
 # ---- drop-in ORBmatcher (compat/ORBmatcher.cc): the reference's C++ signatures on mock Frame / KeyFrame / MapPoint
 # objects (compat/slam_min.h), results as the reference's callers observe them, against the oracle ----
 def _exe():
