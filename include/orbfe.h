@@ -50,7 +50,12 @@ typedef struct orbfe_extractor orbfe_extractor;
  * is fixed per handle (the camera's); max_batch images can be processed by
  * one call.  Each handle owns a CUDA stream and its device arenas, so two
  * handles may be driven concurrently from two host threads like the left /
- * right extractors of src/Frame.cc:89-92. */
+ * right extractors of src/Frame.cc:89-92.
+ * Limits (ORBFE_ERR_ARG with a message otherwise): 1..8 levels, scale factor > 1, every level at most 4096 + 32
+ * pixels wide / high and not taller than wide by more than the reference's round(w/h) >= 1 allows (it divides by
+ * zero there, :543-545), at most 255 x 255 cells per level, at most ~2550 features on one level (the quadtree of a
+ * level lives in one CTA's shared memory: 88 bytes per node; 8 levels at scale 1.2 reach that at nfeatures ~ 11 700)
+ * and at most 65 535 keypoints per image. */
 int orbfe_extractor_create(const orbfe_extractor_params* params, int width, int height, int max_batch, int device,
                            orbfe_extractor** out);
 void orbfe_extractor_destroy(orbfe_extractor* e);

@@ -19,8 +19,15 @@ KEYPOINT_DTYPE = np.dtype(
 assert KEYPOINT_DTYPE.itemsize == 28  # layout of cv::KeyPoint / orbfe_keypoint
 
 
+ERR_ARG, ERR_CUDA, ERR_CAPACITY, ERR_STATE = -1, -2, -3, -4  # include/orbfe.h:30-34
+
+
 class OrbfeError(RuntimeError):
-    pass
+    """A non-zero status of the C ABI; `code` is the ORBFE_ERR_* value (None when the library itself is missing)."""
+
+    def __init__(self, msg, code=None):
+        super().__init__(msg)
+        self.code = code
 
 
 class ExtractorParams(C.Structure):
@@ -190,7 +197,7 @@ def lib():
 
 def check(rc):
     if rc != 0:
-        raise OrbfeError("orbfe status %d: %s" % (rc, lib().orbfe_last_error().decode()))
+        raise OrbfeError("orbfe status %d: %s" % (rc, lib().orbfe_last_error().decode()), rc)
 
 
 def device_count():

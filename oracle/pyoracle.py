@@ -274,7 +274,16 @@ class Extractor:
                               cap)
         if n < 0:
             raise RuntimeError("orc_extract failed: %d" % n)
-        assert n <= cap
+        if n > cap:
+            # the first quadtree round splits all round(w/h) root nodes before the count is looked at
+            # (src/ORBextractor.cc:543-560, :574-660), so a wide image with a small per-level quota returns up to
+            # 4 * round(w/h) keypoints on that level: more than info.capacity, which does not know the image size
+            cap = n
+            kps = np.zeros(cap, KEYPOINT_DTYPE)
+            desc = np.zeros((cap, 32), np.uint8)
+            n = lib().orc_extract(self._h, _p(image), image.shape[1], image.shape[0], image.shape[1], _p(kps),
+                                  _p(desc), cap)
+            assert n == cap
         return kps[:n].copy(), desc[:n].copy()
 
     def level(self, lv, blurred=False):
