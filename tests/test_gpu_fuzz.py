@@ -27,3 +27,15 @@ def test_random_cases_match_oracle(oracle):
             bad.append("%s: %s" % (d, st))
     assert not bad, "\n".join(bad)
     assert ok >= count * 0.7, "%d of %d cases refused" % (refused, count)
+
+
+def test_random_matcher_cases_match_oracle(oracle):
+    """Every ORBmatcher member once per seed with drawn thresholds / ratios / windows / motion (tests/fuzz_matchers.py)."""
+    import fuzz_matchers
+    from my_orb_slam2_b200 import frontend
+    first = int(os.environ.get("ORBFE_FUZZ_FIRST", "0"))
+    count = int(os.environ.get("ORBFE_FUZZ_MATCHER_N", "25"))
+    bad = []
+    for seed in range(first, first + count):
+        bad += ["seed %d %s" % (seed, name) for name, st, _ in fuzz_matchers.run_case(seed, oracle, frontend) if st != "ok"]
+    assert not bad, "\n".join(bad)
