@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <set>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "ORBVocabulary.h"
@@ -159,30 +160,51 @@ static int index_in(const std::vector<T>& owned, const T* p) {
 int main(int argc, char** argv) {
   if (argc < 3) return 2;
   const std::string mode = argv[1], dir = argv[2];
-  if (mode == "map") {
-    Frame F;
-    std::vector<MapPoint> owned;
-    load_frame(dir, F, owned);
-    std::vector<float> px = rd<float>(dir, "proj_x"), py = rd<float>(dir, "proj_y"), pxr = rd<float>(dir, "proj_xr"),
-                       vc = rd<float>(dir, "view_cos");
-    std::vector<int32_t> lvl = rd<int32_t>(dir, "level"), obs = rd<int32_t>(dir, "obs");
-    std::vector<uint8_t> inv = rd<uint8_t>(dir, "in_view"), d = rd<uint8_t>(dir, "mp_desc");
-    const int M = (int)px.size();
-    std::vector<MapPoint> mps(M);
-    std::vector<MapPoint*> vp(M);
-    for (int i = 0; i < M; ++i) {
-      mps[i].mTrackProjX = px[i]; mps[i].mTrackProjY = py[i]; mps[i].mTrackProjXR = pxr[i];
-      mps[i].mnTrackScaleLevel = lvl[i]; mps[i].mTrackViewCos = vc[i]; mps[i].mbTrackInView = inv[i] != 0;
-      mps[i].nObs = obs[i]; mps[i].mDescriptor = desc_row(d, i);
-      vp[i] = &mps[i];
+  if (mode == "map" || mode == "map_threads") {
+    // one SearchByProjection(F, MapPoints) from scratch: own Frame, own MapPoints, own (stack-local) matcher
+    auto run_once = [&dir]() {
+      Frame F;
+      std::vector<MapPoint> owned;
+      load_frame(dir, F, owned);
+      std::vector<float> px = rd<float>(dir, "proj_x"), py = rd<float>(dir, "proj_y"), pxr = rd<float>(dir, "proj_xr"),
+                         vc = rd<float>(dir, "view_cos");
+      std::vector<int32_t> lvl = rd<int32_t>(dir, "level"), obs = rd<int32_t>(dir, "obs");
+      std::vector<uint8_t> inv = rd<uint8_t>(dir, "in_view"), d = rd<uint8_t>(dir, "mp_desc");
+      const int M = (int)px.size();
+      std::vector<MapPoint> mps(M);
+      std::vector<MapPoint*> vp(M);
+      for (int i = 0; i < M; ++i) {
+        mps[i].mTrackProjX = px[i]; mps[i].mTrackProjY = py[i]; mps[i].mTrackProjXR = pxr[i];
+        mps[i].mnTrackScaleLevel = lvl[i]; mps[i].mTrackViewCos = vc[i]; mps[i].mbTrackInView = inv[i] != 0;
+        mps[i].nObs = obs[i]; mps[i].mDescriptor = desc_row(d, i);
+        vp[i] = &mps[i];
+      }
+      std::vector<float> par = rd<float>(dir, "params");  // th, nnratio
+      ORBmatcher matcher(par[1], true);
+      const int n = matcher.SearchByProjection(F, vp, par[0]);
+      std::vector<int32_t> out(F.N + 1, -1);
+      for (int f = 0; f < F.N; ++f)
+        if (F.mvpMapPoints[f] >= &mps[0] && F.mvpMapPoints[f] < &mps[0] + M) out[f] = (int32_t)(F.mvpMapPoints[f] - &mps[0]);
+      out[F.N] = n;
+      return out;
+    };
+    const std::vector<int32_t> out = run_once();
+    if (mode == "map_threads") {
+      // Tracking, LocalMapping and LoopClosing use their own matcher objects at the same time:
+      // three threads repeat the call concurrently; every result must equal the one computed alone
+      int bad[3] = {0, 0, 0};
+      std::vector<std::thread> ts;
+      for (int t = 0; t < 3; ++t)
+        ts.emplace_back([&, t] {
+          for (int r = 0; r < 6; ++r)
+            if (run_once() != out) ++bad[t];
+        });
+      for (std::thread& t : ts) t.join();
+      if (bad[0] + bad[1] + bad[2]) {
+        std::fprintf(stderr, "concurrent results differ: %d %d %d of 6\n", bad[0], bad[1], bad[2]);
+        return 3;
+      }
     }
-    std::vector<float> par = rd<float>(dir, "params");  // th, nnratio
-    ORBmatcher matcher(par[1], true);
-    const int n = matcher.SearchByProjection(F, vp, par[0]);
-    std::vector<int32_t> out(F.N + 1, -1);
-    for (int f = 0; f < F.N; ++f)
-      if (F.mvpMapPoints[f] >= &mps[0] && F.mvpMapPoints[f] < &mps[0] + M) out[f] = (int32_t)(F.mvpMapPoints[f] - &mps[0]);
-    out[F.N] = n;
     write_i32(dir, "result", out);
   } else if (mode == "last") {
     Frame Cur, Last;

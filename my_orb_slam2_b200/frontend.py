@@ -11,6 +11,7 @@ The C++ drop-in classes for linking Tracking / LocalMapping / LoopClosing are in
 harness used by tests/ and bench.py.  Everything is computed by liborbfe.so on the GPU; nothing here has a CPU path.
 """
 import ctypes as C
+import threading
 
 import numpy as np
 
@@ -180,16 +181,20 @@ class ORBmatcher:
     """ORBmatcher(nnratio=0.6, checkOri=true) (include/ORBmatcher.h:45; src/ORBmatcher.cc:40-42)."""
 
     TH_LOW, TH_HIGH, HISTO_LENGTH = TH_LOW, TH_HIGH, HISTO_LENGTH
-    _ctx = {}
+    # one C-ABI matcher handle (stream + workspace) per host thread and device: the reference's matcher objects are
+    # stack-local and used concurrently by the Tracking, LocalMapping and LoopClosing threads (SURVEY.md 8(b)); a
+    # handle serves one call at a time (compat/ORBmatcher.cc keeps a thread_local handle the same way)
+    _tls = threading.local()
 
     def __init__(self, nnratio=0.6, checkOri=True, device=0):
         self.mfNNratio, self.mbCheckOrientation, self.device = nnratio, checkOri, device
 
     @classmethod
     def _matcher(cls, device):
-        if device not in cls._ctx:
-            cls._ctx[device] = orbfe.Matcher(device)
-        return cls._ctx[device]
+        ctx = cls._tls.__dict__.setdefault("ctx", {})
+        if device not in ctx:
+            ctx[device] = orbfe.Matcher(device)
+        return ctx[device]
 
     @staticmethod
     def DescriptorDistance(a, b, device=0):

@@ -107,7 +107,10 @@ def kitti_frame(oracle):
     return synth.frame_arrays(kp, desc, (0.0, 0.0, float(w), float(h)), seed=0)
 
 
-def test_cpp_matcher_search_by_projection_map(oracle, kitti_frame, tmp_path):
+@pytest.mark.parametrize("mode", ["map", "map_threads"])
+def test_cpp_matcher_search_by_projection_map(oracle, kitti_frame, tmp_path, mode):
+    """mode map_threads: three std::threads repeat the call with their own stack-local ORBmatcher at the same time (the
+    executable exits 3 if any concurrent result differs from the one computed alone)."""
     from cases import views
     frame = kitti_frame
     mps = synth.map_points_case(frame, 20000, 1500, seed=0)
@@ -116,7 +119,7 @@ def test_cpp_matcher_search_by_projection_map(oracle, kitti_frame, tmp_path):
     _dump(d, proj_x=mps["proj_x"], proj_y=mps["proj_y"], proj_xr=mps["proj_xr"], view_cos=mps["view_cos"],
           level=mps["level"].astype(np.int32), obs=mps["obs"].astype(np.int32), in_view=mps["in_view"],
           mp_desc=mps["desc"], params=np.array([1.0, 0.8], np.float32))
-    subprocess.check_call([_exe(), "map", d])
+    subprocess.check_call([_exe(), mode, d])
     res = np.fromfile(os.path.join(d, "result.bin"), np.int32)
     fv, mv = views(oracle, frame=frame, mps=mps)
     want, n = oracle.search_by_projection_map(fv, mv, 1.0, 0.8)
