@@ -179,7 +179,8 @@ int orbfe_stereo_frame(orbfe_extractor* left, orbfe_extractor* right, const uint
 /* ------------------------------------------------------------------ */
 typedef struct orbfe_matcher orbfe_matcher;
 /* A matcher context owns a stream + workspace; one per host thread (the
- * reference constructs ORBmatcher objects on the stack per use). */
+ * reference constructs ORBmatcher objects on the stack per use).  A handle serves one call at a time: a second host
+ * thread that enters the same handle while a call is inside it gets ORBFE_ERR_STATE (never a wrong result). */
 int orbfe_matcher_create(int device, orbfe_matcher** out);
 void orbfe_matcher_destroy(orbfe_matcher* m);
 int64_t orbfe_matcher_launch_count(const orbfe_matcher* m);

@@ -427,7 +427,7 @@ int orbfe_hamming_bruteforce_sharded(orbfe_matcher* hm, orbfe_comm* hc, const ui
     set_error("orbfe_hamming_bruteforce_sharded: peer-memory exchange asked for, but the ranks cannot map each other");
     return ORBFE_ERR_ARG;
   }
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   int slice_len = 0;
   const int slices = nm_local > 0 ? (tensor ? 1 : bruteforce_slices(nq, nm_local, &slice_len)) : 0;
   const int nparts = std::max(slices, 1);

@@ -2,9 +2,12 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <functional>
+#include <thread>
 
 #include "../../include/orbfe.h"
 
@@ -45,6 +48,39 @@ struct DeviceGuard {
     if (prev >= 0) cudaSetDevice(prev);
   }
 };
+
+// A handle (stream + workspace) serves ONE call at a time: the reference's matcher objects are stack-local, one per
+// calling thread.  Two host threads inside the same handle would overwrite each other's staged
+// inputs; instead of wrong matches the second caller gets ORBFE_ERR_STATE.  Entry points that call other entry points
+// of the same handle (same thread) pass through.
+struct BusyState {
+  std::atomic<int> busy{0};
+  std::atomic<size_t> owner{0};
+};
+struct BusyGuard {
+  BusyState* st;
+  bool ok = false, outer = false;
+  explicit BusyGuard(BusyState* s) : st(s) {
+    const size_t me = std::hash<std::thread::id>()(std::this_thread::get_id()) | 1u;
+    if (st->busy.load(std::memory_order_acquire) && st->owner.load(std::memory_order_relaxed) == me) { ok = true; return; }
+    int expected = 0;
+    ok = outer = st->busy.compare_exchange_strong(expected, 1, std::memory_order_acq_rel);
+    if (outer) st->owner.store(me, std::memory_order_relaxed);
+  }
+  ~BusyGuard() {
+    if (outer) {
+      st->owner.store(0, std::memory_order_relaxed);
+      st->busy.store(0, std::memory_order_release);
+    }
+  }
+};
+#define ORBFE_MATCHER_ENTER(m)                                                                                      \
+  orbfe::BusyGuard busy_guard_(&(m)->busy);                                                                         \
+  if (!busy_guard_.ok) {                                                                                            \
+    orbfe::set_error("%s: this matcher handle is inside another call (one orbfe_matcher per host thread)", __func__); \
+    return ORBFE_ERR_STATE;                                                                                         \
+  }                                                                                                                 \
+  orbfe::DeviceGuard guard((m)->device)
 
 // Capture `issue()` (kernel launches on `stream`) into an executable graph.  Whatever fails between BeginCapture and
 // Instantiate, the capture is always ended and the intermediate graph destroyed, so the stream never stays in capture

@@ -79,7 +79,7 @@ void* orbfe_matcher_stream(orbfe_matcher* h) { return h ? reinterpret_cast<Match
 int orbfe_matcher_sync(orbfe_matcher* h) {
   ORBFE_ARG(h);
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   ORBFE_CUDA(cudaStreamSynchronize(m->stream));
   if (m->tc_pending) {  // the tensor-core brute force reports a pipeline time-out through a pinned word
     m->tc_pending = false;
@@ -96,7 +96,7 @@ int orbfe_hamming_bruteforce_tc_device(orbfe_matcher* h, const uint8_t* d_query,
   ORBFE_ARG(h && d_query && d_best && d_second && nq >= 1 && nm >= 1 && d_map);
   ORBFE_ARG(index_base >= 0 && index_base + (int64_t)nm <= ((int64_t)1 << 32));
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   return matcher_tc_launch(m, d_query, nq, d_map, nm, index_base, d_best, d_second);
 }
 
@@ -105,7 +105,7 @@ int orbfe_descriptor_distance(orbfe_matcher* h, const uint8_t* a, const uint8_t*
   if (n == 0) return ORBFE_OK;
   ORBFE_ARG(a && b && out);
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   int rc = arena_reserve(m, 2 * padded((size_t)n * 32) + padded((size_t)n * 4));
   if (rc != ORBFE_OK) return rc;
   const uint8_t* da = arena_put(m, a, (size_t)n * 32);
@@ -130,7 +130,7 @@ int orbfe_compute_distinctive_descriptors(orbfe_matcher* h, const uint8_t* desc,
   const size_t total = (size_t)offsets[n_points];
   ORBFE_ARG(total == 0 || desc);
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   const size_t P = (size_t)n_points;
   int rc = arena_reserve(m, padded(total * 32) + padded((P + 1) * 4) + padded(P * 4) + padded(P * 32));
   if (rc != ORBFE_OK) return rc;
@@ -154,7 +154,7 @@ int orbfe_hamming_merge_device(orbfe_matcher* h, const uint64_t* d_best_all, con
                                int nq, uint64_t* d_best, uint64_t* d_second) {
   ORBFE_ARG(h && d_best_all && d_second_all && d_best && d_second && shards >= 1 && nq >= 1);
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   launch_hamming_merge(reinterpret_cast<const unsigned long long*>(d_best_all),
                        reinterpret_cast<const unsigned long long*>(d_second_all), shards, nq,
                        reinterpret_cast<unsigned long long*>(d_best), reinterpret_cast<unsigned long long*>(d_second),
@@ -167,7 +167,7 @@ int orbfe_hamming_merge_device(orbfe_matcher* h, const uint64_t* d_best_all, con
 int orbfe_measure_popc_peak(orbfe_matcher* h, double* popc32_per_second) {
   ORBFE_ARG(h && popc32_per_second);
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   ORBFE_CUDA(cudaStreamSynchronize(m->stream));
   *popc32_per_second = measure_popc_peak(m->stream);
   ORBFE_CUDA(cudaGetLastError());
@@ -179,7 +179,7 @@ int orbfe_hamming_bruteforce_device(orbfe_matcher* h, const uint8_t* d_query, in
   ORBFE_ARG(h && d_query && d_best && d_second && nq >= 1 && nm >= 0);
   ORBFE_ARG(nm == 0 || d_map);
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   int slice_len = 0;
   const int slices = nm > 0 ? bruteforce_slices(nq, nm, &slice_len) : 0;
   // the partial results live in the candidate buffer (2 x slices x nq u64)
@@ -207,7 +207,7 @@ int orbfe_hamming_bruteforce(orbfe_matcher* h, const uint8_t* query, int nq, con
   if (nq == 0) return ORBFE_OK;
   ORBFE_ARG(query && best && second && (nm == 0 || map));
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   int rc = arena_reserve(m, padded((size_t)nq * 32) + padded((size_t)nm * 32) + 2 * padded((size_t)nq * 8));
   if (rc != ORBFE_OK) return rc;
   const uint8_t* dq = arena_put(m, query, (size_t)nq * 32);
@@ -236,7 +236,7 @@ int orbfe_search_by_projection_map(orbfe_matcher* h, const orbfe_frame_view* fra
   ORBFE_ARG(mps->proj_x && mps->proj_y && mps->proj_xr && mps->level && mps->view_cos && mps->in_view && mps->obs &&
             mps->desc);
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   const size_t M = (size_t)mps->m;
   rc = arena_reserve(m, frame_bytes(frame) + 6 * padded(M * 4) + padded(M) + padded(M * 32) +
                             scratch_bytes(mps->m, frame->n));
@@ -281,7 +281,7 @@ int orbfe_search_by_projection_last(orbfe_matcher* h, const orbfe_frame_view* cu
   if (last->n == 0 || cur->n == 0) return ORBFE_OK;
   ORBFE_ARG(last->valid && last->world_pos && last->obs && last->desc && last->octave && last->angle);
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   const size_t N = (size_t)last->n;
   rc = arena_reserve(m, frame_bytes(cur) + padded(N) + padded(N * 12) + 3 * padded(N * 4) + padded(N * 32) +
                             scratch_bytes(last->n, cur->n));
@@ -325,7 +325,7 @@ int orbfe_search_for_triangulation(orbfe_matcher* h, const orbfe_keyframe_view* 
   *n_pairs = 0;
   if (kf1->n == 0 || kf2->n == 0 || kf1->n_nodes == 0 || kf2->n_nodes == 0) return ORBFE_OK;
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   const size_t n1 = (size_t)kf1->n;
   const int out_cap = (int)std::min<size_t>((size_t)cap, n1);
   rc = arena_reserve(m, kf_bytes(kf1) + kf_bytes(kf2) + padded(64) + 2 * padded((n1 + 1) * 4) +

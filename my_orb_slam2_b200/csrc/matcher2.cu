@@ -88,7 +88,7 @@ static int projection_claims(orbfe_matcher* h, int mode, const orbfe_frame_view*
   for (int i = 0; i < frame->n; ++i) assigned[i] = -1;
   if (pts->m == 0 || frame->n == 0) return ORBFE_OK;
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   rc = arena_reserve(m, frame_bytes(frame) + points_bytes(pts) + scratch_bytes(pts->m, frame->n));
   if (rc != ORBFE_OK) return rc;
   DevFrame f;
@@ -146,7 +146,7 @@ int orbfe_search_local_points(orbfe_matcher* h, const orbfe_frame_view* frame, c
   for (int i = 0; i < frame->n; ++i) assigned[i] = -1;
   if (pts->m == 0) return ORBFE_OK;
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   const size_t M = (size_t)pts->m;
   rc = arena_reserve(m, frame_bytes(frame) + points_bytes(pts) + 7 * padded(M * 4) + scratch_bytes(pts->m, frame->n));
   if (rc != ORBFE_OK) return rc;
@@ -212,7 +212,7 @@ int orbfe_fuse(orbfe_matcher* h, const orbfe_frame_view* kf, const orbfe_project
   for (int i = 0; i < pts->m; ++i) best_idx[i] = -1;
   if (pts->m == 0 || kf->n == 0) return ORBFE_OK;
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   const size_t M = (size_t)pts->m;
   rc = arena_reserve(m, frame_bytes(kf) + points_bytes(pts) + padded(64) + grid_bytes(kf->n) + padded(M * 4) + padded(64));
   if (rc != ORBFE_OK) return rc;
@@ -261,7 +261,7 @@ int orbfe_search_by_sim3(orbfe_matcher* h, const orbfe_frame_view* kf1, const or
   for (int i = 0; i < p1->m; ++i) match12[i] = -1;
   if (p1->m == 0 || p2->m == 0) return ORBFE_OK;
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   const size_t n1 = (size_t)p1->m, n2 = (size_t)p2->m;
   rc = arena_reserve(m, frame_bytes(kf1) + frame_bytes(kf2) + points_bytes(p1) + points_bytes(p2) + grid_bytes(kf1->n) +
                             grid_bytes(kf2->n) + 2 * padded(n1 * 4) + padded(n2 * 4) + padded(64));
@@ -329,7 +329,7 @@ int orbfe_search_by_bow(orbfe_matcher* h, const orbfe_keyframe_view* kf1, const 
   for (int i = 0; i < n_out; ++i) matches[i] = -1;
   if (kf1->n == 0 || kf2->n == 0 || kf1->n_nodes == 0 || kf2->n_nodes == 0) return ORBFE_OK;
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   rc = arena_reserve(m, kf_bytes(kf1) + kf_bytes(kf2) + padded((size_t)kf2->n * 4) + padded((size_t)n_out * 4) + padded(64));
   if (rc != ORBFE_OK) return rc;
   DevKeyFrame a, b;
@@ -365,7 +365,7 @@ int orbfe_search_for_initialization(orbfe_matcher* h, const orbfe_frame_view* f1
   for (int i = 0; i < f1->n; ++i) matches12[i] = -1;
   if (f1->n == 0 || f2->n == 0) return ORBFE_OK;
   Matcher* m = reinterpret_cast<Matcher*>(h);
-  DeviceGuard guard(m->device);
+  ORBFE_MATCHER_ENTER(m);
   const size_t n1 = (size_t)f1->n, n2 = (size_t)f2->n;
   rc = arena_reserve(m, frame_bytes(f2) + padded(n1 * sizeof(orbfe_keypoint)) + padded(n1 * 32) + padded(n1 * 8) +
                             scratch_bytes(f1->n, f2->n) + padded(n1 * 4) + padded(n2 * 4) + padded(64));

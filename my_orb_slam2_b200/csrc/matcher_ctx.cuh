@@ -26,6 +26,7 @@ struct Matcher {
   unsigned* h_tc_err = nullptr;  // pinned: error word of the last tensor-core call
   bool tc_pending = false;
   int sms = 0;
+  BusyState busy;      // one call at a time per handle (common.cuh)
 };
 
 int matcher_tc_launch(Matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_map, int nm, int64_t index_base,

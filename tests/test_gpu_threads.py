@@ -106,3 +106,31 @@ def test_stereo_pair_extracted_on_two_threads_then_matched(oracle):
         assert np.array_equal(res["l"][0], kl) and np.array_equal(res["l"][1], dl)
         assert np.array_equal(res["r"][0], kr) and np.array_equal(res["r"][1], dr)
         assert np.array_equal(ur[0][:len(kl)], our) and np.array_equal(dp[0][:len(kl)], odp) and n[0] == on
+
+
+def test_one_matcher_handle_from_two_threads_fails_loudly(oracle):
+    """Two threads inside ONE orbfe_matcher: a call either completes with the right answer or is refused with
+    ORBFE_ERR_STATE — never a silently wrong result (the handle's staging arena would be overwritten)."""
+    from my_orb_slam2_b200 import orbfe
+    m = orbfe.Matcher(0)
+    q, mp = synth.bruteforce_case(nq=2048, nm=60000, n_planted=500, seed=9)
+    want_b, want_s = m.hamming_bruteforce(q, mp)
+    stats = {"ok": 0, "refused": 0}
+    lock = threading.Lock()
+
+    def worker():
+        for _ in range(30):
+            try:
+                b, s = m.hamming_bruteforce(q, mp)
+            except orbfe.OrbfeError as e:
+                assert e.code == orbfe.ERR_STATE, e
+                with lock:
+                    stats["refused"] += 1
+                continue
+            assert np.array_equal(b, want_b) and np.array_equal(s, want_s)
+            with lock:
+                stats["ok"] += 1
+
+    _run_threads([worker, worker, worker])
+    assert stats["ok"] >= 1 and stats["ok"] + stats["refused"] == 90
+    print("one handle, three threads: %(ok)d calls completed, %(refused)d refused" % stats)
