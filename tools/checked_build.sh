@@ -20,6 +20,9 @@ fi
 {
   echo "== checked build (-DORBFE_CHECKS): pytest -m gpu"
   python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+  echo "== checked build: randomised sweeps (tests/fuzz_parity.py, tests/fuzz_matchers.py)"
+  python tests/fuzz_parity.py --first ${FUZZ_FIRST:-5000} --count ${FUZZ_COUNT:-300} 2>&1 | grep -v "refused:" | tail -3
+  python tests/fuzz_matchers.py --first ${FUZZ_FIRST:-5000} --count ${FUZZ_COUNT:-300} 2>&1 | tail -13
   echo "== checked build: smoke()"
   python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -3
   echo "== ORBFE_DCHECK failures / guard reports in the output above: $(grep -c 'ORBFE_DCHECK failed\|ORBFE_CHECKS:' $OUT/checked_$TAG.log 2>/dev/null || echo 0)"
