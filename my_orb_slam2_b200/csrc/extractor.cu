@@ -323,7 +323,7 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
 // tensor over one of the level-major arenas with a box_w x box_h x 1 box.  cuTensorMapEncodeTiled is a driver entry
 // point; it is fetched through the runtime so that liborbfe.so does not link libcuda.
 static int build_level_maps(const PyrGeom& g, uint8_t* arena, int max_batch, int box_w, int box_h,
-                            CUtensorMapSwizzle swizzle, void** out) {
+                            CUtensorMapSwizzle swizzle, void** out, bool resize_sources = false) {
   typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -338,7 +338,8 @@ static int build_level_maps(const PyrGeom& g, uint8_t* arena, int max_batch, int
   memset(maps, 0, sizeof(maps));
   for (int l = 0; l < g.nlevels; ++l) {
     const LevelGeom& L = g.lv[l];
-    if (L.fast_strips_x <= 0) continue;
+    // resize_sources: level l is read by the staged resize kernel of level l+1
+    if (resize_sources ? !(l + 1 < g.nlevels && g.lv[l + 1].resize_tile) : L.fast_strips_x <= 0) continue;
     const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.h, (cuuint64_t)max_batch};
     const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.lvl_bytes};
     const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
@@ -363,6 +364,8 @@ int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
   static_assert(kDescBoxW == 64, "CU_TENSOR_MAP_SWIZZLE_64B: the box's inner extent is the swizzle span");
   if (rc == ORBFE_OK)
     rc = build_level_maps(g, a.blur, max_batch, kDescBoxW, kDescBoxH, CU_TENSOR_MAP_SWIZZLE_64B, &a.desc_maps);
+  if (rc == ORBFE_OK)  // k_pyramid.cu: the source window of a 128 x 32 destination tile
+    rc = build_level_maps(g, a.pyr, max_batch, kPyrTileW, kPyrTileH, CU_TENSOR_MAP_SWIZZLE_NONE, &a.pyr_maps, true);
   return rc;
 }
 
@@ -372,7 +375,7 @@ static void free_arenas(Extractor* e) {
   dfree(a.cand_count); dfree(a.cell_hi); dfree(a.kept); dfree(a.kept_count); cudaFree(e->result_block);
   if (e->h_result) cudaFreeHost(e->h_result);
   dfree(a.st_sad); dfree(a.st_band); dfree(a.st_bucket_start); dfree(a.st_bucket_items);
-  cudaFree(a.fast_maps); cudaFree(a.desc_maps);
+  cudaFree(a.fast_maps); cudaFree(a.desc_maps); cudaFree(a.pyr_maps);
   cudaFree(a.kp_un); cudaFree(a.depth_img);
   if (e->h_flags) cudaFreeHost(e->h_flags);
   if (e->prof_ev) {

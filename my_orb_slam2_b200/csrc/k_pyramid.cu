@@ -14,6 +14,8 @@
 // vertical pass walks down the column: consecutive rows share a source row).
 // The vertical pass is two IMAD.HI per pixel.  One 32-bit store per 4 pixels.
 // pyramid_level_generic_kernel: byte loads through the tables, any scale factor.
+#include <cuda.h>
+
 #include "kernels.h"
 
 namespace orbfe {
@@ -56,20 +58,23 @@ __global__ void __launch_bounds__(256) pyramid_level_generic_kernel(const __grid
 constexpr int PY_WARPS = 4;  // warps per CTA, stacked vertically: a CTA covers 128 x (4 * PY_ROWS) destination pixels
 // PY_ROWS = destination rows per thread: 8 in throughput mode (source rows are reused by the rows that share them), 2
 // when the launch would not fill the GPU (single frames: shorter dependent chains per thread, 4x more CTAs).
-// TILE: the CTA first requests every source byte it needs with asynchronous 16-byte copies into shared memory, so
-// a thread waits for HBM once instead of once per source row (the row-by-row variant keeps one 154-byte row per
-// warp in flight: 0.9 TB/s); needs the source window of the CTA to fit (LevelGeom::resize_tile, checked on the host).
-constexpr int PT_CHUNKS = 12;             // 16-byte chunks per staged source row
-constexpr int PT_STRIDE = PT_CHUNKS * 16;
-constexpr int PT_ROWS = 44;               // staged source rows (32 destination rows)
+// TILE: the CTA's whole source window arrives in shared memory by ONE TMA tile load (cp.async.bulk.tensor, issued by
+// one thread; round 1 used up to six 16-byte cp.async per thread, whose address arithmetic was a fifth of the kernel's
+// instructions), so a thread waits for HBM once instead of once per source row (the row-by-row variant keeps one
+// 154-byte row per warp in flight: 0.9 TB/s); needs the source window of the CTA to fit (LevelGeom::resize_tile,
+// checked on the host).
+constexpr int PT_STRIDE = kPyrTileW;      // bytes per staged source row
+constexpr int PT_ROWS = kPyrTileH;        // staged source rows (32 destination rows)
 
 template <int PY_ROWS, bool TILE>
 __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __grid_constant__ PyrGeom g,
                                                                       uint8_t* __restrict__ pyr,
                                                                       const XTab* __restrict__ xtab,
-                                                                      const YTab* __restrict__ ytab, int lvl) {
+                                                                      const YTab* __restrict__ ytab, int lvl,
+                                                                      const CUtensorMap* __restrict__ maps) {
   static_assert(!TILE || PY_ROWS * PY_WARPS == 32, "PT_ROWS is sized for 32 destination rows");
-  __shared__ __align__(16) uint8_t s_src[TILE ? PT_ROWS * PT_STRIDE : 16];
+  __shared__ __align__(128) uint8_t s_src[TILE ? PT_ROWS * PT_STRIDE : 16];
+  __shared__ unsigned long long s_bar;
   const LevelGeom& D = g.lv[lvl];
   const LevelGeom& S = g.lv[lvl - 1];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -81,22 +86,22 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
   const uint8_t* src = pyr + S.lvl_base + (size_t)b * S.lvl_bytes;
   int c0 = 0, s_first = 0;
   if (TILE) {
+    // the CTA's source window: PT_STRIDE bytes from the 16-byte aligned column below its first tap, PT_ROWS rows from
+    // its first source row — ONE TMA tile load by one thread (rows / columns past the level are zero-filled and only
+    // feed pixels that are dropped); the table loads below overlap its flight
     const int xc = blockIdx.x * 128, yc = blockIdx.y * (PY_WARPS * PY_ROWS);
     c0 = __ldg(&xt[xc].sx0) & ~15;
-    const int ws_last = __ldg(&xt[min(xc + 124, (D.w - 1) & ~3)].sx0) & ~3;
-    const int nchunks = ((ws_last + 11 - c0) >> 4) + 1;  // <= PT_CHUNKS
-    ORBFE_DCHECK(nchunks >= 1 && nchunks <= PT_CHUNKS);
-    const YTab* ytc = ytab + D.ytab_off;
-    s_first = __ldg(&ytc[yc].sy0);
-    const int nrows = __ldg(&ytc[min(yc + PY_WARPS * PY_ROWS, D.h) - 1].sy1) - s_first + 1;  // <= PT_ROWS
-    ORBFE_DCHECK(nrows >= 1 && nrows <= PT_ROWS);
-    const int c = threadIdx.x & 15;
-    if (c < nchunks) {
-      const uint8_t* gp = src + (size_t)s_first * spitch + c0 + c * 16;
-      const unsigned sp = (unsigned)__cvta_generic_to_shared(s_src) + c * 16;
-      for (int r = threadIdx.x >> 4; r < nrows; r += PY_WARPS * 2)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sp + r * PT_STRIDE), "l"(gp + (size_t)r * spitch)
-                     : "memory");
+    s_first = __ldg(&ytab[D.ytab_off + yc].sy0);
+    if (threadIdx.x == 0) {
+      const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(bar) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+      asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(PT_ROWS * PT_STRIDE) : "memory");
+      asm volatile(
+          "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n" ::
+              "r"((unsigned)__cvta_generic_to_shared(s_src)), "l"(maps + (lvl - 1)), "r"(c0), "r"(s_first), "r"(b), "r"(bar)
+          : "memory");
     }
   }
   const bool active = x4 < D.w && y0 < D.h;
@@ -115,8 +120,17 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
     selB[k] = o == 7 ? 0x40u : 0x10u;
   }
   if (TILE) {
-    asm volatile("cp.async.wait_all;\n" ::: "memory");
-    __syncthreads();
+    __syncthreads();  // the barrier's initialisation is visible to every waiter
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "PY_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n"
+        "@p bra PY_DONE;\n"
+        "bra PY_WAIT;\n"
+        "PY_DONE:\n"
+        "}\n" ::"r"((unsigned)__cvta_generic_to_shared(&s_bar))
+        : "memory");
   }
   if (!active) return;
   const uint8_t* sbase = TILE ? s_src + (ws - c0) : src + ws;
@@ -180,17 +194,18 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
 
 void launch_pyramid_level(const PyrGeom& g, const ExtractorArena& a, int lvl, int batch, cudaStream_t s) {
   const LevelGeom& D = g.lv[lvl];
+  const CUtensorMap* maps = static_cast<const CUtensorMap*>(a.pyr_maps);
   if (D.resize_fast) {
     const int cols = (D.w + 127) / 128;
     // 8 rows per thread + staged tiles as soon as the launch has two CTAs per SM (the 2-row variant is for single
     // frames: at 64 images it ran levels 6 and 7 in 12.4 / 10.1 us where level 5 took 11.8 us with the 8-row kernel)
     if ((long long)cols * ((D.h + 31) / 32) * batch >= 2 * 148) {
       dim3 grid(cols, (D.h + 8 * PY_WARPS - 1) / (8 * PY_WARPS), batch);
-      if (D.resize_tile) pyramid_level_kernel<8, true><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
-      else pyramid_level_kernel<8, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+      if (D.resize_tile) pyramid_level_kernel<8, true><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl, maps);
+      else pyramid_level_kernel<8, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl, maps);
     } else {
       dim3 grid(cols, (D.h + 2 * PY_WARPS - 1) / (2 * PY_WARPS), batch);
-      pyramid_level_kernel<2, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl);
+      pyramid_level_kernel<2, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl, maps);
     }
     return;
   }

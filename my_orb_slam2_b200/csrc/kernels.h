@@ -37,6 +37,7 @@ struct ExtractorArena {
   // kFastTileW x kFastTileH box: the FAST kernel stages a strip's image tile with ONE cp.async.bulk.tensor
   void* fast_maps = nullptr;  // [kMaxLevels]
   void* desc_maps = nullptr;  // [kMaxLevels] the BLURRED levels with a kDescBoxW x kDescBoxH box (k_describe.cu)
+  void* pyr_maps = nullptr;   // [kMaxLevels] level l as the SOURCE of level l+1: kPyrTileW x kPyrTileH box (k_pyramid.cu)
   // the rest of the mono / RGB-D Frame constructors (frame.cu), allocated on first use
   orbfe_keypoint* kp_un = nullptr;  // [batch][out_cap] undistorted keypoints (Frame::mvKeysUn)
   float* depth_img = nullptr;       // [batch][h][w] CV_32F depth images (ComputeStereoFromRGBD)
@@ -45,6 +46,8 @@ struct ExtractorArena {
 
 constexpr int kFastTileW = 144;                    // bytes per tile row (multiple of 16): 136 used + 8 of start alignment
 constexpr int kFastTileH = kFastOwnRows + 2 + 6;   // computed rows + the FAST ring (+-3)
+constexpr int kPyrTileW = 192;  // bytes per staged source row of the resize (12 x 16): the source window of 128 destination columns
+constexpr int kPyrTileH = 44;   // staged source rows (32 destination rows)
 constexpr int kDescBoxW = 64;   // bytes: the 37 columns a rotated pattern reaches, from the 16-byte aligned column below
 constexpr int kDescBoxH = 37;   // rows ky-18 .. ky+18
 // one-time host setup of ExtractorArena::fast_maps / desc_maps (extractor.cu; needs the driver's cuTensorMapEncodeTiled)
