@@ -110,6 +110,7 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
   g.min_th = e->params.min_th_fast < 0 ? 0 : (e->params.min_th_fast > 255 ? 255 : e->params.min_th_fast);
   unsigned long long pyr_off = 0;
   int cells = 0, cand = 0, kept = 0, node_cap_max = 8, blur_tiles = 0, blur_tiles_small = 0, fast_strips = 0;
+  int xw_total = 0;
   for (int l = 0; l < g.nlevels; ++l) {
     LevelGeom& L = g.lv[l];
     L.scale = info.scale_factors[l];
@@ -175,6 +176,8 @@ static int build_geometry(Extractor* e, std::vector<XTab>& xt, std::vector<YTab>
     if (l > 0) {
       L.xtab_off = (int)xt.size();
       L.ytab_off = (int)yt.size();
+      L.xw_off = xw_total;
+      xw_total += (L.w + 3) / 4;
       build_resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, L.w, L.h, xt, yt);
       // k_pyramid.cu's word-based kernel needs the taps of pixels x4..x4+3 at bytes <= 8 of (sx0(x4) & ~3), and b >= 0
       L.resize_fast = 1;
@@ -310,6 +313,29 @@ static int alloc_arenas(Extractor* e, const std::vector<XTab>& xt, const std::ve
   ORBFE_CUDA(dalloc(&a.st_bucket_items, B * g.out_cap * a.st_items_per_kp));
   if (!xt.empty()) ORBFE_CUDA(cudaMemcpy(a.xtab, xt.data(), xt.size() * sizeof(XTab), cudaMemcpyHostToDevice));
   if (!yt.empty()) ORBFE_CUDA(cudaMemcpy(a.ytab, yt.data(), yt.size() * sizeof(YTab), cudaMemcpyHostToDevice));
+  {
+    // k_pyramid.cu's per-word records: what a thread (4 destination columns) needs of the column table, in two
+    // 16-byte loads.  Pixels past the row end repeat the last column (computed and dropped).
+    std::vector<XWord> xw;
+    for (int l = 1; l < g.nlevels; ++l) {
+      const LevelGeom& L = g.lv[l];
+      for (int x4 = 0; x4 < L.w; x4 += 4) {
+        XWord r;
+        memset(&r, 0, sizeof(r));
+        r.ws = xt[L.xtab_off + x4].sx0 & ~3;
+        for (int k = 0; k < 4; ++k) {
+          const XTab& t = xt[L.xtab_off + std::min(x4 + k, L.w - 1)];
+          const int o = L.resize_fast ? t.sx0 - r.ws : 0;  // 0 .. 7 (build_geometry checked it)
+          r.selA |= ((unsigned)o | ((unsigned)std::min(o + 1, 7) << 4)) << (8 * k);
+          r.selB |= (o == 7 ? 0x40u : 0x10u) << (8 * k);
+          r.a01[k] = (unsigned)(unsigned short)t.a0 | ((unsigned)(unsigned short)t.a1 << 16);
+        }
+        xw.push_back(r);
+      }
+    }
+    ORBFE_CUDA(dalloc(&a.xword, xw.size() + 1));
+    if (!xw.empty()) ORBFE_CUDA(cudaMemcpy(a.xword, xw.data(), xw.size() * sizeof(XWord), cudaMemcpyHostToDevice));
+  }
   ORBFE_CUDA(cudaMemset(a.pyr, 0, e->pyr_bytes + 256));
   ORBFE_CUDA(cudaMemset(a.blur, 0, e->pyr_bytes + 256));
   ORBFE_CUDA(cudaMemset(a.out_count, 0, B * sizeof(int32_t)));
@@ -371,7 +397,7 @@ int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
 
 static void free_arenas(Extractor* e) {
   ExtractorArena& a = e->arena;
-  dfree(a.pyr); dfree(a.blur); dfree(a.stage); dfree(a.xtab); dfree(a.ytab); dfree(a.cand); dfree(a.node_of);
+  dfree(a.pyr); dfree(a.blur); dfree(a.stage); dfree(a.xtab); dfree(a.xword); dfree(a.ytab); dfree(a.cand); dfree(a.node_of);
   dfree(a.cand_count); dfree(a.cell_hi); dfree(a.kept); dfree(a.kept_count); cudaFree(e->result_block);
   if (e->h_result) cudaFreeHost(e->h_result);
   dfree(a.st_sad); dfree(a.st_band); dfree(a.st_bucket_start); dfree(a.st_bucket_items);

@@ -50,6 +50,7 @@ struct LevelGeom {
   int cand_off, cand_cap;   // slice of the per-image candidate array
   int kept_off, kept_cap;   // slice of the per-image kept-keypoint array
   int xtab_off, ytab_off;   // resize coefficient tables (level >= 1)
+  int xw_off;               // ... and the per-word records of k_pyramid.cu's word-based kernel (resize_fast levels)
   int resize_fast;          // the 4 pixels of an aligned group take their taps within 9 bytes of an aligned address
   int resize_tile;          // ... and the source window of a 128x32 destination tile fits k_pyramid.cu's shared-memory stage
   float scale;              // mvScaleFactor[level]
@@ -76,6 +77,9 @@ struct PyrGeom {
 // resize tables (cv::resize INTER_LINEAR)
 struct XTab { int sx0, sx1; short a0, a1; };          // per destination column
 struct __align__(16) YTab { int sy0, sy1; short b0, b1; int pad; };  // per destination row; one 16-byte load
+// per aligned group of 4 destination columns (k_pyramid.cu): ws = 4-byte aligned source column of the group's window;
+// byte k of selA / selB = the two PRMT selectors that bring pixel k's taps into the low half-word; a01[k] = a0 | a1 << 16
+struct __align__(16) XWord { int ws; unsigned selA, selB, pad; unsigned a01[4]; };
 
 // candidate / kept keypoint record: x | y<<12 | score<<24, x,y relative to minBorder
 __host__ __device__ inline uint32_t pack_cand(int x, int y, int score) {

@@ -69,7 +69,7 @@ constexpr int PT_ROWS = kPyrTileH;        // staged source rows (32 destination 
 template <int PY_ROWS, bool TILE>
 __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __grid_constant__ PyrGeom g,
                                                                       uint8_t* __restrict__ pyr,
-                                                                      const XTab* __restrict__ xtab,
+                                                                      const XWord* __restrict__ xword,
                                                                       const YTab* __restrict__ ytab, int lvl,
                                                                       const CUtensorMap* __restrict__ maps) {
   static_assert(!TILE || PY_ROWS * PY_WARPS == 32, "PT_ROWS is sized for 32 destination rows");
@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
   const int x4 = (blockIdx.x * 32 + lane) * 4;
   const int y0 = (blockIdx.y * PY_WARPS + wid) * PY_ROWS;
   const int b = blockIdx.z;
-  const XTab* xt = xtab + D.xtab_off;
+  const XWord* xw = xword + D.xw_off;
   const unsigned spitch = (unsigned)S.pitch, dpitch = (unsigned)D.pitch;
   const uint8_t* src = pyr + S.lvl_base + (size_t)b * S.lvl_bytes;
   int c0 = 0, s_first = 0;
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
     // its first source row — ONE TMA tile load by one thread (rows / columns past the level are zero-filled and only
     // feed pixels that are dropped); the table loads below overlap its flight
     const int xc = blockIdx.x * 128, yc = blockIdx.y * (PY_WARPS * PY_ROWS);
-    c0 = __ldg(&xt[xc].sx0) & ~15;
+    c0 = __ldg(&xw[xc >> 2].ws) & ~15;
     s_first = __ldg(&ytab[D.ytab_off + yc].sy0);
     if (threadIdx.x == 0) {
       const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
@@ -108,16 +108,17 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
   // per-pixel taps: bytes o, o+1 of the 12-byte window at ws (o <= 7, checked on the host: LevelGeom::resize_fast).
   // Two byte permutes bring them into the low half-word: PRMT(w0, w1, selA) takes byte o and (o < 7) byte o+1 of the
   // first two words, PRMT(t, w2, selB) replaces byte 1 by the first byte of the third word when o == 7.
-  const int x4c = min(x4, (D.w - 1) & ~3);
-  const int ws = __ldg(&xt[x4c].sx0) & ~3;
-  unsigned a01[4], selA[4], selB[4];
+  // (selectors: only bits 0..7 of a PRMT selector register matter for the two bytes kept, and the packed neighbours
+  // above them are valid selector nibbles, so the records' bytes are used after a plain shift)
+  const uint4* rec = reinterpret_cast<const uint4*>(xw + min(x4, D.w - 1) / 4);
+  const uint4 q0 = __ldg(rec), q1 = __ldg(rec + 1);
+  const int ws = (int)q0.x;
+  const unsigned a01[4] = {q1.x, q1.y, q1.z, q1.w};
+  unsigned selA[4], selB[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const int xi = min(x4c + k, D.w - 1);  // pixels past the row end are computed and dropped
-    const int o = __ldg(&xt[xi].sx0) - ws;
-    a01[k] = __ldg(reinterpret_cast<const unsigned*>(&xt[xi].a0));  // a0 | a1 << 16
-    selA[k] = (unsigned)o | ((unsigned)min(o + 1, 7) << 4);
-    selB[k] = o == 7 ? 0x40u : 0x10u;
+    selA[k] = q0.y >> (8 * k);
+    selB[k] = q0.z >> (8 * k);
   }
   if (TILE) {
     __syncthreads();  // the barrier's initialisation is visible to every waiter
@@ -201,11 +202,11 @@ void launch_pyramid_level(const PyrGeom& g, const ExtractorArena& a, int lvl, in
     // frames: at 64 images it ran levels 6 and 7 in 12.4 / 10.1 us where level 5 took 11.8 us with the 8-row kernel)
     if ((long long)cols * ((D.h + 31) / 32) * batch >= 2 * 148) {
       dim3 grid(cols, (D.h + 8 * PY_WARPS - 1) / (8 * PY_WARPS), batch);
-      if (D.resize_tile) pyramid_level_kernel<8, true><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl, maps);
-      else pyramid_level_kernel<8, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl, maps);
+      if (D.resize_tile) pyramid_level_kernel<8, true><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xword, a.ytab, lvl, maps);
+      else pyramid_level_kernel<8, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xword, a.ytab, lvl, maps);
     } else {
       dim3 grid(cols, (D.h + 2 * PY_WARPS - 1) / (2 * PY_WARPS), batch);
-      pyramid_level_kernel<2, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xtab, a.ytab, lvl, maps);
+      pyramid_level_kernel<2, false><<<grid, PY_WARPS * 32, 0, s>>>(g, a.pyr, a.xword, a.ytab, lvl, maps);
     }
     return;
   }

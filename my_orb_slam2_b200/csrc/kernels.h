@@ -13,6 +13,7 @@ struct ExtractorArena {
   uint8_t* blur = nullptr;         // blurred levels, same layout as pyr
   uint8_t* stage = nullptr;        // [batch][h][w] landing buffer of linear H2D uploads
   XTab* xtab = nullptr;
+  XWord* xword = nullptr;  // per-word resize records (levels with resize_fast)
   YTab* ytab = nullptr;
   uint32_t* cand = nullptr;        // [batch][cand_total]
   uint16_t* node_of = nullptr;     // [batch][cand_total]
