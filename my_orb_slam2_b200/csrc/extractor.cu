@@ -390,6 +390,8 @@ int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch) {
   static_assert(kDescBoxW == 64, "CU_TENSOR_MAP_SWIZZLE_64B: the box's inner extent is the swizzle span");
   if (rc == ORBFE_OK)
     rc = build_level_maps(g, a.blur, max_batch, kDescBoxW, kDescBoxH, CU_TENSOR_MAP_SWIZZLE_64B, &a.desc_maps);
+  if (rc == ORBFE_OK)  // k_describe.cu: the IC_Angle disc of a keypoint
+    rc = build_level_maps(g, a.pyr, max_batch, kDiscBoxW, kDiscBoxH, CU_TENSOR_MAP_SWIZZLE_NONE, &a.disc_maps);
   if (rc == ORBFE_OK)  // k_pyramid.cu: the source window of a 128 x 32 destination tile
     rc = build_level_maps(g, a.pyr, max_batch, kPyrTileW, kPyrTileH, CU_TENSOR_MAP_SWIZZLE_NONE, &a.pyr_maps, true);
   return rc;
@@ -401,7 +403,7 @@ static void free_arenas(Extractor* e) {
   dfree(a.cand_count); dfree(a.cell_hi); dfree(a.kept); dfree(a.kept_count); cudaFree(e->result_block);
   if (e->h_result) cudaFreeHost(e->h_result);
   dfree(a.st_sad); dfree(a.st_band); dfree(a.st_bucket_start); dfree(a.st_bucket_items);
-  cudaFree(a.fast_maps); cudaFree(a.desc_maps); cudaFree(a.pyr_maps);
+  cudaFree(a.fast_maps); cudaFree(a.desc_maps); cudaFree(a.disc_maps); cudaFree(a.pyr_maps);
   cudaFree(a.kp_un); cudaFree(a.depth_img);
   if (e->h_flags) cudaFreeHost(e->h_flags);
   if (e->prof_ev) {

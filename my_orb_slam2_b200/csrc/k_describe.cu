@@ -1,7 +1,8 @@
 // k_describe.cu — everything after DistributeOctTree for the kept keypoints.  A CTA takes 32 output rows; after the
 // row -> (level, kept record) lookup (one thread per keypoint, one CTA barrier) every warp owns 4 keypoints through all
-// steps, with its global loads issued early (moments: the disc rows of all 4 keypoints in flight at once; descriptor
-// patches: two TMA boxes in flight per warp), because the kernel is bound by memory latency, not by issue slots:
+// steps, with its global loads issued early (moments: the disc boxes of all 4 keypoints in flight at once; descriptor
+// patches: two boxes in flight per warp; all of them TMA tile loads that bypass the LSU / L1), because the kernel is
+// bound by memory latency, not by issue slots:
 //   * the fix-up of src/ORBextractor.cc:859-870 (pt += minBorder, octave, size);
 //   * computeOrientation -> IC_Angle (:472-479, :77-104): m10/m01 over the radius-15 disc of the UN-blurred level
 //     (lane = row of the disc, DP4A against a weight table), warp-shuffle reduction, cv::fastAtan2 polynomial;
@@ -106,6 +107,15 @@ __device__ __forceinline__ void tma_load_box(void* dst, const void* tmap, int x,
           "r"(smem_u32(dst)), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(b)
       : "memory");
 }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, int bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_issue_box(void* dst, const void* tmap, int x, int y, int z, unsigned long long* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n" ::
+          "r"(smem_u32(dst)), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
+      : "memory");
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
   asm volatile(
       "{\n"
@@ -120,10 +130,34 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
       : "memory");
 }
 
+// one disc row (12 staged words, the disc's 9 words start at word WO) against the weight table: sum(u * I), sum(I)
+template <int WO>
+__device__ __forceinline__ void ic_row(const unsigned (&w)[12], const uint2* wt, int& a, int& s1) {
+#pragma unroll
+  for (int j = 0; j < IC_PW; ++j) {
+    const uint2 wgt = wt[j * 16];
+    a = dp4a_us(w[WO + j], wgt.x, a);
+    s1 = (int)__dp4a(w[WO + j], wgt.y, (unsigned)s1);
+  }
+}
+
 struct KpSlot {
   int kx, ky, lvl, score;  // level coordinates (minBorder added, :865-866); lvl < 0: no keypoint in this slot
   int m01, m10;
   float ca, sb;            // cos, sin of the orientation
+};
+
+constexpr int PBUF = 3072 / 4;  // words per patch buffer: the 64 x 37 blurred box (2368 bytes), a multiple of 512 bytes; a
+                                // warp's two buffers also hold its four disc boxes (4 x 1536 bytes, 128-byte aligned)
+static_assert(PBUF * 4 >= kDescBoxW * kDescBoxH && PBUF * 4 % 512 == 0, "patch buffer");
+constexpr int DISC_STRIDE = 1536;  // bytes between the disc boxes of a warp (kDiscBoxW * kDiscBoxH = 1488, TMA wants 128)
+static_assert(DISC_STRIDE >= kDiscBoxW * kDiscBoxH && DISC_STRIDE % 128 == 0, "disc box");
+struct __align__(1024) DescSmem {
+  unsigned patch_all[DESC_WARPS][2][PBUF];
+  uint2 ic_tab[4 * IC_PW * 16];
+  KpSlot slot[DESC_KP];
+  unsigned long long patch_bar[DESC_WARPS][2];
+  unsigned long long disc_bar[DESC_WARPS];
 };
 
 __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_constant__ PyrGeom g,
@@ -135,9 +169,15 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
                                                                    uint8_t* __restrict__ out_desc,
                                                                    int32_t* __restrict__ out_count,
                                                                    int32_t* __restrict__ flags,
-                                                                   const CUtensorMap* __restrict__ blur_maps) {
-  __shared__ KpSlot slot[DESC_KP];
-  __shared__ uint2 ic_tab[4 * IC_PW * 16];
+                                                                   const CUtensorMap* __restrict__ blur_maps,
+                                                                   const CUtensorMap* __restrict__ disc_maps) {
+  // dynamic shared memory (DescSmem, > 48 KB in all): patch / disc buffers first (512-byte aligned for the swizzle)
+  extern __shared__ __align__(1024) unsigned char desc_smem_raw[];
+  DescSmem& sm = *reinterpret_cast<DescSmem*>(desc_smem_raw);
+  KpSlot* slot = sm.slot;
+  uint2* ic_tab = sm.ic_tab;
+  auto& patch_all = sm.patch_all;
+  auto& patch_bar = sm.patch_bar;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
   const int oi0 = blockIdx.x * DESC_KP;  // first output row of this CTA
@@ -181,14 +221,11 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
   // the samples on the waits of this step with one keypoint in flight).  Then lane = ROW v of the disc: 9 words x two
   // DP4A against the weight table give sum(u * I) and sum(I) over the row's part of the disc; m01 = v * sum(I).
   // (Reading the rows straight from global memory, one row per lane, was measured 2x slower: 31 sectors per load.) ----
-  constexpr int PBUF = (kDescBoxW * kDescBoxH + 511) / 512 * 128;  // words per patch buffer, a multiple of 512 bytes
   constexpr int KPW = DESC_KP / DESC_WARPS;                        // keypoints per warp
   // two patch buffers per warp, 512-byte aligned: the TMA writes the box with the 64-byte swizzle (16-byte chunk
   // index ^= bits 7-8 of the shared address = (row >> 1) & 3), so that the 512 scattered byte gathers of a keypoint
   // spread over all 32 banks: with plain 64-byte rows a warp's 32 gathers cost 4.8 shared-memory wavefronts on
   // average, swizzled 3.1 (simulated over the pattern, all alignments and angles; 3.0 is what 32 random words do)
-  __shared__ __align__(512) unsigned patch_all[DESC_WARPS][2][PBUF];
-  __shared__ unsigned long long patch_bar[DESC_WARPS][2];
   // rows ky-18 .. ky+18 of the blurred level from the 16-byte aligned column at or below kx-18: one TMA box
   auto stage_patch = [&](int i, int buf) {
     const KpSlot k = slot[i];
@@ -199,58 +236,50 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
   if (lane == 0) {
     mbar_init(&patch_bar[warp][0]);
     mbar_init(&patch_bar[warp][1]);
+    mbar_init(&sm.disc_bar[warp]);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
   }
-  // rows ky-15 .. ky+15 of the un-blurred level from the aligned address at or below kx-15, 3 rows (3 x 36 contiguous
-  // bytes) per warp instruction; the warp's 4 discs (4 x 1116 bytes) share the two patch buffers (5120 bytes), which
-  // the descriptor patches only need afterwards
-  static_assert(KPW * 31 * IC_PW <= 2 * PBUF, "the discs of a warp's keypoints are staged in its two patch buffers");
-  unsigned* disc_all = patch_all[warp][0];
-  {
-    const int prow = lane / IC_PW, pcol = lane - prow * IC_PW;  // lanes 0..26: (row within a group of 3, word)
+  // rows ky-15 .. ky+15 of the un-blurred level from the 16-byte aligned column at or below kx-15: one TMA box of
+  // 48 x 31 bytes per keypoint, all four of the warp in flight on one mbarrier (round 1 used 11 four-byte cp.async per
+  // lane and keypoint: as many L1 wavefronts as the descriptor gathers themselves).  The warp's 4 boxes share its two
+  // patch buffers, which the descriptor patches only need afterwards.
+  unsigned char* disc_all = reinterpret_cast<unsigned char*>(patch_all[warp][0]);
+  if (lane == 0) {
+    int nvalid = 0;
+#pragma unroll
+    for (int q = 0; q < KPW; ++q) nvalid += slot[warp + q * DESC_WARPS].lvl >= 0;
+    mbar_expect_tx(&sm.disc_bar[warp], nvalid * (kDiscBoxW * kDiscBoxH));  // nvalid >= 1 is not needed: see the wait
 #pragma unroll
     for (int q = 0; q < KPW; ++q) {
       const KpSlot k = slot[warp + q * DESC_WARPS];
-      if (k.lvl >= 0 && prow < 3) {
-        const LevelGeom& L = g.lv[k.lvl];
-        const int pitch = L.pitch;
-        const uint8_t* base = pyr + L.lvl_base + (size_t)b * L.lvl_bytes + (size_t)(k.ky - 15 + prow) * pitch +
-                              ((k.kx - 15) & ~3) + 4 * pcol;
-        unsigned* d = disc_all + q * (31 * IC_PW) + prow * IC_PW + pcol;
-#pragma unroll
-        for (int r0 = 0; r0 < 33; r0 += 3) {
-          if (r0 + prow < 31) cp_async4(d, base);
-          base += 3 * pitch;
-          d += 3 * IC_PW;
-        }
-      }
-      cp_async_commit();
+      if (k.lvl >= 0)
+        tma_issue_box(disc_all + q * DISC_STRIDE, disc_maps + k.lvl, (k.kx - 15) & ~15, k.ky - 15, b, &sm.disc_bar[warp]);
     }
   }
   {
     const int v = lane - 15;
     const int av = lane < 31 ? (v < 0 ? -v : v) : 15;
     int m10[KPW], m01[KPW];
+    __syncwarp();
+    mbar_wait(&sm.disc_bar[warp], 0u);  // (with no valid keypoint the arrive alone completes the phase)
 #pragma unroll
     for (int q = 0; q < KPW; ++q) {
-      if (q == 0) cp_async_wait<KPW - 1>();
-      if (q == 1) cp_async_wait<(KPW > 2 ? KPW - 2 : 0)>();
-      if (q == 2) cp_async_wait<(KPW > 3 ? KPW - 3 : 0)>();
-      if (q >= 3) cp_async_wait<0>();
-      __syncwarp();
-      const unsigned* disc = disc_all + q * (31 * IC_PW);
-      const int al = (slot[warp + q * DESC_WARPS].kx - 15) & 3;
-      ORBFE_DCHECK(al >= 0 && al < 4 && av >= 0 && av < 16);
+      // lane = ROW v of the disc: its 48 staged bytes are three 16-byte loads (rows are 48 bytes apart: a quarter
+      // warp's eight 16-byte chunks fall into eight different bank groups), the disc's 9 words start at word `wo`
+      const int off = (slot[warp + q * DESC_WARPS].kx - 15) & 15;
+      const int al = off & 3, wo = off >> 2;  // warp-uniform
+      ORBFE_DCHECK(av >= 0 && av < 16);
       const uint2* wt = ic_tab + al * (IC_PW * 16) + av;
       int a = 0, s1 = 0;
       if (lane < 31) {
-#pragma unroll
-        for (int j = 0; j < IC_PW; ++j) {
-          const unsigned px = disc[lane * IC_PW + j];
-          const uint2 wgt = wt[j * 16];
-          a = dp4a_us(px, wgt.x, a);
-          s1 = (int)__dp4a(px, wgt.y, (unsigned)s1);
-        }
+        const uint4* row = reinterpret_cast<const uint4*>(disc_all + q * DISC_STRIDE + lane * kDiscBoxW);
+        const uint4 r0 = row[0], r1 = row[1], r2 = row[2];
+        const unsigned w[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
+        if (wo == 0) ic_row<0>(w, wt, a, s1);
+        else if (wo == 1) ic_row<1>(w, wt, a, s1);
+        else if (wo == 2) ic_row<2>(w, wt, a, s1);
+        else ic_row<3>(w, wt, a, s1);
       }
       m10[q] = a;
       m01[q] = v * s1;
@@ -264,8 +293,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
       }
     }
     __syncwarp();  // every lane has read the discs
-    // the first two descriptor patches travel while the angles are computed; the buffers were last written through
-    // the generic proxy (cp.async), the TMA writes through the async proxy
+    // the first two descriptor patches travel while the angles are computed; the buffers were last READ through the
+    // generic proxy, the TMA writes through the async proxy
     if (lane == 0) asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
     stage_patch(warp, 0);
     stage_patch(warp + DESC_WARPS, 1);
@@ -355,8 +384,14 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
 
 void launch_describe(const PyrGeom& g, const ExtractorArena& a, int batch, cudaStream_t s) {
   dim3 grid((g.out_cap + DESC_KP - 1) / DESC_KP, batch);
-  describe_kernel<<<grid, DESC_WARPS * 32, 0, s>>>(g, a.pyr, a.blur, a.kept, a.kept_count, a.out_kp, a.out_desc,
-                                                   a.out_count, a.flags, static_cast<const CUtensorMap*>(a.desc_maps));
+  describe_kernel<<<grid, DESC_WARPS * 32, sizeof(DescSmem), s>>>(
+      g, a.pyr, a.blur, a.kept, a.kept_count, a.out_kp, a.out_desc, a.out_count, a.flags,
+      static_cast<const CUtensorMap*>(a.desc_maps), static_cast<const CUtensorMap*>(a.disc_maps));
+}
+
+int configure_describe_kernel() {
+  return cudaFuncSetAttribute(describe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DescSmem)) ==
+                 cudaSuccess ? 0 : -1;
 }
 
 }  // namespace orbfe

@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(PY_WARPS * 32) pyramid_level_kernel(const __gr
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const unsigned v = (__umulhi(b0s, h0[k]) + __umulhi(b1s, h1[k]) + 2u) >> 2;
-      out |= v << (8 * k);
+      out |= v << (8 * k);  // (two 16-bit fields per register + one PRMT was measured slower: 0.1032 vs 0.1008 ms)
     }
     *reinterpret_cast<unsigned*>(dp) = out;  // pitch is a multiple of 128: the padding bytes may be written
     dp += dpitch;

@@ -356,6 +356,7 @@ int configure_kernels(const PyrGeom& g) {
   if (upload_pattern() != 0) { set_error("rBRIEF pattern upload failed"); return ORBFE_ERR_CUDA; }
   if (configure_stereo_kernels(g) != 0) { set_error("cudaFuncSetAttribute(stereo_bucket_kernel) failed"); return ORBFE_ERR_CUDA; }
   if (configure_fast_kernel() != 0) { set_error("cudaFuncSetAttribute(fast_detect_kernel) failed"); return ORBFE_ERR_CUDA; }
+  if (configure_describe_kernel() != 0) { set_error("cudaFuncSetAttribute(describe_kernel) failed"); return ORBFE_ERR_CUDA; }
   return ORBFE_OK;
 }
 

@@ -38,6 +38,7 @@ struct ExtractorArena {
   // kFastTileW x kFastTileH box: the FAST kernel stages a strip's image tile with ONE cp.async.bulk.tensor
   void* fast_maps = nullptr;  // [kMaxLevels]
   void* desc_maps = nullptr;  // [kMaxLevels] the BLURRED levels with a kDescBoxW x kDescBoxH box (k_describe.cu)
+  void* disc_maps = nullptr;  // [kMaxLevels] the un-blurred levels with a kDiscBoxW x kDiscBoxH box (k_describe.cu, IC_Angle)
   void* pyr_maps = nullptr;   // [kMaxLevels] level l as the SOURCE of level l+1: kPyrTileW x kPyrTileH box (k_pyramid.cu)
   // the rest of the mono / RGB-D Frame constructors (frame.cu), allocated on first use
   orbfe_keypoint* kp_un = nullptr;  // [batch][out_cap] undistorted keypoints (Frame::mvKeysUn)
@@ -49,9 +50,12 @@ constexpr int kFastTileW = 144;                    // bytes per tile row (multip
 constexpr int kFastTileH = kFastOwnRows + 2 + 6;   // computed rows + the FAST ring (+-3)
 constexpr int kPyrTileW = 192;  // bytes per staged source row of the resize (12 x 16): the source window of 128 destination columns
 constexpr int kPyrTileH = 44;   // staged source rows (32 destination rows)
+constexpr int kDiscBoxW = 48;   // bytes: the 31 columns of the IC_Angle disc, from the 16-byte aligned column at or below kx-15
+constexpr int kDiscBoxH = 31;   // rows ky-15 .. ky+15 of the UN-blurred level
 constexpr int kDescBoxW = 64;   // bytes: the 37 columns a rotated pattern reaches, from the 16-byte aligned column below
 constexpr int kDescBoxH = 37;   // rows ky-18 .. ky+18
 // one-time host setup of ExtractorArena::fast_maps / desc_maps (extractor.cu; needs the driver's cuTensorMapEncodeTiled)
+int configure_describe_kernel();  // k_describe.cu: opt-in dynamic shared memory
 int build_fast_tensor_maps(const PyrGeom& g, ExtractorArena& a, int max_batch);
 
 enum : int { FLAG_CAND_OVERFLOW = 1, FLAG_NODE_OVERFLOW = 2, FLAG_OUT_OVERFLOW = 4 };
