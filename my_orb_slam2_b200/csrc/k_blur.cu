@@ -8,7 +8,8 @@
 //     columns x-4..x+7, forms the four 7-tap horizontal sums with funnel shifts + two DP4A each, and keeps the last
 //     seven rows of sums in registers (sliding window) for the vertical pass;
 //   * one 32-bit store per 4 output pixels; reads are served by L1/L2 (each source word is read by 3 lanes and each
-//     source row by the strips above/below only at the 6 halo rows);
+//     source row by the strips above/below only at the 6 halo rows); the vertical pass works on PAIRS of rows (two
+//     16-bit sums per register): three IDP.2A + one IMAD per pixel;
 //   * reflect-101 at the level edges: rows by index reflection, columns by byte shuffles (left edge) or a byte-wise
 //     slow path (last words of a row).
 // HBM-bound by design: reads each level once, writes it once.
@@ -144,7 +145,13 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
   if (y0 >= 3 && y0 + BL_ROWS + 3 <= h) {
     // strip with all its 6 halo rows inside the level (warp-uniform): no row reflection, no row-count tests, the
     // source and destination rows are reached by bumping two pointers
-    unsigned win[7][4];
+    // vertical pass on PAIRS of rows: pr[r % 6][j] = h(r-1) | h(r) << 16 (h <= 65280 fits 16 bits; one multiply-add
+    // per row and pixel), and v = 18 h(r-6) + 34 h(r-5) + 48 h(r-4) + 56 h(r-3) + 48 h(r-2) + 34 h(r-1) + 18 h(r) + 32768
+    // is three 16-bit x 8-bit two-way dot products (IDP.2A) on the pairs ending at rows r-5, r-3, r-1 plus one multiply-add:
+    // 5 instructions per pixel instead of 7 (2 adds + 5 multiply-adds)
+    constexpr unsigned W_A = 18u | (34u << 8) | (48u << 16) | (56u << 24), W_B = 48u | (34u << 8);
+    unsigned pr[6][4];
+    unsigned hprev[4] = {0u, 0u, 0u, 0u};
     unsigned pf[BL_PF][3];
     const uint8_t* rp = src + (size_t)(y0 - 3) * pitch + x4;
     uint8_t* wp = dst + (size_t)y0 * pitch + x4;
@@ -166,7 +173,7 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
         pf[r % BL_PF][2] = __ldg(reinterpret_cast<const unsigned*>(rp + 4));
         rp += pitch;
       }
-      unsigned* hs = win[r % 7];
+      unsigned hs[4];
       hs[0] = __dp4a(__funnelshift_r(w0, w1, 8), K_LO, __dp4a(__funnelshift_r(w1, w2, 8), K_HI, 0u));
       hs[1] = __dp4a(__funnelshift_r(w0, w1, 16), K_LO, __dp4a(__funnelshift_r(w1, w2, 16), K_HI, 0u));
       hs[2] = __dp4a(__funnelshift_r(w0, w1, 24), K_LO, __dp4a(__funnelshift_r(w1, w2, 24), K_HI, 0u));
@@ -174,24 +181,36 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
       if (r >= 6) {
         unsigned v[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          v[j] = vsum(win[(r + 1) % 7][j], win[(r + 2) % 7][j], win[(r + 3) % 7][j], win[(r + 4) % 7][j],
-                      win[(r + 5) % 7][j], win[(r + 6) % 7][j], win[r % 7][j]);
+        for (int j = 0; j < 4; ++j) {
+          unsigned t = mad_u32(hs[j], 18u, 32768u);
+          t = __dp2a_lo(pr[(r + 1) % 6][j], W_A, t);  // pair ending at row r-5: 18 h(r-6) + 34 h(r-5)
+          t = __dp2a_hi(pr[(r + 3) % 6][j], W_A, t);  // pair ending at row r-3: 48 h(r-4) + 56 h(r-3)
+          v[j] = __dp2a_lo(pr[(r + 5) % 6][j], W_B, t);  // pair ending at row r-1: 48 h(r-2) + 34 h(r-1)
+        }
         const unsigned out = pack_round(v);
         *reinterpret_cast<unsigned*>(wp) = out;
         wp += pitch;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (r >= 1) pr[r % 6][j] = mad_u32(hs[j], 65536u, hprev[j]);
+        hprev[j] = hs[j];
       }
     }
     return;
   }
   // strips touching the top or bottom of the level: row reflection and a row count, window moved instead of renamed
-  // (rolled loop: these are the minority of strips and a second unrolled body would double the kernel's code size)
+  // (rolled loop: these are the minority of strips and a second unrolled body would double the kernel's code size);
+  // the same pair form of the vertical pass: at row r, pr[i] = pair ending at row r-5+i
   {
-    unsigned win[7][4];
+    constexpr unsigned W_A = 18u | (34u << 8) | (48u << 16) | (56u << 24), W_B = 48u | (34u << 8);
+    unsigned pr[5][4], hprev[4];
 #pragma unroll
-    for (int i = 0; i < 7; ++i)
+    for (int j = 0; j < 4; ++j) {
+      hprev[j] = 0;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) win[i][j] = 0;
+      for (int i = 0; i < 5; ++i) pr[i][j] = 0;
+    }
     unsigned q[3], nq[3];
     auto load_row = [&](int r, unsigned (&o)[3]) {
       const int y = reflect101i(y0 + r - 3, h);
@@ -211,19 +230,24 @@ __global__ void __launch_bounds__(BL_TX * BL_TY) blur_levels_kernel(const __grid
       hs[1] = __dp4a(__funnelshift_r(w0, w1, 16), K_LO, __dp4a(__funnelshift_r(w1, w2, 16), K_HI, 0u));
       hs[2] = __dp4a(__funnelshift_r(w0, w1, 24), K_LO, __dp4a(__funnelshift_r(w1, w2, 24), K_HI, 0u));
       hs[3] = __dp4a(w1, K_LO, __dp4a(w2, K_HI, 0u));
-#pragma unroll
-      for (int i = 0; i < 6; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) win[i][j] = win[i + 1][j];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) win[6][j] = hs[j];
       if (r >= 6) {
         unsigned v[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          v[j] = vsum(win[0][j], win[1][j], win[2][j], win[3][j], win[4][j], win[5][j], win[6][j]);
+        for (int j = 0; j < 4; ++j) {
+          unsigned t = mad_u32(hs[j], 18u, 32768u);
+          t = __dp2a_lo(pr[0][j], W_A, t);
+          t = __dp2a_hi(pr[2][j], W_A, t);
+          v[j] = __dp2a_lo(pr[4][j], W_B, t);
+        }
         const unsigned out = pack_round(v);
         *reinterpret_cast<unsigned*>(dst + (size_t)(y0 + r - 6) * pitch + x4) = out;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) pr[i][j] = pr[i + 1][j];
+        pr[4][j] = mad_u32(hs[j], 65536u, hprev[j]);
+        hprev[j] = hs[j];
       }
       q[0] = nq[0]; q[1] = nq[1]; q[2] = nq[2];
     }
