@@ -19,7 +19,10 @@ namespace orbfe {
 
 constexpr int BL_TX = 32;  // a CTA is BL_TY warps stacked vertically and covers 128 x (BL_TY * BL_ROWS) pixels: 128 x 32 either as
                            // one warp of 32-row strips (throughput) or as four warps of 8-row strips (few images)
-constexpr int BL_PF = 3;                            // rows of loads in flight per thread
+#ifndef ORBFE_BL_PF
+#define ORBFE_BL_PF 3
+#endif
+constexpr int BL_PF = ORBFE_BL_PF;                  // rows of loads in flight per thread
 
 __device__ __forceinline__ int reflect101i(int p, int len) {
   if (p < 0) p = -p;
