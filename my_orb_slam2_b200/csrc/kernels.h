@@ -88,6 +88,9 @@ void launch_undistort(const PyrGeom& g, const ExtractorArena& a, int batch, cons
 void launch_stereo_from_rgbd(const PyrGeom& g, const ExtractorArena& a, int batch, int w, int h, float mbf, cudaStream_t s);
 
 // ---- k_input.cu: cvtColor *2GRAY and remap INTER_LINEAR straight into level 0 ----
+// rows of w bytes at any alignment (device memory) -> level 0 of the arena
+void launch_repitch(const uint8_t* src, size_t image_stride, size_t row_stride, uint8_t* dst, int pitch, size_t dst_image,
+                    int w, int h, int batch, cudaStream_t s);
 void launch_gray(const uint8_t* src, size_t image_stride, int row_stride, int channels, int rgb, uint8_t* dst, int pitch,
                  size_t dst_image, int w, int h, int batch, cudaStream_t s);
 void launch_remap(const uint8_t* src, size_t image_stride, int row_stride, int sw, int sh, const float* mapx,
