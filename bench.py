@@ -749,10 +749,8 @@ def run_gpu(args):
     def batch_device(j, ptrs=None):
         pl, pr = dptr[j % len(dptr)] if ptrs is None else ptrs
         g = rigs[j % n_vrigs]
-        # diagnostic only (what the D2D re-pitch copy costs): after the first batches every rig keeps its images
-        if not os.environ.get("ORBFE_BENCH_SKIP_UPLOAD") or j < 4 * n_vrigs:
-            g.L.upload(pl, B, on_device=True)
-            g.R.upload(pr, B, on_device=True)
+        g.L.upload(pl, B, on_device=True)
+        g.R.upload(pr, B, on_device=True)
         g.kernels()
 
     def step_device():
