@@ -177,3 +177,36 @@ def test_odd_shapes(fe, oracle, w, h, params):
         kp, desc = fe.ORBextractor(*params)(img)
         assert len(okp) > 0
         _assert_same(kp, desc, okp, odesc)
+
+
+@pytest.mark.parametrize("offset,row_pad,img_pad", [(0, 0, 0), (1, 0, 0), (7, 3, 0), (13, 39, 5), (16, 128, 64)])
+def test_upload_from_device_memory_at_any_alignment(oracle, offset, row_pad, img_pad):
+    """orbfe_extract_upload(images_on_device=1): rows at any byte alignment, padded rows, padded images (the library's
+    re-pitch kernel, k_input.cu) — level 0 must equal the images byte for byte, and the features the oracle's."""
+    import torch
+    from my_orb_slam2_b200 import orbfe
+    w, h, B = 333, 77, 3
+    params = (150, 1.2, 3, 20, 7)
+    imgs = np.stack([synth.synth_image(w, h, 300 + i) for i in range(B)])
+    row_stride = w + row_pad
+    image_stride = row_stride * h + img_pad
+    host = np.full(offset + image_stride * B + 64, 0xEE, np.uint8)  # 0xEE: padding that must never reach level 0
+    for b in range(B):
+        for y in range(h):
+            o = offset + b * image_stride + y * row_stride
+            host[o:o + w] = imgs[b, y]
+    dev = torch.from_numpy(host).cuda()
+    ex = orbfe.Extractor(*params, w, h, max_batch=B)
+    ex.upload(dev.data_ptr() + offset, B, image_stride=image_stride, row_stride=row_stride, on_device=True)
+    ex.run(B)
+    ex.sync()
+    for b in range(B):
+        assert np.array_equal(ex.level(0, b), imgs[b]), "level 0 of image %d" % b
+    cap = ex.capacity
+    kps = np.zeros((B, cap), orbfe.KEYPOINT_DTYPE)
+    desc = np.zeros((B, cap, 32), np.uint8)
+    n = np.zeros(B, np.int32)
+    ex.download(B, kps, desc, n)
+    for b in range(B):
+        okp, odesc = oracle.Extractor(*params).extract(imgs[b])
+        assert n[b] == len(okp) and np.array_equal(kps[b][:n[b]], okp) and np.array_equal(desc[b][:n[b]], odesc)
