@@ -75,7 +75,8 @@ int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* images, size_t image_
                         orbfe_keypoint* keypoints, uint8_t* descriptors, int capacity, int32_t* counts);
 
 /* Asynchronous pieces of the same call, for pipelining:
- *   upload  : host (ideally pinned) or device images -> level 0 of the pyramids
+ *   upload  : host (ideally pinned) or device images -> level 0 of the pyramids (device images: any byte
+ *             alignment, row_stride >= width, any image_stride; re-pitched by a kernel on the handle's stream)
  *   run     : all kernels, results stay on the device
  *   download: results -> host
  *   sync    : wait for the handle's stream. */
